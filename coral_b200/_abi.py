@@ -1,0 +1,190 @@
+"""ctypes binding of the C ABI in include/coral_b200.h (the stub INTEGRATION.md shows to maintainers).
+
+The library is built in-tree by ``coral_b200.build``.  There is no CPU fallback: every compute entry
+point needs a CUDA device and raises ``CoralError`` otherwise.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcoral_b200.so")
+
+CHR_IDX = {('chr%d' % (i + 1)): i for i in range(22)}
+CHR_IDX.update({'chrX': 22, 'chrY': 23, 'chrM': 24})
+
+
+class CoralError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("coral_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+class Params(ctypes.Structure):
+    _fields_ = [("min_del_len", ctypes.c_int32), ("min_bp_match_cutoff", ctypes.c_int32),
+                ("min_mapq", ctypes.c_int32), ("gap_mapq", ctypes.c_int32), ("gap", ctypes.c_int32),
+                ("bp_distance_cutoff", ctypes.c_int32)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libcoral_b200.so (fails loudly when it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("libcoral_b200.so is missing: run `python -m coral_b200.build` (no CPU fallback exists)")
+        L = ctypes.CDLL(LIB_PATH)
+        L.coral_last_error.restype = ctypes.c_char_p
+        L.coral_n_records.restype = ctypes.c_int64
+        L.coral_launch_count.restype = ctypes.c_uint64
+        L.coral_stage_ms.restype = ctypes.c_float
+        L.coral_bam_n_records.restype = ctypes.c_int64
+        L.coral_bam_ref_len.restype = ctypes.c_int64
+        L.coral_bam_ref_name.restype = ctypes.c_char_p
+        L.coral_bam_records.restype = ctypes.c_void_p
+        L.coral_bam_offsets.restype = ctypes.c_void_p
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+class BamFile(object):
+    """Host-side ingest: inflated, framed records in one (pinned) buffer."""
+
+    def __init__(self, path, n_threads=0):
+        L = lib()
+        h = ctypes.c_void_p()
+        err = ctypes.create_string_buffer(512)
+        rc = L.coral_bam_read(path.encode(), int(n_threads), ctypes.byref(h), err, 512)
+        if rc != 0:
+            raise CoralError(rc, err.value.decode())
+        self._h = h
+        self.path = path
+        n_ref = L.coral_bam_n_ref(h)
+        self.references = tuple(L.coral_bam_ref_name(h, i).decode() for i in range(n_ref))
+        self.lengths = tuple(int(L.coral_bam_ref_len(h, i)) for i in range(n_ref))
+        self.n_records = int(L.coral_bam_n_records(h))
+        nb = ctypes.c_uint64()
+        ptr = L.coral_bam_records(h, ctypes.byref(nb))
+        self.nbytes = int(nb.value)
+        self.rec_ptr = ptr
+        buf = (ctypes.c_uint8 * max(self.nbytes, 1)).from_address(ptr)
+        self.rec = np.frombuffer(buf, dtype=np.uint8, count=self.nbytes)
+        obuf = (ctypes.c_uint64 * (self.n_records + 1)).from_address(L.coral_bam_offsets(h))
+        self.rec_off = np.frombuffer(obuf, dtype=np.uint64, count=self.n_records + 1)
+
+    def query_name(self, i):
+        o = int(self.rec_off[i])
+        ln = int(self.rec[o + 12])
+        return self.rec[o + 36:o + 36 + ln - 1].tobytes().decode()
+
+    def close(self):
+        if self._h is not None:
+            self.rec = None
+            self.rec_off = None
+            lib().coral_bam_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Context(object):
+    """One coral_ctx bound to one GPU."""
+
+    def __init__(self, device=0):
+        L = lib()
+        h = ctypes.c_void_p()
+        rc = L.coral_create(int(device), ctypes.byref(h))
+        if rc != 0:
+            raise CoralError(rc, "coral_create failed (no CUDA device? the hot path has no CPU fallback)")
+        self._h = h
+        self._L = L
+        self.references = ()
+        self._keep = []
+
+    def _check(self, rc):
+        if rc != 0:
+            raise CoralError(rc, self._L.coral_last_error(self._h).decode())
+
+    def close(self):
+        if self._h is not None:
+            self._L.coral_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_params(self, **kw):
+        p = Params()
+        self._L.coral_default_params(ctypes.byref(p))
+        for k, v in kw.items():
+            setattr(p, k, int(v))
+        self._check(self._L.coral_set_params(self._h, ctypes.byref(p)))
+
+    def set_references(self, names):
+        self.references = tuple(names)
+        blob = b"".join(n.encode() + b"\x00" for n in names)
+        rank = np.array([CHR_IDX.get(n, -1) for n in names], dtype=np.int32)
+        self._check(self._L.coral_set_references(self._h, blob, len(names), _p(rank)))
+
+    def load_records(self, rec, rec_off, global_ordinal=None):
+        """rec: uint8 array (host) of framed records; rec_off: uint64[n+1]."""
+        rec = np.ascontiguousarray(rec, dtype=np.uint8)
+        rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+        n = len(rec_off) - 1
+        go = None if global_ordinal is None else np.ascontiguousarray(global_ordinal, dtype=np.uint64)
+        self._check(self._L.coral_load_records(self._h, _p(rec), ctypes.c_uint64(int(rec_off[-1]) if n >= 0 and len(rec_off) else 0),
+                                               _p(rec_off), ctypes.c_int64(n), _p(go), 0))
+
+    def load_records_device(self, dev_ptr, nbytes, rec_off, global_ordinal=None):
+        rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+        go = None if global_ordinal is None else np.ascontiguousarray(global_ordinal, dtype=np.uint64)
+        self._check(self._L.coral_load_records(self._h, ctypes.c_void_p(dev_ptr), ctypes.c_uint64(nbytes), _p(rec_off),
+                                               ctypes.c_int64(len(rec_off) - 1), _p(go), 1))
+
+    def rescan(self):
+        self._check(self._L.coral_rescan(self._h))
+
+    def stage_ms(self, stage):
+        return float(self._L.coral_stage_ms(self._h, int(stage)))
+
+    @property
+    def n_records(self):
+        return int(self._L.coral_n_records(self._h))
+
+    @property
+    def launch_count(self):
+        return int(self._L.coral_launch_count(self._h))
+
+    def record_table(self):
+        n = self.n_records
+        cols = {k: np.zeros(n, np.int32) for k in ("tid", "pos", "endpos", "flag", "mapq", "n_cigar")}
+        cols.update({k: np.zeros(n, np.int64) for k in ("l_seq", "infer_len", "aligned_bases", "non_acgt")})
+        self._check(self._L.coral_get_record_table(
+            self._h, _p(cols["tid"]), _p(cols["pos"]), _p(cols["endpos"]), _p(cols["flag"]), _p(cols["mapq"]),
+            _p(cols["l_seq"]), _p(cols["n_cigar"]), _p(cols["infer_len"]), _p(cols["aligned_bases"]), _p(cols["non_acgt"])))
+        return cols
+
+    def region_coverage(self, tid, start, stop):
+        """Regions [start, stop) sorted by (tid, start), disjoint -> (base_sum int64[n], rec_count int64[n])."""
+        tid = np.ascontiguousarray(tid, dtype=np.int32)
+        start = np.ascontiguousarray(start, dtype=np.int32)
+        stop = np.ascontiguousarray(stop, dtype=np.int32)
+        n = len(tid)
+        bs = np.zeros(n, np.int64)
+        rc = np.zeros(n, np.int64)
+        self._check(self._L.coral_region_coverage(self._h, _p(tid), _p(start), _p(stop), n, _p(bs), _p(rc)))
+        return bs, rc

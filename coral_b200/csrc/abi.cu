@@ -1,0 +1,146 @@
+// coral_b200/csrc/abi.cu — extern "C" entry points (include/coral_b200.h).
+#include <algorithm>
+#include <cstring>
+#include <new>
+
+#include "ctx.h"
+
+extern "C" {
+
+void coral_default_params(coral_params* p) {
+    p->min_del_len = 600;
+    p->min_bp_match_cutoff = 100;
+    p->min_mapq = 20;
+    p->gap_mapq = 10;
+    p->gap = 100;
+    p->bp_distance_cutoff = 2000;
+}
+
+int coral_create(int device, coral_ctx** out) {
+    if (!out) return CORAL_E_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) return CORAL_E_CUDA;  // no CPU fallback
+    if (device < 0 || device >= ndev) return CORAL_E_ARG;
+    coral_ctx* c = new (std::nothrow) coral_ctx();
+    if (!c) return CORAL_E_NOMEM;
+    c->device = device;
+    coral_default_params(&c->prm);
+    if (cudaSetDevice(device) != cudaSuccess || cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete c;
+        return CORAL_E_CUDA;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
+    *out = c;
+    return CORAL_OK;
+}
+
+void coral_destroy(coral_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status,
+                     &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->s6, &c->s7, &c->cub_tmp,
+                     &c->rt.tid, &c->rt.pos, &c->rt.endpos, &c->rt.flag_mapq, &c->rt.lseq, &c->rt.ncig, &c->rt.infer,
+                     &c->rt.mbases, &c->rt.nonacgt, &c->rt.fbs, &c->rt.lbe, &c->rt.name_lo, &c->rt.name_hi,
+                     &c->rt.sa_off, &c->rt.sa_len, &c->rt.nm, &c->rt.ngap, &c->rt.gap_base,
+                     &c->gaps.rec, &c->gaps.k, &c->gaps.next_start, &c->gaps.prev_end, &c->gaps.counter};
+    for (DevBuf* b : all) b->release();
+    coral_release_tables(c);
+    for (int i = 0; i < CORAL_N_STAGES; i++) {
+        if (c->ev_beg[i]) cudaEventDestroy(c->ev_beg[i]);
+        if (c->ev_end[i]) cudaEventDestroy(c->ev_end[i]);
+    }
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char* coral_last_error(const coral_ctx* c) { return c ? c->err.c_str() : "null ctx"; }
+
+int coral_set_params(coral_ctx* c, const coral_params* p) {
+    if (!c || !p) return CORAL_E_ARG;
+    c->prm = *p;
+    return CORAL_OK;
+}
+
+int coral_set_references(coral_ctx* c, const char* names, int32_t n, const int32_t* chr_rank) {
+    if (!c || !names || n < 0 || !chr_rank) return CORAL_E_ARG;
+    cudaSetDevice(c->device);
+    c->ref_names.clear();
+    const char* p = names;
+    for (int32_t i = 0; i < n; i++) {
+        c->ref_names.emplace_back(p);
+        p += c->ref_names.back().size() + 1;
+    }
+    c->chr_rank_h.assign(chr_rank, chr_rank + n);
+    CORAL_CUDA(c, c->d_chr_rank.ensure((size_t)std::max(n, 1) * 4));
+    CORAL_CUDA(c, cudaMemcpyAsync(c->d_chr_rank.p, chr_rank, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    CORAL_TRY(coral_upload_ref_hashes(c));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    return CORAL_OK;
+}
+
+int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const uint64_t* offsets, int64_t n,
+                       const uint64_t* global_ordinal, int on_device) {
+    if (!c || n < 0 || (n > 0 && (!recs || !offsets))) return CORAL_E_ARG;
+    cudaSetDevice(c->device);
+    c->loaded = false;
+    for (int64_t i = 0; i < n; i++) {
+        if (offsets[i] & 15) { c->err = "record offsets must be 16-byte aligned"; return CORAL_E_ARG; }
+        if (offsets[i] + 36 > nbytes || offsets[i + 1] < offsets[i] + 36 || offsets[i + 1] > nbytes) {
+            c->err = "record offsets out of range";
+            return CORAL_E_ARG;
+        }
+    }
+    if (n >= (int64_t)1 << 32) { c->err = "more than 2^32 records per ctx"; return CORAL_E_ARG; }
+    if (on_device) {
+        if (reinterpret_cast<uintptr_t>(recs) & 15) { c->err = "device record buffer must be 16-byte aligned"; return CORAL_E_ARG; }
+        c->d_recs = recs;
+    } else {
+        CORAL_CUDA(c, c->recs_owned.ensure(nbytes + 64));
+        CORAL_CUDA(c, cudaMemcpyAsync(c->recs_owned.p, recs, nbytes, cudaMemcpyHostToDevice, c->stream));
+        CORAL_CUDA(c, cudaMemsetAsync((uint8_t*)c->recs_owned.p + nbytes, 0, 64, c->stream));
+        c->d_recs = c->recs_owned.as<uint8_t>();
+    }
+    c->nbytes = nbytes;
+    c->nrec = n;
+    CORAL_CUDA(c, c->d_off.ensure((size_t)(n + 1) * 8));
+    if (n > 0) CORAL_CUDA(c, cudaMemcpyAsync(c->d_off.p, offsets, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, c->stream));
+    c->has_ordinal = global_ordinal != nullptr;
+    if (global_ordinal && n > 0) {
+        CORAL_CUDA(c, c->d_ordinal.ensure((size_t)n * 8));
+        CORAL_CUDA(c, cudaMemcpyAsync(c->d_ordinal.p, global_ordinal, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
+    }
+    CORAL_TRY(coral_run_scan(c));
+    c->loaded = true;
+    return CORAL_OK;
+}
+
+int coral_rescan(coral_ctx* c) {
+    if (!c) return CORAL_E_ARG;
+    if (!c->loaded) { c->err = "coral_rescan before coral_load_records"; return CORAL_E_STATE; }
+    cudaSetDevice(c->device);
+    return coral_run_scan(c);
+}
+
+float coral_stage_ms(coral_ctx* c, int stage) {
+    if (!c || stage < 0 || stage >= CORAL_N_STAGES || !c->ev_valid[stage]) return -1.f;
+    cudaSetDevice(c->device);
+    float ms = -1.f;
+    if (cudaEventSynchronize(c->ev_end[stage]) != cudaSuccess) return -1.f;
+    if (cudaEventElapsedTime(&ms, c->ev_beg[stage], c->ev_end[stage]) != cudaSuccess) return -1.f;
+    return ms;
+}
+
+int64_t coral_n_records(const coral_ctx* c) { return c ? c->nrec : -1; }
+uint64_t coral_launch_count(const coral_ctx* c) { return c ? c->n_launches : 0; }
+
+int coral_region_coverage(coral_ctx* c, const int32_t* tid, const int32_t* start, const int32_t* stop, int32_t n,
+                          int64_t* base_sum, int64_t* rec_count) {
+    if (!c) return CORAL_E_ARG;
+    cudaSetDevice(c->device);
+    return coral_run_region_coverage(c, tid, start, stop, n, base_sum, rec_count);
+}
+
+}  // extern "C"

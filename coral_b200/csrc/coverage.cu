@@ -1,0 +1,205 @@
+// coral_b200/csrc/coverage.cu — region coverage from the scan table.
+//
+// Replaces AlignmentFile.count_coverage(contig, start, stop, quality_threshold=0, 'nofilter') summed
+// over its four arrays (reference infer_breakpoint_graph.py:131-132 and :1033-1034) and the record
+// count `len([read for read in fetch(...) if read.infer_read_length()])` (:1031-1032).
+//
+// The reference walks every aligned base in Python/Cython.  Here the sum over a region is closed
+// form: a record lying entirely inside a region contributes its aligned-base count (known from the
+// scan) minus its non-ACGT aligned bases; only records that straddle a region boundary, or carry
+// non-ACGT query bases, re-walk their own CIGAR (and SEQ) in a second, warp-per-pair kernel.
+#include "ctx.h"
+#include "dev_util.cuh"
+
+namespace coral {
+
+struct Regions {
+    const int32_t *tid, *start, *stop;
+    int32_t n;
+};
+
+// lowest region index i with (rtid[i], rstop[i]) > (tid, pos): first region not entirely left of pos
+__device__ __forceinline__ int32_t first_region_after(const Regions& R, int32_t tid, int32_t pos) {
+    int32_t lo = 0, hi = R.n;
+    while (lo < hi) {
+        int32_t mid = (lo + hi) >> 1;
+        int32_t t = R.tid[mid];
+        bool left = (t < tid) || (t == tid && R.stop[mid] <= pos);
+        if (left) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// Warp-aggregated atomicAdd of (key, value) pairs: one atomic per distinct key per warp.
+__device__ __forceinline__ void warp_agg_add(unsigned long long* acc, int32_t key, unsigned long long val, bool active) {
+    uint32_t todo = __ballot_sync(FULL_MASK, active);
+    const uint32_t lane = lane_id();
+    while (todo) {
+        const int leader = __ffs(todo) - 1;
+        const int32_t k = __shfl_sync(FULL_MASK, key, leader);
+        const bool mine = active && key == k;
+        unsigned long long v = mine ? val : 0ull;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(FULL_MASK, v, d);
+        if ((int)lane == leader && v) atomicAdd(acc + k, v);
+        todo &= ~__ballot_sync(FULL_MASK, mine);
+    }
+}
+
+__global__ void k_region_cov_fast(int64_t n, const int32_t* __restrict__ tid, const int32_t* __restrict__ pos,
+                                  const int32_t* __restrict__ endpos, const uint32_t* __restrict__ flag_mapq,
+                                  const uint32_t* __restrict__ lseq, const uint32_t* __restrict__ infer,
+                                  const uint32_t* __restrict__ mbases, const uint32_t* __restrict__ nonacgt,
+                                  Regions R, unsigned long long* base_sum, unsigned long long* rec_count,
+                                  uint32_t* slow_rec, int32_t* slow_reg, unsigned long long* slow_n, int64_t slow_cap) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = i < n;
+    int32_t t = -1, p = 0, e = 0, ri = R.n;
+    uint32_t fm = 0, ls = 0, inf = 0, mb = 0, bad = 0;
+    if (live) {
+        t = tid[i]; p = pos[i]; e = endpos[i];
+        fm = flag_mapq[i]; ls = lseq[i]; inf = infer[i]; mb = mbases[i]; bad = nonacgt[i];
+        if (t >= 0) ri = first_region_after(R, t, p);
+    }
+    // A record overlaps a (possibly empty) run of consecutive regions; iterate warp-synchronously.
+    while (true) {
+        const bool ov = live && ri < R.n && R.tid[ri] == t && R.start[ri] < e;
+        if (!__any_sync(FULL_MASK, ov)) break;
+        const bool inside = ov && p >= R.start[ri] && e <= R.stop[ri];
+        const bool clean = inside && bad == 0 && !(fm & 4u);
+        warp_agg_add(rec_count, ri, 1ull, ov && inf > 0);
+        warp_agg_add(base_sum, ri, (unsigned long long)mb, clean && ls > 0);
+        if (ov && !clean && ls > 0 && mb > 0) {
+            unsigned long long s = atomicAdd(slow_n, 1ull);
+            if ((int64_t)s < slow_cap) { slow_rec[s] = (uint32_t)i; slow_reg[s] = ri; }
+        }
+        if (ov) ri++;
+    }
+}
+
+// Exact walk for (record, region) pairs: clipped M/=/X overlap minus non-ACGT aligned query bases.
+__global__ void k_region_cov_slow(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off,
+                                  const uint32_t* __restrict__ slow_rec, const int32_t* __restrict__ slow_reg,
+                                  int64_t n_pairs, const uint32_t* __restrict__ nonacgt, Regions R,
+                                  unsigned long long* base_sum) {
+    const uint32_t lane = lane_id();
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; w < n_pairs; w += nw) {
+        const uint32_t rec = slow_rec[w];
+        const int32_t ri = slow_reg[w];
+        const int32_t rs = R.start[ri], re = R.stop[ri];
+        const uint8_t* r = recs + off[rec];
+        const int32_t pos = (int32_t)ld_u32_any(r + 8);
+        const uint32_t l_name = r[12];
+        const uint32_t n_cig = ld_u32_any(r + 16) & 0xffffu;
+        const uint8_t* cig = r + 36 + l_name;
+        const uint8_t* seq = cig + 4ull * n_cig;
+        const bool check_seq = nonacgt[rec] != 0;
+        int32_t refpos = pos;
+        int64_t qpos = 0;
+        unsigned long long total = 0;
+        for (uint32_t base = 0; base < n_cig; base += 32) {
+            const uint32_t k = base + lane;
+            uint32_t v = (k < n_cig) ? ld_u32_any(cig + 4ull * k) : 0xFu;
+            const uint32_t op = v & 15u;
+            const int32_t len = (int32_t)(v >> 4);
+            const bool is_m = (op == 0 || op == 7 || op == 8);
+            const int32_t rlen = (is_m || op == 2 || op == 3) ? len : 0;
+            const int32_t qlen = (is_m || op == 1 || op == 4) ? len : 0;
+            const int32_t ri_incl = warp_incl_sum_i32(rlen);
+            const int32_t qi_incl = warp_incl_sum_i32(qlen);
+            if (is_m) {
+                const int32_t s = refpos + ri_incl - rlen;
+                const int32_t a = max(s, rs), b = min(s + len, re);
+                if (b > a) {
+                    total += (unsigned long long)(b - a);
+                    if (check_seq) {
+                        int64_t q0 = qpos + (qi_incl - qlen) + (a - s);
+                        for (int32_t x = 0; x < b - a; x++) {
+                            int64_t q = q0 + x;
+                            uint32_t by = seq[q >> 1];
+                            uint32_t nib = (q & 1) ? (by & 15u) : (by >> 4);
+                            if (!(nib == 1 || nib == 2 || nib == 4 || nib == 8)) total -= 1;
+                        }
+                    }
+                }
+            }
+            refpos += __shfl_sync(FULL_MASK, ri_incl, 31);
+            qpos += __shfl_sync(FULL_MASK, qi_incl, 31);
+        }
+        total = warp_sum_u64(total);
+        if (lane == 0 && total) atomicAdd(base_sum + ri, total);
+    }
+}
+
+}  // namespace coral
+
+int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
+                              int32_t n, int64_t* base_sum, int64_t* rec_count) {
+    using namespace coral;
+    if (!ctx->loaded) { ctx->err = "coral_region_coverage before coral_load_records"; return CORAL_E_STATE; }
+    if (n < 0) { ctx->err = "negative region count"; return CORAL_E_ARG; }
+    if (n == 0) return CORAL_OK;
+    for (int32_t i = 0; i < n; i++) {
+        if (stop[i] < start[i] || tid[i] < 0) { ctx->err = "bad region"; return CORAL_E_ARG; }
+        if (i > 0 && (tid[i] < tid[i - 1] || (tid[i] == tid[i - 1] && start[i] < stop[i - 1]))) {
+            ctx->err = "regions must be sorted by (tid, start) and disjoint";
+            return CORAL_E_ARG;
+        }
+    }
+    cudaStream_t st = ctx->stream;
+    const size_t rb = (size_t)n * 4;
+    CORAL_CUDA(ctx, ctx->s0.ensure(rb * 3));
+    CORAL_CUDA(ctx, ctx->s1.ensure((size_t)n * 16 + 8));
+    int32_t* d_reg = ctx->s0.as<int32_t>();
+    CORAL_CUDA(ctx, cudaMemcpyAsync(d_reg, tid, rb, cudaMemcpyHostToDevice, st));
+    CORAL_CUDA(ctx, cudaMemcpyAsync(d_reg + n, start, rb, cudaMemcpyHostToDevice, st));
+    CORAL_CUDA(ctx, cudaMemcpyAsync(d_reg + 2 * (size_t)n, stop, rb, cudaMemcpyHostToDevice, st));
+    unsigned long long* d_sum = ctx->s1.as<unsigned long long>();
+    unsigned long long* d_cnt = d_sum + n;
+    unsigned long long* d_slow_n = d_cnt + n;
+    CORAL_CUDA(ctx, cudaMemsetAsync(d_sum, 0, (size_t)n * 16 + 8, st));
+    Regions R{d_reg, d_reg + n, d_reg + 2 * (size_t)n, n};
+    const int64_t nrec = ctx->nrec;
+    int64_t slow_cap = std::max<int64_t>(1 << 16, (int64_t)(ctx->s2.cap / 4));
+    RecordTable& t = ctx->rt;
+    for (int attempt = 0; attempt < 2 && nrec > 0; attempt++) {
+        CORAL_CUDA(ctx, ctx->s2.ensure((size_t)slow_cap * 4));
+        CORAL_CUDA(ctx, ctx->s3.ensure((size_t)slow_cap * 4));
+        if (attempt) CORAL_CUDA(ctx, cudaMemsetAsync(d_sum, 0, (size_t)n * 16 + 8, st));
+        const int threads = 256;
+        const int blocks = (int)((nrec + threads - 1) / threads);
+        if (attempt == 0) ctx->stage_begin(CORAL_STAGE_COVERAGE);
+        k_region_cov_fast<<<blocks, threads, 0, st>>>(
+            nrec, t.tid.as<int32_t>(), t.pos.as<int32_t>(), t.endpos.as<int32_t>(), t.flag_mapq.as<uint32_t>(),
+            t.lseq.as<uint32_t>(), t.infer.as<uint32_t>(), t.mbases.as<uint32_t>(), t.nonacgt.as<uint32_t>(), R, d_sum,
+            d_cnt, ctx->s2.as<uint32_t>(), ctx->s3.as<int32_t>(), d_slow_n, slow_cap);
+        ctx->n_launches++;
+        CORAL_CUDA(ctx, cudaGetLastError());
+        unsigned long long n_slow = 0;
+        CORAL_CUDA(ctx, cudaMemcpyAsync(&n_slow, d_slow_n, 8, cudaMemcpyDeviceToHost, st));
+        CORAL_CUDA(ctx, cudaStreamSynchronize(st));
+        if ((int64_t)n_slow > slow_cap) { slow_cap = (int64_t)n_slow + 1024; continue; }
+        if (n_slow) {
+            const int64_t warps_per_block = 8;
+            int sblocks = (int)std::min<int64_t>(((int64_t)n_slow + warps_per_block - 1) / warps_per_block,
+                                                 (int64_t)ctx->sm_count * 8);
+            k_region_cov_slow<<<sblocks, 256, 0, st>>>(ctx->d_recs, ctx->d_off.as<uint64_t>(), ctx->s2.as<uint32_t>(),
+                                                       ctx->s3.as<int32_t>(), (int64_t)n_slow, t.nonacgt.as<uint32_t>(),
+                                                       R, d_sum);
+            ctx->n_launches++;
+            CORAL_CUDA(ctx, cudaGetLastError());
+        }
+        break;
+    }
+    ctx->stage_end(CORAL_STAGE_COVERAGE);
+    std::vector<unsigned long long> h((size_t)n * 2);
+    CORAL_CUDA(ctx, cudaMemcpyAsync(h.data(), d_sum, (size_t)n * 16, cudaMemcpyDeviceToHost, st));
+    CORAL_CUDA(ctx, cudaStreamSynchronize(st));
+    for (int32_t i = 0; i < n; i++) {
+        if (base_sum) base_sum[i] = (int64_t)h[i];
+        if (rec_count) rec_count[i] = (int64_t)h[(size_t)n + i];
+    }
+    return CORAL_OK;
+}

@@ -1,0 +1,112 @@
+// coral_b200/csrc/ctx.h — context object behind the C ABI (include/coral_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/coral_b200.h"
+
+#define CORAL_CUDA(ctx, call)                                                                  \
+    do {                                                                                       \
+        cudaError_t e__ = (call);                                                              \
+        if (e__ != cudaSuccess) {                                                              \
+            char b__[512];                                                                     \
+            snprintf(b__, sizeof b__, "%s:%d %s -> %s", __FILE__, __LINE__, #call,             \
+                     cudaGetErrorString(e__));                                                 \
+            (ctx)->err = b__;                                                                  \
+            return CORAL_E_CUDA;                                                               \
+        }                                                                                      \
+    } while (0)
+
+#define CORAL_TRY(expr)                  \
+    do {                                 \
+        int r__ = (expr);                \
+        if (r__ != CORAL_OK) return r__; \
+    } while (0)
+
+// Grow-only device buffer.
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        cap = (e == cudaSuccess) ? want : 0;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// Per-record scan table (SoA), produced once by k_scan_records.
+struct RecordTable {
+    DevBuf tid, pos, endpos, flag_mapq, lseq, ncig, infer, mbases, nonacgt, fbs, lbe, name_lo, name_hi,
+        sa_off, sa_len, nm, ngap, gap_base;
+};
+
+// In-CIGAR gap events (> min_del_len between consecutive aligned blocks).
+struct GapEvents {
+    DevBuf rec, k, next_start, prev_end;
+    DevBuf counter;  // uint64 total (may exceed capacity -> rescan)
+    int64_t capacity = 0;
+    int64_t n = 0;
+};
+
+struct coral_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    coral_params prm;
+
+    // references
+    std::vector<std::string> ref_names;
+    std::vector<int32_t> chr_rank_h;
+    DevBuf d_chr_rank, d_ref_hash;
+
+    // records
+    DevBuf recs_owned;
+    const uint8_t* d_recs = nullptr;
+    uint64_t nbytes = 0;
+    DevBuf d_off, d_ordinal;
+    int64_t nrec = 0;
+    bool loaded = false;
+    bool has_ordinal = false;
+
+    RecordTable rt;
+    GapEvents gaps;
+    DevBuf status;  // int32[8] device status words (format errors etc.)
+
+    // scratch
+    DevBuf s0, s1, s2, s3, s4, s5, s6, s7;
+    DevBuf cub_tmp;
+
+    // launch accounting (bench reports gpu_launches)
+    uint64_t n_launches = 0;
+    int sm_count = 148;
+
+    // per-stage CUDA-event timing on ctx->stream (coral_stage_ms)
+    cudaEvent_t ev_beg[CORAL_N_STAGES] = {};
+    cudaEvent_t ev_end[CORAL_N_STAGES] = {};
+    bool ev_valid[CORAL_N_STAGES] = {};
+    void stage_begin(int s) {
+        if (!ev_beg[s]) { cudaEventCreate(&ev_beg[s]); cudaEventCreate(&ev_end[s]); }
+        cudaEventRecord(ev_beg[s], stream);
+    }
+    void stage_end(int s) { cudaEventRecord(ev_end[s], stream); ev_valid[s] = true; }
+};
+
+// kernels / stages implemented in the .cu files
+int coral_upload_ref_hashes(coral_ctx* ctx);
+void coral_release_tables(coral_ctx* ctx);
+int coral_run_scan(coral_ctx* ctx);
+int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
+                              int32_t n, int64_t* base_sum, int64_t* rec_count);
