@@ -188,3 +188,24 @@ class Context(object):
         rc = np.zeros(n, np.int64)
         self._check(self._L.coral_region_coverage(self._h, _p(tid), _p(start), _p(stop), n, _p(bs), _p(rc)))
         return bs, rc
+
+    def fetch(self):
+        """coral_fetch + coral_get_chimeric -> dict of numpy arrays (see include/coral_b200.h)."""
+        nr = ctypes.c_int64(); na = ctypes.c_int64(); s1 = ctypes.c_double(); s2 = ctypes.c_double()
+        nn = ctypes.c_int64(); zd = ctypes.c_int64()
+        self._check(self._L.coral_fetch(self._h, ctypes.byref(nr), ctypes.byref(na), ctypes.byref(s1), ctypes.byref(s2),
+                                        ctypes.byref(nn), ctypes.byref(zd)))
+        nr, na = nr.value, na.value
+        out = {"n_reads": nr, "n_aln": na, "nm_sum": s1.value, "nm_sumsq": s2.value, "nm_n": nn.value,
+               "nm_zero_div": zd.value,
+               "read_first_rec": np.zeros(nr, np.uint32), "read_len": np.zeros(nr, np.int64),
+               "read_status": np.zeros(nr, np.int32), "aln_ptr": np.zeros(nr + 1, np.uint32)}
+        for k in ("qs", "qe", "tid", "rstart", "rend", "mapq"):
+            out[k] = np.zeros(na, np.int32)
+        out["strand"] = np.zeros(na, np.uint8)
+        out["nm"] = np.zeros(na, np.int64)
+        self._check(self._L.coral_get_chimeric(
+            self._h, _p(out["read_first_rec"]), _p(out["read_len"]), _p(out["read_status"]), _p(out["aln_ptr"]),
+            _p(out["qs"]), _p(out["qe"]), _p(out["tid"]), _p(out["rstart"]), _p(out["rend"]), _p(out["strand"]),
+            _p(out["mapq"]), _p(out["nm"])))
+        return out

@@ -45,7 +45,9 @@ void coral_destroy(coral_ctx* c) {
                      &c->rt.tid, &c->rt.pos, &c->rt.endpos, &c->rt.flag_mapq, &c->rt.lseq, &c->rt.ncig, &c->rt.infer,
                      &c->rt.mbases, &c->rt.nonacgt, &c->rt.fbs, &c->rt.lbe, &c->rt.name_lo, &c->rt.name_hi,
                      &c->rt.sa_off, &c->rt.sa_len, &c->rt.nm, &c->rt.ngap, &c->rt.gap_base,
-                     &c->gaps.rec, &c->gaps.k, &c->gaps.next_start, &c->gaps.prev_end, &c->gaps.counter};
+                     &c->gaps.rec, &c->gaps.k, &c->gaps.next_start, &c->gaps.prev_end, &c->gaps.counter,
+                     &c->chim.read_first_rec, &c->chim.read_len, &c->chim.read_status, &c->chim.aln_ptr, &c->chim.qs,
+                     &c->chim.qe, &c->chim.tid, &c->chim.rs, &c->chim.re, &c->chim.strand, &c->chim.mapq, &c->chim.nm};
     for (DevBuf* b : all) b->release();
     coral_release_tables(c);
     for (int i = 0; i < CORAL_N_STAGES; i++) {

@@ -61,6 +61,17 @@ struct GapEvents {
     int64_t n = 0;
 };
 
+// Chimeric-alignment table produced by coral_fetch (reads in reference dict order, CSR alignments).
+struct ChimericTable {
+    DevBuf read_first_rec, read_len, read_status, aln_ptr;
+    DevBuf qs, qe, tid, rs, re, strand, mapq, nm;
+    int64_t n_reads = 0, n_aln = 0;
+    bool valid = false;
+    double nm_sum = 0, nm_sq = 0;
+    int64_t nm_n = 0;
+    int64_t nm_zero_div = 0;
+};
+
 struct coral_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -83,6 +94,7 @@ struct coral_ctx {
 
     RecordTable rt;
     GapEvents gaps;
+    ChimericTable chim;
     DevBuf status;  // int32[8] device status words (format errors etc.)
 
     // scratch
@@ -108,5 +120,6 @@ struct coral_ctx {
 int coral_upload_ref_hashes(coral_ctx* ctx);
 void coral_release_tables(coral_ctx* ctx);
 int coral_run_scan(coral_ctx* ctx);
+int coral_run_fetch(coral_ctx* ctx);
 int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
                               int32_t n, int64_t* base_sum, int64_t* rec_count);

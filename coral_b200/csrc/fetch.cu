@@ -1,0 +1,566 @@
+// coral_b200/csrc/fetch.cu — chimeric-alignment extraction (reference infer_breakpoint_graph.py:139-174
+// `fetch` + cigar_parsing.py:232-269 `alignment_from_satags` and the nine cigar2pos* forms :17-215).
+//
+// Input is the scan table (SA tag location, name hash, flag, l_seq per record).  Steps:
+//   1. ordered compaction of SA-bearing records; per record count of ';'-separated entries
+//   2. entry table: byte range of every entry in emission order (record order, then entry order)
+//   3. parse every entry (thread per entry): rname -> tid, pos, strand, CIGAR signature + numbers, mapq, NM
+//   4. stable sort by read-name hash => reads; first-seen de-duplication of identical entry strings
+//   5. read_length = l_seq of the first record with flag < 256 carrying the same name (binary-search join)
+//   6. per read: (qs, qe, al) by signature, rint by strand, stable insertion sort by (qs, qe)
+//   7. reads ordered by their first SA-bearing record (dict insertion order of the reference)
+#include <vector>
+
+#include "ctx.h"
+#include "dev_util.cuh"
+#include "relops.cuh"
+#include "tables.h"
+
+namespace coral {
+
+// ---- 1. ------------------------------------------------------------------------------------------
+__global__ void k_flag_sa(int64_t n, const uint32_t* __restrict__ sa_off, uint8_t* __restrict__ flag) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flag[i] = sa_off[i] != 0;
+}
+
+// warp per SA record: number of entries of s[:-1].split(';')
+__global__ void k_count_entries(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off,
+                                const uint32_t* __restrict__ sa_rec, int64_t n_sa, const uint32_t* __restrict__ sa_off,
+                                const uint32_t* __restrict__ sa_len, uint32_t* __restrict__ n_ent) {
+    const uint32_t lane = lane_id();
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= n_sa) return;
+    const uint32_t rec = sa_rec[w];
+    const uint8_t* s = recs + off[rec] + sa_off[rec];
+    const uint32_t len = sa_len[rec] ? sa_len[rec] - 1 : 0;  // [:-1]
+    uint32_t cnt = 0;
+    for (uint32_t b = lane; b < len; b += 32) cnt += s[b] == ';';
+    cnt = (uint32_t)warp_sum_i64(cnt);
+    if (lane == 0) n_ent[w] = cnt + 1;
+}
+
+// ---- 2. ------------------------------------------------------------------------------------------
+__global__ void k_entry_ranges(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off,
+                               const uint32_t* __restrict__ sa_rec, int64_t n_sa, const uint32_t* __restrict__ sa_off,
+                               const uint32_t* __restrict__ sa_len, const uint32_t* __restrict__ ent_base,
+                               uint32_t* __restrict__ e_rec, uint32_t* __restrict__ e_beg, uint32_t* __restrict__ e_end) {
+    const uint32_t lane = lane_id();
+    const uint32_t lt = (1u << lane) - 1u;
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= n_sa) return;
+    const uint32_t rec = sa_rec[w];
+    const uint32_t so = sa_off[rec];
+    const uint8_t* s = recs + off[rec] + so;
+    const uint32_t len = sa_len[rec] ? sa_len[rec] - 1 : 0;
+    const uint32_t base = ent_base[w];
+    uint32_t seen = 0;
+    if (lane == 0) { e_rec[base] = rec; e_beg[base] = so; }
+    for (uint32_t b0 = 0; b0 < len; b0 += 32) {
+        const uint32_t b = b0 + lane;
+        const bool sep = b < len && s[b] == ';';
+        const uint32_t m = __ballot_sync(FULL_MASK, sep);
+        if (sep) {
+            const uint32_t k = seen + __popc(m & lt);
+            e_end[base + k] = so + b;
+            e_rec[base + k + 1] = rec;
+            e_beg[base + k + 1] = so + b + 1;
+        }
+        seen += __popc(m);
+    }
+    if (lane == 0) e_end[base + seen] = so + len;
+}
+
+// ---- 3. ------------------------------------------------------------------------------------------
+// signature codes: index into {"SM","MS","SMS","SMD","MDS","SMDS","SMI","MIS","SMIS"}; 100 = reject
+// (no 'S' or no 'M', cp:248-253); 101 = KeyError (signature not in cp:219-229); 102 = malformed.
+__device__ __forceinline__ int sig_code(const char* sig, int n) {
+    const char* keys[9] = {"SM", "MS", "SMS", "SMD", "MDS", "SMDS", "SMI", "MIS", "SMIS"};
+    for (int k = 0; k < 9; k++) {
+        int j = 0;
+        while (j < n && keys[k][j] && keys[k][j] == sig[j]) j++;
+        if (j == n && keys[k][j] == 0) return k;
+    }
+    return 101;
+}
+
+__global__ void k_parse_entries(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off, int64_t n_ent,
+                                const uint32_t* __restrict__ e_rec, const uint32_t* __restrict__ e_beg,
+                                const uint32_t* __restrict__ e_end, const uint64_t* __restrict__ ref_hash, int32_t n_ref,
+                                SaEntry* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_ent) return;
+    const uint8_t* s = recs + off[e_rec[i]];
+    uint32_t p = e_beg[i];
+    const uint32_t end = e_end[i];
+    SaEntry e;
+    e.rec = e_rec[i];
+    e.tid = -1; e.pos1 = 0; e.strand = 1; e.sig = 102; e.mapq = 0; e.nm = 0;
+    e.num[0] = e.num[1] = e.num[2] = e.num[3] = 0;
+    // entry hash over raw bytes (exact-string de-duplication, ibg:148)
+    uint64_t h1 = 0, h2 = 0;
+    for (uint32_t b = p; b < end; b++) { h1 += hterm1(b - p, s[b]); h2 += hterm2(b - p, s[b]); }
+    e.h1 = h1 + mix64(end - p);
+    e.h2 = h2 + mix64((end - p) ^ 0xABCDull);
+    // field 0: rname
+    uint32_t f0 = p;
+    while (p < end && s[p] != ',') p++;
+    {
+        uint64_t a = 0, b2 = 0;
+        for (uint32_t b = f0; b < p; b++) { a += hterm1(b - f0, s[b]); b2 += hterm2(b - f0, s[b]); }
+        a += mix64(p - f0); b2 += mix64((p - f0) ^ 0xABCDull);
+        for (int32_t t = 0; t < n_ref; t++)
+            if (ref_hash[t] == a && ref_hash[n_ref + t] == b2) { e.tid = t; break; }
+    }
+    bool ok = p < end;
+    p++;
+    // field 1: pos
+    int64_t v = 0; uint32_t nd = 0;
+    while (ok && p < end && s[p] != ',') { uint32_t d = s[p] - '0'; if (d > 9) ok = false; v = v * 10 + d; nd++; p++; }
+    ok = ok && nd > 0 && p < end; e.pos1 = v; p++;
+    // field 2: strand ("+" exactly, anything else behaves as '-', cp:257 / cigar2pos*)
+    uint32_t f2 = p;
+    while (ok && p < end && s[p] != ',') p++;
+    e.strand = (ok && p - f2 == 1 && s[f2] == '+') ? 0 : 1;
+    ok = ok && p < end; p++;
+    // field 3: CIGAR
+    char sig[6]; int ns = 0, nn = 0; bool has_s = false, has_m = false, num_open = false, bad_num = false;
+    int64_t cur = 0;
+    while (ok && p < end && s[p] != ',') {
+        const uint8_t ch = s[p];
+        if (ch >= '0' && ch <= '9') { cur = cur * 10 + (ch - '0'); num_open = true; }
+        else {
+            if (ch == 'S') has_s = true;
+            if (ch == 'M') has_m = true;
+            if (ns < 5) sig[ns] = (char)ch;
+            ns++;
+            if (!num_open) bad_num = true;
+            if (nn < 4) e.num[nn] = cur;
+            nn++; cur = 0; num_open = false;
+        }
+        p++;
+    }
+    if (num_open) bad_num = true;  // trailing digits without an op letter
+    ok = ok && p < end; p++;
+    // field 4: mapq
+    v = 0; nd = 0;
+    while (ok && p < end && s[p] != ',') { uint32_t d = s[p] - '0'; if (d > 9) ok = false; v = v * 10 + d; nd++; p++; }
+    ok = ok && nd > 0; e.mapq = (int32_t)v;
+    // last field: NM (float(t[-1]))
+    if (ok) {
+        uint32_t q = end;
+        while (q > e_beg[i] && s[q - 1] != ',') q--;
+        v = 0; nd = 0;
+        for (uint32_t b = q; b < end; b++) { uint32_t d = s[b] - '0'; if (d > 9) ok = false; v = v * 10 + d; nd++; }
+        ok = ok && nd > 0; e.nm = v;
+    }
+    if (!ok) e.sig = 102;
+    else if (!has_s || !has_m) e.sig = 100;
+    else if (ns > 4) e.sig = 101;
+    else { int c = sig_code(sig, ns); e.sig = (c <= 8 && bad_num) ? 102 : c; }
+    out[i] = e;
+}
+
+// ---- 4. ------------------------------------------------------------------------------------------
+__global__ void k_gather_name(int64_t n, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
+                              const uint64_t* __restrict__ name, uint64_t* __restrict__ key) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) key[i] = name[ent[perm ? perm[i] : i].rec];
+}
+__global__ void k_iota(int64_t n, uint32_t* p) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = (uint32_t)i;
+}
+// head[i] = 1 when sorted position i starts a new read name
+__global__ void k_heads(int64_t n, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
+                        const uint64_t* __restrict__ nlo, const uint64_t* __restrict__ nhi, uint32_t* __restrict__ head) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (i == 0) { head[0] = 1; return; }
+    const uint32_t a = ent[perm[i]].rec, b = ent[perm[i - 1]].rec;
+    head[i] = (nlo[a] != nlo[b] || nhi[a] != nhi[b]) ? 1u : 0u;
+}
+// seg_id (0-based) from inclusive scan of heads; records segment starts; marks duplicates within a segment
+__global__ void k_segments(int64_t n, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
+                           const uint32_t* __restrict__ head_incl, uint32_t* __restrict__ seg_start,
+                           uint32_t* __restrict__ seg_of) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t sgm = head_incl[i] - 1;
+    seg_of[i] = sgm;
+    if (i == 0 || head_incl[i - 1] != head_incl[i]) seg_start[sgm] = (uint32_t)i;
+}
+__global__ void k_mark_dups(int64_t n, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
+                            const uint32_t* __restrict__ seg_of, const uint32_t* __restrict__ seg_start,
+                            uint8_t* __restrict__ keep) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const SaEntry& me = ent[perm[i]];
+    bool dup = false;
+    for (uint32_t j = seg_start[seg_of[i]]; j < (uint32_t)i && !dup; j++) {
+        const SaEntry& o = ent[perm[j]];
+        dup = (o.h1 == me.h1 && o.h2 == me.h2);
+    }
+    keep[i] = !dup;
+}
+
+// ---- 5. ------------------------------------------------------------------------------------------
+// names of the segments, sorted by (hi, lo) because the sort was LSD lo-then-hi; binary search join.
+__global__ void k_first_primary(int64_t n_rec, const uint32_t* __restrict__ flag_mapq, const uint64_t* __restrict__ nlo,
+                                const uint64_t* __restrict__ nhi, int64_t n_seg, const uint64_t* __restrict__ seg_lo,
+                                const uint64_t* __restrict__ seg_hi, uint32_t* __restrict__ first_primary) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_rec) return;
+    if ((flag_mapq[i] & 0xffffu) >= 256u) return;
+    const uint64_t lo_k = nlo[i], hi_k = nhi[i];
+    int64_t lo = 0, hi = n_seg;
+    while (lo < hi) {
+        int64_t mid = (lo + hi) >> 1;
+        bool less = seg_hi[mid] < hi_k || (seg_hi[mid] == hi_k && seg_lo[mid] < lo_k);
+        if (less) lo = mid + 1; else hi = mid;
+    }
+    if (lo < n_seg && seg_hi[lo] == hi_k && seg_lo[lo] == lo_k) atomicMin(&first_primary[lo], (uint32_t)i);
+}
+__global__ void k_seg_names(int64_t n_seg, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
+                            const uint32_t* __restrict__ seg_start, const uint64_t* __restrict__ nlo,
+                            const uint64_t* __restrict__ nhi, uint64_t* __restrict__ seg_lo, uint64_t* __restrict__ seg_hi,
+                            uint64_t* __restrict__ seg_first_emit, uint32_t* __restrict__ first_primary) {
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_seg) return;
+    const uint32_t e0 = perm[seg_start[s]];  // stable sort => smallest emission index of the segment
+    const uint32_t rec = ent[e0].rec;
+    seg_lo[s] = nlo[rec];
+    seg_hi[s] = nhi[rec];
+    seg_first_emit[s] = e0;
+    first_primary[s] = 0xFFFFFFFFu;
+}
+
+}  // namespace coral
+
+namespace coral {
+
+// ---- 6. ------------------------------------------------------------------------------------------
+// cigar2pos{SM,MS,SMS,SMD,MDS,SMDS,SMI,MIS,SMIS} (cp:17-215), n = CIGAR numbers in order.
+__device__ __forceinline__ void cigar2pos_dev(int sig, const int64_t* n, bool minus, int64_t rl, int64_t& qs,
+                                              int64_t& qe, int64_t& al) {
+    switch (sig) {
+        case 0: al = n[1];        if (!minus) { qs = n[0]; qe = rl - 1; }            else { qs = 0;    qe = n[1] - 1; }         break;
+        case 1: al = n[0];        if (!minus) { qs = 0;    qe = n[0] - 1; }          else { qs = n[1]; qe = rl - 1; }           break;
+        case 2: al = n[1];        if (!minus) { qs = n[0]; qe = n[0] + n[1] - 1; }   else { qs = n[2]; qe = n[2] + n[1] - 1; }  break;
+        case 3: al = n[1] + n[2]; if (!minus) { qs = n[0]; qe = rl - 1; }            else { qs = 0;    qe = n[1] - 1; }         break;
+        case 4: al = n[0] + n[1]; if (!minus) { qs = 0;    qe = n[0] - 1; }          else { qs = n[2]; qe = rl - 1; }           break;
+        case 5: al = n[1] + n[2]; if (!minus) { qs = n[0]; qe = rl - n[3] - 1; }     else { qs = n[3]; qe = rl - n[0] - 1; }    break;
+        case 6: al = n[1];        if (!minus) { qs = n[0]; qe = rl - 1; }            else { qs = 0;    qe = rl - n[0] - 1; }    break;
+        case 7: al = n[0];        if (!minus) { qs = 0;    qe = rl - n[2] - 1; }     else { qs = n[2]; qe = rl - 1; }           break;
+        default: al = n[1];       if (!minus) { qs = n[0]; qe = rl - n[3] - 1; }     else { qs = n[3]; qe = rl - n[0] - 1; }    break;
+    }
+}
+
+struct ChimCols {
+    uint32_t *read_first_rec, *aln_ptr;
+    int64_t *read_len, *nm;
+    int32_t *read_status, *qs, *qe, *tid, *rs, *re, *mapq;
+    uint8_t* strand;
+};
+
+// thread per segment (read): status + number of alignments
+__global__ void k_read_counts(int64_t n_seg, int64_t n_ent, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
+                              const uint32_t* __restrict__ seg_start, const uint8_t* __restrict__ keep,
+                              const uint32_t* __restrict__ first_primary, int32_t* __restrict__ seg_status,
+                              uint32_t* __restrict__ seg_cnt) {
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_seg) return;
+    const uint32_t b = seg_start[s], e = (s + 1 < n_seg) ? seg_start[s + 1] : (uint32_t)n_ent;
+    int32_t st = READ_OK;
+    uint32_t cnt = 0;
+    if (first_primary[s] == 0xFFFFFFFFu) st = READ_NO_PRIMARY;
+    else {
+        for (uint32_t i = b; i < e && st == READ_OK; i++) {
+            if (!keep[i]) continue;
+            const uint8_t sg = ent[perm[i]].sig;
+            if (sg == 100) st = READ_REJECTED;
+            else if (sg == 101) st = READ_KEYERROR;
+            else if (sg == 102 || ent[perm[i]].tid < 0) st = READ_MALFORMED;
+            else cnt++;
+        }
+    }
+    seg_status[s] = st;
+    seg_cnt[s] = st == READ_OK ? cnt : 0;
+}
+
+__global__ void k_gather_u32(int64_t n, const uint32_t* __restrict__ idx, const uint32_t* __restrict__ src, uint32_t* __restrict__ dst) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[idx[i]];
+}
+
+// thread per read rank: fill alignments, stable insertion sort by (qs, qe) (cp:263)
+__global__ void k_read_fill(int64_t n_seg, int64_t n_ent, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
+                            const uint32_t* __restrict__ seg_start, const uint8_t* __restrict__ keep,
+                            const uint32_t* __restrict__ first_primary, const int32_t* __restrict__ seg_status,
+                            const uint32_t* __restrict__ order, const uint32_t* __restrict__ lseq, uint32_t total_aln,
+                            ChimCols o) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_seg) return;
+    const uint32_t s = order[r];
+    const uint32_t b = seg_start[s], e = (s + 1 < (uint32_t)n_seg) ? seg_start[s + 1] : (uint32_t)n_ent;
+    const int32_t st = seg_status[s];
+    o.read_status[r] = st;
+    o.read_first_rec[r] = ent[perm[b]].rec;
+    const uint32_t fp = first_primary[s];
+    const int64_t rl = fp == 0xFFFFFFFFu ? -1 : (int64_t)lseq[fp];
+    o.read_len[r] = rl;
+    if (r == n_seg - 1) o.aln_ptr[n_seg] = total_aln;
+    if (st != READ_OK) return;
+    const uint32_t base = o.aln_ptr[r];
+    uint32_t k = 0;
+    for (uint32_t i = b; i < e; i++) {
+        if (!keep[i]) continue;
+        const SaEntry& a = ent[perm[i]];
+        int64_t qs, qe, al;
+        cigar2pos_dev(a.sig, a.num, a.strand != 0, rl, qs, qe, al);
+        const int64_t lo = a.pos1 - 1, hi = a.pos1 + al - 2;
+        const int32_t rs = (int32_t)(a.strand ? hi : lo), re = (int32_t)(a.strand ? lo : hi);
+        // insertion point: after every earlier element with (qs, qe) <= mine (stable)
+        uint32_t j = k;
+        while (j > 0 && (o.qs[base + j - 1] > qs || (o.qs[base + j - 1] == qs && o.qe[base + j - 1] > qe))) {
+            const uint32_t d = base + j, sft = base + j - 1;
+            o.qs[d] = o.qs[sft]; o.qe[d] = o.qe[sft]; o.tid[d] = o.tid[sft]; o.rs[d] = o.rs[sft]; o.re[d] = o.re[sft];
+            o.strand[d] = o.strand[sft]; o.mapq[d] = o.mapq[sft]; o.nm[d] = o.nm[sft];
+            j--;
+        }
+        const uint32_t d = base + j;
+        o.qs[d] = (int32_t)qs; o.qe[d] = (int32_t)qe; o.tid[d] = a.tid; o.rs[d] = rs; o.re[d] = re;
+        o.strand[d] = a.strand; o.mapq[d] = a.mapq; o.nm[d] = a.nm;
+        k++;
+    }
+}
+
+// ---- nm_stats (ibg:153-160): records without SA and MAPQ 60 contribute e = NM / query_length -------
+constexpr int NM_BLOCK = 256;
+__global__ void k_nm_stats(int64_t n, const uint32_t* __restrict__ sa_off, const uint32_t* __restrict__ flag_mapq,
+                           const int32_t* __restrict__ tid, const int32_t* __restrict__ nm, const uint32_t* __restrict__ lseq,
+                           double* __restrict__ part) {
+    __shared__ double s1[NM_BLOCK], s2[NM_BLOCK], s3[NM_BLOCK], s4[NM_BLOCK];
+    const int64_t i = (int64_t)blockIdx.x * NM_BLOCK + threadIdx.x;
+    double e = 0, cnt = 0, zd = 0;
+    if (i < n && tid[i] >= 0 && sa_off[i] == 0 && (flag_mapq[i] >> 16) == 60u) {
+        if (lseq[i] == 0) zd = 1;
+        else { e = (double)nm[i] / (double)lseq[i]; cnt = 1; }
+    }
+    s1[threadIdx.x] = e; s2[threadIdx.x] = e * e; s3[threadIdx.x] = cnt; s4[threadIdx.x] = zd;
+    __syncthreads();
+    for (int d = NM_BLOCK / 2; d > 0; d >>= 1) {
+        if (threadIdx.x < d) {
+            s1[threadIdx.x] += s1[threadIdx.x + d]; s2[threadIdx.x] += s2[threadIdx.x + d];
+            s3[threadIdx.x] += s3[threadIdx.x + d]; s4[threadIdx.x] += s4[threadIdx.x + d];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        part[4 * (size_t)blockIdx.x] = s1[0]; part[4 * (size_t)blockIdx.x + 1] = s2[0];
+        part[4 * (size_t)blockIdx.x + 2] = s3[0]; part[4 * (size_t)blockIdx.x + 3] = s4[0];
+    }
+}
+
+}  // namespace coral
+
+// ---- host orchestration ----------------------------------------------------------------------------
+#define LAUNCH_1D(kern, n, ...)                                                          \
+    do {                                                                                 \
+        if ((n) > 0) {                                                                   \
+            kern<<<(unsigned)(((n) + 255) / 256), 256, 0, c->stream>>>(__VA_ARGS__);      \
+            c->n_launches++;                                                             \
+            CORAL_CUDA(c, cudaGetLastError());                                           \
+        }                                                                                \
+    } while (0)
+#define LAUNCH_WARP(kern, nw, ...)                                                       \
+    do {                                                                                 \
+        if ((nw) > 0) {                                                                  \
+            kern<<<(unsigned)(((nw) + 7) / 8), 256, 0, c->stream>>>(__VA_ARGS__);         \
+            c->n_launches++;                                                             \
+            CORAL_CUDA(c, cudaGetLastError());                                           \
+        }                                                                                \
+    } while (0)
+
+int coral_run_fetch(coral_ctx* c) {
+    using namespace coral;
+    if (!c->loaded) { c->err = "coral_fetch before coral_load_records"; return CORAL_E_STATE; }
+    if (c->ref_names.empty()) { c->err = "coral_fetch before coral_set_references"; return CORAL_E_STATE; }
+    ChimericTable& T = c->chim;
+    T.valid = false; T.n_reads = 0; T.n_aln = 0;
+    const int64_t n = c->nrec;
+    RecordTable& rt = c->rt;
+    const uint8_t* recs = c->d_recs;
+    const uint64_t* off = c->d_off.as<uint64_t>();
+    c->stage_begin(CORAL_STAGE_FETCH);
+
+    // nm_stats partials
+    const int64_t nblk = (n + NM_BLOCK - 1) / NM_BLOCK;
+    CORAL_CUDA(c, c->s7.ensure((size_t)std::max<int64_t>(nblk, 1) * 32));
+    if (n > 0) {
+        k_nm_stats<<<(unsigned)nblk, NM_BLOCK, 0, c->stream>>>(n, rt.sa_off.as<uint32_t>(), rt.flag_mapq.as<uint32_t>(),
+                                                              rt.tid.as<int32_t>(), rt.nm.as<int32_t>(), rt.lseq.as<uint32_t>(),
+                                                              c->s7.as<double>());
+        c->n_launches++;
+        CORAL_CUDA(c, cudaGetLastError());
+    }
+    // 1. SA-bearing records in record order
+    CORAL_CUDA(c, c->s0.ensure((size_t)std::max<int64_t>(n, 1)));          // flags u8
+    CORAL_CUDA(c, c->s1.ensure((size_t)std::max<int64_t>(n, 1) * 4 + 16)); // sa_rec u32 + count
+    uint8_t* d_flag = c->s0.as<uint8_t>();
+    uint32_t* d_sa_rec = c->s1.as<uint32_t>();
+    uint32_t* d_cnt = d_sa_rec + std::max<int64_t>(n, 1);
+    LAUNCH_1D(k_flag_sa, n, n, rt.sa_off.as<uint32_t>(), d_flag);
+    CORAL_TRY(select_flagged_iota(c, d_flag, d_sa_rec, d_cnt, n));
+    uint32_t n_sa = 0;
+    CORAL_TRY(d2h(c, &n_sa, d_cnt, 1));
+    std::vector<double> part((size_t)std::max<int64_t>(nblk, 1) * 4, 0.0);
+    CORAL_TRY(d2h(c, part.data(), c->s7.p, (size_t)nblk * 4));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    T.nm_sum = T.nm_sq = 0; T.nm_n = 0; T.nm_zero_div = 0;
+    for (int64_t b = 0; b < nblk; b++) {
+        T.nm_sum += part[4 * b]; T.nm_sq += part[4 * b + 1];
+        T.nm_n += (int64_t)part[4 * b + 2]; T.nm_zero_div += (int64_t)part[4 * b + 3];
+    }
+    if (n_sa == 0) { T.valid = true; c->stage_end(CORAL_STAGE_FETCH); return CORAL_OK; }
+
+    // entries per SA record -> bases
+    CORAL_CUDA(c, c->s2.ensure((size_t)(n_sa + 1) * 8 + 16));
+    uint32_t* d_nent = c->s2.as<uint32_t>();
+    uint32_t* d_base = d_nent + n_sa + 1;
+    LAUNCH_WARP(k_count_entries, n_sa, recs, off, d_sa_rec, (int64_t)n_sa, rt.sa_off.as<uint32_t>(), rt.sa_len.as<uint32_t>(), d_nent);
+    CORAL_CUDA(c, cudaMemsetAsync(d_nent + n_sa, 0, 4, c->stream));
+    CORAL_TRY(exclusive_sum_u32(c, d_nent, d_base, (int64_t)n_sa + 1));
+    uint32_t n_ent = 0;
+    CORAL_TRY(d2h(c, &n_ent, d_base + n_sa, 1));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+
+    // 2-3. entry ranges + parse
+    CORAL_CUDA(c, c->s3.ensure((size_t)n_ent * 12));
+    uint32_t* e_rec = c->s3.as<uint32_t>();
+    uint32_t* e_beg = e_rec + n_ent;
+    uint32_t* e_end = e_beg + n_ent;
+    LAUNCH_WARP(k_entry_ranges, n_sa, recs, off, d_sa_rec, (int64_t)n_sa, rt.sa_off.as<uint32_t>(), rt.sa_len.as<uint32_t>(),
+                d_base, e_rec, e_beg, e_end);
+    CORAL_CUDA(c, c->s4.ensure((size_t)n_ent * sizeof(SaEntry)));
+    SaEntry* ent = c->s4.as<SaEntry>();
+    LAUNCH_1D(k_parse_entries, (int64_t)n_ent, recs, off, (int64_t)n_ent, e_rec, e_beg, e_end, c->d_ref_hash.as<uint64_t>(),
+              (int32_t)c->ref_names.size(), ent);
+
+    // 4. stable sort of entry indices by name (lo then hi)
+    CORAL_CUDA(c, c->s5.ensure((size_t)n_ent * 24 + 64));
+    uint64_t* key_a = c->s5.as<uint64_t>();
+    uint64_t* key_b = key_a + n_ent;
+    uint32_t* perm_a = reinterpret_cast<uint32_t*>(key_b + n_ent);
+    uint32_t* perm_b = perm_a + n_ent;
+    LAUNCH_1D(k_iota, (int64_t)n_ent, (int64_t)n_ent, perm_a);
+    LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, (const uint32_t*)nullptr, rt.name_lo.as<uint64_t>(), key_a);
+    CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_a, perm_b, n_ent));
+    LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, perm_b, rt.name_hi.as<uint64_t>(), key_a);
+    CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_b, perm_a, n_ent));
+    const uint32_t* perm = perm_a;
+
+    // segments
+    CORAL_CUDA(c, c->s6.ensure((size_t)n_ent * 13 + 64));
+    uint32_t* head = c->s6.as<uint32_t>();
+    uint32_t* seg_of = head + n_ent;
+    uint32_t* seg_start = seg_of + n_ent;
+    uint8_t* keep = reinterpret_cast<uint8_t*>(seg_start + n_ent);
+    LAUNCH_1D(k_heads, (int64_t)n_ent, (int64_t)n_ent, ent, perm, rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(), head);
+    CORAL_TRY(inclusive_sum_u32(c, head, head, n_ent));
+    uint32_t n_seg = 0;
+    CORAL_TRY(d2h(c, &n_seg, head + n_ent - 1, 1));
+    LAUNCH_1D(k_segments, (int64_t)n_ent, (int64_t)n_ent, ent, perm, head, seg_start, seg_of);
+    LAUNCH_1D(k_mark_dups, (int64_t)n_ent, (int64_t)n_ent, ent, perm, seg_of, seg_start, keep);
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+
+    // 5. per-read names, first primary
+    CORAL_CUDA(c, c->s7.ensure((size_t)n_seg * 48 + 64));
+    uint64_t* seg_lo = c->s7.as<uint64_t>();
+    uint64_t* seg_hi = seg_lo + n_seg;
+    uint64_t* seg_emit = seg_hi + n_seg;
+    uint64_t* seg_emit_sorted = seg_emit + n_seg;
+    uint32_t* first_primary = reinterpret_cast<uint32_t*>(seg_emit_sorted + n_seg);
+    uint32_t* seg_idx = first_primary + n_seg;
+    uint32_t* order = seg_idx + n_seg;
+    int32_t* seg_status = reinterpret_cast<int32_t*>(order + n_seg);
+    LAUNCH_1D(k_seg_names, (int64_t)n_seg, (int64_t)n_seg, ent, perm, seg_start, rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(),
+              seg_lo, seg_hi, seg_emit, first_primary);
+    LAUNCH_1D(k_first_primary, n, n, rt.flag_mapq.as<uint32_t>(), rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(), (int64_t)n_seg,
+              seg_lo, seg_hi, first_primary);
+
+    // 6-7. counts, read order, CSR
+    CORAL_CUDA(c, T.read_first_rec.ensure((size_t)n_seg * 4));
+    CORAL_CUDA(c, T.read_len.ensure((size_t)n_seg * 8));
+    CORAL_CUDA(c, T.read_status.ensure((size_t)n_seg * 4));
+    CORAL_CUDA(c, T.aln_ptr.ensure((size_t)(n_seg + 1) * 4));
+    CORAL_CUDA(c, c->s0.ensure((size_t)n_seg * 8 + 64));
+    uint32_t* seg_cnt = c->s0.as<uint32_t>();
+    uint32_t* cnt_ranked = seg_cnt + n_seg;
+    LAUNCH_1D(k_read_counts, (int64_t)n_seg, (int64_t)n_seg, (int64_t)n_ent, ent, perm, seg_start, keep, first_primary, seg_status, seg_cnt);
+    LAUNCH_1D(k_iota, (int64_t)n_seg, (int64_t)n_seg, seg_idx);
+    CORAL_TRY(sort_pairs_u64(c, seg_emit, seg_emit_sorted, seg_idx, order, n_seg));
+    LAUNCH_1D(k_gather_u32, (int64_t)n_seg, (int64_t)n_seg, order, seg_cnt, cnt_ranked);
+    CORAL_TRY(exclusive_sum_u32(c, cnt_ranked, T.aln_ptr.as<uint32_t>(), n_seg));
+    uint32_t last_ptr = 0, last_cnt = 0;
+    CORAL_TRY(d2h(c, &last_ptr, T.aln_ptr.as<uint32_t>() + n_seg - 1, 1));
+    CORAL_TRY(d2h(c, &last_cnt, cnt_ranked + n_seg - 1, 1));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    const uint32_t n_aln = last_ptr + last_cnt;
+    const size_t na = std::max<uint32_t>(n_aln, 1);
+    DevBuf* a4[] = {&T.qs, &T.qe, &T.tid, &T.rs, &T.re, &T.mapq};
+    for (DevBuf* b : a4) CORAL_CUDA(c, b->ensure(na * 4));
+    CORAL_CUDA(c, T.strand.ensure(na));
+    CORAL_CUDA(c, T.nm.ensure(na * 8));
+    ChimCols o{T.read_first_rec.as<uint32_t>(), T.aln_ptr.as<uint32_t>(), T.read_len.as<int64_t>(), T.nm.as<int64_t>(),
+               T.read_status.as<int32_t>(), T.qs.as<int32_t>(), T.qe.as<int32_t>(), T.tid.as<int32_t>(), T.rs.as<int32_t>(),
+               T.re.as<int32_t>(), T.mapq.as<int32_t>(), T.strand.as<uint8_t>()};
+    LAUNCH_1D(k_read_fill, (int64_t)n_seg, (int64_t)n_seg, (int64_t)n_ent, ent, perm, seg_start, keep, first_primary, seg_status, order,
+              rt.lseq.as<uint32_t>(), n_aln, o);
+    c->stage_end(CORAL_STAGE_FETCH);
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    T.n_reads = n_seg;
+    T.n_aln = n_aln;
+    T.valid = true;
+    return CORAL_OK;
+}
+
+extern "C" int coral_fetch(coral_ctx* c, int64_t* n_reads, int64_t* n_alignments, double* nm_sum, double* nm_sumsq,
+                           int64_t* nm_n, int64_t* nm_zero_div) {
+    if (!c) return CORAL_E_ARG;
+    cudaSetDevice(c->device);
+    CORAL_TRY(coral_run_fetch(c));
+    if (n_reads) *n_reads = c->chim.n_reads;
+    if (n_alignments) *n_alignments = c->chim.n_aln;
+    if (nm_sum) *nm_sum = c->chim.nm_sum;
+    if (nm_sumsq) *nm_sumsq = c->chim.nm_sq;
+    if (nm_n) *nm_n = c->chim.nm_n;
+    if (nm_zero_div) *nm_zero_div = c->chim.nm_zero_div;
+    return CORAL_OK;
+}
+
+extern "C" int coral_get_chimeric(coral_ctx* c, uint32_t* read_first_rec, int64_t* read_len, int32_t* read_status,
+                                  uint32_t* aln_ptr, int32_t* qs, int32_t* qe, int32_t* tid, int32_t* rstart, int32_t* rend,
+                                  uint8_t* strand, int32_t* mapq, int64_t* nm) {
+    using namespace coral;
+    if (!c) return CORAL_E_ARG;
+    if (!c->chim.valid) { c->err = "coral_get_chimeric before coral_fetch"; return CORAL_E_STATE; }
+    cudaSetDevice(c->device);
+    ChimericTable& T = c->chim;
+    const size_t nr = (size_t)T.n_reads, na = (size_t)T.n_aln;
+    if (nr == 0) { if (aln_ptr) aln_ptr[0] = 0; return CORAL_OK; }
+    if (read_first_rec) CORAL_TRY(d2h(c, read_first_rec, T.read_first_rec.p, nr));
+    if (read_len) CORAL_TRY(d2h(c, read_len, T.read_len.p, nr));
+    if (read_status) CORAL_TRY(d2h(c, read_status, T.read_status.p, nr));
+    if (aln_ptr) CORAL_TRY(d2h(c, aln_ptr, T.aln_ptr.p, nr + 1));
+    if (qs) CORAL_TRY(d2h(c, qs, T.qs.p, na));
+    if (qe) CORAL_TRY(d2h(c, qe, T.qe.p, na));
+    if (tid) CORAL_TRY(d2h(c, tid, T.tid.p, na));
+    if (rstart) CORAL_TRY(d2h(c, rstart, T.rs.p, na));
+    if (rend) CORAL_TRY(d2h(c, rend, T.re.p, na));
+    if (strand) CORAL_TRY(d2h(c, strand, T.strand.p, na));
+    if (mapq) CORAL_TRY(d2h(c, mapq, T.mapq.p, na));
+    if (nm) CORAL_TRY(d2h(c, nm, T.nm.p, na));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    return CORAL_OK;
+}

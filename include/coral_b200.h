@@ -117,6 +117,25 @@ int coral_get_record_table(coral_ctx* ctx, int32_t* tid, int32_t* pos, int32_t* 
 int coral_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
                           int32_t n_regions, int64_t* base_sum, int64_t* rec_count);
 
+/* ---- fetch ------------------------------------------------------------------------------------- *
+ * replaces bam_to_breakpoint_nanopore.fetch (ibg:139-174) + cigar_parsing.alignment_from_satags
+ * (cigar_parsing.py:232-269, cigar2pos* :17-215) over ALL loaded records.
+ * Result (kept on the device for coral_candidates and readable with coral_get_chimeric):
+ *   reads in the reference's dict order (order of each name's first SA-bearing record);
+ *   read_first_rec[r] = index of that record (the caller takes the name string from its own buffer);
+ *   read_len[r]       = l_seq of the first record with flag < 256 and the same name (-1: none);
+ *   read_status[r]    = 0 ok | 1 no primary (ibg:164-169) | 2 rejected -> ([],[],[]) (cp:248-253)
+ *                       | 3 KeyError signature (cp:255) | 4 malformed entry text;
+ *   alignments CSR aln_ptr[n_reads+1], stably sorted by (qs, qe): qs, qe, tid, rstart, rend (rint[1], rint[2];
+ *   start > end on '-'), strand (0 '+', 1 '-'), mapq, nm (raw last field; the caller divides by qe - qs, cp:268).
+ * nm_*: sum of e = NM/l_seq, sum of e*e and count over records without SA and MAPQ 60 (ibg:153-157);
+ * nm_zero_div counts such records with l_seq == 0 (the reference raises ZeroDivisionError). */
+int coral_fetch(coral_ctx* ctx, int64_t* n_reads, int64_t* n_alignments, double* nm_sum, double* nm_sumsq,
+                int64_t* nm_n, int64_t* nm_zero_div);
+int coral_get_chimeric(coral_ctx* ctx, uint32_t* read_first_rec, int64_t* read_len, int32_t* read_status,
+                       uint32_t* aln_ptr, int32_t* qs, int32_t* qe, int32_t* tid, int32_t* rstart, int32_t* rend,
+                       uint8_t* strand, int32_t* mapq, int64_t* nm);
+
 #ifdef __cplusplus
 }
 #endif

@@ -28,7 +28,7 @@ def dataset(tmp_path_factory):
     from sim.generate import simulate, write_dataset
 
     def get(name, **kw):
-        key = (name, tuple(sorted(kw.items())))
+        key = (name, repr(sorted(kw.items())))
         if key not in _DATASETS:
             cfg = configs.CONFIGS[name](**kw)
             data = simulate(cfg)
