@@ -209,3 +209,122 @@ class Context(object):
             _p(out["qs"]), _p(out["qe"]), _p(out["tid"]), _p(out["rstart"]), _p(out["rend"]), _p(out["strand"]),
             _p(out["mapq"]), _p(out["nm"])))
         return out
+
+    @staticmethod
+    def _ivals(intervals_tid, start, end_incl):
+        return (np.ascontiguousarray(intervals_tid, dtype=np.int32), np.ascontiguousarray(start, dtype=np.int32),
+                np.ascontiguousarray(end_incl, dtype=np.int32))
+
+    def smalldel(self, tid, start, end_incl):
+        t, s, e = self._ivals(tid, start, end_incl)
+        n = ctypes.c_int64()
+        self._check(self._L.coral_smalldel(self._h, _p(t), _p(s), _p(e), len(t), ctypes.byref(n)))
+        n = n.value
+        out = {"n": n, "rec": np.zeros(n, np.uint32)}
+        for k in ("ai", "next_start", "prev_end", "first_start", "last_end", "mapq"):
+            out[k] = np.zeros(n, np.int32)
+        if n:
+            self._check(self._L.coral_get_smalldel(self._h, _p(out["rec"]), _p(out["ai"]), _p(out["next_start"]),
+                                                   _p(out["prev_end"]), _p(out["first_start"]), _p(out["last_end"]),
+                                                   _p(out["mapq"])))
+        return out
+
+    def candidates_l(self, tid, start, end_incl):
+        t, s, e = self._ivals(tid, start, end_incl)
+        n = ctypes.c_int64()
+        self._check(self._L.coral_candidates_l(self._h, _p(t), _p(s), _p(e), len(t), ctypes.byref(n)))
+        n = n.value
+        out = {"n": n, "read": np.zeros(n, np.uint32)}
+        for k in ("i", "j", "chr1", "pos1", "chr2", "pos2", "rgap", "mq1", "mq2"):
+            out[k] = np.zeros(n, np.int32)
+        for k in ("o1", "o2", "flag"):
+            out[k] = np.zeros(n, np.uint8)
+        if n:
+            self._check(self._L.coral_get_candidates(
+                self._h, _p(out["read"]), _p(out["i"]), _p(out["j"]), _p(out["chr1"]), _p(out["pos1"]), _p(out["o1"]),
+                _p(out["chr2"]), _p(out["pos2"]), _p(out["o2"]), _p(out["rgap"]), _p(out["flag"]), _p(out["mq1"]),
+                _p(out["mq2"])))
+        return out
+
+    def cluster_call(self, chr1, pos1, o1, chr2, pos2, o2, rgap, flag, mq1, mq2, min_cluster_size, bp_distance_cutoff,
+                     peel_cutoff, match_cutoff, max_peels=0):
+        i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+        u8 = lambda a: np.ascontiguousarray(a, dtype=np.uint8)
+        chr1, pos1, chr2, pos2, rgap, mq1, mq2 = map(i32, (chr1, pos1, chr2, pos2, rgap, mq1, mq2))
+        o1, o2, flag = map(u8, (o1, o2, flag))
+        n = len(chr1)
+        nc = ctypes.c_int64()
+        self._check(self._L.coral_cluster_call(
+            self._h, ctypes.c_int64(n), _p(chr1), _p(pos1), _p(o1), _p(chr2), _p(pos2), _p(o2), _p(rgap), _p(flag),
+            _p(mq1), _p(mq2), ctypes.c_double(min_cluster_size), ctypes.c_int32(bp_distance_cutoff),
+            ctypes.c_double(peel_cutoff), ctypes.c_int32(match_cutoff), ctypes.c_int32(max_peels), ctypes.byref(nc)))
+        nc = nc.value
+        out = {"n_clusters": nc, "order": np.zeros(n, np.uint32), "cluster_ptr": np.zeros(nc + 1, np.uint32),
+               "n_sub": np.zeros(nc, np.int32), "sub_of": np.zeros(n, np.int32), "row_pos1": np.zeros(n, np.int32),
+               "row_pos2": np.zeros(n, np.int32), "row_nb": np.zeros(n, np.int32), "row_first": np.zeros(n, np.uint32),
+               "row_stats": np.zeros((n, 6), np.float64)}
+        if n:
+            self._check(self._L.coral_get_clusters(
+                self._h, _p(out["order"]), _p(out["cluster_ptr"]), _p(out["n_sub"]), _p(out["sub_of"]), _p(out["row_pos1"]),
+                _p(out["row_pos2"]), _p(out["row_nb"]), _p(out["row_first"]), _p(out["row_stats"])))
+        return out
+
+    def concordant(self, tid, p, rb_edge, rb_rec):
+        """Edges sorted by (tid, p).  -> (lr_count int64[n], rows dict(edge, rec, mask))."""
+        tid = np.ascontiguousarray(tid, dtype=np.int32)
+        p = np.ascontiguousarray(p, dtype=np.int32)
+        rb_edge = np.ascontiguousarray(rb_edge, dtype=np.uint32)
+        rb_rec = np.ascontiguousarray(rb_rec, dtype=np.uint32)
+        n = len(tid)
+        cnt = np.zeros(n, np.int64)
+        nr = ctypes.c_int64()
+        self._check(self._L.coral_concordant(self._h, _p(tid), _p(p), n, ctypes.c_int64(len(rb_edge)), _p(rb_edge), _p(rb_rec),
+                                             _p(cnt), ctypes.byref(nr)))
+        nr = nr.value
+        rows = {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
+        if nr:
+            self._check(self._L.coral_get_concordant_rows(self._h, _p(rows["edge"]), _p(rows["rec"]), _p(rows["mask"])))
+        return cnt, rows
+
+    def sa_text(self, text, ent_ptr, ent_beg, ent_end, read_len):
+        n_reads = len(read_len)
+        ne = int(ent_ptr[-1])
+        out = {"status": np.zeros(n_reads, np.int32)}
+        for k in ("qs", "qe", "al", "rstart", "rend", "nm"):
+            out[k] = np.zeros(ne, np.int64)
+        out["strand"] = np.zeros(ne, np.uint8); out["mapq"] = np.zeros(ne, np.int32); out["src"] = np.zeros(ne, np.uint32)
+        self._check(self._L.coral_sa_text(
+            self._h, text, ctypes.c_uint64(len(text)), ctypes.c_int64(n_reads), _p(ent_ptr), _p(ent_beg), _p(ent_end),
+            _p(read_len), _p(out["status"]), _p(out["qs"]), _p(out["qe"]), _p(out["al"]), _p(out["rstart"]), _p(out["rend"]),
+            _p(out["strand"]), _p(out["mapq"]), _p(out["nm"]), _p(out["src"])))
+        return out
+
+    def _get_candidates(self, n):
+        out = {"n": n, "read": np.zeros(n, np.uint32)}
+        for k in ("i", "j", "chr1", "pos1", "chr2", "pos2", "rgap", "mq1", "mq2"):
+            out[k] = np.zeros(n, np.int32)
+        for k in ("o1", "o2", "flag"):
+            out[k] = np.zeros(n, np.uint8)
+        if n:
+            self._check(self._L.coral_get_candidates(
+                self._h, _p(out["read"]), _p(out["i"]), _p(out["j"]), _p(out["chr1"]), _p(out["pos1"]), _p(out["o1"]),
+                _p(out["chr2"]), _p(out["pos2"]), _p(out["o2"]), _p(out["rgap"]), _p(out["flag"]), _p(out["mq1"]),
+                _p(out["mq2"])))
+        return out
+
+    def candidates_pair(self, reads, tid2, start2, end2):
+        reads = np.ascontiguousarray(reads, dtype=np.uint32)
+        t, s, e = self._ivals(tid2, start2, end2)
+        assert len(t) == 2
+        n = ctypes.c_int64()
+        self._check(self._L.coral_candidates_pair(self._h, _p(reads), ctypes.c_int64(len(reads)), _p(t), _p(s), _p(e),
+                                                  ctypes.byref(n)))
+        return self._get_candidates(n.value)
+
+    def set_chimeric(self, aln_ptr, qs, qe, tid, rstart, rend, strand, mapq):
+        aln_ptr = np.ascontiguousarray(aln_ptr, dtype=np.uint32)
+        i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+        qs, qe, tid, rstart, rend, mapq = map(i32, (qs, qe, tid, rstart, rend, mapq))
+        strand = np.ascontiguousarray(strand, dtype=np.uint8)
+        self._check(self._L.coral_set_chimeric(self._h, ctypes.c_int64(len(aln_ptr) - 1), _p(aln_ptr), _p(qs), _p(qe), _p(tid),
+                                               _p(rstart), _p(rend), _p(strand), _p(mapq)))

@@ -72,6 +72,19 @@ struct ChimericTable {
     int64_t nm_zero_div = 0;
 };
 
+// Small-deletion rows in emission order (interval, file order, block order), ibg:750-762.
+struct SmallDelTable {
+    DevBuf rec, ai, next_start, prev_end, first_start, last_end, mapq;
+    int64_t n = 0;
+    bool valid = false;
+};
+// alignment2bp_l candidates in reference order (read order, then pass, then index).
+struct CandTable {
+    DevBuf read, i, j, chr1, pos1, chr2, pos2, rgap, mq1, mq2, o1, o2, flag;
+    int64_t n = 0;
+    bool valid = false;
+};
+
 struct coral_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -95,6 +108,14 @@ struct coral_ctx {
     RecordTable rt;
     GapEvents gaps;
     ChimericTable chim;
+    SmallDelTable sdel;
+    CandTable cand;
+    DevBuf sw[8];    // concordant-edge (stab) work buffers and rows
+    int64_t stab_n = 0;
+    bool stab_valid = false;
+    DevBuf cw[32];   // cluster / peel work buffers and results
+    int64_t cl_n = 0, cl_n_clusters = 0;
+    bool cl_valid = false;
     DevBuf status;  // int32[8] device status words (format errors etc.)
 
     // scratch

@@ -564,3 +564,93 @@ extern "C" int coral_get_chimeric(coral_ctx* c, uint32_t* read_first_rec, int64_
     CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
     return CORAL_OK;
 }
+
+// ---- operator form: alignment_from_satags on caller-supplied SA text ---------------------------------
+namespace coral {
+// thread per read: cigar2pos + rint + stable (qs, qe) insertion sort, over entries [ptr[r], ptr[r+1])
+__global__ void k_sa_text_assemble(int64_t n_reads, const uint32_t* __restrict__ ptr, const SaEntry* __restrict__ ent,
+                                   const int64_t* __restrict__ read_len, int32_t* __restrict__ status,
+                                   int64_t* __restrict__ qs, int64_t* __restrict__ qe, int64_t* __restrict__ al,
+                                   int64_t* __restrict__ rs, int64_t* __restrict__ re, uint8_t* __restrict__ strand,
+                                   int32_t* __restrict__ mapq, int64_t* __restrict__ nm, uint32_t* __restrict__ src) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_reads) return;
+    const uint32_t b = ptr[r], e = ptr[r + 1];
+    int32_t st = READ_OK;
+    for (uint32_t i = b; i < e && st == READ_OK; i++) {
+        const uint8_t sg = ent[i].sig;
+        if (sg == 100) st = READ_REJECTED; else if (sg == 101) st = READ_KEYERROR; else if (sg == 102) st = READ_MALFORMED;
+    }
+    status[r] = st;
+    if (st != READ_OK) return;
+    const int64_t rl = read_len[r];
+    uint32_t k = 0;
+    for (uint32_t i = b; i < e; i++) {
+        const SaEntry& a = ent[i];
+        int64_t q0, q1, l;
+        cigar2pos_dev(a.sig, a.num, a.strand != 0, rl, q0, q1, l);
+        const int64_t lo = a.pos1 - 1, hi = a.pos1 + l - 2;
+        uint32_t j = k;
+        while (j > 0 && (qs[b + j - 1] > q0 || (qs[b + j - 1] == q0 && qe[b + j - 1] > q1))) {
+            const uint32_t d = b + j, s = b + j - 1;
+            qs[d] = qs[s]; qe[d] = qe[s]; al[d] = al[s]; rs[d] = rs[s]; re[d] = re[s]; strand[d] = strand[s];
+            mapq[d] = mapq[s]; nm[d] = nm[s]; src[d] = src[s];
+            j--;
+        }
+        const uint32_t d = b + j;
+        qs[d] = q0; qe[d] = q1; al[d] = l; rs[d] = a.strand ? hi : lo; re[d] = a.strand ? lo : hi; strand[d] = a.strand;
+        mapq[d] = a.mapq; nm[d] = a.nm; src[d] = i - b;
+        k++;
+    }
+}
+}  // namespace coral
+
+extern "C" int coral_sa_text(coral_ctx* c, const char* text, uint64_t text_len, int64_t n_reads, const uint32_t* ent_ptr,
+                             const uint32_t* ent_beg, const uint32_t* ent_end, const int64_t* read_len, int32_t* status,
+                             int64_t* qs, int64_t* qe, int64_t* al, int64_t* rstart, int64_t* rend, uint8_t* strand,
+                             int32_t* mapq, int64_t* nm, uint32_t* src) {
+    using namespace coral;
+    if (!c || n_reads < 0 || !ent_ptr) return CORAL_E_ARG;
+    cudaSetDevice(c->device);
+    if (n_reads == 0) return CORAL_OK;
+    const uint32_t n_ent = ent_ptr[n_reads];
+    for (uint32_t i = 0; i < n_ent; i++)
+        if (ent_beg[i] > ent_end[i] || ent_end[i] > text_len) { c->err = "entry range outside text"; return CORAL_E_ARG; }
+    const size_t ne = std::max<uint32_t>(n_ent, 1);
+    CORAL_CUDA(c, c->s0.ensure(text_len + 64));
+    CORAL_CUDA(c, c->s1.ensure(ne * 12 + 16));
+    CORAL_CUDA(c, c->s2.ensure(ne * sizeof(SaEntry)));
+    CORAL_CUDA(c, c->s3.ensure((size_t)(n_reads + 1) * 4 + (size_t)n_reads * 12 + 32));
+    CORAL_CUDA(c, c->s4.ensure(ne * 64));
+    CORAL_TRY(h2d(c, c->s0.p, text, (size_t)text_len));
+    uint32_t* e_rec = c->s1.as<uint32_t>(); uint32_t* e_beg = e_rec + ne; uint32_t* e_end = e_beg + ne;
+    CORAL_CUDA(c, cudaMemsetAsync(e_rec, 0, ne * 4, c->stream));
+    CORAL_TRY(h2d(c, e_beg, ent_beg, (size_t)n_ent));
+    CORAL_TRY(h2d(c, e_end, ent_end, (size_t)n_ent));
+    uint8_t* p3 = c->s3.as<uint8_t>();
+    int64_t* d_rl = reinterpret_cast<int64_t*>(p3);
+    uint64_t* d_zero = reinterpret_cast<uint64_t*>(p3 + (size_t)n_reads * 8);
+    uint32_t* d_ptr = reinterpret_cast<uint32_t*>(p3 + (size_t)n_reads * 8 + 8);
+    int32_t* d_status = reinterpret_cast<int32_t*>(d_ptr + n_reads + 1);
+    CORAL_TRY(h2d(c, d_rl, read_len, (size_t)n_reads));
+    CORAL_CUDA(c, cudaMemsetAsync(d_zero, 0, 8, c->stream));
+    CORAL_TRY(h2d(c, d_ptr, ent_ptr, (size_t)n_reads + 1));
+    SaEntry* ent = c->s2.as<SaEntry>();
+    LAUNCH_1D(k_parse_entries, (int64_t)n_ent, c->s0.as<uint8_t>(), d_zero, (int64_t)n_ent, e_rec, e_beg, e_end,
+              (const uint64_t*)nullptr, 0, ent);
+    int64_t* o8 = c->s4.as<int64_t>();
+    int64_t *d_qs = o8, *d_qe = o8 + ne, *d_al = o8 + 2 * ne, *d_rs = o8 + 3 * ne, *d_re = o8 + 4 * ne, *d_nm = o8 + 5 * ne;
+    int32_t* d_mq = reinterpret_cast<int32_t*>(o8 + 6 * ne);
+    uint32_t* d_src = reinterpret_cast<uint32_t*>(d_mq + ne);
+    uint8_t* d_strand = reinterpret_cast<uint8_t*>(d_src + ne);
+    LAUNCH_1D(k_sa_text_assemble, n_reads, n_reads, d_ptr, ent, d_rl, d_status, d_qs, d_qe, d_al, d_rs, d_re, d_strand, d_mq,
+              d_nm, d_src);
+    CORAL_TRY(d2h(c, status, d_status, (size_t)n_reads));
+    CORAL_TRY(d2h(c, qs, d_qs, (size_t)n_ent)); CORAL_TRY(d2h(c, qe, d_qe, (size_t)n_ent));
+    CORAL_TRY(d2h(c, al, d_al, (size_t)n_ent)); CORAL_TRY(d2h(c, rstart, d_rs, (size_t)n_ent));
+    CORAL_TRY(d2h(c, rend, d_re, (size_t)n_ent)); CORAL_TRY(d2h(c, nm, d_nm, (size_t)n_ent));
+    CORAL_TRY(d2h(c, mapq, d_mq, (size_t)n_ent)); CORAL_TRY(d2h(c, src, d_src, (size_t)n_ent));
+    CORAL_TRY(d2h(c, strand, d_strand, (size_t)n_ent));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    return CORAL_OK;
+}

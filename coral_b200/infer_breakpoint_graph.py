@@ -1,0 +1,304 @@
+"""Drop-in for the hot methods of reference ``infer_breakpoint_graph.bam_to_breakpoint_nanopore``
+(``:20-1330``): same class name, attributes, method names and call order
+(``read_cns -> fetch -> hash_alignment_to_seg -> find_amplicon_intervals -> find_smalldel_breakpoints ->
+find_breakpoints -> build_graph -> assign_cov``, reference ``reconstruct_graph`` ``:1354-1386``).
+
+The hot methods run on the GPU through the C ABI (``_abi.Context``); this file only converts result tables
+into the reference's Python containers.  Without a CUDA device the constructor raises — there is no CPU path.
+"""
+import logging
+import math
+import time
+
+import numpy as np
+
+from . import _abi, breakpoint_utilities, global_names, gpu_ops
+from .breakpoint_graph import output_breakpoint_graph_lr, output_breakpoint_info_lr
+from .host_steps import HostSteps, _t
+
+
+class bam_to_breakpoint_nanopore(HostSteps):
+    _ops = breakpoint_utilities
+
+    def __init__(self, lr_bamfile, seedfile, device=0, n_threads=0):
+        self._init_state()
+        self.lr_bamfh = _abi.BamFile(lr_bamfile, n_threads)          # replaces pysam.AlignmentFile (ibg:65)
+        self._ctx = _abi.Context(device)
+        self._ctx.set_references(self.lr_bamfh.references)
+        self._ctx.load_records(self.lr_bamfh.rec, self.lr_bamfh.rec_off)
+        self._tid = {c: i for i, c in enumerate(self.lr_bamfh.references)}
+        self._name_rec = {}     # read name -> index of one record carrying it (for concordant-edge rbps)
+        self._read_names = []   # chimeric read order of the device table
+        self._read_index = {}
+        self._read_seeds(seedfile)
+
+    # ---- a12: ibg:75-136 ---------------------------------------------------------------------------------
+    def read_cns(self, cns):
+        self._parse_cns(cns)
+        segs, total = self._median_cn_segments()
+        order = sorted(range(len(segs)), key=lambda k: (self._tid[segs[k][0]], segs[k][1]))
+        nnc = self._coverage_sum([segs[k] for k in order])
+        self.normal_cov = nnc * 1.0 / total
+        logging.info(_t() + "LR normal cov = %f." % (self.normal_cov))
+        self.min_cluster_cutoff = max(self.min_cluster_cutoff, self.min_bp_cov_factor * self.normal_cov)
+
+    def _coverage_sum(self, segs):
+        """Sum of count_coverage over inclusive segments; overlapping requests are issued in disjoint batches."""
+        total = 0
+        pending = list(segs)
+        while pending:
+            batch, rest, last = [], [], None
+            for s in pending:
+                if last is not None and self._tid[s[0]] == self._tid[last[0]] and s[1] <= last[2]:
+                    rest.append(s)
+                else:
+                    batch.append(s)
+                    last = s
+            bs, _ = self._ctx.region_coverage([self._tid[s[0]] for s in batch], [s[1] for s in batch], [s[2] + 1 for s in batch])
+            total += int(bs.sum())
+            pending = rest
+        return total
+
+    # ---- a1/a2: ibg:139-174 ------------------------------------------------------------------------------
+    def fetch(self):
+        f = self._ctx.fetch()
+        if f["nm_zero_div"] or f["nm_n"] == 0:
+            raise ZeroDivisionError("division by zero")              # ibg:154 / ibg:159
+        mean = f["nm_sum"] / f["nm_n"]
+        self.nm_stats = [mean, math.sqrt(f["nm_sumsq"] / f["nm_n"] - mean ** 2), f["nm_n"]]
+        refs = self.lr_bamfh.references
+        ap = f["aln_ptr"]
+        qs, qe, tid, rs, re = f["qs"].tolist(), f["qe"].tolist(), f["tid"].tolist(), f["rstart"].tolist(), f["rend"].tolist()
+        strand, mapq, nm = f["strand"].tolist(), f["mapq"].tolist(), f["nm"].tolist()
+        logging.info(_t() + "Fetched %d chimeric reads." % f["n_reads"])
+        self._read_names = []
+        for r in range(f["n_reads"]):
+            rec = int(f["read_first_rec"][r])
+            name = self.lr_bamfh.query_name(rec)
+            self._read_names.append(name)
+            self._read_index[name] = r
+            self._name_rec[name] = rec
+            st = int(f["read_status"][r])
+            if st == 1:      # ibg:164-169
+                logging.warning(_t() + "Found chimeric read without primary alignment.")
+                logging.warning(_t() + "\tRead name: %s; Read length: N/A." % name)
+                continue
+            self.read_length[name] = int(f["read_len"][r])
+            if st == 2:      # cp:248-253
+                logging.warning(_t() + "Found chimeric alignment without match or soft clips.")
+                self.chimeric_alignments[name] = ([], [], [])
+                continue
+            if st == 3:
+                raise KeyError("CIGAR signature of an SA entry of read %s is not in cigar2pos_ops" % name)
+            if st != 0:
+                raise ValueError("malformed SA entry on read %s" % name)
+            a, b = int(ap[r]), int(ap[r + 1])
+            qint = [[qs[k], qe[k]] for k in range(a, b)]
+            rint = [[refs[tid[k]], rs[k], re[k], '-' if strand[k] else '+'] for k in range(a, b)]
+            qual = mapq[a:b]
+            nmn = [float(nm[k]) / (qe[k] - qs[k]) for k in range(a, b)]   # cp:268
+            self.chimeric_alignments[name] = (qint, rint, qual, nmn)
+        logging.info(_t() + "Computed alignment intervals on all chimeric reads.")
+
+    # ---- shared tail of ibg:691-718 and ibg:775-802 -------------------------------------------------------
+    def _call_clusters(self, cand, tuples):
+        """cand: dict of candidate arrays (chr ids = BAM tids); tuples[k] = the (name, i, j) of candidate k."""
+        n = len(tuples)
+        if n == 0:
+            return
+        refs = self.lr_bamfh.references
+        cutoff = self.min_cluster_cutoff
+        r = gpu_ops.cluster_arrays(self._ctx, cand, cutoff, self.max_breakpoint_distance_cutoff, cutoff,
+                                   self.min_bp_match_cutoff_)
+        order, ptr, sub_of = r["order"], r["cluster_ptr"], r["sub_of"]
+        accept2 = max(self.normal_cov * self.min_bp_cov_factor, 3.0)
+        for c in range(r["n_clusters"]):
+            b, e = int(ptr[c]), int(ptr[c + 1])
+            if e - b < cutoff:
+                continue
+            members = order[b:e]
+            subs = sub_of[members]
+            for k in range(int(r["n_sub"][c])):
+                row = b + k
+                bpr = [tuples[int(m)] for m in members[subs == k]]
+                support = len(set(bpr))
+                if (k == 0 and support >= cutoff) or support >= accept2:
+                    f0 = int(r["row_first"][row])
+                    bp = [refs[cand["chr1"][f0]], int(r["row_pos1"][row]), '+-'[cand["o1"][f0]], refs[cand["chr2"][f0]],
+                          int(r["row_pos2"][row]), '+-'[cand["o2"][f0]], tuples[f0], int(cand["rgap"][f0]), int(cand["flag"][f0])]
+                    io1 = breakpoint_utilities.interval_overlap_l([bp[0], bp[1], bp[1]], self.amplicon_intervals)
+                    io2 = breakpoint_utilities.interval_overlap_l([bp[3], bp[4], bp[4]], self.amplicon_intervals)
+                    if io1 >= 0 and io2 >= 0:
+                        assert self.amplicon_intervals[io1][3] == self.amplicon_intervals[io2][3]
+                        bpi = self.addbp(bp, set(bpr), gpu_ops.stats_row(r["row_stats"][row]), self.amplicon_intervals[io1][3])
+                        self.amplicon_interval_connections.setdefault((min(io1, io2), max(io1, io2)), set()).add(bpi)
+
+    def _interval_arrays(self):
+        ivs = self.amplicon_intervals
+        return [self._tid[a[0]] for a in ivs], [a[1] for a in ivs], [a[2] for a in ivs]
+
+    # ---- a3: ibg:721-802 ------------------------------------------------------------------------------------
+    def find_smalldel_breakpoints(self):
+        t, s, e = self._interval_arrays()
+        self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
+        rows = self._ctx.smalldel(t, s, e)
+        names = {}
+        lia = self.large_indel_alignments
+        recs = rows["rec"].tolist()
+        ai, ns, pe, fs, le, mq = (rows[k].tolist() for k in ("ai", "next_start", "prev_end", "first_start", "last_end", "mapq"))
+        for k in range(rows["n"]):
+            rec = recs[k]
+            name = names.get(rec)
+            if name is None:
+                name = names[rec] = self.lr_bamfh.query_name(rec)
+                self._name_rec.setdefault(name, rec)
+            lia.setdefault(name, []).append([self.amplicon_intervals[ai[k]][0], ns[k], pe[k], fs[k], le[k], mq[k]])
+        logging.info(_t() + "Fetched %d reads with large indels in CIGAR." % (len(lia)))
+        tuples, chrs, p1, p2 = [], [], [], []
+        for name, lst in lia.items():          # ibg:765-772
+            for idx, row in enumerate(lst):
+                hi, lo = row[1], row[2]
+                if lo > hi:
+                    lo = hi
+                tuples.append((name, idx, idx)); chrs.append(self._tid[row[0]]); p1.append(hi); p2.append(lo)
+        n = len(tuples)
+        cand = {"chr1": np.array(chrs, np.int32), "pos1": np.array(p1, np.int32), "o1": np.ones(n, np.uint8),
+                "chr2": np.array(chrs, np.int32), "pos2": np.array(p2, np.int32), "o2": np.zeros(n, np.uint8),
+                "rgap": np.zeros(n, np.int32), "flag": np.zeros(n, np.uint8), "mq1": np.full(n, -1, np.int32),
+                "mq2": np.full(n, -1, np.int32)}
+        self._call_clusters(cand, tuples)
+
+    # ---- a4/a5: ibg:676-718 ---------------------------------------------------------------------------------
+    def find_breakpoints(self):
+        t, s, e = self._interval_arrays()
+        self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
+        c = self._ctx.candidates_l(t, s, e)
+        names = self._read_names
+        rd, ii, jj = c["read"].tolist(), c["i"].tolist(), c["j"].tolist()
+        tuples = [(names[rd[k]], ii[k], jj[k]) for k in range(c["n"])]
+        self._call_clusters(c, tuples)
+
+    def _pair_candidates(self, reads, intrvl1, intrvl2):
+        """One batched launch of alignment2bp over the device chimeric table (ibg:432-434)."""
+        idx = [self._read_index[r] for r in reads]
+        c = self._ctx.candidates_pair(idx, [self._tid[intrvl1[0]], self._tid[intrvl2[0]]], [intrvl1[1], intrvl2[1]],
+                                      [intrvl1[2], intrvl2[2]])
+        refs = self.lr_bamfh.references
+        names = self._read_names
+        return [[refs[c["chr1"][k]], int(c["pos1"][k]), '+-'[c["o1"][k]], refs[c["chr2"][k]], int(c["pos2"][k]),
+                 '+-'[c["o2"][k]], (names[c["read"][k]], int(c["i"][k]), int(c["j"][k])), int(c["rgap"][k]), int(c["flag"][k]),
+                 int(c["mq1"][k]), int(c["mq2"][k])] for k in range(c["n"])]
+
+    # ---- a10/a11: ibg:1019-1056 -----------------------------------------------------------------------------
+    def assign_cov(self):
+        # sequence edges of every graph in one launch (disjoint by construction, App. A.14)
+        todo = []
+        for gi, g in enumerate(self.lr_graph):
+            for si, se in enumerate(g.sequence_edges):
+                if se[5] == -1:
+                    todo.append((self._tid[se[0]], se[1], se[2] + 1, gi, si))
+        todo.sort()
+        batches = [[]]
+        for row in todo:   # keep each launch's regions disjoint
+            if batches[-1] and batches[-1][-1][0] == row[0] and row[1] < batches[-1][-1][2]:
+                batches.append([])
+            batches[-1].append(row)
+        for batch in batches:
+            if not batch:
+                continue
+            bs, rc = self._ctx.region_coverage([r[0] for r in batch], [r[1] for r in batch], [r[2] for r in batch])
+            for k, (_, _, _, gi, si) in enumerate(batch):
+                self.lr_graph[gi].sequence_edges[si][5] = int(rc[k])
+                self.lr_graph[gi].sequence_edges[si][6] = int(bs[k])
+        # concordant edges
+        edges = []
+        for gi, g in enumerate(self.lr_graph):
+            for ci, ce in enumerate(g.concordant_edges):
+                edges.append((self._tid[ce[0]], ce[1], gi, ci))
+        edges.sort()
+        uniq, owners = [], []
+        for (t, p, gi, ci) in edges:
+            if uniq and uniq[-1] == (t, p):
+                owners[-1].append((gi, ci))
+            else:
+                uniq.append((t, p)); owners.append([(gi, ci)])
+        rb_edge, rb_rec = [], []
+        for k, own in enumerate(owners):
+            gi, ci = own[0]
+            g = self.lr_graph[gi]
+            ce = g.concordant_edges[ci]
+            seen = set()
+            for node in ((ce[0], ce[1], ce[2]), (ce[3], ce[4], ce[5])):
+                for bpi in g.nodes[node][2]:
+                    for r in g.discordant_edges[bpi][10]:
+                        if r[0] not in seen:
+                            seen.add(r[0])
+                            if r[0] in self._name_rec:   # reads of no loaded record cannot overlap any point
+                                rb_edge.append(k); rb_rec.append(self._name_rec[r[0]])
+        if not uniq:
+            return
+        self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
+        cnt, rows = self._ctx.concordant([u[0] for u in uniq], [u[1] for u in uniq], rb_edge, rb_rec)
+        sel = (rows["mask"] & 3) != 0
+        r_edge, r_rec = rows["edge"][sel], rows["rec"][sel]
+        o = np.argsort(r_edge, kind="stable")
+        r_edge, r_rec = r_edge[o], r_rec[o]
+        bounds = np.searchsorted(r_edge, np.arange(len(uniq) + 1))
+        name_of = {}
+        for k, own in enumerate(owners):
+            names = set()
+            for rec in r_rec[bounds[k]:bounds[k + 1]].tolist():
+                nm = name_of.get(rec)
+                if nm is None:
+                    nm = name_of[rec] = self.lr_bamfh.query_name(rec)
+                names.add(nm)
+            for (gi, ci) in own:
+                ce = self.lr_graph[gi].concordant_edges[ci]
+                ce[9] = set(names) if len(own) > 1 else names
+                ce[8] = int(cnt[k])
+
+    def closebam(self):
+        self.lr_bamfh.close()
+        self._ctx.close()
+
+
+BamToBreakpointNanopore = bam_to_breakpoint_nanopore   # name used by BASELINE.json's north_star
+
+
+def reconstruct_graph(args):
+    """Reference :1333-1395 up to (not including) compute_cn_lr, which stays on the reference's cvxopt code."""
+    global_names.TSTART = time.time()
+    b2bn = bam_to_breakpoint_nanopore(args.lr_bam, args.cnv_seed)
+    b2bn.min_bp_cov_factor = args.min_bp_support
+    logging.info(_t() + "Opened LR bam files.")
+    b2bn.read_cns(args.cn_seg)
+    logging.info(_t() + "Completed parsing CN segment files.")
+    b2bn.fetch()
+    logging.info(_t() + "Completed fetching reads containing breakpoints.")
+    b2bn.hash_alignment_to_seg()
+    logging.info(_t() + "Completed hashing chimeric reads to CN segments.")
+    b2bn.find_amplicon_intervals()
+    logging.info(_t() + "Completed finding amplicon intervals.")
+    b2bn.find_smalldel_breakpoints()
+    logging.info(_t() + "Completed finding small del breakpoints.")
+    b2bn.find_breakpoints()
+    logging.info(_t() + "Completed finding all discordant breakpoints.")
+    b2bn.build_graph()
+    logging.info(_t() + "Breakpoint graph built for all amplicons.")
+    if getattr(args, "output_bp", False):
+        for gi, g in enumerate(b2bn.lr_graph):
+            stats = []
+            for de in g.discordant_edges:
+                for bpi, bp_ in enumerate(b2bn.new_bp_list):
+                    if de[:6] == bp_[:6]:
+                        stats.append(b2bn.new_bp_stats[bpi])
+                        break
+            output_breakpoint_info_lr(g, args.output_prefix + "_amplicon" + str(gi + 1) + "_breakpoints.txt", stats)
+    else:
+        b2bn.assign_cov()
+        logging.info(_t() + "Fetched read coverage for all sequence and concordant edges.")
+        for gi, g in enumerate(b2bn.lr_graph):
+            if hasattr(g, "compute_cn_lr"):
+                g.compute_cn_lr(b2bn.normal_cov)
+            output_breakpoint_graph_lr(g, args.output_prefix + "_amplicon" + str(gi + 1) + "_graph.txt")
+    return b2bn

@@ -136,6 +136,81 @@ int coral_get_chimeric(coral_ctx* ctx, uint32_t* read_first_rec, int64_t* read_l
                        uint32_t* aln_ptr, int32_t* qs, int32_t* qe, int32_t* tid, int32_t* rstart, int32_t* rend,
                        uint8_t* strand, int32_t* mapq, int64_t* nm);
 
+/* Operator form of cigar_parsing.alignment_from_satags / cigar2pos* (cigar_parsing.py:17-269) on SA text the
+ * caller supplies: `text` holds the entries, read r owns entries [ent_ptr[r], ent_ptr[r+1]) whose bytes are
+ * text[ent_beg[k] : ent_end[k]].  Per read: status as in coral_fetch; per entry, in the read's stable
+ * (qs, qe) order: qs, qe, al, rint start/end, strand, mapq, raw NM, and src = index of the entry in the input
+ * list (the caller takes the rname string from it). */
+int coral_sa_text(coral_ctx* ctx, const char* text, uint64_t text_len, int64_t n_reads, const uint32_t* ent_ptr,
+                  const uint32_t* ent_beg, const uint32_t* ent_end, const int64_t* read_len, int32_t* status,
+                  int64_t* qs, int64_t* qe, int64_t* al, int64_t* rstart, int64_t* rend, uint8_t* strand,
+                  int32_t* mapq, int64_t* nm, uint32_t* src);
+
+/* ---- small-deletion rows ------------------------------------------------------------------------- *
+ * replaces the record loop of find_smalldel_breakpoints (ibg:750-762): for every amplicon interval
+ * [start, end_incl] in LIST order, every record overlapping it (fetch(chr, start, end_incl + 1)) with
+ * MAPQ >= min_mapq in file order, every pair of consecutive aligned blocks more than min_del_len apart.
+ * Rows come back in that emission order: record index, interval index, next block start, previous block
+ * end, first block start, last block end, MAPQ (= large_indel_alignments[name] entries, ibg:760). */
+int coral_smalldel(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* end_incl,
+                   int32_t n_intervals, int64_t* n_rows);
+int coral_get_smalldel(coral_ctx* ctx, uint32_t* rec, int32_t* ai, int32_t* next_start, int32_t* prev_end,
+                       int32_t* first_start, int32_t* last_end, int32_t* mapq);
+
+/* ---- chimeric breakpoint candidates ---------------------------------------------------------------- *
+ * replaces `for r in chimeric_alignments: alignment2bp_l(r, ..., 100, 20, 100, amplicon_intervals)`
+ * (ibg:687-688 -> breakpoint_utilities.py:129-186, interval2bp :289-295) over the table left on the device
+ * by coral_fetch.  Candidates in reference order.  Row = interval2bp fields: chr1 (tid), pos1, o1, chr2, pos2,
+ * o2 (0 '+', 1 '-'), read index (into the coral_fetch read order) with alignment indices (i, j) already
+ * swapped when flag == 1, rgap, flag, and the two MAPQs in (first, second) alignment order (bu:148). */
+int coral_candidates_l(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* end_incl,
+                       int32_t n_intervals, int64_t* n_candidates);
+int coral_get_candidates(coral_ctx* ctx, uint32_t* read, int32_t* i, int32_t* j, int32_t* chr1, int32_t* pos1,
+                         uint8_t* o1, int32_t* chr2, int32_t* pos2, uint8_t* o2, int32_t* rgap, uint8_t* flag,
+                         int32_t* mq1, int32_t* mq2);
+
+/* Two-interval form, breakpoint_utilities.alignment2bp (bu:70-96), as called by the amplicon-interval search
+ * (ibg:432-434) for a chosen subset of reads: intervals [0] = intrvl1, [1] = intrvl2 (end inclusive).
+ * Candidates come back through coral_get_candidates, in the order of `reads`. */
+int coral_candidates_pair(coral_ctx* ctx, const uint32_t* reads, int64_t n_reads_selected, const int32_t* tid2,
+                          const int32_t* start2, const int32_t* end2, int64_t* n_candidates);
+/* Replace the device chimeric table by a caller-supplied one (operator forms of alignment2bp / alignment2bp_l
+ * on Python-side chimeric alignments). */
+int coral_set_chimeric(coral_ctx* ctx, int64_t n_reads, const uint32_t* aln_ptr, const int32_t* qs, const int32_t* qe,
+                       const int32_t* tid, const int32_t* rstart, const int32_t* rend, const uint8_t* strand,
+                       const int32_t* mapq);
+
+/* ---- clustering + exact breakpoint calling --------------------------------------------------------- *
+ * replaces cluster_bp_list(bp_list, min_cluster_size, bp_distance_cutoff) (breakpoint_utilities.py:252-286)
+ * followed, for every cluster with len >= peel_cutoff, by the peel loop
+ *   while len(rest) >= peel_cutoff: bp, bpr, stats, rest = bpc2bp(rest, match_cutoff)
+ * (ibg:698-716; bpc2bp/bp_match breakpoint_utilities.py:299-416), at most max_peels times (0 = unbounded).
+ * Input: n candidates as parallel arrays (chr ids are opaque equal/not-equal labels).
+ * Output (coral_get_clusters):
+ *   order[n], cluster_ptr[n_clusters+1]: clusters in the reference's output order, members in input order;
+ *   n_sub[c]: number of bpc2bp calls made for cluster c; sub_of[i]: the call (0-based) whose bpr received
+ *   candidate i, or -1;
+ *   row arrays indexed cluster_ptr[c] + k for call k: called pos1/pos2, len(bpr), the candidate that was
+ *   bp_cluster[0] of that call (supplies bp[0], bp[2], bp[3], bp[5..8]), and bp_stats_[6]. */
+int coral_cluster_call(coral_ctx* ctx, int64_t n, const int32_t* chr1, const int32_t* pos1, const uint8_t* o1,
+                       const int32_t* chr2, const int32_t* pos2, const uint8_t* o2, const int32_t* rgap,
+                       const uint8_t* flag, const int32_t* mq1, const int32_t* mq2, double min_cluster_size,
+                       int32_t bp_distance_cutoff, double peel_cutoff, int32_t match_cutoff, int32_t max_peels,
+                       int64_t* n_clusters);
+int coral_get_clusters(coral_ctx* ctx, uint32_t* order, uint32_t* cluster_ptr, int32_t* n_sub, int32_t* sub_of,
+                       int32_t* row_pos1, int32_t* row_pos2, int32_t* row_nb, uint32_t* row_first, double* row_stats);
+
+/* ---- concordant edges ------------------------------------------------------------------------------ *
+ * replaces the concordant-edge loop of assign_cov (ibg:1039-1055) for n edges (tid, p) -> (tid, p+1),
+ * sorted by (tid, p).  rbps: rows (edge index, record index) naming, through any record of the read, the
+ * reads on discordant edges incident to either node of that edge (ibg:1047-1053).
+ *   lr_count[e] = len((names(p) & names(p+1) & names(p-d-1) & names(p+1+d)) - rbps)     (ce[8])
+ * coral_get_concordant_rows returns (edge, record, mask) for every record covering one of the four points
+ * (mask bit0 = p, bit1 = p+1, bit2 = p-d-1, bit3 = p+1+d); ce[9] = names of rows with mask & 3. */
+int coral_concordant(coral_ctx* ctx, const int32_t* tid, const int32_t* p, int32_t n_edges, int64_t n_rbps,
+                     const uint32_t* rb_edge, const uint32_t* rb_rec, int64_t* lr_count, int64_t* n_rows);
+int coral_get_concordant_rows(coral_ctx* ctx, uint32_t* edge, uint32_t* rec, uint32_t* mask);
+
 #ifdef __cplusplus
 }
 #endif

@@ -400,3 +400,27 @@ class OracleHotPath(object):
                             rbps.add(r[0])
                 ce[9] = rls | rrs
                 ce[8] = len((rls & rrs & rls1 & rrs1) - rbps)
+
+
+# ---- remaining interval helpers used by the host steps (bu:18-34, :54-67) ---------------------------------
+def interval_adjacent(a, b):
+    """bu:25-34."""
+    if a[0] != b[0]:
+        return False
+    return (b[1] == a[2] + 1) if a[1] <= b[1] else (a[1] == b[2] + 1)
+
+
+def interval_exclusive(a, lst):
+    """bu:54-67."""
+    covered, parts = set(), [[x for x in a]]
+    for k in range(len(lst)):
+        for j in range(len(parts))[::-1]:
+            p = parts[j]
+            if interval_overlap(p, lst[k]):
+                covered.add(k)
+                del parts[j]
+                if p[1] < lst[k][1]:
+                    parts.append([p[0], p[1], lst[k][1] - 1, -1])
+                if p[2] > lst[k][2]:
+                    parts.append([p[0], lst[k][2] + 1, p[2], -1])
+    return covered, parts
