@@ -2,10 +2,19 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--scale S]
 
-One "step" = one pass of the hot path over one batch of synthetic long-read alignment records
-(BASELINE.json configs[1]: 3 seeds / 6 Mb, CN 40, 50x ONT 30 kb).  `value` = records/s with the records
-resident in HBM; `e2e` = the same pass through the C ABI from pinned HOST buffers (H2D of the records
-and D2H of the results inside the timed region).  Prints ONE JSON line on rank 0.
+Workload (config.workload): BASELINE.json configs[1] — synthetic multi-segment ecDNA, 3 seeds over 6 Mb,
+CN 40, 50x ONT 30 kb reads (sim/configs.py::c2_multi_segment, scale 1.0).  One "step" = one pass of the hot
+path over that batch of alignment records:
+  record scan -> normal-coverage regions -> fetch (SA parse / chimeric table) -> small-del rows -> cluster+peel
+  -> alignment2bp_l candidates -> cluster+peel -> sequence-edge coverage -> concordant-edge support,
+every result table copied back to the host.
+  value : records/s with the records resident in HBM when the timed region starts (device pass through the C ABI)
+  e2e   : records/s through the public drop-in class (bam_to_breakpoint_nanopore) starting from a pinned HOST
+          record buffer: H2D of the records, all kernels, D2H of all tables, Python materialisation, graph build
+  roofline : the record-scan kernel (the only kernel that touches record bytes): algorithmic bytes / CUDA-event time
+  cpu_baseline : the oracle (CPU port of the reference path) on a bounded sample, 1 core
+`--impl reference` times that CPU port alone (the reference itself is Python and cannot travel to the GPU box;
+pysam is unavailable — the port is oracle/coral_oracle.py over oracle/pysam_shim.py, "reference-on-shim").
 """
 import argparse
 import json
@@ -19,10 +28,15 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "long reads/sec & aligned Gbases/sec (breakpoint+coverage pass), % HBM roofline"
+CPU_SAMPLE_SCALE = 0.06
 
 
 def record_field_bytes(rec, rec_off):
-    """Algorithmic bytes of the record-scan kernel: every field but QUAL, read once."""
+    """Algorithmic bytes of the record scan: every record field but QUAL read once + 76 B of table written
+    (sum(36 + l_name + 4 n_cigar + ceil(l_seq / 2) + aux))."""
     off = rec_off[:-1].astype(np.int64)
 
     def u32(o):
@@ -33,7 +47,7 @@ def record_field_bytes(rec, rec_off):
     n_cig = rec[off + 16].astype(np.int64) | (rec[off + 17].astype(np.int64) << 8)
     l_seq = u32(20)
     aux = bs - 32 - l_name - 4 * n_cig - (l_seq + 1) // 2 - l_seq
-    return int((36 + l_name + 4 * n_cig + (l_seq + 1) // 2 + aux).sum()), int(n_cig.sum()), int(l_seq.sum())
+    return int((36 + l_name + 4 * n_cig + (l_seq + 1) // 2 + aux).sum()) + 76 * len(off)
 
 
 class ClockSampler(threading.Thread):
@@ -66,45 +80,132 @@ class ClockSampler(threading.Thread):
                 "sm_max_mhz": int(self.rows[0][1]) if self.rows[0][1].isdigit() else None, "reasons": reasons}
 
 
-def make_workload(scale, seed_shift=0):
+def write_inputs(cfg, outdir):
+    os.makedirs(outdir, exist_ok=True)
+    cns = os.path.join(outdir, "cn_seg.bed")
+    with open(cns, "w") as fp:
+        for (c, s, e, cn) in cfg.cn_rows:
+            fp.write("%s\t%d\t%d\t%g\n" % (c, s, e, cn))
+    seed = os.path.join(outdir, "seed.bed")
+    with open(seed, "w") as fp:
+        for (c, s, e) in cfg.seeds:
+            fp.write("%s\t%d\t%d\n" % (c, s, e))
+    return cns, seed
+
+
+def workload_config(scale, seed_shift=0):
     from sim import configs
-    from sim.generate import simulate
-    cfg = configs.c2_multi_segment(scale=scale, seed=20240215 + 2 + seed_shift)
-    data = simulate(cfg)
-    tid_of = {c: i for i, (c, _) in enumerate(cfg.refs)}
-    regs = sorted((tid_of[c], s, e) for (c, s, e, _cn) in cfg.cn_rows)
-    reg = np.array(regs, dtype=np.int32)
-    return cfg, data, reg
+    return configs.c2_multi_segment(scale=scale, seed=20240215 + 2 + 1000 * seed_shift)
 
 
-def cpu_baseline_sample(cfg, data, reg, budget_s=15.0):
-    """Oracle ("port") timed on host cores over a bounded sample: count_coverage + record counts."""
+# ------------------------------------------------------------------------------------------------------------
+def reference_arm(a, rank, world):
+    """CPU port of the reference path, one pipeline run per step over a bounded sample of the workload."""
+    if rank != 0:
+        return
     import tempfile
-    from sim.generate import write_dataset, SimData
+    import util
+    from sim.generate import simulate, write_dataset
+    cfg = workload_config(CPU_SAMPLE_SCALE)
+    data = simulate(cfg)
+    d = tempfile.mkdtemp(prefix="coral_ref_")
+    paths = write_dataset(data, d)
     from oracle import pysam_shim
-    # sample: the first K records (coordinate order) written as a BAM, regions clipped to their span
-    k = min(data.n_records, 3000)
-    sub = SimData(cfg, data.rec[:int(data.rec_off[k])], data.rec_off[:k + 1], 0, 0, None, None, None)
-    d = tempfile.mkdtemp(prefix="coral_cpu_")
-    paths = write_dataset(sub, d)
     fh = pysam_shim.AlignmentFile(paths["bam"])
-    t0 = time.perf_counter()
-    n_units = 0
-    for (t, s, e) in reg:
-        c = fh.references[int(t)]
-        sel = fh._select(c, int(s), int(e))
-        if len(sel) == 0:
-            continue
-        sum(sum(a) for a in fh.count_coverage(c, int(s), int(e), quality_threshold=0, read_callback='nofilter'))
-        len([r for r in fh.fetch(c, int(s), int(e)) if r.infer_read_length()])
-        for r in fh.fetch(c, int(s), int(e)):
-            r.get_blocks()
-        n_units += len(sel)
-        if time.perf_counter() - t0 > budget_s:
-            break
-    dt = time.perf_counter() - t0
-    return {"value": n_units / dt if dt > 0 else 0.0, "unit": "records/s", "cores": 1, "kind": "port",
-            "sample": "first %d records of the workload; oracle count_coverage + record count + get_blocks per CN segment" % k}
+    aligned = int(fh._mb.sum())
+    n_rec = fh._n
+    del fh
+
+    def step():
+        eng = util.oracle_engine(paths["bam"], paths["seed"])   # BAM inflate happens here, outside the stage timers
+        t = {}
+        for name, fn, args in (("read_cns", eng.read_cns, (paths["cn_seg"],)), ("fetch", eng.fetch, ()),
+                               ("hash", eng.hash_alignment_to_seg, ()), ("intervals", eng.find_amplicon_intervals, ()),
+                               ("smalldel", eng.find_smalldel_breakpoints, ()), ("breakpoints", eng.find_breakpoints, ()),
+                               ("graph", eng.build_graph, ()), ("assign_cov", eng.assign_cov, ())):
+            t0 = time.perf_counter()
+            fn(*args)
+            t[name] = time.perf_counter() - t0
+        return sum(t[k] for k in ("read_cns", "fetch", "smalldel", "breakpoints", "assign_cov")), t
+
+    warm = max(1, min(a.warmup, 1))
+    for _ in range(warm):
+        step()
+    tot = 0.0
+    stages = {}
+    for _ in range(a.steps):
+        dt, st = step()
+        tot += dt
+        stages = st
+    v = n_rec * a.steps / tot
+    sample = ("C2 at scale %g (%d records, %.3f aligned Gbases) written as BGZF BAM; one full hot-path pass per step; "
+              "hot stages summed (read_cns coverage, fetch, smalldel, breakpoints, assign_cov), BAM inflate excluded"
+              % (CPU_SAMPLE_SCALE, n_rec, aligned / 1e9))
+    out = {"impl": "reference", "metric": METRIC, "value": v, "unit": "records/s", "n_gpus": world, "steps": a.steps,
+           "warmup": warm, "ms_per_step": tot / a.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "u8/int32/int64 (f64 stats)", "data": "synthetic",
+           "config": {"workload": "C2 multi-segment ecDNA: 3 seeds/6 Mb, CN 40, 50x ONT 30 kb",
+                      "note": "reference-on-shim: CPU port of the reference path (oracle/), pysam unavailable on this box"},
+           "aligned_gbases_per_s": aligned * a.steps / tot / 1e9,
+           "cpu_baseline": {"value": v, "unit": "records/s", "cores": 1, "kind": "port", "sample": sample,
+                            "stage_s": stages},
+           "e2e": {"value": v, "unit": "records/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------
+def build_plan(eng, cn_seg):
+    """Run the public pipeline once and capture the inputs of every device call (fixed for the timed passes)."""
+    from coral_b200 import infer_breakpoint_graph  # noqa: F401
+    eng.read_cns(cn_seg)
+    segs, total = eng._median_cn_segments()
+    segs = sorted(segs, key=lambda s: (eng._tid[s[0]], s[1]))
+    plan = {"normal": ([eng._tid[s[0]] for s in segs], [s[1] for s in segs], [s[2] + 1 for s in segs])}
+    eng.fetch()
+    eng.hash_alignment_to_seg()
+    eng.find_amplicon_intervals()
+    plan["intervals"] = eng._interval_arrays()
+    eng.find_smalldel_breakpoints()
+    plan["smalldel_cand"] = eng._smalldel_candidates()[0]
+    eng.find_breakpoints()
+    eng.build_graph()
+    batches, uniq, owners, rb_edge, rb_rec = eng._edge_queries()
+    b = batches[0]
+    plan["seq_edges"] = ([r[0] for r in b], [r[1] for r in b], [r[2] for r in b])
+    plan["conc"] = ([u[0] for u in uniq], [u[1] for u in uniq], rb_edge, rb_rec)
+    plan["cutoff"] = eng.min_cluster_cutoff
+    eng.assign_cov()
+    return plan
+
+
+def device_pass(ctx, plan, gpu_ops):
+    """One pass of the hot path on device-resident records; every result table is read back."""
+    ctx.rescan()
+    out = {}
+    out["normal"] = ctx.region_coverage(*plan["normal"])
+    out["fetch"] = ctx.fetch()
+    out["smalldel"] = ctx.smalldel(*plan["intervals"])
+    c = plan["smalldel_cand"]
+    if len(c["chr1"]):
+        out["cl1"] = gpu_ops.cluster_arrays(ctx, c, plan["cutoff"], 2000, plan["cutoff"], 100)
+    cand = ctx.candidates_l(*plan["intervals"])
+    if cand["n"]:
+        out["cl2"] = gpu_ops.cluster_arrays(ctx, cand, plan["cutoff"], 2000, plan["cutoff"], 100)
+    out["seq"] = ctx.region_coverage(*plan["seq_edges"])
+    out["conc"] = ctx.concordant(*plan["conc"])
+    return out
+
+
+def result_bytes(out):
+    n = 0
+    for v in out.values():
+        items = v.values() if isinstance(v, dict) else (v if isinstance(v, (tuple, list)) else [v])
+        for x in items:
+            if isinstance(x, np.ndarray):
+                n += x.nbytes
+            elif isinstance(x, dict):
+                n += sum(y.nbytes for y in x.values() if isinstance(y, np.ndarray))
+    return n
 
 
 def main():
@@ -118,6 +219,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference":
+        reference_arm(a, rank, world)
+        return
     warm = max(a.warmup, 3)
 
     import torch
@@ -126,28 +230,42 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
 
-    cfg, data, reg = make_workload(a.scale, seed_shift=rank)
-    from coral_b200 import _abi
-    ctx = _abi.Context(local)
-    ctx.set_references([c for c, _ in cfg.refs])
-    rec_pinned = torch.from_numpy(data.rec).pin_memory()
-    rec_np = rec_pinned.numpy()
+    from sim.generate import simulate
+    from coral_b200 import _abi, gpu_ops
+    from coral_b200.infer_breakpoint_graph import bam_to_breakpoint_nanopore
+    from coral_b200.records import RecordSet
+    import tempfile
+
+    cfg = workload_config(a.scale, seed_shift=rank)      # weak scaling: one C2-sized sample per GPU
+    pinned = {}
+
+    def alloc(nbytes):
+        pinned["t"] = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+        return pinned["t"].numpy()
+
+    data = simulate(cfg, alloc=alloc)
     n_rec = data.n_records
-    alg_bytes, n_ops, n_bases_q = record_field_bytes(data.rec, data.rec_off)
+    nbytes = int(data.rec_off[-1])
+    recs = RecordSet([c for c, _ in cfg.refs], data.rec, data.rec_off)
+    cns, seed = write_inputs(cfg, tempfile.mkdtemp(prefix="coral_bench_%d_" % rank))
+    alg_bytes = record_field_bytes(data.rec, data.rec_off)
 
-    def step_resident():
-        ctx.rescan()
-        return ctx.region_coverage(reg[:, 0], reg[:, 1], reg[:, 2])
+    def e2e_pass():
+        eng = bam_to_breakpoint_nanopore(None, seed, device=local, records=recs)
+        eng.read_cns(cns); eng.fetch(); eng.hash_alignment_to_seg(); eng.find_amplicon_intervals()
+        eng.find_smalldel_breakpoints(); eng.find_breakpoints(); eng.build_graph(); eng.assign_cov()
+        return eng
 
-    def step_e2e():
-        ctx.load_records(rec_np, data.rec_off)
-        return ctx.region_coverage(reg[:, 0], reg[:, 1], reg[:, 2])
-
-    ctx.load_records(rec_np, data.rec_off)
+    # plan + resident context
+    eng0 = bam_to_breakpoint_nanopore(None, seed, device=local, records=recs)
+    plan = build_plan(eng0, cns)
+    ctx = eng0._ctx
     tab = ctx.record_table()
     aligned = int(tab["aligned_bases"].sum())
+    n_bp = len(eng0.new_bp_list)
     for _ in range(warm):
-        step_resident()
+        out = device_pass(ctx, plan, gpu_ops)
+    d2h = result_bytes(out)
     sampler = ClockSampler(local)
     sampler.start()
 
@@ -160,20 +278,21 @@ def main():
     l0 = ctx.launch_count
     barrier()
     t0 = time.perf_counter()
-    scan_ms = []
+    scan_ms, stage_ms = [], np.zeros(8)
     for _ in range(a.steps):
-        step_resident()
+        device_pass(ctx, plan, gpu_ops)
         scan_ms.append(ctx.stage_ms(0))
+        stage_ms += np.array([max(ctx.stage_ms(s), 0.0) for s in range(8)])
     barrier()
     dt = time.perf_counter() - t0
     launches = ctx.launch_count - l0
-    # e2e
-    step_e2e()
+    # e2e through the public class, from pinned host records
+    e2e_pass()
     barrier()
     t1 = time.perf_counter()
     e2e_steps = max(1, min(a.steps, 3))
     for _ in range(e2e_steps):
-        bs, rc = step_e2e()
+        e2e_pass()
     barrier()
     dt_e2e = time.perf_counter() - t1
     sampler.stop_flag = True
@@ -183,7 +302,6 @@ def main():
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     dt, dt_e2e = float(tt[0]), float(tt[1])
-    total_rec = n_rec * world
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -192,28 +310,37 @@ def main():
     peak = float(peaks.get("hbm_gbs", 6650.0))
     k_ms = float(np.mean(scan_ms))
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    names = ["scan", "coverage", "fetch", "smalldel", "candidates", "cluster", "bpc2bp", "concordant"]
     out = {
-        "metric": "long reads/sec (breakpoint+coverage pass)", "value": total_rec * a.steps / dt, "unit": "records/s",
+        "metric": METRIC, "value": n_rec * world * a.steps / dt, "unit": "records/s",
         "n_gpus": world, "steps": a.steps, "warmup": warm, "ms_per_step": dt / a.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/int32", "data": "synthetic",
-        "config": {"workload": "C2 multi-segment ecDNA: 3 seeds/6 Mb, CN 40, %gx ONT 30 kb" % cfg.cov,
-                   "scale": a.scale, "records_per_gpu": n_rec, "record_bytes_per_gpu": int(data.rec_off[-1]),
-                   "aligned_gbases_per_gpu": aligned / 1e9, "l2_policy": "inputs (%.1f GB) larger than L2" % (alg_bytes / 1e9)},
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8/int32/int64 (f64 stats)", "data": "synthetic",
+        "config": {"workload": "C2 multi-segment ecDNA: 3 seeds/6 Mb, CN 40, 50x ONT 30 kb", "scale": a.scale,
+                   "records_per_gpu": n_rec, "record_bytes_per_gpu": nbytes, "aligned_gbases_per_gpu": aligned / 1e9,
+                   "breakpoints_found": n_bp, "sharding": "one independent sample per GPU, no collective",
+                   "l2_policy": "inputs (%.2f GB of record fields per pass) larger than the 126 MB L2" % (alg_bytes / 1e9)},
         "aligned_gbases_per_s": aligned * world * a.steps / dt / 1e9,
-        "e2e": {"value": total_rec * e2e_steps / dt_e2e, "unit": "records/s",
-                "h2d_bytes_per_step": int(data.rec_off[-1]) + 8 * (n_rec + 1) + 12 * len(reg),
-                "d2h_bytes_per_step": 16 * len(reg) + 16},
+        "e2e": {"value": n_rec * world * e2e_steps / dt_e2e, "unit": "records/s", "ms_per_step": dt_e2e / e2e_steps * 1e3,
+                "h2d_bytes_per_step": nbytes + 8 * (n_rec + 1), "d2h_bytes_per_step": d2h},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "k_scan_records", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                     "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+        "roofline": {"bound": "hbm", "kernel": "k_scan_records", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None,
+                     "peak_source": "MEASURED_PEAKS.json (of measured)" if peaks else "fallback 6650 (of fallback)",
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": k_ms},
+        "stage_ms_per_step": {n: float(stage_ms[i] / a.steps) for i, n in enumerate(names)},
         "clocks": sampler.summary(),
     }
     if rank == 0:
         if world == 1:
             try:
-                out["cpu_baseline"] = cpu_baseline_sample(cfg, data, reg)
+                import io
+                import contextlib
+                buf = io.StringIO()
+                with contextlib.redirect_stdout(buf):
+                    reference_arm(argparse.Namespace(steps=2, warmup=1), 0, 1)
+                ref = json.loads(buf.getvalue().strip().splitlines()[-1])
+                out["cpu_baseline"] = ref["cpu_baseline"]
             except Exception as ex:  # noqa
                 out["cpu_baseline"] = {"error": repr(ex)}
         print(json.dumps(out), flush=True)

@@ -20,9 +20,11 @@ from .host_steps import HostSteps, _t
 class bam_to_breakpoint_nanopore(HostSteps):
     _ops = breakpoint_utilities
 
-    def __init__(self, lr_bamfile, seedfile, device=0, n_threads=0):
+    def __init__(self, lr_bamfile, seedfile, device=0, n_threads=0, records=None):
+        """`records` (optional): an object with .references, .rec (uint8 host buffer of framed records), .rec_off and
+        .query_name(i) — lets a caller that already holds decompressed records skip the BAM file."""
         self._init_state()
-        self.lr_bamfh = _abi.BamFile(lr_bamfile, n_threads)          # replaces pysam.AlignmentFile (ibg:65)
+        self.lr_bamfh = records if records is not None else _abi.BamFile(lr_bamfile, n_threads)   # replaces pysam (ibg:65)
         self._ctx = _abi.Context(device)
         self._ctx.set_references(self.lr_bamfh.references)
         self._ctx.load_records(self.lr_bamfh.rec, self.lr_bamfh.rec_off)
@@ -154,8 +156,11 @@ class bam_to_breakpoint_nanopore(HostSteps):
                 self._name_rec.setdefault(name, rec)
             lia.setdefault(name, []).append([self.amplicon_intervals[ai[k]][0], ns[k], pe[k], fs[k], le[k], mq[k]])
         logging.info(_t() + "Fetched %d reads with large indels in CIGAR." % (len(lia)))
+        self._call_clusters(*self._smalldel_candidates())
+
+    def _smalldel_candidates(self):
         tuples, chrs, p1, p2 = [], [], [], []
-        for name, lst in lia.items():          # ibg:765-772
+        for name, lst in self.large_indel_alignments.items():          # ibg:765-772
             for idx, row in enumerate(lst):
                 hi, lo = row[1], row[2]
                 if lo > hi:
@@ -166,7 +171,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
                 "chr2": np.array(chrs, np.int32), "pos2": np.array(p2, np.int32), "o2": np.zeros(n, np.uint8),
                 "rgap": np.zeros(n, np.int32), "flag": np.zeros(n, np.uint8), "mq1": np.full(n, -1, np.int32),
                 "mq2": np.full(n, -1, np.int32)}
-        self._call_clusters(cand, tuples)
+        return cand, tuples
 
     # ---- a4/a5: ibg:676-718 ---------------------------------------------------------------------------------
     def find_breakpoints(self):
@@ -190,8 +195,9 @@ class bam_to_breakpoint_nanopore(HostSteps):
                  int(c["mq1"][k]), int(c["mq2"][k])] for k in range(c["n"])]
 
     # ---- a10/a11: ibg:1019-1056 -----------------------------------------------------------------------------
-    def assign_cov(self):
-        # sequence edges of every graph in one launch (disjoint by construction, App. A.14)
+    def _edge_queries(self):
+        """Device queries of assign_cov: sequence-edge regions in disjoint sorted batches, concordant-edge points
+        (sorted, de-duplicated) with their owners, and the rbps rows (edge index, a record of the read)."""
         todo = []
         for gi, g in enumerate(self.lr_graph):
             for si, se in enumerate(g.sequence_edges):
@@ -199,18 +205,10 @@ class bam_to_breakpoint_nanopore(HostSteps):
                     todo.append((self._tid[se[0]], se[1], se[2] + 1, gi, si))
         todo.sort()
         batches = [[]]
-        for row in todo:   # keep each launch's regions disjoint
+        for row in todo:   # disjoint by construction (App. A.14); split defensively otherwise
             if batches[-1] and batches[-1][-1][0] == row[0] and row[1] < batches[-1][-1][2]:
                 batches.append([])
             batches[-1].append(row)
-        for batch in batches:
-            if not batch:
-                continue
-            bs, rc = self._ctx.region_coverage([r[0] for r in batch], [r[1] for r in batch], [r[2] for r in batch])
-            for k, (_, _, _, gi, si) in enumerate(batch):
-                self.lr_graph[gi].sequence_edges[si][5] = int(rc[k])
-                self.lr_graph[gi].sequence_edges[si][6] = int(bs[k])
-        # concordant edges
         edges = []
         for gi, g in enumerate(self.lr_graph):
             for ci, ce in enumerate(g.concordant_edges):
@@ -233,8 +231,19 @@ class bam_to_breakpoint_nanopore(HostSteps):
                     for r in g.discordant_edges[bpi][10]:
                         if r[0] not in seen:
                             seen.add(r[0])
-                            if r[0] in self._name_rec:   # reads of no loaded record cannot overlap any point
+                            if r[0] in self._name_rec:   # a read with no loaded record cannot cover any point
                                 rb_edge.append(k); rb_rec.append(self._name_rec[r[0]])
+        return batches, uniq, owners, rb_edge, rb_rec
+
+    def assign_cov(self):
+        batches, uniq, owners, rb_edge, rb_rec = self._edge_queries()
+        for batch in batches:
+            if not batch:
+                continue
+            bs, rc = self._ctx.region_coverage([r[0] for r in batch], [r[1] for r in batch], [r[2] for r in batch])
+            for k, (_, _, _, gi, si) in enumerate(batch):
+                self.lr_graph[gi].sequence_edges[si][5] = int(rc[k])
+                self.lr_graph[gi].sequence_edges[si][6] = int(bs[k])
         if not uniq:
             return
         self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)

@@ -186,7 +186,8 @@ def _plan_pieces(cfg: SimConfig, rng):
     return arr, next_read
 
 
-def simulate(cfg: SimConfig, n_threads: int = 0, record_align: int = 16) -> SimData:
+def simulate(cfg: SimConfig, n_threads: int = 0, record_align: int = 16, alloc=None) -> SimData:
+    """`alloc(nbytes) -> uint8 ndarray` lets the caller provide the record buffer (e.g. pinned host memory)."""
     lib = _load()
     rng = np.random.Generator(np.random.PCG64(cfg.seed))
     arr, n_reads = _plan_pieces(cfg, rng)
@@ -247,7 +248,7 @@ def simulate(cfg: SimConfig, n_threads: int = 0, record_align: int = 16) -> SimD
     args = [P(pieces), ctypes.c_int64(npc), ctypes.byref(prm), P(f_off_a), P(f_len_a), P(qlen), P(nm), P(qs),
             P(read_len), P(order), ctypes.c_int64(len(order)), names_buf, P(name_off)]
     total = lib.sim_write(*args, None, P(rec_off))
-    rec = np.zeros(max(int(total), 1), np.uint8)
+    rec = alloc(max(int(total), 1) + 64) if alloc is not None else np.zeros(max(int(total), 1), np.uint8)
     lib.sim_write(*args, P(rec), P(rec_off))
     return SimData(cfg, rec[:int(total)], rec_off, n_reads, 0, pieces, qlen, read_len)
 
