@@ -95,7 +95,8 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
             return CORAL_E_ARG;
         }
     }
-    if (n >= (int64_t)1 << 32) { c->err = "more than 2^32 records per ctx"; return CORAL_E_ARG; }
+    if (n > 0 && (offsets[n] & 15)) { c->err = "record offsets must be 16-byte aligned (including the end offset)"; return CORAL_E_ARG; }
+    if (n >= ((int64_t)1 << 32) - 65536) { c->err = "more than 2^32 - 65536 records per ctx"; return CORAL_E_ARG; }
     if (on_device) {
         if (reinterpret_cast<uintptr_t>(recs) & 15) { c->err = "device record buffer must be 16-byte aligned"; return CORAL_E_ARG; }
         c->d_recs = recs;
