@@ -215,6 +215,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--scale", type=float, default=float(os.environ.get("CORAL_BENCH_SCALE", "1.0")))
+    ap.add_argument("--only", default="", help="'scan': time the record-scan kernel alone (development aid)")
+    ap.add_argument("--profile", action="store_true",
+                    help="bracket ONE device pass with cudaProfilerStart/Stop and exit (for ncu --profile-from-start off)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -250,6 +253,22 @@ def main():
     cns, seed = write_inputs(cfg, tempfile.mkdtemp(prefix="coral_bench_%d_" % rank))
     alg_bytes = record_field_bytes(data.rec, data.rec_off)
 
+    if a.only == "scan":
+        ctx = _abi.Context(local)
+        ctx.set_references([c for c, _ in cfg.refs])
+        ctx.load_records(data.rec, data.rec_off)
+        for _ in range(warm):
+            ctx.rescan()
+        ms = []
+        for _ in range(a.steps):
+            ctx.rescan()
+            ms.append(ctx.stage_ms(0))
+        k_ms = float(np.mean(ms))
+        print(json.dumps({"only": "scan", "records": n_rec, "alg_bytes": alg_bytes, "record_bytes": nbytes,
+                          "kernel_ms": k_ms, "min_ms": float(np.min(ms)), "GBps": alg_bytes / k_ms / 1e6,
+                          "frac": alg_bytes / k_ms / 1e6 / 6447.5}), flush=True)
+        return
+
     def e2e_pass():
         eng = bam_to_breakpoint_nanopore(None, seed, device=local, records=recs)
         eng.read_cns(cns); eng.fetch(); eng.hash_alignment_to_seg(); eng.find_amplicon_intervals()
@@ -266,6 +285,14 @@ def main():
     for _ in range(warm):
         out = device_pass(ctx, plan, gpu_ops)
     d2h = result_bytes(out)
+    if a.profile:
+        torch.cuda.synchronize()
+        torch.cuda.cudart().cudaProfilerStart()
+        device_pass(ctx, plan, gpu_ops)
+        torch.cuda.synchronize()
+        torch.cuda.cudart().cudaProfilerStop()
+        print(json.dumps({"profile": "one device pass", "records": n_rec}), flush=True)
+        return
     sampler = ClockSampler(local)
     sampler.start()
 

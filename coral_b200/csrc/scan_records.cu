@@ -100,7 +100,7 @@ __device__ __forceinline__ uint32_t not_onehot_test(uint32_t w) {
 }
 
 // Aux TLV walk (warp-uniform; p/end may point into shared or global memory).  Finds the first SA:Z and NM.
-__device__ __forceinline__ bool aux_walk(const uint8_t* p, const uint8_t* end, uint32_t p_rel, uint32_t lane,
+__device__ __noinline__ bool aux_walk(const uint8_t* p, const uint8_t* end, uint32_t p_rel, uint32_t lane,
                                          uint32_t& sa_off, uint32_t& sa_len, int32_t& nm, bool& have_sa) {
     bool have_nm = false, bad_aux = false;
     const uint8_t* const p_org = p;       // p_rel = offset of p_org from the start of the record
@@ -179,7 +179,7 @@ enum { G_NEW = 0, G_R1 = 1, G_AUX = 2, G_DONE = 3 };
 
 // Lane 0: produce the next segment of the warp's record stream into stage s.
 // `ahead` = record index fetched from the queue one grab early (the atomic's latency is off the critical path).
-__device__ __forceinline__ void gen_next(WarpCtl* ctl, int s, uint32_t bar, uint32_t dst, const uint8_t* __restrict__ recs,
+__device__ __noinline__ void gen_next(WarpCtl* ctl, int s, uint32_t bar, uint32_t dst, const uint8_t* __restrict__ recs,
                                          const uint64_t* __restrict__ off, uint32_t n, unsigned int* queue,
                                          uint32_t& ahead) {
     uint32_t st = ctl->g_state;
@@ -269,7 +269,7 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
         ctl->g_rec = 0;
         ctl->g_base = 0;
         ahead = atomicAdd(queue, 1u);
-#pragma unroll
+#pragma unroll 1
         for (int s = 0; s < SC_NST; s++)
             gen_next(ctl, s, bar0 + 8 * s, smem_u32(ring + (size_t)s * SC_SB), recs, off, n, queue, ahead);
     }
@@ -284,14 +284,12 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
     uint32_t gcount = 0;
     uint32_t parity = 0;
 
-    bool running = true;
-    while (running) {
-#pragma unroll
-        for (int s = 0; s < SC_NST; s++) {
-            if (!running) break;
+    {
+#pragma unroll 1
+        for (int s = 0;; s = (s + 1 == SC_NST) ? 0 : s + 1) {
             const uint4 dq = *reinterpret_cast<const uint4*>(&ctl->desc[s]);
             const uint32_t fl = dq.x & 255u;
-            if (!(fl & SF_VALID)) { running = false; break; }
+            if (!(fl & SF_VALID)) break;
             mbar_wait(bar0 + 8 * s, (parity >> s) & 1u);
             parity ^= 1u << s;
             const uint8_t* buf = ring + (size_t)s * SC_SB;
