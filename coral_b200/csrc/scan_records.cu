@@ -36,16 +36,45 @@ struct ScanEvents {
 };
 
 constexpr int SC_WARPS = 8;                 // warps per block
-constexpr int SC_NST = 3;                   // stages per warp
-constexpr int SC_CH = 2048;                 // payload bytes per staged segment
+#ifndef SC_NST
+#define SC_NST 2                            // stages per warp
+#endif
+#ifndef SC_CH
+#define SC_CH 3072                          // payload bytes per staged segment
+#endif
 constexpr int SC_SB = SC_CH + 16;           // stage bytes: 16 B of overlap so no CIGAR op straddles two segments
 
 // segment flags
 constexpr uint32_t SF_VALID = 1, SF_FIRST = 2, SF_LAST = 4, SF_AUX = 8, SF_AUXG = 16, SF_BAD = 32;
-// CIGAR op classes (ops 0..8 = MIDNSHP=X): M-type {M,=,X}, D/N, query-only {I,S,H}; P consumes nothing.
+
+// ---- shared-memory access by 32-bit shared-window address (no generic-pointer arithmetic in the hot loops) --
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t lds8(uint32_t a) {
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint4 lds128(uint32_t a) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void sts128(uint32_t a, uint4 v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// 32-bit little-endian load from an arbitrarily aligned shared address (stage buffers keep 16 B of slack)
+__device__ __forceinline__ uint32_t lds32_any(uint32_t a) {
+    const uint32_t lo = lds32(a & ~3u), hi = lds32((a & ~3u) + 4);
+    return __funnelshift_r(lo, hi, (a & 3u) * 8u);
+}
 
 // ---- mbarrier / bulk copy (sm_90+ PTX; SASS: SYNCS.*, UBLKCP) ---------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
@@ -71,21 +100,23 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "memory");
 }
 
-__device__ __forceinline__ uint32_t lds32(const uint8_t* p) { return *reinterpret_cast<const uint32_t*>(p); }
-__device__ __forceinline__ uint4 lds128(const uint8_t* p) { return *reinterpret_cast<const uint4*>(p); }
-
-// Class byte of a raw CIGAR word by ONE PRMT: the op nibble selects a table byte; selector bit 3 means
-// "replicate the sign bit of byte (op & 7)", so op 8 ('X') lands on M's entry (top bit set) and reads 0xFF.
-// Encoding that makes 0xFF decode as M-type only: bit 0 SET = M-type, bit 1 CLEAR = D/N, bit 2 CLEAR = I/S/H.
-// (Only result byte 0 is meaningful; the other selector nibbles are length bits.)
-__device__ __forceinline__ uint32_t cigar_class(uint32_t v) {
-    //             op:   3 N   2 D   1 I   0 M                   7 =   6 P   5 H   4 S
-    const uint32_t lo = 0x04040287u, hi = 0x87060202u;
-    return __byte_perm(lo, hi, v);
+// CIGAR op classes (ops 0..8 = MIDNSHP=X): M-type {M,=,X}, D/N, query-only {I,S,H}; P consumes nothing.
+// One PRMT per class turns the op code into a clean 0/1 multiplier: selector nibble 0 = op & 7 (X = 8 lands on
+// M's entry), selector nibbles 1..3 = 6 (P's entry, 0 in every table) so the upper result bytes are zero.  The
+// masked adds then run as IMADs on the FMA pipe while the ALU pipe does the selects.
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
 }
-__device__ __forceinline__ bool cls_m(uint32_t c) { return (c & 1u) != 0; }
-__device__ __forceinline__ bool cls_dn(uint32_t c) { return (c & 2u) == 0; }
-__device__ __forceinline__ bool cls_ish(uint32_t c) { return (c & 4u) == 0; }
+//                                   op:   3 N 2 D 1 I 0 M           7 = 6 P 5 H 4 S
+#define CIG_TM_LO 0x00000001u          //   0   0   0   1
+#define CIG_TM_HI 0x01000000u          //                              1   0   0   0
+#define CIG_TD_LO 0x01010000u          //   1   1   0   0
+#define CIG_TD_HI 0x00000000u
+#define CIG_TQ_LO 0x00000100u          //   0   0   1   0
+#define CIG_TQ_HI 0x00000101u          //                              0   0   1   1
+
 // nibbles of w that are one-hot (BAM codes A=1, C=2, G=4, T=8): bit 0 of each such nibble is set in the result
 __device__ __forceinline__ uint32_t onehot_nibbles(uint32_t w) {
     const uint32_t w1 = w >> 1;
@@ -99,109 +130,166 @@ __device__ __forceinline__ uint32_t not_onehot_test(uint32_t w) {
     return (w & t) | (t & ~w & 0x88888888u);
 }
 
-// Aux TLV walk (warp-uniform; p/end may point into shared or global memory).  Finds the first SA:Z and NM.
-__device__ __noinline__ bool aux_walk(const uint8_t* p, const uint8_t* end, uint32_t p_rel, uint32_t lane,
-                                         uint32_t& sa_off, uint32_t& sa_len, int32_t& nm, bool& have_sa) {
-    bool have_nm = false, bad_aux = false;
-    const uint8_t* const p_org = p;       // p_rel = offset of p_org from the start of the record
-    have_sa = false;
-    sa_off = 0; sa_len = 0; nm = 0;
+// value-size class of an aux type byte: 1/2/4 = fixed size, 0x80 = NUL-terminated (Z, H), 0x81 = array (B), 0 = invalid
+__constant__ uint8_t c_aux_size[128] = {
+    0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0,
+    0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0,
+    //  A     B     C                             H     I
+    0, 1, 0x81, 1, 0, 0, 0, 0, 0x80, 4, 0, 0, 0, 0, 0, 0,
+    //        S                                         Z
+    0, 0, 0, 2, 0, 0, 0, 0, 0, 0, 0x80, 0, 0, 0, 0, 0,
+    //           c           f        i
+    0, 0, 0, 1, 0, 0, 4, 0, 0, 4, 0, 0, 0, 0, 0, 0,
+    //        s
+    0, 0, 0, 2, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+
+struct AuxOut { uint32_t sa_off, sa_len; int32_t nm; uint32_t have_sa, bad; };
+
+// Aux TLV walk over a staged copy (warp-uniform).  p/end are shared-window addresses; p_rel = record offset of p.
+__device__ __noinline__ AuxOut aux_walk_smem(uint32_t p, uint32_t end, uint32_t p_rel, uint32_t lane) {
+    AuxOut r{0, 0, 0, 0, 0};
+    const uint32_t p_org = p;
+    bool have_nm = false;
+    while (p + 3 <= end) {
+        const uint32_t hd = lds32_any(p);                 // tag[2], type, first value byte
+        const uint32_t tag = hd & 0xffffu, ty = (hd >> 16) & 255u;
+        p += 3;
+        const uint32_t sz = ty < 128 ? c_aux_size[ty] : 0u;
+        if (sz == 0) { r.bad = 1; break; }
+        if (sz < 0x80) {
+            if (p + sz > end) { r.bad = 1; break; }
+            if (tag == (('M' << 8) | 'N') && !have_nm) {
+                have_nm = true;
+                const uint32_t raw = lds32_any(p);
+                if (ty == 'c') r.nm = (int32_t)(int8_t)raw;
+                else if (ty == 'C') r.nm = (int32_t)(raw & 255u);
+                else if (ty == 's') r.nm = (int32_t)(int16_t)raw;
+                else if (ty == 'S') r.nm = (int32_t)(raw & 0xffffu);
+                else if (ty == 'f' || ty == 'A') r.nm = 0;
+                else r.nm = (int32_t)raw;
+            }
+            p += sz;
+        } else if (sz == 0x80) {
+            uint32_t len = 0;
+            bool found = false;
+            while (p + len < end) {
+                const uint32_t q = p + len + lane;
+                const uint32_t b = (q < end) ? lds8(q) : 1u;
+                const uint32_t zb = __ballot_sync(FULL_MASK, b == 0);
+                if (zb) { len += __ffs(zb) - 1; found = true; break; }
+                len += 32;
+            }
+            if (!found) { r.bad = 1; break; }
+            if (tag == (('A' << 8) | 'S') && !r.have_sa) {
+                r.have_sa = 1;
+                r.sa_off = (p - p_org) + p_rel;
+                r.sa_len = len;
+            }
+            p += len + 1;
+        } else {
+            if (p + 5 > end) { r.bad = 1; break; }
+            const uint32_t sub = lds8(p);
+            const uint32_t cnt = lds32_any(p + 1);
+            const uint32_t es = sub < 128 ? c_aux_size[sub] : 0u;
+            if (es == 0 || es >= 0x80 || (uint64_t)cnt * es > (uint64_t)(end - p - 5)) { r.bad = 1; break; }
+            p += 5 + cnt * es;
+        }
+    }
+    if (p > end) r.bad = 1;
+    return r;
+}
+
+// The same walk in global memory, for the rare record whose aux block is longer than a stage.
+__device__ __noinline__ AuxOut aux_walk_global(const uint8_t* p, const uint8_t* end, uint32_t p_rel, uint32_t lane) {
+    AuxOut r{0, 0, 0, 0, 0};
+    const uint8_t* const p_org = p;
+    bool have_nm = false;
     while (p + 3 <= end) {
         const uint32_t t0 = p[0], t1 = p[1], ty = p[2];
         p += 3;
-        uint32_t sz = 0;
-        if (ty == 'A' || ty == 'c' || ty == 'C') sz = 1;
-        else if (ty == 's' || ty == 'S') sz = 2;
-        else if (ty == 'i' || ty == 'I' || ty == 'f') sz = 4;
-        if (sz) {
-            if (p + sz > end) { bad_aux = true; break; }
+        const uint32_t sz = ty < 128 ? c_aux_size[ty] : 0u;
+        if (sz == 0) { r.bad = 1; break; }
+        if (sz < 0x80) {
+            if (p + sz > end) { r.bad = 1; break; }
             if (t0 == 'N' && t1 == 'M' && !have_nm) {
                 have_nm = true;
                 uint32_t raw = 0;
                 for (uint32_t b = 0; b < sz; b++) raw |= (uint32_t)p[b] << (8 * b);
-                if (ty == 'c') nm = (int32_t)(int8_t)raw;
-                else if (ty == 's') nm = (int32_t)(int16_t)raw;
-                else if (ty == 'f' || ty == 'A') nm = 0;
-                else nm = (int32_t)raw;
+                if (ty == 'c') r.nm = (int32_t)(int8_t)raw;
+                else if (ty == 's') r.nm = (int32_t)(int16_t)raw;
+                else if (ty == 'f' || ty == 'A') r.nm = 0;
+                else r.nm = (int32_t)raw;
             }
             p += sz;
-        } else if (ty == 'Z' || ty == 'H') {
+        } else if (sz == 0x80) {
             uint32_t len = 0;
             bool found = false;
             while (p + len < end) {
                 const uint8_t* q = p + len + lane;
-                uint32_t b = (q < end) ? *q : 0u;
-                uint32_t zb = __ballot_sync(FULL_MASK, b == 0);
+                const uint32_t b = (q < end) ? *q : 1u;
+                const uint32_t zb = __ballot_sync(FULL_MASK, b == 0);
                 if (zb) { len += __ffs(zb) - 1; found = true; break; }
                 len += 32;
             }
-            if (!found || p + len >= end) { bad_aux = true; break; }
-            if (t0 == 'S' && t1 == 'A' && !have_sa) {
-                have_sa = true;
-                sa_off = (uint32_t)(p - p_org) + p_rel;
-                sa_len = len;
+            if (!found) { r.bad = 1; break; }
+            if (t0 == 'S' && t1 == 'A' && !r.have_sa) {
+                r.have_sa = 1;
+                r.sa_off = (uint32_t)(p - p_org) + p_rel;
+                r.sa_len = len;
             }
             p += len + 1;
-        } else if (ty == 'B') {
-            if (p + 5 > end) { bad_aux = true; break; }
+        } else {
+            if (p + 5 > end) { r.bad = 1; break; }
             const uint32_t sub = p[0];
             uint32_t cnt = 0;
             for (uint32_t b = 0; b < 4; b++) cnt |= (uint32_t)p[1 + b] << (8 * b);
-            uint32_t es = (sub == 'c' || sub == 'C') ? 1 : (sub == 's' || sub == 'S') ? 2 :
-                          (sub == 'i' || sub == 'I' || sub == 'f') ? 4 : 0;
-            if (!es || (uint64_t)cnt * es > (uint64_t)(end - p)) { bad_aux = true; break; }
+            const uint32_t es = sub < 128 ? c_aux_size[sub] : 0u;
+            if (es == 0 || es >= 0x80 || (uint64_t)cnt * es > (uint64_t)(end - p - 5)) { r.bad = 1; break; }
             p += 5 + (size_t)cnt * es;
-        } else {
-            bad_aux = true;
-            break;
         }
     }
-    if (p > end) bad_aux = true;
-    return bad_aux;
+    if (p > end) r.bad = 1;
+    return r;
 }
 
-// Per-warp control block in shared memory.  Lane 0 is the warp's producer: it owns the generator state,
-// pulls record indices from the global queue, issues the bulk copies and publishes one descriptor per
-// stage; all lanes consume.  Keeping this state out of registers is what lets 32 warps live on an SM.
-struct SegDesc { uint32_t flags_len, gbeg, rec, pad; };                 // flags | len << 8
-struct WarpCtl {
-    SegDesc desc[SC_NST];
-    // generator (lane 0 only)
-    uint64_t g_base;
-    uint32_t g_rec, g_cov, g_r1_end, g_a0, g_a1, g_state;                // state | auxseg << 8 | auxglob << 9
-    // record constants (written when the first segment is decoded)
-    uint32_t pos, l_seq, n_cig, c0, s1, rec_size, unmapped, rec_bad;
-};
-constexpr size_t SC_SMEM_TOTAL = (size_t)SC_WARPS * SC_NST * SC_SB + (size_t)SC_WARPS * SC_NST * 8 +
-                                 (size_t)SC_WARPS * sizeof(WarpCtl);
+// Per-warp control block in shared memory (addressed by shared-window offsets).  Lane 0 is the warp's producer:
+// it owns the generator state, pulls record indices from the global queue, issues the bulk copies and publishes
+// one descriptor per stage; all lanes consume.  Keeping this state out of registers is what lets 32 warps live
+// on an SM.
+constexpr uint32_t WC_DESC = 0;                          // SC_NST x {flags | len << 8, gbeg, rec, pad}
+constexpr uint32_t WC_GEN = WC_DESC + 16 * SC_NST;       // {base lo, base hi, rec, cov} {r1_end, a0, a1, state}
+constexpr uint32_t WC_REC = WC_GEN + 32;                 // {pos, l_seq, n_cig, c0} {s1, rec_size, unmapped, -}
+constexpr uint32_t WC_BYTES = WC_REC + 32;
+constexpr size_t SC_RING_BYTES = (size_t)SC_WARPS * SC_NST * SC_SB;
+constexpr size_t SC_BAR_BYTES = ((size_t)SC_WARPS * SC_NST * 8 + 15) & ~(size_t)15;
+constexpr size_t SC_SMEM_TOTAL = SC_RING_BYTES + SC_BAR_BYTES + (size_t)SC_WARPS * WC_BYTES;
 
 enum { G_NEW = 0, G_R1 = 1, G_AUX = 2, G_DONE = 3 };
 
 // Lane 0: produce the next segment of the warp's record stream into stage s.
 // `ahead` = record index fetched from the queue one grab early (the atomic's latency is off the critical path).
-__device__ __noinline__ void gen_next(WarpCtl* ctl, int s, uint32_t bar, uint32_t dst, const uint8_t* __restrict__ recs,
-                                         const uint64_t* __restrict__ off, uint32_t n, unsigned int* queue,
-                                         uint32_t& ahead) {
-    uint32_t st = ctl->g_state;
+__device__ __noinline__ uint32_t gen_next(uint32_t ctl, uint32_t s, uint32_t bar, uint32_t dst, const uint8_t* __restrict__ recs,
+                                          const uint64_t* __restrict__ off, uint32_t n, unsigned int* queue, uint32_t ahead) {
+    uint4 g0 = lds128(ctl + WC_GEN), g1 = lds128(ctl + WC_GEN + 16);     // base lo/hi, rec, cov | r1_end, a0, a1, state
+    const uint32_t st = g1.w;
     uint32_t flags = 0, beg = 0, end = 0;
     if ((st & 255u) == G_R1) {
-        const uint32_t cov = ctl->g_cov, r1_end = ctl->g_r1_end;
-        beg = cov - 16;
-        end = min(cov + (uint32_t)SC_CH, r1_end);
-        ctl->g_cov = end;
+        beg = g0.w - 16;
+        end = min(g0.w + (uint32_t)SC_CH, g1.x);
+        g0.w = end;
         flags = SF_VALID;
-        if (end >= r1_end) {
-            if (st & 256u) ctl->g_state = (st & ~255u) | G_AUX;
-            else { flags |= SF_LAST | ((st & 512u) ? SF_AUXG : 0u); ctl->g_state = G_NEW; }
+        if (end >= g1.x) {
+            if (st & 256u) g1.w = (st & ~255u) | G_AUX;
+            else { flags |= SF_LAST | ((st & 512u) ? SF_AUXG : 0u); g1.w = G_NEW; }
         }
     } else if ((st & 255u) == G_AUX) {
-        beg = ctl->g_a0; end = ctl->g_a1;
+        beg = g1.y; end = g1.z;
         flags = SF_VALID | SF_LAST | SF_AUX;
-        ctl->g_state = G_NEW;
+        g1.w = G_NEW;
     } else if ((st & 255u) == G_NEW) {
         const uint32_t idx = ahead;
         if (idx >= n) {
-            ctl->g_state = G_DONE;
+            g1.w = G_DONE;
         } else {
             ahead = atomicAdd(queue, 1u);
             const uint64_t o0 = __ldg(off + idx), o1 = __ldg(off + idx + 1);
@@ -212,8 +300,7 @@ __device__ __noinline__ void gen_next(WarpCtl* ctl, int s, uint32_t bar, uint32_
             const uint64_t seq_end = 36ull + (w3 & 255u) + 4ull * (w4 & 0xffffu) + ((uint64_t)l_seq + 1) / 2;
             const uint64_t aux_beg = seq_end + l_seq, rec_size = 4ull + block_size;
             const uint32_t e0 = min((uint32_t)SC_CH, len16);
-            ctl->g_base = o0;
-            ctl->g_rec = idx;
+            g0.x = (uint32_t)o0; g0.y = (uint32_t)(o0 >> 32); g0.z = idx;
             flags = SF_VALID | SF_FIRST;
             end = e0;
             if (aux_beg > rec_size || rec_size > len16) {
@@ -226,7 +313,7 @@ __device__ __noinline__ void gen_next(WarpCtl* ctl, int s, uint32_t bar, uint32_
                 const bool has_aux = aux_beg < rec_size;
                 const bool auxseg = has_aux && (a1 - a0) <= (uint32_t)SC_SB;
                 const bool auxglob = has_aux && !auxseg;
-                ctl->g_r1_end = r1_end; ctl->g_cov = e0; ctl->g_a0 = a0; ctl->g_a1 = a1;
+                g1.x = r1_end; g0.w = e0; g1.y = a0; g1.z = a1;
                 uint32_t ns = G_NEW;
                 if (e0 >= r1_end) {
                     if (auxseg) ns = G_AUX;
@@ -234,20 +321,18 @@ __device__ __noinline__ void gen_next(WarpCtl* ctl, int s, uint32_t bar, uint32_
                 } else {
                     ns = G_R1;
                 }
-                ctl->g_state = ns | (auxseg ? 256u : 0u) | (auxglob ? 512u : 0u);
+                g1.w = ns | (auxseg ? 256u : 0u) | (auxglob ? 512u : 0u);
             }
         }
     }
-    SegDesc d;
-    d.flags_len = flags | ((end - beg) << 8);
-    d.gbeg = beg;
-    d.rec = ctl->g_rec;
-    d.pad = 0;
-    *reinterpret_cast<uint4*>(&ctl->desc[s]) = *reinterpret_cast<const uint4*>(&d);
+    sts128(ctl + WC_GEN, g0);
+    sts128(ctl + WC_GEN + 16, g1);
+    sts128(ctl + WC_DESC + 16 * s, make_uint4(flags | ((end - beg) << 8), beg, g0.z, 0));
     if (flags & SF_VALID) {
         mbar_expect_tx(bar, end - beg);
-        bulk_g2s(dst, recs + ctl->g_base + beg, end - beg, bar);
+        bulk_g2s(dst, recs + (((uint64_t)g0.y << 32) | g0.x) + beg, end - beg, bar);
     }
+    return ahead;
 }
 
 __global__ void __launch_bounds__(SC_WARPS * 32, 4)
@@ -257,21 +342,21 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
     const uint32_t lane = lane_id();
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    uint8_t* const ring = smem + (size_t)warp * SC_NST * SC_SB;
-    const uint32_t bar0 = smem_u32(smem + (size_t)SC_WARPS * SC_NST * SC_SB) + warp * SC_NST * 8;
-    WarpCtl* const ctl = reinterpret_cast<WarpCtl*>(smem + (size_t)SC_WARPS * SC_NST * SC_SB + (size_t)SC_WARPS * SC_NST * 8) + warp;
+    const uint32_t smem0 = smem_u32(smem);
+    const uint32_t ring = smem0 + warp * (SC_NST * SC_SB);
+    const uint32_t bar0 = smem0 + (uint32_t)SC_RING_BYTES + warp * (SC_NST * 8);
+    const uint32_t ctl = smem0 + (uint32_t)(SC_RING_BYTES + SC_BAR_BYTES) + warp * WC_BYTES;
     uint32_t ahead = 0;          // lane 0: next record index, fetched one grab early
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < SC_NST; s++) mbar_init(bar0 + 8 * s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        ctl->g_state = G_NEW;
-        ctl->g_rec = 0;
-        ctl->g_base = 0;
+        sts128(ctl + WC_GEN, make_uint4(0, 0, 0, 0));
+        sts128(ctl + WC_GEN + 16, make_uint4(0, 0, 0, G_NEW));
         ahead = atomicAdd(queue, 1u);
 #pragma unroll 1
-        for (int s = 0; s < SC_NST; s++)
-            gen_next(ctl, s, bar0 + 8 * s, smem_u32(ring + (size_t)s * SC_SB), recs, off, n, queue, ahead);
+        for (uint32_t s = 0; s < SC_NST; s++)
+            ahead = gen_next(ctl, s, bar0 + 8 * s, ring + s * SC_SB, recs, off, n, queue, ahead);
     }
     __syncwarp();
 
@@ -283,265 +368,273 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
     int32_t first_start = -1;
     uint32_t gcount = 0;
     uint32_t parity = 0;
+    const uint32_t sel_or = 0x6660u;
 
-    {
 #pragma unroll 1
-        for (int s = 0;; s = (s + 1 == SC_NST) ? 0 : s + 1) {
-            const uint4 dq = *reinterpret_cast<const uint4*>(&ctl->desc[s]);
-            const uint32_t fl = dq.x & 255u;
-            if (!(fl & SF_VALID)) break;
-            mbar_wait(bar0 + 8 * s, (parity >> s) & 1u);
-            parity ^= 1u << s;
-            const uint8_t* buf = ring + (size_t)s * SC_SB;
-            const uint32_t gbeg = dq.y, seg_end = gbeg + (dq.x >> 8);
-            const uint32_t rec = dq.z;
+    for (uint32_t s = 0;; s = (s + 1 == SC_NST) ? 0 : s + 1) {
+        const uint4 dq = lds128(ctl + WC_DESC + 16 * s);
+        const uint32_t fl = dq.x & 255u;
+        if (!(fl & SF_VALID)) break;
+        mbar_wait(bar0 + 8 * s, (parity >> s) & 1u);
+        parity ^= 1u << s;
+        const uint32_t buf = ring + s * SC_SB;
+        const uint32_t gbeg = dq.y, seg_end = gbeg + (dq.x >> 8);
+        const uint32_t rec = dq.z;
 
-            if (fl & SF_FIRST) {
-                const uint32_t cw = lane < 9 ? lds32(buf + 4 * lane) : 0u;
-                const uint32_t block_size = __shfl_sync(FULL_MASK, cw, 0);
-                const uint32_t tid = __shfl_sync(FULL_MASK, cw, 1);
-                const uint32_t pos_ = __shfl_sync(FULL_MASK, cw, 2);
-                const uint32_t w3 = __shfl_sync(FULL_MASK, cw, 3), w4 = __shfl_sync(FULL_MASK, cw, 4);
-                uint32_t l_seq = __shfl_sync(FULL_MASK, cw, 5);
-                const uint32_t l_name = w3 & 255u;
-                uint32_t n_cig = w4 & 0xffffu;
-                const uint32_t flag = w4 >> 16;
-                const bool rec_bad = (fl & SF_BAD) != 0;
-                const uint32_t c0 = 36 + l_name;
-                if (rec_bad) { n_cig = 0; l_seq = 0; }
-                const uint32_t s0 = c0 + 4 * n_cig;
-                cig_next = 0; seq_next = s0;
-                msum = dnsum = ishsum = bad = 0;
-                carried = 0; seen_m = false; first_start = -1; gcount = 0;
-                // read-name hash
-                const uint32_t nl = (l_name && !rec_bad) ? l_name - 1 : 0;
-                uint64_t h1 = 0, h2 = 0;
-                for (uint32_t i = lane; i < nl; i += 32) {
-                    const uint32_t b = buf[36 + i];
-                    h1 += hterm1(i, b);
-                    h2 += hterm2(i, b);
-                }
-                h1 = warp_sum_u64(h1) + mix64(nl);
-                h2 = warp_sum_u64(h2) + mix64(nl ^ 0xABCDull);
-                if (lane == 0) {
-                    ctl->pos = pos_; ctl->l_seq = l_seq; ctl->n_cig = n_cig; ctl->c0 = c0;
-                    ctl->s1 = s0 + ((l_seq + 1) >> 1); ctl->rec_size = 4 + block_size;
-                    ctl->unmapped = (flag & 4u); ctl->rec_bad = rec_bad ? 1u : 0u;
-                    o.tid[rec] = (int32_t)tid;
-                    o.pos[rec] = (int32_t)pos_;
-                    o.flag_mapq[rec] = flag | (((w3 >> 8) & 255u) << 16);
-                    o.lseq[rec] = l_seq;
-                    o.ncig[rec] = n_cig;
-                    o.name_lo[rec] = h1;
-                    o.name_hi[rec] = h2;
-                    o.sa_off[rec] = 0; o.sa_len[rec] = 0; o.nm[rec] = 0;     // overwritten by the aux walk
-                    if (rec_bad) atomicAdd(&status[1], 1);
-                }
-                __syncwarp();
+        if (fl & SF_FIRST) {
+            const uint32_t cw = lane < 9 ? lds32(buf + 4 * lane) : 0u;
+            const uint32_t block_size = __shfl_sync(FULL_MASK, cw, 0);
+            const uint32_t tid = __shfl_sync(FULL_MASK, cw, 1);
+            const uint32_t pos_ = __shfl_sync(FULL_MASK, cw, 2);
+            const uint32_t w3 = __shfl_sync(FULL_MASK, cw, 3), w4 = __shfl_sync(FULL_MASK, cw, 4);
+            uint32_t l_seq = __shfl_sync(FULL_MASK, cw, 5);
+            const uint32_t l_name = w3 & 255u;
+            uint32_t n_cig = w4 & 0xffffu;
+            const uint32_t flag = w4 >> 16;
+            const bool rec_bad = (fl & SF_BAD) != 0;
+            const uint32_t c0 = 36 + l_name;
+            if (rec_bad) { n_cig = 0; l_seq = 0; }
+            const uint32_t s0 = c0 + 4 * n_cig;
+            cig_next = 0; seq_next = s0;
+            msum = dnsum = ishsum = bad = 0;
+            carried = 0; seen_m = false; first_start = -1; gcount = 0;
+            // read-name hash
+            const uint32_t nl = (l_name && !rec_bad) ? l_name - 1 : 0;
+            uint64_t h1 = 0, h2 = 0;
+            for (uint32_t i = lane; i < nl; i += 32) {
+                const uint32_t b = lds8(buf + 36 + i);
+                h1 += hterm1(i, b);
+                h2 += hterm2(i, b);
             }
-            const uint32_t n_cig = ctl->n_cig, c0 = ctl->c0;
-            const int32_t pos = (int32_t)ctl->pos;
-
-            // ---- CIGAR ops fully inside this segment -----------------------------------------------------
-            if (cig_next < n_cig && seg_end >= c0 + 4) {
-                const uint32_t i_hi = min(n_cig, (seg_end - c0) >> 2);
-                if (i_hi > cig_next) {
-                    const uint32_t sh = (c0 & 3u) * 8u;
-                    const int32_t wc = ((int32_t)(c0 & ~3u) - (int32_t)gbeg) >> 2;   // word of op 0 in buf (may be < 0)
-                    const int32_t w_first = wc + (int32_t)cig_next;
-                    const int32_t w_end = wc + (int32_t)i_hi;                          // first word slot past the last op
-                    for (int32_t w0 = w_first & ~3; w0 < w_end; w0 += 128) {
-                        const int32_t mw = w0 + 4 * (int32_t)lane;
-                        uint4 q = make_uint4(0, 0, 0, 0);
-                        if (mw * 4 + 16 <= SC_SB) q = lds128(buf + 4 * mw);
-                        uint32_t nx = __shfl_down_sync(FULL_MASK, q.x, 1);
-                        if (lane == 31) nx = (mw * 4 + 20 <= SC_SB) ? lds32(buf + 4 * mw + 16) : 0u;
-                        uint32_t v[4];
-                        v[0] = __funnelshift_r(q.x, q.y, sh);
-                        v[1] = __funnelshift_r(q.y, q.z, sh);
-                        v[2] = __funnelshift_r(q.z, q.w, sh);
-                        v[3] = __funnelshift_r(q.w, nx, sh);
-                        if (w0 < w_first || w0 + 128 > w_end) {    // edge window: neutralise slots outside [cig_next, i_hi)
-#pragma unroll
-                            for (int j = 0; j < 4; j++)
-                                if (mw + j < w_first || mw + j >= w_end) v[j] = 6u;   // 0P: consumes nothing
-                        }
-                        uint32_t cls[4], m_it = 0, dn_it = 0, dn_after = 0;
-                        bool lane_m = false;
-#pragma unroll
-                        for (int j = 0; j < 4; j++) {
-                            cls[j] = cigar_class(v[j]);
-                            const uint32_t len = v[j] >> 4;
-                            if (cls_m(cls[j])) { m_it += len; dn_after = 0; lane_m = true; }
-                            if (cls_dn(cls[j])) { dn_it += len; dn_after += len; }
-                            if (cls_ish(cls[j])) ishsum += len;
-                        }
-                        const uint32_t dn_tot = __reduce_add_sync(FULL_MASK, dn_it);
-                        const uint32_t mball = __ballot_sync(FULL_MASK, lane_m);
-                        // exact gap events: only when the D/N bases of this window (+ the open gap) could exceed the cut
-                        if (mball && (int64_t)carried + dn_tot > (int64_t)min_del_len) {
-                            const uint32_t run_r = __reduce_add_sync(FULL_MASK, msum + dnsum);
-                            const int32_t base_ref = pos + (int32_t)run_r;
-                            const int32_t lane_tot = (int32_t)(m_it + dn_it);
-                            const int32_t incl = warp_incl_sum_i32(lane_tot);
-                            int32_t cur = base_ref + incl - lane_tot;
-                            int32_t st[4], last_m_end = -1;
-#pragma unroll
-                            for (int j = 0; j < 4; j++) {
-                                st[j] = cur;
-                                if (cls_m(cls[j]) || cls_dn(cls[j])) cur += (int32_t)(v[j] >> 4);
-                                if (cls_m(cls[j])) last_m_end = cur;
-                            }
-                            const uint32_t before = mball & lt_mask;
-                            const int src = before ? 31 - __clz(before) : 0;
-                            int32_t prev = __shfl_sync(FULL_MASK, last_m_end, src);
-                            bool have_prev = before != 0;
-                            if (!have_prev) { prev = base_ref - (int32_t)carried; have_prev = seen_m; }
-                            bool evj[4];
-                            int32_t evprev[4];
-                            uint32_t nbefore = 0, ntot = 0;
-#pragma unroll
-                            for (int j = 0; j < 4; j++) {
-                                evj[j] = false; evprev[j] = 0;
-                                if (cls_m(cls[j])) {
-                                    evj[j] = have_prev && (st[j] - prev) > min_del_len;
-                                    evprev[j] = prev;
-                                    prev = st[j] + (int32_t)(v[j] >> 4);
-                                    have_prev = true;
-                                }
-                                const uint32_t b = __ballot_sync(FULL_MASK, evj[j]);
-                                nbefore += __popc(b & lt_mask);
-                                ntot += __popc(b);
-                            }
-                            if (ntot) {
-                                unsigned long long slot0 = 0;
-                                if (lane == 0) slot0 = atomicAdd(ev.counter, (unsigned long long)ntot);
-                                slot0 = __shfl_sync(FULL_MASK, slot0, 0);
-                                uint32_t r = nbefore;
-#pragma unroll
-                                for (int j = 0; j < 4; j++) {
-                                    if (evj[j]) {
-                                        const unsigned long long sl = slot0 + r;
-                                        if ((int64_t)sl < ev.capacity) {
-                                            ev.rec[sl] = rec;
-                                            ev.k[sl] = gcount + r;
-                                            ev.next_start[sl] = st[j];
-                                            ev.prev_end[sl] = evprev[j];
-                                        }
-                                        r++;
-                                    }
-                                }
-                                gcount += ntot;
-                            }
-                        }
-                        if (mball) {
-                            if (!seen_m) {      // first aligned block of the record: D/N bases in front of it
-                                const int fl_ = __ffs(mball) - 1;
-                                uint32_t lead = 0;
-                                if ((int)lane < fl_) lead = dn_it;
-                                else if ((int)lane == fl_) {
-                                    bool hit = false;
-#pragma unroll
-                                    for (int j = 0; j < 4; j++) {
-                                        if (cls_m(cls[j])) hit = true;
-                                        if (!hit && cls_dn(cls[j])) lead += v[j] >> 4;
-                                    }
-                                }
-                                lead = __reduce_add_sync(FULL_MASK, lead);
-                                first_start = pos + (int32_t)(carried + lead);
-                                seen_m = true;
-                            }
-                            const int ll = 31 - __clz(mball);
-                            const uint32_t tr = ((int)lane > ll) ? dn_it : ((int)lane == ll ? dn_after : 0u);
-                            carried = __reduce_add_sync(FULL_MASK, tr);
-                        } else {
-                            carried += dn_tot;
-                        }
-                        msum += m_it;
-                        dnsum += dn_it;
-                    }
-                    cig_next = i_hi;
-                }
+            h1 = warp_sum_u64(h1) + mix64(nl);
+            h2 = warp_sum_u64(h2) + mix64(nl ^ 0xABCDull);
+            if (lane == 0) {
+                sts128(ctl + WC_REC, make_uint4(pos_, l_seq, n_cig, c0));
+                sts128(ctl + WC_REC + 16, make_uint4(s0 + ((l_seq + 1) >> 1), 4 + block_size, flag & 4u, 0));
+                o.tid[rec] = (int32_t)tid;
+                o.pos[rec] = (int32_t)pos_;
+                o.flag_mapq[rec] = flag | (((w3 >> 8) & 255u) << 16);
+                o.lseq[rec] = l_seq;
+                o.ncig[rec] = n_cig;
+                o.name_lo[rec] = h1;
+                o.name_hi[rec] = h2;
+                o.sa_off[rec] = 0; o.sa_len[rec] = 0; o.nm[rec] = 0;     // overwritten by the aux walk
+                if (rec_bad) atomicAdd(&status[1], 1);
             }
-
-            // ---- SEQ bytes inside this segment ---------------------------------------------------------------
-            {
-                const uint32_t s1 = ctl->s1;
-                const uint32_t b_hi = min(s1, seg_end);
-                if (b_hi > seq_next) {
-                    const uint32_t o_lo = seq_next - gbeg, o_hi = b_hi - gbeg;
-                    const int32_t pad_o = ((ctl->l_seq & 1u) && b_hi == s1) ? (int32_t)(o_hi - 1) : -1;
-                    for (uint32_t oo = (o_lo & ~15u) + 16u * lane; oo < o_hi; oo += 512u) {
-                        const uint4 q = lds128(buf + oo);
-                        uint32_t w[4] = {q.x, q.y, q.z, q.w};
-                        if (oo < o_lo || oo + 16 > o_hi || (pad_o >> 4) == (int32_t)(oo >> 4)) {
-#pragma unroll
-                            for (int k = 0; k < 4; k++) {
-                                const int32_t wb = (int32_t)oo + 4 * k;
-                                const int32_t lo = max(0, min(4, (int32_t)o_lo - wb));
-                                const int32_t hi = max(0, min(4, (int32_t)o_hi - wb));
-                                const uint32_t m = hi > lo ? ((0xFFFFFFFFu >> (8 * (4 - hi))) & (0xFFFFFFFFu << (8 * lo))) : 0u;
-                                w[k] = (w[k] & m) | (0x11111111u & ~m);
-                                if (pad_o >= wb && pad_o < wb + 4) {     // odd l_seq: the last low nibble is padding
-                                    const uint32_t shp = (uint32_t)(pad_o - wb) * 8u;
-                                    w[k] = (w[k] & ~(0xFu << shp)) | (0x1u << shp);
-                                }
-                            }
-                        }
-                        const uint32_t acc = not_onehot_test(w[0]) | not_onehot_test(w[1]) | not_onehot_test(w[2]) |
-                                             not_onehot_test(w[3]);
-                        if (acc) {
-                            bad += 32u - __popc(onehot_nibbles(w[0])) - __popc(onehot_nibbles(w[1])) -
-                                   __popc(onehot_nibbles(w[2])) - __popc(onehot_nibbles(w[3]));
-                        }
-                    }
-                    seq_next = b_hi;
-                }
-            }
-
-            // ---- aux block -------------------------------------------------------------------------------------
-            if (fl & (SF_AUX | SF_AUXG)) {
-                const uint32_t rec_size = ctl->rec_size, aux_beg = ctl->s1 + ctl->l_seq;
-                uint32_t sa_off, sa_len;
-                int32_t nm;
-                bool have_sa, bad_aux;
-                if (fl & SF_AUX) {
-                    bad_aux = aux_walk(buf + (aux_beg - gbeg), buf + (rec_size - gbeg), aux_beg, lane, sa_off, sa_len, nm, have_sa);
-                } else {                              // aux longer than a stage: walk it in global memory
-                    const uint8_t* r0 = recs + __ldg(off + rec);
-                    bad_aux = aux_walk(r0 + aux_beg, r0 + rec_size, aux_beg, lane, sa_off, sa_len, nm, have_sa);
-                }
-                if (lane == 0) {
-                    if (bad_aux) atomicAdd(&status[0], 1);
-                    o.sa_off[rec] = have_sa ? sa_off : 0u;
-                    o.sa_len[rec] = sa_len;
-                    o.nm[rec] = nm;
-                }
-            }
-            if (fl & SF_LAST) {
-                const uint32_t m_tot = __reduce_add_sync(FULL_MASK, msum);
-                const uint32_t dn_all = __reduce_add_sync(FULL_MASK, dnsum);
-                const uint32_t ish_tot = __reduce_add_sync(FULL_MASK, ishsum);
-                const uint32_t bad_tot = __reduce_add_sync(FULL_MASK, bad);
-                int32_t reflen = (int32_t)(m_tot + dn_all);
-                const int32_t lbe = seen_m ? pos + reflen - (int32_t)carried : -1;
-                if (ctl->unmapped || n_cig == 0) reflen = 0;
-                const int32_t endpos = pos + (reflen > 0 ? reflen : 1);   // htslib bam_endpos
-                if (lane == 0) {
-                    o.endpos[rec] = endpos;
-                    o.fbs[rec] = first_start;
-                    o.lbe[rec] = lbe;
-                    o.infer[rec] = m_tot + ish_tot;
-                    o.mbases[rec] = m_tot;
-                    o.nonacgt[rec] = bad_tot;
-                    o.ngap[rec] = gcount;
-                }
-            }
-            __syncwarp();          // every lane is done with the stage before the copy engine overwrites it
-            if (lane == 0)
-                gen_next(ctl, s, bar0 + 8 * s, smem_u32(ring + (size_t)s * SC_SB), recs, off, n, queue, ahead);
             __syncwarp();
         }
+        const uint4 rc0 = lds128(ctl + WC_REC);           // pos, l_seq, n_cig, c0
+        const uint4 rc1 = lds128(ctl + WC_REC + 16);      // s1, rec_size, unmapped
+        const int32_t pos = (int32_t)rc0.x;
+        const uint32_t n_cig = rc0.z, c0 = rc0.w;
+
+        // ---- CIGAR ops fully inside this segment ---------------------------------------------------------
+        if (cig_next < n_cig && seg_end >= c0 + 4) {
+            const uint32_t i_hi = min(n_cig, (seg_end - c0) >> 2);
+            if (i_hi > cig_next) {
+                const uint32_t sh = (c0 & 3u) * 8u;
+                const int32_t wc = ((int32_t)(c0 & ~3u) - (int32_t)gbeg) >> 2;   // word of op 0 in buf (may be < 0)
+                const int32_t w_first = wc + (int32_t)cig_next;
+                const int32_t w_end = wc + (int32_t)i_hi;                          // first word slot past the last op
+#pragma unroll 1
+                for (int32_t w0 = w_first & ~3; w0 < w_end; w0 += 128) {
+                    const int32_t mw = w0 + 4 * (int32_t)lane;
+                    uint4 q = make_uint4(0, 0, 0, 0);
+                    if (mw * 4 + 16 <= SC_SB) q = lds128(buf + 4 * mw);
+                    uint32_t nx = __shfl_down_sync(FULL_MASK, q.x, 1);
+                    if (lane == 31) nx = (mw * 4 + 20 <= SC_SB) ? lds32(buf + 4 * mw + 16) : 0u;
+                    uint32_t v[4];
+                    v[0] = __funnelshift_r(q.x, q.y, sh);
+                    v[1] = __funnelshift_r(q.y, q.z, sh);
+                    v[2] = __funnelshift_r(q.z, q.w, sh);
+                    v[3] = __funnelshift_r(q.w, nx, sh);
+                    if (w0 < w_first || w0 + 128 > w_end) {    // edge window: neutralise slots outside [cig_next, i_hi)
+#pragma unroll
+                        for (int j = 0; j < 4; j++)
+                            if ((uint32_t)(mw + j - w_first) >= (uint32_t)(w_end - w_first)) v[j] = 6u;   // 0P: consumes nothing
+                    }
+                    uint32_t bm[4], bd[4], len[4], m_it = 0, dn_it = 0, dn_after = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const uint32_t sel = (v[j] & 7u) | sel_or;
+                        bm[j] = prmt(CIG_TM_LO, CIG_TM_HI, sel);
+                        bd[j] = prmt(CIG_TD_LO, CIG_TD_HI, sel);
+                        const uint32_t bq = prmt(CIG_TQ_LO, CIG_TQ_HI, sel);
+                        len[j] = v[j] >> 4;
+                        m_it = bm[j] * len[j] + m_it;
+                        dn_it = bd[j] * len[j] + dn_it;
+                        ishsum = bq * len[j] + ishsum;
+                        dn_after = bd[j] * len[j] + dn_after * (bm[j] ^ 1u);
+                    }
+                    const bool lane_m = (bm[0] | bm[1] | bm[2] | bm[3]) != 0;
+                    const uint32_t dn_tot = __reduce_add_sync(FULL_MASK, dn_it);
+                    const uint32_t mball = __ballot_sync(FULL_MASK, lane_m);
+                    // exact gap events: only when the D/N bases of this window (+ the open gap) could exceed the cut
+                    if (mball && (min_del_len < 0 || carried + dn_tot > (uint32_t)min_del_len)) {
+                        const uint32_t run_r = __reduce_add_sync(FULL_MASK, msum + dnsum);
+                        const int32_t base_ref = pos + (int32_t)run_r;
+                        const int32_t lane_tot = (int32_t)(m_it + dn_it);
+                        const int32_t incl = warp_incl_sum_i32(lane_tot);
+                        int32_t cur = base_ref + incl - lane_tot;
+                        int32_t st[4], last_m_end = -1;
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            st[j] = cur;
+                            cur += (int32_t)((bm[j] | bd[j]) * len[j]);
+                            if (bm[j]) last_m_end = cur;
+                        }
+                        const uint32_t before = mball & lt_mask;
+                        const int src = before ? 31 - __clz(before) : 0;
+                        int32_t prev = __shfl_sync(FULL_MASK, last_m_end, src);
+                        bool have_prev = before != 0;
+                        if (!have_prev) { prev = base_ref - (int32_t)carried; have_prev = seen_m; }
+                        uint32_t evmask = 0, nbefore = 0, ntot = 0;
+                        int32_t evprev[4];
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            evprev[j] = prev;
+                            bool e = false;
+                            if (bm[j]) {
+                                e = have_prev && (st[j] - prev) > min_del_len;
+                                prev = st[j] + (int32_t)len[j];
+                                have_prev = true;
+                            }
+                            if (e) evmask |= 1u << j;
+                            const uint32_t b = __ballot_sync(FULL_MASK, e);
+                            nbefore += __popc(b & lt_mask);
+                            ntot += __popc(b);
+                        }
+                        if (ntot) {
+                            unsigned long long slot0 = 0;
+                            if (lane == 0) slot0 = atomicAdd(ev.counter, (unsigned long long)ntot);
+                            slot0 = __shfl_sync(FULL_MASK, slot0, 0);
+                            uint32_t r = nbefore;
+#pragma unroll
+                            for (int j = 0; j < 4; j++) {
+                                if (evmask & (1u << j)) {
+                                    const unsigned long long sl = slot0 + r;
+                                    if ((int64_t)sl < ev.capacity) {
+                                        ev.rec[sl] = rec;
+                                        ev.k[sl] = gcount + r;
+                                        ev.next_start[sl] = st[j];
+                                        ev.prev_end[sl] = evprev[j];
+                                    }
+                                    r++;
+                                }
+                            }
+                            gcount += ntot;
+                        }
+                    }
+                    if (mball) {
+                        if (!seen_m) {      // first aligned block of the record: D/N bases in front of it
+                            const int fl_ = __ffs(mball) - 1;
+                            uint32_t lead = 0;
+                            if ((int)lane < fl_) lead = dn_it;
+                            else if ((int)lane == fl_) {
+                                uint32_t open = 1;
+#pragma unroll
+                                for (int j = 0; j < 4; j++) {
+                                    open &= bm[j] ^ 1u;
+                                    lead += open * bd[j] * len[j];
+                                }
+                            }
+                            lead = __reduce_add_sync(FULL_MASK, lead);
+                            first_start = pos + (int32_t)(carried + lead);
+                            seen_m = true;
+                        }
+                        const int ll = 31 - __clz(mball);
+                        const uint32_t tr = ((int)lane > ll) ? dn_it : ((int)lane == ll ? dn_after : 0u);
+                        carried = __reduce_add_sync(FULL_MASK, tr);
+                    } else {
+                        carried += dn_tot;
+                    }
+                    msum += m_it;
+                    dnsum += dn_it;
+                }
+                cig_next = i_hi;
+            }
+        }
+
+        // ---- SEQ bytes inside this segment -------------------------------------------------------------------
+        {
+            const uint32_t s1 = rc1.x;
+            const uint32_t b_hi = min(s1, seg_end);
+            if (b_hi > seq_next) {
+                const uint32_t o_lo = seq_next - gbeg, o_hi = b_hi - gbeg;
+                // odd l_seq: the low nibble of the last SEQ byte is padding, kept out of the count
+                const uint32_t o_body_hi = ((rc0.y & 1u) && b_hi == s1) ? o_hi - 1 : o_hi;
+                const uint32_t a_lo = (o_lo + 15u) & ~15u, a_hi = o_body_hi & ~15u;     // whole 16-byte chunks
+                if (a_hi > a_lo) {
+#pragma unroll 1
+                    for (uint32_t oo = a_lo + 16u * lane; oo < a_hi; oo += 512u) {
+                        const uint4 q = lds128(buf + oo);
+                        const uint32_t acc = not_onehot_test(q.x) | not_onehot_test(q.y) | not_onehot_test(q.z) |
+                                             not_onehot_test(q.w);
+                        if (acc) {
+                            bad += 32u - __popc(onehot_nibbles(q.x)) - __popc(onehot_nibbles(q.y)) -
+                                   __popc(onehot_nibbles(q.z)) - __popc(onehot_nibbles(q.w));
+                        }
+                    }
+                }
+                // ragged head / tail (< 16 bytes each, or the whole range when it holds no full chunk): one byte per lane
+                {
+                    const uint32_t h_hi = a_hi > a_lo ? a_lo : o_body_hi;     // head = [o_lo, h_hi)
+                    uint32_t x = o_lo + lane;
+                    bool in = x < h_hi;
+                    if (!in && a_hi > a_lo) { x = a_hi + (lane - 16u); in = lane >= 16 && x < o_body_hi; }   // tail = [a_hi, o_body_hi)
+                    if (in) {
+                        const uint32_t b = lds8(buf + x);
+                        const uint32_t hi4 = b >> 4, lo4 = b & 15u;
+                        bad += (__popc(hi4) != 1) + (__popc(lo4) != 1);
+                    }
+                    if (o_body_hi != o_hi && lane == 0) {              // the last byte of an odd-length SEQ: high nibble only
+                        const uint32_t b = lds8(buf + o_hi - 1);
+                        bad += (__popc(b >> 4) != 1);
+                    }
+                }
+                seq_next = b_hi;
+            }
+        }
+
+        // ---- aux block -------------------------------------------------------------------------------------------
+        if (fl & (SF_AUX | SF_AUXG)) {
+            const uint32_t rec_size = rc1.y, aux_beg = rc1.x + rc0.y;
+            AuxOut a;
+            if (fl & SF_AUX) {
+                a = aux_walk_smem(buf + (aux_beg - gbeg), buf + (rec_size - gbeg), aux_beg, lane);
+            } else {                              // aux longer than a stage: walk it in global memory
+                const uint8_t* r0 = recs + __ldg(off + rec);
+                a = aux_walk_global(r0 + aux_beg, r0 + rec_size, aux_beg, lane);
+            }
+            if (lane == 0) {
+                if (a.bad) atomicAdd(&status[0], 1);
+                o.sa_off[rec] = a.have_sa ? a.sa_off : 0u;
+                o.sa_len[rec] = a.sa_len;
+                o.nm[rec] = a.nm;
+            }
+        }
+        if (fl & SF_LAST) {
+            const uint32_t m_tot = __reduce_add_sync(FULL_MASK, msum);
+            const uint32_t dn_all = __reduce_add_sync(FULL_MASK, dnsum);
+            const uint32_t ish_tot = __reduce_add_sync(FULL_MASK, ishsum);
+            const uint32_t bad_tot = __reduce_add_sync(FULL_MASK, bad);
+            int32_t reflen = (int32_t)(m_tot + dn_all);
+            const int32_t lbe = seen_m ? pos + reflen - (int32_t)carried : -1;
+            if (rc1.z || n_cig == 0) reflen = 0;
+            const int32_t endpos = pos + (reflen > 0 ? reflen : 1);   // htslib bam_endpos
+            if (lane == 0) {
+                o.endpos[rec] = endpos;
+                o.fbs[rec] = first_start;
+                o.lbe[rec] = lbe;
+                o.infer[rec] = m_tot + ish_tot;
+                o.mbases[rec] = m_tot;
+                o.nonacgt[rec] = bad_tot;
+                o.ngap[rec] = gcount;
+            }
+        }
+        __syncwarp();          // every lane is done with the stage before the copy engine overwrites it
+        if (lane == 0) ahead = gen_next(ctl, s, bar0 + 8 * s, buf, recs, off, n, queue, ahead);
+        __syncwarp();
     }
 }
 
