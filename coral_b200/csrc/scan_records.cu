@@ -130,6 +130,25 @@ __device__ __forceinline__ uint32_t not_onehot_test(uint32_t w) {
     return (w & t) | (t & ~w & 0x88888888u);
 }
 
+// Rare paths kept out of line so the compiler cannot if-convert them into the hot loops.
+__device__ __noinline__ uint32_t seq_bad_count(uint4 q) {     // non-ACGT nibbles among the 32 of one 16-byte chunk
+    return 32u - __popc(onehot_nibbles(q.x)) - __popc(onehot_nibbles(q.y)) - __popc(onehot_nibbles(q.z)) -
+           __popc(onehot_nibbles(q.w));
+}
+__device__ __noinline__ uint4 cigar_mask_edge(uint4 v, int32_t mw, int32_t w_first, int32_t w_end) {
+    const uint32_t span = (uint32_t)(w_end - w_first);       // slots outside [w_first, w_end) become 0P: consume nothing
+    if ((uint32_t)(mw - w_first) >= span) v.x = 6u;
+    if ((uint32_t)(mw + 1 - w_first) >= span) v.y = 6u;
+    if ((uint32_t)(mw + 2 - w_first) >= span) v.z = 6u;
+    if ((uint32_t)(mw + 3 - w_first) >= span) v.w = 6u;
+    return v;
+}
+__device__ __forceinline__ uint32_t redux_add_volatile(uint32_t x) {   // not speculated above its guard
+    uint32_t r;
+    asm volatile("redux.sync.add.u32 %0, %1, 0xffffffff;" : "=r"(r) : "r"(x));
+    return r;
+}
+
 // value-size class of an aux type byte: 1/2/4 = fixed size, 0x80 = NUL-terminated (Z, H), 0x81 = array (B), 0 = invalid
 __constant__ uint8_t c_aux_size[128] = {
     0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0,
@@ -256,20 +275,22 @@ __device__ __noinline__ AuxOut aux_walk_global(const uint8_t* p, const uint8_t* 
 // it owns the generator state, pulls record indices from the global queue, issues the bulk copies and publishes
 // one descriptor per stage; all lanes consume.  Keeping this state out of registers is what lets 32 warps live
 // on an SM.
-constexpr uint32_t WC_DESC = 0;                          // SC_NST x {flags | len << 8, gbeg, rec, pad}
-constexpr uint32_t WC_GEN = WC_DESC + 16 * SC_NST;       // {base lo, base hi, rec, cov} {r1_end, a0, a1, state}
+constexpr uint32_t WC_DESC = 0;                          // SC_NST x {flags | len << 8, gbeg, rec, stage address}
+constexpr uint32_t WC_BAR = WC_DESC + 16 * SC_NST;       // SC_NST mbarriers (8 B each)
+constexpr uint32_t WC_GEN = WC_BAR + ((8 * SC_NST + 15) & ~15);   // {base lo, base hi, rec, cov} {r1_end, a0, a1, state}
 constexpr uint32_t WC_REC = WC_GEN + 32;                 // {pos, l_seq, n_cig, c0} {s1, rec_size, unmapped, -}
 constexpr uint32_t WC_BYTES = WC_REC + 32;
 constexpr size_t SC_RING_BYTES = (size_t)SC_WARPS * SC_NST * SC_SB;
-constexpr size_t SC_BAR_BYTES = ((size_t)SC_WARPS * SC_NST * 8 + 15) & ~(size_t)15;
-constexpr size_t SC_SMEM_TOTAL = SC_RING_BYTES + SC_BAR_BYTES + (size_t)SC_WARPS * WC_BYTES;
+constexpr size_t SC_SMEM_TOTAL = SC_RING_BYTES + (size_t)SC_WARPS * WC_BYTES;
 
 enum { G_NEW = 0, G_R1 = 1, G_AUX = 2, G_DONE = 3 };
 
 // Lane 0: produce the next segment of the warp's record stream into stage s.
 // `ahead` = record index fetched from the queue one grab early (the atomic's latency is off the critical path).
-__device__ __noinline__ uint32_t gen_next(uint32_t ctl, uint32_t s, uint32_t bar, uint32_t dst, const uint8_t* __restrict__ recs,
+__device__ __noinline__ uint32_t gen_next(uint32_t ctl, uint32_t s, const uint8_t* __restrict__ recs,
                                           const uint64_t* __restrict__ off, uint32_t n, unsigned int* queue, uint32_t ahead) {
+    const uint32_t bar = ctl + WC_BAR + 8 * s;
+    const uint32_t dst = lds32(ctl + WC_DESC + 16 * s + 12);
     uint4 g0 = lds128(ctl + WC_GEN), g1 = lds128(ctl + WC_GEN + 16);     // base lo/hi, rec, cov | r1_end, a0, a1, state
     const uint32_t st = g1.w;
     uint32_t flags = 0, beg = 0, end = 0;
@@ -327,7 +348,7 @@ __device__ __noinline__ uint32_t gen_next(uint32_t ctl, uint32_t s, uint32_t bar
     }
     sts128(ctl + WC_GEN, g0);
     sts128(ctl + WC_GEN + 16, g1);
-    sts128(ctl + WC_DESC + 16 * s, make_uint4(flags | ((end - beg) << 8), beg, g0.z, 0));
+    sts128(ctl + WC_DESC + 16 * s, make_uint4(flags | ((end - beg) << 8), beg, g0.z, dst));
     if (flags & SF_VALID) {
         mbar_expect_tx(bar, end - beg);
         bulk_g2s(dst, recs + (((uint64_t)g0.y << 32) | g0.x) + beg, end - beg, bar);
@@ -343,20 +364,21 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
     const uint32_t smem0 = smem_u32(smem);
-    const uint32_t ring = smem0 + warp * (SC_NST * SC_SB);
-    const uint32_t bar0 = smem0 + (uint32_t)SC_RING_BYTES + warp * (SC_NST * 8);
-    const uint32_t ctl = smem0 + (uint32_t)(SC_RING_BYTES + SC_BAR_BYTES) + warp * WC_BYTES;
+    const uint32_t ctl = smem0 + (uint32_t)SC_RING_BYTES + warp * WC_BYTES;
     uint32_t ahead = 0;          // lane 0: next record index, fetched one grab early
     if (lane == 0) {
 #pragma unroll
-        for (int s = 0; s < SC_NST; s++) mbar_init(bar0 + 8 * s, 1);
+        for (int s = 0; s < SC_NST; s++) {
+            mbar_init(ctl + WC_BAR + 8 * s, 1);
+            sts32(ctl + WC_DESC + 16 * s + 12, smem0 + (warp * SC_NST + s) * SC_SB);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         sts128(ctl + WC_GEN, make_uint4(0, 0, 0, 0));
         sts128(ctl + WC_GEN + 16, make_uint4(0, 0, 0, G_NEW));
         ahead = atomicAdd(queue, 1u);
 #pragma unroll 1
         for (uint32_t s = 0; s < SC_NST; s++)
-            ahead = gen_next(ctl, s, bar0 + 8 * s, ring + s * SC_SB, recs, off, n, queue, ahead);
+            ahead = gen_next(ctl, s, recs, off, n, queue, ahead);
     }
     __syncwarp();
 
@@ -368,16 +390,17 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
     int32_t first_start = -1;
     uint32_t gcount = 0;
     uint32_t parity = 0;
-    const uint32_t sel_or = 0x6660u;
+    uint32_t sel_or;                                          // kept in a register so (v & 7) | sel_or is one LOP3
+    asm volatile("mov.u32 %0, 0x6660;" : "=r"(sel_or));
 
 #pragma unroll 1
     for (uint32_t s = 0;; s = (s + 1 == SC_NST) ? 0 : s + 1) {
         const uint4 dq = lds128(ctl + WC_DESC + 16 * s);
         const uint32_t fl = dq.x & 255u;
         if (!(fl & SF_VALID)) break;
-        mbar_wait(bar0 + 8 * s, (parity >> s) & 1u);
+        mbar_wait(ctl + WC_BAR + 8 * s, (parity >> s) & 1u);
         parity ^= 1u << s;
-        const uint32_t buf = ring + s * SC_SB;
+        const uint32_t buf = dq.w;
         const uint32_t gbeg = dq.y, seg_end = gbeg + (dq.x >> 8);
         const uint32_t rec = dq.z;
 
@@ -449,9 +472,8 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
                     v[2] = __funnelshift_r(q.z, q.w, sh);
                     v[3] = __funnelshift_r(q.w, nx, sh);
                     if (w0 < w_first || w0 + 128 > w_end) {    // edge window: neutralise slots outside [cig_next, i_hi)
-#pragma unroll
-                        for (int j = 0; j < 4; j++)
-                            if ((uint32_t)(mw + j - w_first) >= (uint32_t)(w_end - w_first)) v[j] = 6u;   // 0P: consumes nothing
+                        const uint4 mv = cigar_mask_edge(make_uint4(v[0], v[1], v[2], v[3]), mw, w_first, w_end);
+                        v[0] = mv.x; v[1] = mv.y; v[2] = mv.z; v[3] = mv.w;
                     }
                     uint32_t bm[4], bd[4], len[4], m_it = 0, dn_it = 0, dn_after = 0;
 #pragma unroll
@@ -471,7 +493,7 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
                     const uint32_t mball = __ballot_sync(FULL_MASK, lane_m);
                     // exact gap events: only when the D/N bases of this window (+ the open gap) could exceed the cut
                     if (mball && (min_del_len < 0 || carried + dn_tot > (uint32_t)min_del_len)) {
-                        const uint32_t run_r = __reduce_add_sync(FULL_MASK, msum + dnsum);
+                        const uint32_t run_r = redux_add_volatile(msum + dnsum);
                         const int32_t base_ref = pos + (int32_t)run_r;
                         const int32_t lane_tot = (int32_t)(m_it + dn_it);
                         const int32_t incl = warp_incl_sum_i32(lane_tot);
@@ -570,10 +592,7 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
                         const uint4 q = lds128(buf + oo);
                         const uint32_t acc = not_onehot_test(q.x) | not_onehot_test(q.y) | not_onehot_test(q.z) |
                                              not_onehot_test(q.w);
-                        if (acc) {
-                            bad += 32u - __popc(onehot_nibbles(q.x)) - __popc(onehot_nibbles(q.y)) -
-                                   __popc(onehot_nibbles(q.z)) - __popc(onehot_nibbles(q.w));
-                        }
+                        if (acc) bad += seq_bad_count(q);
                     }
                 }
                 // ragged head / tail (< 16 bytes each, or the whole range when it holds no full chunk): one byte per lane
@@ -633,7 +652,7 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
             }
         }
         __syncwarp();          // every lane is done with the stage before the copy engine overwrites it
-        if (lane == 0) ahead = gen_next(ctl, s, bar0 + 8 * s, buf, recs, off, n, queue, ahead);
+        if (lane == 0) ahead = gen_next(ctl, s, recs, off, n, queue, ahead);
         __syncwarp();
     }
 }
