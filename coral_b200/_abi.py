@@ -76,6 +76,7 @@ class BamFile(object):
         self.rec_ptr = ptr
         buf = (ctypes.c_uint8 * max(self.nbytes, 1)).from_address(ptr)
         self.rec = np.frombuffer(buf, dtype=np.uint8, count=self.nbytes)
+        self.rec_slack = 64            # coral_bam_read allocates 64 bytes past the last record (page-locked buffer)
         obuf = (ctypes.c_uint64 * (self.n_records + 1)).from_address(L.coral_bam_offsets(h))
         self.rec_off = np.frombuffer(obuf, dtype=np.uint64, count=self.n_records + 1)
 
@@ -140,14 +141,22 @@ class Context(object):
         rank = np.array([CHR_IDX.get(n, -1) for n in names], dtype=np.int32)
         self._check(self._L.coral_set_references(self._h, blob, len(names), _p(rank)))
 
-    def load_records(self, rec, rec_off, global_ordinal=None):
-        """rec: uint8 array (host) of framed records; rec_off: uint64[n+1]."""
+    def load_records(self, rec, rec_off, global_ordinal=None, placement="copy", slack=0):
+        """rec: uint8 array (host) of framed records; rec_off: uint64[n+1].
+        placement "copy": records are copied to HBM; "mapped": they stay in (page-locked) host memory and the
+        kernels read them in place over PCIe — `rec` must then extend >= 64 bytes past rec_off[-1] and stay alive."""
         rec = np.ascontiguousarray(rec, dtype=np.uint8)
         rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
         n = len(rec_off) - 1
         go = None if global_ordinal is None else np.ascontiguousarray(global_ordinal, dtype=np.uint64)
-        self._check(self._L.coral_load_records(self._h, _p(rec), ctypes.c_uint64(int(rec_off[-1]) if n >= 0 and len(rec_off) else 0),
-                                               _p(rec_off), ctypes.c_int64(n), _p(go), 0))
+        mode = {"copy": 0, "mapped": 2}[placement]
+        nbytes = int(rec_off[-1]) if n >= 0 and len(rec_off) else 0
+        if mode == 2:
+            if rec.nbytes + int(slack) < nbytes + 64:     # `slack`: bytes the caller guarantees behind the view
+                raise ValueError("mapped placement needs 64 bytes of slack after the last record")
+            self._keep = [rec]
+        self._check(self._L.coral_load_records(self._h, _p(rec), ctypes.c_uint64(nbytes), _p(rec_off), ctypes.c_int64(n),
+                                               _p(go), mode))
 
     def load_records_device(self, dev_ptr, nbytes, rec_off, global_ordinal=None):
         rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)

@@ -40,6 +40,7 @@ void coral_destroy(coral_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->host_registered) cudaHostUnregister(c->host_registered);
     DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status,
                      &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->s6, &c->s7, &c->cub_tmp,
                      &c->rt.tid, &c->rt.pos, &c->rt.endpos, &c->rt.flag_mapq, &c->rt.lseq, &c->rt.ncig, &c->rt.infer,
@@ -97,9 +98,32 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     }
     if (n > 0 && (offsets[n] & 15)) { c->err = "record offsets must be 16-byte aligned (including the end offset)"; return CORAL_E_ARG; }
     if (n >= ((int64_t)1 << 32) - 65536) { c->err = "more than 2^32 - 65536 records per ctx"; return CORAL_E_ARG; }
-    if (on_device) {
+    if (c->host_registered) {             // a previous CORAL_RECORDS_HOST_MAPPED load page-locked the caller's buffer
+        cudaHostUnregister(c->host_registered);
+        c->host_registered = nullptr;
+    }
+    if (on_device == CORAL_RECORDS_DEVICE) {
         if (reinterpret_cast<uintptr_t>(recs) & 15) { c->err = "device record buffer must be 16-byte aligned"; return CORAL_E_ARG; }
         c->d_recs = recs;
+    } else if (on_device == CORAL_RECORDS_HOST_MAPPED) {
+        // Records stay in page-locked host memory; every kernel reads them in place over PCIe (the scan only
+        // fetches the fields it needs, so QUAL never crosses the link).
+        if (reinterpret_cast<uintptr_t>(recs) & 15) { c->err = "host record buffer must be 16-byte aligned"; return CORAL_E_ARG; }
+        cudaPointerAttributes at;
+        bool mapped = cudaPointerGetAttributes(&at, recs) == cudaSuccess && at.type == cudaMemoryTypeHost &&
+                      at.devicePointer != nullptr;
+        cudaGetLastError();
+        if (!mapped) {
+            if (n > 0) CORAL_CUDA(c, cudaHostRegister(const_cast<uint8_t*>(recs), nbytes, cudaHostRegisterMapped | cudaHostRegisterPortable));
+            c->host_registered = const_cast<uint8_t*>(recs);
+            if (n > 0) CORAL_CUDA(c, cudaPointerGetAttributes(&at, recs));
+        }
+        void* dp = nullptr;
+        if (n > 0) CORAL_CUDA(c, cudaHostGetDevicePointer(&dp, const_cast<uint8_t*>(recs), 0));
+        c->d_recs = static_cast<const uint8_t*>(dp);
+    } else if (on_device != CORAL_RECORDS_HOST_COPY) {
+        c->err = "unknown record placement";
+        return CORAL_E_ARG;
     } else {
         CORAL_CUDA(c, c->recs_owned.ensure(nbytes + 64));
         CORAL_CUDA(c, cudaMemcpyAsync(c->recs_owned.p, recs, nbytes, cudaMemcpyHostToDevice, c->stream));

@@ -99,6 +99,7 @@ struct coral_ctx {
     // records
     DevBuf recs_owned;
     const uint8_t* d_recs = nullptr;
+    uint8_t* host_registered = nullptr;   // caller buffer this ctx page-locked (CORAL_RECORDS_HOST_MAPPED)
     uint64_t nbytes = 0;
     DevBuf d_off, d_ordinal;
     int64_t nrec = 0;

@@ -20,14 +20,22 @@ from .host_steps import HostSteps, _t
 class bam_to_breakpoint_nanopore(HostSteps):
     _ops = breakpoint_utilities
 
-    def __init__(self, lr_bamfile, seedfile, device=0, n_threads=0, records=None):
+    def __init__(self, lr_bamfile, seedfile, device=0, n_threads=0, records=None, placement="auto"):
         """`records` (optional): an object with .references, .rec (uint8 host buffer of framed records), .rec_off and
-        .query_name(i) — lets a caller that already holds decompressed records skip the BAM file."""
+        .query_name(i) — lets a caller that already holds decompressed records skip the BAM file.
+        `placement`: "copy" (records copied to HBM), "mapped" (kernels read the page-locked host buffer in place; the
+        scan runs once per BAM, so only the fields it needs cross PCIe) or "auto" (mapped when the buffer has the
+        64 bytes of slack that mode needs)."""
         self._init_state()
         self.lr_bamfh = records if records is not None else _abi.BamFile(lr_bamfile, n_threads)   # replaces pysam (ibg:65)
         self._ctx = _abi.Context(device)
         self._ctx.set_references(self.lr_bamfh.references)
-        self._ctx.load_records(self.lr_bamfh.rec, self.lr_bamfh.rec_off)
+        rec, rec_off = self.lr_bamfh.rec, self.lr_bamfh.rec_off
+        slack = int(getattr(self.lr_bamfh, "rec_slack", 0))
+        if placement == "auto":
+            nb = int(rec_off[-1]) if len(rec_off) else 0
+            placement = "mapped" if nb > 0 and getattr(rec, "nbytes", 0) + slack >= nb + 64 else "copy"
+        self._ctx.load_records(rec, rec_off, placement=placement, slack=slack)
         self._tid = {c: i for i, c in enumerate(self.lr_bamfh.references)}
         self._name_rec = {}     # read name -> index of one record carrying it (for concordant-edge rbps)
         self._read_names = []   # chimeric read order of the device table

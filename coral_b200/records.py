@@ -3,7 +3,8 @@ import numpy as np
 
 
 class RecordSet(object):
-    def __init__(self, references, rec, rec_off, lengths=None):
+    def __init__(self, references, rec, rec_off, lengths=None, rec_slack=0):
+        self.rec_slack = int(rec_slack)   # bytes guaranteed readable behind `rec` (64 enables the mapped placement)
         self.references = tuple(references)
         self.lengths = tuple(lengths) if lengths is not None else tuple(0 for _ in references)
         self.rec = rec

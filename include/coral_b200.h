@@ -75,11 +75,22 @@ const uint8_t* coral_bam_records(const coral_bam* b, uint64_t* nbytes);   /* pin
 const uint64_t* coral_bam_offsets(const coral_bam* b);                     /* n_records + 1 */
 
 /* ---- load + scan (replaces htslib record decode under every pysam call of the path) -------------
- * Copies the records to the device (unless `on_device` != 0, then `recs` is a device pointer that
- * must outlive the ctx's use of it) and runs the record-scan kernel once: per record core fields,
+ * Makes the records visible to the device and runs the record-scan kernel once.  `on_device` says where
+ * `recs` lives and where it stays:
+ *   CORAL_RECORDS_HOST_COPY    host buffer, copied to HBM (every later pass runs at HBM speed);
+ *   CORAL_RECORDS_DEVICE       device pointer, used in place (must outlive the ctx's use of it);
+ *   CORAL_RECORDS_HOST_MAPPED  page-locked host buffer read IN PLACE by the kernels over PCIe: the scan
+ *                              only pulls the fields it needs (QUAL, about half of a record, never crosses
+ *                              the link).  A pageable buffer is page-locked for the lifetime of the load.
+ *                              The buffer must stay valid and extend >= 64 bytes past `nbytes`.
+ * Every record starts at a 16-byte-aligned offset and offsets[n_records] is 16-byte aligned too.
+ * The scan computes, per record: the core fields,
  * reference end (bam_endpos), infer_read_length, aligned bases, non-ACGT count, name hash, SA/NM tag
  * location, and the in-CIGAR gap events > min_del_len.  `global_ordinal` (nullable) is the record's
  * index in the whole file when this ctx holds one shard. */
+#define CORAL_RECORDS_HOST_COPY 0
+#define CORAL_RECORDS_DEVICE 1
+#define CORAL_RECORDS_HOST_MAPPED 2
 int coral_load_records(coral_ctx* ctx, const uint8_t* recs, uint64_t nbytes, const uint64_t* offsets,
                        int64_t n_records, const uint64_t* global_ordinal, int on_device);
 int64_t coral_n_records(const coral_ctx* ctx);
