@@ -169,7 +169,8 @@ def build_plan(eng, cn_seg):
     plan["smalldel_cand"] = eng._smalldel_candidates()[0]
     eng.find_breakpoints()
     eng.build_graph()
-    batches, uniq, owners, rb_edge, rb_rec = eng._edge_queries()
+    batches, uniq, owners, rbps = eng._edge_queries()
+    rb_edge, rb_rec = eng._rbps_rows(rbps)
     b = batches[0]
     plan["seq_edges"] = ([r[0] for r in b], [r[1] for r in b], [r[2] for r in b])
     plan["conc"] = ([u[0] for u in uniq], [u[1] for u in uniq], rb_edge, rb_rec)

@@ -164,6 +164,30 @@ class Context(object):
         self._check(self._L.coral_load_records(self._h, ctypes.c_void_p(dev_ptr), ctypes.c_uint64(nbytes), _p(rec_off),
                                                ctypes.c_int64(len(rec_off) - 1), _p(go), 1))
 
+    # ---- multi-GPU exchange of fetch (include/coral_b200.h) ---------------------------------------------------
+    def record_keys(self):
+        n = self.n_records
+        out = {"name_lo": np.zeros(n, np.uint64), "name_hi": np.zeros(n, np.uint64), "sa_off": np.zeros(n, np.uint32),
+               "sa_len": np.zeros(n, np.uint32), "nm": np.zeros(n, np.int32)}
+        self._check(self._L.coral_get_record_keys(self._h, _p(out["name_lo"]), _p(out["name_hi"]), _p(out["sa_off"]),
+                                                  _p(out["sa_len"]), _p(out["nm"])))
+        return out
+
+    def nm_partials(self):
+        s1 = ctypes.c_double(); s2 = ctypes.c_double(); nn = ctypes.c_int64(); zd = ctypes.c_int64()
+        self._check(self._L.coral_nm_partials(self._h, ctypes.byref(s1), ctypes.byref(s2), ctypes.byref(nn), ctypes.byref(zd)))
+        return s1.value, s2.value, nn.value, zd.value
+
+    def load_rows(self, text, text_off, name_lo, name_hi, flag, mapq, l_seq, nm):
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        text_off = np.ascontiguousarray(text_off, dtype=np.uint64)
+        a = [np.ascontiguousarray(name_lo, np.uint64), np.ascontiguousarray(name_hi, np.uint64),
+             np.ascontiguousarray(flag, np.uint32), np.ascontiguousarray(mapq, np.uint32),
+             np.ascontiguousarray(l_seq, np.uint32), np.ascontiguousarray(nm, np.int32)]
+        n = len(text_off) - 1
+        self._check(self._L.coral_load_rows(self._h, ctypes.c_int64(n), _p(text), ctypes.c_uint64(text.nbytes), _p(text_off),
+                                            *[_p(x) for x in a]))
+
     def rescan(self):
         self._check(self._L.coral_rescan(self._h))
 

@@ -89,6 +89,7 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     if (!c || n < 0 || (n > 0 && (!recs || !offsets))) return CORAL_E_ARG;
     cudaSetDevice(c->device);
     c->loaded = false;
+    c->rows_only = false;
     for (int64_t i = 0; i < n; i++) {
         if (offsets[i] & 15) { c->err = "record offsets must be 16-byte aligned"; return CORAL_E_ARG; }
         if (offsets[i] + 36 > nbytes || offsets[i + 1] < offsets[i] + 36 || offsets[i + 1] > nbytes) {
@@ -146,7 +147,7 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
 
 int coral_rescan(coral_ctx* c) {
     if (!c) return CORAL_E_ARG;
-    if (!c->loaded) { c->err = "coral_rescan before coral_load_records"; return CORAL_E_STATE; }
+    if (!c->loaded || c->rows_only) { c->err = "coral_rescan before coral_load_records"; return CORAL_E_STATE; }
     cudaSetDevice(c->device);
     return coral_run_scan(c);
 }
@@ -166,6 +167,7 @@ uint64_t coral_launch_count(const coral_ctx* c) { return c ? c->n_launches : 0; 
 int coral_region_coverage(coral_ctx* c, const int32_t* tid, const int32_t* start, const int32_t* stop, int32_t n,
                           int64_t* base_sum, int64_t* rec_count) {
     if (!c) return CORAL_E_ARG;
+    if (c->rows_only) { c->err = "coral_region_coverage on a rows-only ctx"; return CORAL_E_STATE; }
     cudaSetDevice(c->device);
     return coral_run_region_coverage(c, tid, start, stop, n, base_sum, rec_count);
 }

@@ -525,6 +525,39 @@ int coral_run_fetch(coral_ctx* c) {
     return CORAL_OK;
 }
 
+// nm_stats partial sums of this ctx's records alone (ibg:153-157); the sharded path all-reduces them.
+extern "C" int coral_nm_partials(coral_ctx* c, double* nm_sum, double* nm_sumsq, int64_t* nm_n, int64_t* nm_zero_div) {
+    using namespace coral;
+    if (!c) return CORAL_E_ARG;
+    if (!c->loaded || c->rows_only) { c->err = "coral_nm_partials before coral_load_records"; return CORAL_E_STATE; }
+    cudaSetDevice(c->device);
+    const int64_t n = c->nrec;
+    const int64_t nblk = (n + NM_BLOCK - 1) / NM_BLOCK;
+    RecordTable& rt = c->rt;
+    double s1 = 0, s2 = 0;
+    int64_t cnt = 0, zd = 0;
+    if (n > 0) {
+        CORAL_CUDA(c, c->s7.ensure((size_t)nblk * 32));
+        k_nm_stats<<<(unsigned)nblk, NM_BLOCK, 0, c->stream>>>(n, rt.sa_off.as<uint32_t>(), rt.flag_mapq.as<uint32_t>(),
+                                                              rt.tid.as<int32_t>(), rt.nm.as<int32_t>(), rt.lseq.as<uint32_t>(),
+                                                              c->s7.as<double>());
+        c->n_launches++;
+        CORAL_CUDA(c, cudaGetLastError());
+        std::vector<double> part((size_t)nblk * 4, 0.0);
+        CORAL_TRY(d2h(c, part.data(), c->s7.p, (size_t)nblk * 4));
+        CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+        for (int64_t b = 0; b < nblk; b++) {
+            s1 += part[4 * b]; s2 += part[4 * b + 1];
+            cnt += (int64_t)part[4 * b + 2]; zd += (int64_t)part[4 * b + 3];
+        }
+    }
+    if (nm_sum) *nm_sum = s1;
+    if (nm_sumsq) *nm_sumsq = s2;
+    if (nm_n) *nm_n = cnt;
+    if (nm_zero_div) *nm_zero_div = zd;
+    return CORAL_OK;
+}
+
 extern "C" int coral_fetch(coral_ctx* c, int64_t* n_reads, int64_t* n_alignments, double* nm_sum, double* nm_sumsq,
                            int64_t* nm_n, int64_t* nm_zero_div) {
     if (!c) return CORAL_E_ARG;

@@ -116,7 +116,7 @@ extern "C" int coral_concordant(coral_ctx* c, const int32_t* tid, const int32_t*
                                 const uint32_t* rb_edge, const uint32_t* rb_rec, int64_t* lr_count, int64_t* n_union_rows) {
     using namespace coral;
     if (!c || n_edges < 0 || n_rbps < 0) return CORAL_E_ARG;
-    if (!c->loaded) { c->err = "coral_concordant before coral_load_records"; return CORAL_E_STATE; }
+    if (!c->loaded || c->rows_only) { c->err = "coral_concordant before coral_load_records"; return CORAL_E_STATE; }
     cudaSetDevice(c->device);
     c->stab_n = 0; c->stab_valid = false;
     if (n_union_rows) *n_union_rows = 0;

@@ -8,16 +8,25 @@ import numpy as np
 
 from . import _abi
 
-_default_ctx = None
+import threading
+
+_tls = threading.local()     # a coral_ctx is not thread-safe: one default context per thread (and per device)
 STRAND = ('+', '-')
 
 
+def set_default_device(device):
+    """Device of this thread's default context (the engine calls this with its own device)."""
+    if getattr(_tls, "device", 0) != int(device):
+        _tls.device = int(device)
+        _tls.ctx = None
+
+
 def default_context():
-    """Process-wide context on cuda:0 for the module-level operators (cluster_bp_list, bpc2bp, ...)."""
-    global _default_ctx
-    if _default_ctx is None:
-        _default_ctx = _abi.Context(0)
-    return _default_ctx
+    """Per-thread context for the module-level operators (cluster_bp_list, bpc2bp, ...)."""
+    ctx = getattr(_tls, "ctx", None)
+    if ctx is None:
+        ctx = _tls.ctx = _abi.Context(getattr(_tls, "device", 0))
+    return ctx
 
 
 def flatten_bp_list(bp_list):

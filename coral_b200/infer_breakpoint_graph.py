@@ -29,6 +29,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
         self._init_state()
         self.lr_bamfh = records if records is not None else _abi.BamFile(lr_bamfile, n_threads)   # replaces pysam (ibg:65)
         self._ctx = _abi.Context(device)
+        gpu_ops.set_default_device(device)
         self._ctx.set_references(self.lr_bamfh.references)
         rec, rec_off = self.lr_bamfh.rec, self.lr_bamfh.rec_off
         slack = int(getattr(self.lr_bamfh, "rec_slack", 0))
@@ -64,14 +65,24 @@ class bam_to_breakpoint_nanopore(HostSteps):
                 else:
                     batch.append(s)
                     last = s
-            bs, _ = self._ctx.region_coverage([self._tid[s[0]] for s in batch], [s[1] for s in batch], [s[2] + 1 for s in batch])
+            bs, _ = self._region_counts([self._tid[s[0]] for s in batch], [s[1] for s in batch], [s[2] + 1 for s in batch])
             total += int(bs.sum())
             pending = rest
         return total
 
     # ---- a1/a2: ibg:139-174 ------------------------------------------------------------------------------
+    def _run_fetch(self):
+        """Device fetch -> (table dict, record index -> read name).  The sharded engine overrides this with the
+        exchange of SURVEY.md §8e (rows all-gathered, fetch on the gathered rows)."""
+        return self._ctx.fetch(), self.lr_bamfh.query_name
+
+    @property
+    def _chim_ctx(self):
+        """The ctx that holds the chimeric table (the shard's own ctx, or the gathered-rows ctx when sharded)."""
+        return self._ctx
+
     def fetch(self):
-        f = self._ctx.fetch()
+        f, name_of = self._run_fetch()
         if f["nm_zero_div"] or f["nm_n"] == 0:
             raise ZeroDivisionError("division by zero")              # ibg:154 / ibg:159
         mean = f["nm_sum"] / f["nm_n"]
@@ -84,7 +95,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
         self._read_names = []
         for r in range(f["n_reads"]):
             rec = int(f["read_first_rec"][r])
-            name = self.lr_bamfh.query_name(rec)
+            name = name_of(rec)
             self._read_names.append(name)
             self._read_index[name] = r
             self._name_rec[name] = rec
@@ -151,20 +162,28 @@ class bam_to_breakpoint_nanopore(HostSteps):
     def find_smalldel_breakpoints(self):
         t, s, e = self._interval_arrays()
         self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
+        lia = self.large_indel_alignments
+        for (name, ai, ns, pe, fs, le, mq) in self._smalldel_rows(t, s, e):
+            lia.setdefault(name, []).append([self.amplicon_intervals[ai][0], ns, pe, fs, le, mq])
+        logging.info(_t() + "Fetched %d reads with large indels in CIGAR." % (len(lia)))
+        self._call_clusters(*self._smalldel_candidates())
+
+    def _smalldel_rows(self, t, s, e):
+        """Rows (name, interval index, next_start, prev_end, first_start, last_end, mapq) in the reference's
+        emission order: interval list order, file order, block order (ibg:750-762)."""
         rows = self._ctx.smalldel(t, s, e)
         names = {}
-        lia = self.large_indel_alignments
         recs = rows["rec"].tolist()
         ai, ns, pe, fs, le, mq = (rows[k].tolist() for k in ("ai", "next_start", "prev_end", "first_start", "last_end", "mapq"))
+        out = []
         for k in range(rows["n"]):
             rec = recs[k]
             name = names.get(rec)
             if name is None:
                 name = names[rec] = self.lr_bamfh.query_name(rec)
                 self._name_rec.setdefault(name, rec)
-            lia.setdefault(name, []).append([self.amplicon_intervals[ai[k]][0], ns[k], pe[k], fs[k], le[k], mq[k]])
-        logging.info(_t() + "Fetched %d reads with large indels in CIGAR." % (len(lia)))
-        self._call_clusters(*self._smalldel_candidates())
+            out.append((name, ai[k], ns[k], pe[k], fs[k], le[k], mq[k]))
+        return out
 
     def _smalldel_candidates(self):
         tuples, chrs, p1, p2 = [], [], [], []
@@ -185,7 +204,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
     def find_breakpoints(self):
         t, s, e = self._interval_arrays()
         self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
-        c = self._ctx.candidates_l(t, s, e)
+        c = self._chim_ctx.candidates_l(t, s, e)
         names = self._read_names
         rd, ii, jj = c["read"].tolist(), c["i"].tolist(), c["j"].tolist()
         tuples = [(names[rd[k]], ii[k], jj[k]) for k in range(c["n"])]
@@ -194,7 +213,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
     def _pair_candidates(self, reads, intrvl1, intrvl2):
         """One batched launch of alignment2bp over the device chimeric table (ibg:432-434)."""
         idx = [self._read_index[r] for r in reads]
-        c = self._ctx.candidates_pair(idx, [self._tid[intrvl1[0]], self._tid[intrvl2[0]]], [intrvl1[1], intrvl2[1]],
+        c = self._chim_ctx.candidates_pair(idx, [self._tid[intrvl1[0]], self._tid[intrvl2[0]]], [intrvl1[1], intrvl2[1]],
                                       [intrvl1[2], intrvl2[2]])
         refs = self.lr_bamfh.references
         names = self._read_names
@@ -228,7 +247,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
                 owners[-1].append((gi, ci))
             else:
                 uniq.append((t, p)); owners.append([(gi, ci)])
-        rb_edge, rb_rec = [], []
+        rbps = []
         for k, own in enumerate(owners):
             gi, ci = own[0]
             g = self.lr_graph[gi]
@@ -237,24 +256,26 @@ class bam_to_breakpoint_nanopore(HostSteps):
             for node in ((ce[0], ce[1], ce[2]), (ce[3], ce[4], ce[5])):
                 for bpi in g.nodes[node][2]:
                     for r in g.discordant_edges[bpi][10]:
-                        if r[0] not in seen:
-                            seen.add(r[0])
-                            if r[0] in self._name_rec:   # a read with no loaded record cannot cover any point
-                                rb_edge.append(k); rb_rec.append(self._name_rec[r[0]])
-        return batches, uniq, owners, rb_edge, rb_rec
+                        seen.add(r[0])
+            rbps.append(seen)
+        return batches, uniq, owners, rbps
 
-    def assign_cov(self):
-        batches, uniq, owners, rb_edge, rb_rec = self._edge_queries()
-        for batch in batches:
-            if not batch:
-                continue
-            bs, rc = self._ctx.region_coverage([r[0] for r in batch], [r[1] for r in batch], [r[2] for r in batch])
-            for k, (_, _, _, gi, si) in enumerate(batch):
-                self.lr_graph[gi].sequence_edges[si][5] = int(rc[k])
-                self.lr_graph[gi].sequence_edges[si][6] = int(bs[k])
-        if not uniq:
-            return
-        self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
+    def _rbps_rows(self, rbps):
+        """rbps name sets -> (edge index, a local record of that read) rows for coral_concordant."""
+        rb_edge, rb_rec = [], []
+        for k, names in enumerate(rbps):
+            for nm in names:
+                if nm in self._name_rec:   # a read with no loaded record cannot cover any point
+                    rb_edge.append(k); rb_rec.append(self._name_rec[nm])
+        return rb_edge, rb_rec
+
+    def _region_counts(self, tid, start, stop):
+        """(base_sum, rec_count) of disjoint sorted regions; the sharded engine all-reduces the shard sums."""
+        return self._ctx.region_coverage(tid, start, stop)
+
+    def _concordant_support(self, uniq, rbps):
+        """Per unique concordant edge: ce[8] and the name set ce[9] (ibg:1043-1055)."""
+        rb_edge, rb_rec = self._rbps_rows(rbps)
         cnt, rows = self._ctx.concordant([u[0] for u in uniq], [u[1] for u in uniq], rb_edge, rb_rec)
         sel = (rows["mask"] & 3) != 0
         r_edge, r_rec = rows["edge"][sel], rows["rec"][sel]
@@ -262,17 +283,35 @@ class bam_to_breakpoint_nanopore(HostSteps):
         r_edge, r_rec = r_edge[o], r_rec[o]
         bounds = np.searchsorted(r_edge, np.arange(len(uniq) + 1))
         name_of = {}
-        for k, own in enumerate(owners):
+        out = []
+        for k in range(len(uniq)):
             names = set()
             for rec in r_rec[bounds[k]:bounds[k + 1]].tolist():
                 nm = name_of.get(rec)
                 if nm is None:
                     nm = name_of[rec] = self.lr_bamfh.query_name(rec)
                 names.add(nm)
+            out.append(names)
+        return [int(x) for x in cnt], out
+
+    def assign_cov(self):
+        batches, uniq, owners, rbps = self._edge_queries()
+        for batch in batches:
+            if not batch:
+                continue
+            bs, rc = self._region_counts([r[0] for r in batch], [r[1] for r in batch], [r[2] for r in batch])
+            for k, (_, _, _, gi, si) in enumerate(batch):
+                self.lr_graph[gi].sequence_edges[si][5] = int(rc[k])
+                self.lr_graph[gi].sequence_edges[si][6] = int(bs[k])
+        if not uniq:
+            return
+        self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
+        cnt, names_of = self._concordant_support(uniq, rbps)
+        for k, own in enumerate(owners):
             for (gi, ci) in own:
                 ce = self.lr_graph[gi].concordant_edges[ci]
-                ce[9] = set(names) if len(own) > 1 else names
-                ce[8] = int(cnt[k])
+                ce[9] = set(names_of[k]) if len(own) > 1 else names_of[k]
+                ce[8] = cnt[k]
 
     def closebam(self):
         self.lr_bamfh.close()

@@ -1,0 +1,304 @@
+"""Multi-GPU form of the hot path: one process per GPU, each holding a contiguous range of the coordinate-sorted
+file (a genomic bin range balanced by decoded bytes), SURVEY.md §8e.
+
+Per-record work (record scan, coverage sums, gap events, stab rows) is local and additive — a record is owned by
+exactly one shard — so sequence-edge and normal-coverage sums only need an integer all-reduce.  The one real
+exchange is `fetch`: the reference unions the SA strings of all records of a read name in file order and takes
+read_length from the first record with flag < 256 anywhere in the file (infer_breakpoint_graph.py:142-151), and
+the records of a chimeric read live on several shards.  Every rank exports one small row per relevant record,
+the rows are all-gathered in rank (= file) order, and every rank runs the same deterministic fetch on the
+gathered rows (coral_load_rows), so candidates and clustering are replicated and identical to the 1-GPU result.
+
+This module holds the communicators and the host-side exchange logic (pure numpy: covered by world_size-2 gloo
+tests on CPU); `ShardedEngine` at the bottom binds it to the CUDA contexts.
+"""
+import threading
+
+import numpy as np
+
+
+# ---- communicators -------------------------------------------------------------------------------------------
+class SingleComm(object):
+    rank, world = 0, 1
+
+    def all_gather(self, obj):
+        return [obj]
+
+    def all_reduce_sum(self, arr):
+        return np.array(arr, copy=True)
+
+
+class TorchComm(object):
+    """torch.distributed (NCCL over NVLink on the GPU box, gloo in the CPU tests)."""
+
+    def __init__(self, group=None, device=None):
+        import torch.distributed as dist
+        self._dist = dist
+        self._group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self._device = device
+
+    def all_gather(self, obj):
+        out = [None] * self.world
+        self._dist.all_gather_object(out, obj, group=self._group)
+        return out
+
+    def all_reduce_sum(self, arr):
+        import torch
+        a = np.ascontiguousarray(arr)
+        t = torch.from_numpy(a.copy())
+        if self._device is not None:
+            t = t.to(self._device)
+        self._dist.all_reduce(t, op=self._dist.ReduceOp.SUM, group=self._group)
+        return t.cpu().numpy()
+
+
+class ThreadComm(object):
+    """N ranks as N threads of one process (shards emulated on one GPU, or on the CPU in tests)."""
+
+    class _Shared(object):
+        def __init__(self, world):
+            self.world = world
+            self.barrier = threading.Barrier(world, timeout=600)
+            self.slots = [None] * world
+
+    def __init__(self, shared, rank):
+        self._s = shared
+        self.rank = rank
+        self.world = shared.world
+
+    @classmethod
+    def make(cls, world):
+        sh = cls._Shared(world)
+        return [cls(sh, r) for r in range(world)]
+
+    def all_gather(self, obj):
+        self._s.slots[self.rank] = obj
+        self._s.barrier.wait()
+        out = list(self._s.slots)
+        self._s.barrier.wait()
+        return out
+
+    def all_reduce_sum(self, arr):
+        parts = self.all_gather(np.asarray(arr))
+        tot = np.array(parts[0], copy=True)
+        for p in parts[1:]:
+            tot = tot + p
+        return tot
+
+
+# ---- pure host logic -------------------------------------------------------------------------------------------
+def shard_ranges(rec_off, world):
+    """Contiguous record ranges [r0, r1) per rank, balanced by decoded bytes (file order = genomic bin order)."""
+    rec_off = np.asarray(rec_off, dtype=np.uint64)
+    n = len(rec_off) - 1
+    total = int(rec_off[-1]) if n > 0 else 0
+    cuts = [0]
+    for r in range(1, world):
+        cuts.append(int(np.searchsorted(rec_off[:-1], np.uint64(total * r // world), side="left")))
+    cuts.append(n)
+    for k in range(1, len(cuts)):
+        cuts[k] = max(cuts[k], cuts[k - 1])
+    return [(cuts[r], cuts[r + 1]) for r in range(world)]
+
+
+def _member(lo, hi, set_lo, set_hi):
+    """Vectorised membership of (lo, hi) pairs in a set of pairs sorted by (lo, hi)."""
+    if len(set_lo) == 0 or len(lo) == 0:
+        return np.zeros(len(lo), bool)
+    pos = np.searchsorted(set_lo, lo, side="left")
+    hit = np.zeros(len(lo), bool)
+    live = pos < len(set_lo)
+    while live.any():
+        idx = np.nonzero(live)[0]
+        p = pos[idx]
+        same_lo = set_lo[p] == lo[idx]
+        ok = same_lo & (set_hi[p] == hi[idx])
+        hit[idx[ok]] = True
+        nxt = idx[same_lo & ~ok]                   # same low word, other high word: look at the next entry
+        pos[nxt] += 1
+        live = np.zeros(len(lo), bool)
+        live[nxt] = pos[nxt] < len(set_lo)
+    return hit
+
+
+def exchange_fetch_rows(comm, local):
+    """The `fetch` exchange.  `local` describes this rank's records in file order:
+         name_lo, name_hi (uint64), has_sa (bool), flag, mapq, l_seq (uint32), nm (int32) — arrays of length n;
+         sa_text(i) -> bytes (the SA:Z value without its NUL), name(i) -> str.
+    Returns the gathered rows in global file order: dict(name_lo, name_hi, flag, mapq, l_seq, nm, text, text_off,
+    names[list of str]) — the same on every rank.  A world-N gather carries up to N primaries per name (the first of
+    each rank) where a 1-rank export carries one; fetch keeps the first in file order, so its result is the same."""
+    lo = np.asarray(local["name_lo"], np.uint64)
+    hi = np.asarray(local["name_hi"], np.uint64)
+    has_sa = np.asarray(local["has_sa"], bool)
+    flag = np.asarray(local["flag"], np.uint32)
+    # round 1: names that carry an SA tag anywhere in the file
+    sa_idx = np.nonzero(has_sa)[0]
+    mine = np.stack([lo[sa_idx], hi[sa_idx]], axis=1) if len(sa_idx) else np.zeros((0, 2), np.uint64)
+    allp = np.concatenate(comm.all_gather(mine), axis=0)
+    if len(allp):
+        o = np.lexsort((allp[:, 1], allp[:, 0]))
+        set_lo, set_hi = allp[o, 0], allp[o, 1]
+    else:
+        set_lo = set_hi = np.zeros(0, np.uint64)
+    # round 2: + the first local record with flag < 256 of each such name (read_length comes from the first primary
+    # in the file, which need not carry an SA tag itself)
+    cand = np.nonzero((flag < 256) & ~has_sa)[0]
+    cand = cand[_member(lo[cand], hi[cand], set_lo, set_hi)]
+    if len(cand):
+        pairs = np.stack([lo[cand], hi[cand]], axis=1)
+        _, first = np.unique(pairs, axis=0, return_index=True)
+        cand = cand[np.sort(first)]
+    rows = np.sort(np.concatenate([sa_idx, cand])).astype(np.int64)
+    texts = [local["sa_text"](int(i)) if has_sa[i] else b"" for i in rows]
+    off = np.zeros(len(rows) + 1, np.uint64)
+    if len(rows):
+        off[1:] = np.cumsum([len(t) for t in texts])
+    payload = {
+        "name_lo": lo[rows], "name_hi": hi[rows], "flag": flag[rows],
+        "mapq": np.asarray(local["mapq"], np.uint32)[rows], "l_seq": np.asarray(local["l_seq"], np.uint32)[rows],
+        "nm": np.asarray(local["nm"], np.int32)[rows], "text": np.frombuffer(b"".join(texts), np.uint8),
+        "text_off": off, "names": [local["name"](int(i)) for i in rows]}
+    parts = comm.all_gather(payload)
+    out = {k: np.concatenate([p[k] for p in parts]) for k in ("name_lo", "name_hi", "flag", "mapq", "l_seq", "nm", "text")}
+    offs, base = [np.zeros(1, np.uint64)], 0
+    for p in parts:
+        offs.append(p["text_off"][1:] + np.uint64(base))
+        base += int(p["text_off"][-1])
+    out["text_off"] = np.concatenate(offs)
+    out["names"] = [nm for p in parts for nm in p["names"]]
+    return out
+
+
+def merge_smalldel_rows(comm, rows):
+    """rows: this rank's (name, interval index, next_start, prev_end, first_start, last_end, mapq) in local emission
+    order.  Global emission order = interval list order, then file order, then block order (ibg:750-762); ranks hold
+    increasing file ranges, so concatenating in rank order and stable-sorting by interval restores it."""
+    allr = [r for part in comm.all_gather(list(rows)) for r in part]
+    allr.sort(key=lambda r: r[1])
+    return allr
+
+
+def combine_concordant(comm, n_edges, rows, rbps):
+    """rows: this rank's (edge, read name, mask) for every local record covering one of the four points of an edge
+    (mask bit0 = p, bit1 = p+1, bit2 = p-d-1, bit3 = p+1+d).  The reference works on NAME sets (ibg:1043-1055), so
+    the masks of all records of a name — on any shard — are OR-ed before the 4-point test.
+    Returns (ce[8] per edge, ce[9] name set per edge)."""
+    acc = [dict() for _ in range(n_edges)]
+    for part in comm.all_gather(list(rows)):
+        for (e, name, m) in part:
+            d = acc[e]
+            d[name] = d.get(name, 0) | m
+    cnt, names = [], []
+    for e in range(n_edges):
+        bad = rbps[e]
+        cnt.append(sum(1 for nm, m in acc[e].items() if m == 15 and nm not in bad))
+        names.append(set(nm for nm, m in acc[e].items() if m & 3))
+    return cnt, names
+
+
+# ---- the engine --------------------------------------------------------------------------------------------------
+class _ShardView(object):
+    """This rank's slice of a record set: the interface the drop-in class needs from its BAM handle."""
+
+    def __init__(self, parent, r0, r1):
+        off = np.asarray(parent.rec_off, dtype=np.uint64)
+        b0, b1 = int(off[r0]), int(off[r1])
+        self.references = tuple(parent.references)
+        self.rec = parent.rec[b0:b1]
+        self.rec_off = (off[r0:r1 + 1] - np.uint64(b0)).astype(np.uint64)
+        self.n_records = r1 - r0
+        # bytes readable behind the slice: the next shard's records, or the parent's own slack after the last one
+        self.rec_slack = 64 if b1 + 64 <= len(parent.rec) + int(getattr(parent, "rec_slack", 0)) else 0
+        self.g0 = r0
+        self._parent = parent
+
+    def query_name(self, i):
+        return self._parent.query_name(self.g0 + i)
+
+    def close(self):
+        pass
+
+
+def make_sharded_engine(records, seedfile, comm, device=0, placement="auto"):
+    """Factory (keeps the CUDA-bound import out of the CPU tests of the exchange logic)."""
+    from . import _abi
+    from .infer_breakpoint_graph import bam_to_breakpoint_nanopore
+
+    class ShardedEngine(bam_to_breakpoint_nanopore):
+        """bam_to_breakpoint_nanopore over one shard of the file + the exchanges of SURVEY.md §8e.  Same public
+        methods, same call order; every rank ends with the same containers as the 1-GPU engine."""
+
+        def __init__(self):
+            self._comm = comm
+            r0, r1 = shard_ranges(records.rec_off, comm.world)[comm.rank]
+            view = _ShardView(records, r0, r1)
+            bam_to_breakpoint_nanopore.__init__(self, None, seedfile, device=device, records=view, placement=placement)
+            self._cctx = _abi.Context(device)          # rows-only ctx: the gathered fetch rows live here
+            self._cctx.set_references(view.references)
+            self._row_names = []
+
+        @property
+        def _chim_ctx(self):
+            return self._cctx
+
+        # a12 / a10: additive over records -> integer all-reduce of the shard sums
+        def _region_counts(self, tid, start, stop):
+            bs, rc = self._ctx.region_coverage(tid, start, stop)
+            tot = self._comm.all_reduce_sum(np.concatenate([bs, rc]).astype(np.int64))
+            return tot[:len(bs)], tot[len(bs):]
+
+        # a1: the exchange
+        def _run_fetch(self):
+            ctx, fh = self._ctx, self.lr_bamfh
+            keys = ctx.record_keys()
+            tab = ctx.record_table()
+            rec, off = fh.rec, fh.rec_off
+
+            def sa_text(i):
+                b = int(off[i]) + int(keys["sa_off"][i])
+                return rec[b:b + int(keys["sa_len"][i])].tobytes()
+
+            rows = exchange_fetch_rows(self._comm, {
+                "name_lo": keys["name_lo"], "name_hi": keys["name_hi"], "has_sa": keys["sa_off"] != 0,
+                "flag": tab["flag"].astype(np.uint32), "mapq": tab["mapq"].astype(np.uint32),
+                "l_seq": tab["l_seq"].astype(np.uint32), "nm": keys["nm"], "sa_text": sa_text, "name": fh.query_name})
+            self._row_names = rows["names"]
+            self._cctx.load_rows(rows["text"], rows["text_off"], rows["name_lo"], rows["name_hi"], rows["flag"],
+                                 rows["mapq"], rows["l_seq"], rows["nm"])
+            f = self._cctx.fetch()
+            # nm_stats (ibg:153-157) run over ALL records: all-reduce the shard partials (f64 sum order differs from
+            # the 1-GPU order: within 1e-9 relative, unused downstream)
+            s1, s2, nn, zd = ctx.nm_partials()
+            parts = self._comm.all_gather((s1, s2, nn, zd))
+            f["nm_sum"] = float(sum(p[0] for p in parts)); f["nm_sumsq"] = float(sum(p[1] for p in parts))
+            f["nm_n"] = int(sum(p[2] for p in parts)); f["nm_zero_div"] = int(sum(p[3] for p in parts))
+            return f, (lambda r: self._row_names[r])
+
+        def find_breakpoints(self):
+            self._cctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
+            bam_to_breakpoint_nanopore.find_breakpoints(self)
+
+        # a3: local gap rows, merged in emission order
+        def _smalldel_rows(self, t, s, e):
+            return merge_smalldel_rows(self._comm, bam_to_breakpoint_nanopore._smalldel_rows(self, t, s, e))
+
+        # a11: name-level set algebra across shards
+        def _concordant_support(self, uniq, rbps):
+            _, rows = self._ctx.concordant([u[0] for u in uniq], [u[1] for u in uniq], [], [])
+            name_of = {}
+            out = []
+            for e, r, m in zip(rows["edge"].tolist(), rows["rec"].tolist(), rows["mask"].tolist()):
+                nm = name_of.get(r)
+                if nm is None:
+                    nm = name_of[r] = self.lr_bamfh.query_name(r)
+                out.append((e, nm, m))
+            return combine_concordant(self._comm, len(uniq), out, rbps)
+
+        def closebam(self):
+            self._cctx.close()
+            bam_to_breakpoint_nanopore.closebam(self)
+
+    return ShardedEngine()

@@ -147,6 +147,23 @@ int coral_get_chimeric(coral_ctx* ctx, uint32_t* read_first_rec, int64_t* read_l
                        uint32_t* aln_ptr, int32_t* qs, int32_t* qe, int32_t* tid, int32_t* rstart, int32_t* rend,
                        uint8_t* strand, int32_t* mapq, int64_t* nm);
 
+/* ---- multi-GPU exchange of `fetch` (one process per GPU, each holding a contiguous range of the file) --------
+ * The reference unions the SA strings of all records of a read name in file order and takes read_length from
+ * the first record with flag < 256 anywhere in the file (ibg:142-151).  A rank exports one row per SA-bearing
+ * record (and per first local primary of a chimeric name), the rows of all ranks are concatenated in rank
+ * (= file) order and loaded into a second, rows-only ctx on which coral_fetch / coral_candidates_* /
+ * coral_cluster_call run unchanged; every other entry point returns CORAL_E_STATE on such a ctx.
+ *   coral_get_record_keys : per-record 128-bit name hash, SA tag location (sa_off == 0: no SA tag) and NM;
+ *   coral_nm_partials     : this ctx's partial sums of ibg:153-157 (all-reduced by the caller);
+ *   coral_load_rows       : row i = name hash, flag, MAPQ, l_seq, NM and SA text text[text_off[i] : text_off[i+1])
+ *                           (empty: the record has no SA tag). */
+int coral_get_record_keys(coral_ctx* ctx, uint64_t* name_lo, uint64_t* name_hi, uint32_t* sa_off, uint32_t* sa_len,
+                          int32_t* nm);
+int coral_nm_partials(coral_ctx* ctx, double* nm_sum, double* nm_sumsq, int64_t* nm_n, int64_t* nm_zero_div);
+int coral_load_rows(coral_ctx* ctx, int64_t n_rows, const uint8_t* text, uint64_t text_bytes, const uint64_t* text_off,
+                    const uint64_t* name_lo, const uint64_t* name_hi, const uint32_t* flag, const uint32_t* mapq,
+                    const uint32_t* l_seq, const int32_t* nm);
+
 /* Operator form of cigar_parsing.alignment_from_satags / cigar2pos* (cigar_parsing.py:17-269) on SA text the
  * caller supplies: `text` holds the entries, read r owns entries [ent_ptr[r], ent_ptr[r+1]) whose bytes are
  * text[ent_beg[k] : ent_end[k]].  Per read: status as in coral_fetch; per entry, in the read's stable

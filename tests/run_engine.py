@@ -14,14 +14,47 @@ sys.path.insert(0, HERE)
 import util  # noqa: E402
 
 
+def sharded_states(world, bam, cn_seg, seed):
+    """`world` shards of the file as `world` threads on cuda:0, exchanging through ThreadComm (the collective's test
+    double; the kernels are the real ones).  Every rank must end in the same state; rank 0's is returned."""
+    import threading
+    from coral_b200 import _abi, sharded
+    fh = _abi.BamFile(bam, 4)
+    comms = sharded.ThreadComm.make(world)
+    out, err = [None] * world, []
+
+    def body(r):
+        try:
+            eng = sharded.make_sharded_engine(fh, seed, comms[r], device=0)
+            out[r] = util.jsonify(util.run_pipeline(eng, cn_seg))
+        except Exception as ex:      # noqa
+            import traceback
+            traceback.print_exc()
+            err.append(ex)
+            comms[r]._s.barrier.abort()
+    th = [threading.Thread(target=body, args=(r,)) for r in range(world)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    if err:
+        raise err[0]
+    for r in range(1, world):
+        a, b = dict(out[0]), dict(out[r])
+        a["fetch"] = dict(a["fetch"], nm_stats=None); b["fetch"] = dict(b["fetch"], nm_stats=None)
+        assert a == b, "rank %d ended in a different state than rank 0" % r
+    return out[0]
+
+
 def main():
     kind, bam, cn_seg, seed, out = sys.argv[1:6]
-    if kind == "oracle":
-        eng = util.oracle_engine(bam, seed)
+    if kind.startswith("cuda-sharded:"):
+        st = sharded_states(int(kind.split(":")[1]), bam, cn_seg, seed)
     else:
-        from coral_b200.infer_breakpoint_graph import bam_to_breakpoint_nanopore
-        eng = bam_to_breakpoint_nanopore(bam, seed)
-    st = util.run_pipeline(eng, cn_seg)
+        if kind == "oracle":
+            eng = util.oracle_engine(bam, seed)
+        else:
+            from coral_b200.infer_breakpoint_graph import bam_to_breakpoint_nanopore
+            eng = bam_to_breakpoint_nanopore(bam, seed)
+        st = util.run_pipeline(eng, cn_seg)
     with open(out, "w") as fp:
         json.dump(st, fp)
 

@@ -1,0 +1,173 @@
+"""CPU tests of the multi-GPU exchange logic (coral_b200/sharded.py): world_size-2 `gloo` processes and in-process
+thread ranks.  The device-free part of the N > 1 path: what every rank gathers must not depend on how the file was
+cut, and must reproduce what the reference's fetch does with the whole file (ibg:139-174 via the oracle shim)."""
+import hashlib
+import os
+import sys
+import threading
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+sys.path.insert(0, HERE)
+
+from coral_b200 import sharded  # noqa: E402
+
+
+def _file_rows(bam_path):
+    """Every placed record of the file, in file order, as the arrays exchange_fetch_rows wants (name hash = md5)."""
+    from oracle import pysam_shim
+    fh = pysam_shim.AlignmentFile(bam_path)
+    names, sa, flag, mapq, lseq, nm = [], [], [], [], [], []
+    for r in fh.fetch():
+        names.append(r.query_name)
+        sa.append(r.get_tag("SA").encode() if r.has_tag("SA") else None)
+        flag.append(r.flag); mapq.append(r.mapping_quality); lseq.append(r.query_length)
+        nm.append(r.get_cigar_stats()[0][-1])
+    h = [hashlib.md5(n.encode()).digest() for n in names]
+    return {"names": names, "sa": sa, "flag": np.array(flag, np.uint32), "mapq": np.array(mapq, np.uint32),
+            "l_seq": np.array(lseq, np.uint32), "nm": np.array(nm, np.int32),
+            "name_lo": np.array([int.from_bytes(x[:8], "little") for x in h], np.uint64),
+            "name_hi": np.array([int.from_bytes(x[8:], "little") for x in h], np.uint64)}
+
+
+def _local(rows, r0, r1):
+    return {"name_lo": rows["name_lo"][r0:r1], "name_hi": rows["name_hi"][r0:r1],
+            "has_sa": np.array([s is not None for s in rows["sa"][r0:r1]], bool), "flag": rows["flag"][r0:r1],
+            "mapq": rows["mapq"][r0:r1], "l_seq": rows["l_seq"][r0:r1], "nm": rows["nm"][r0:r1],
+            "sa_text": lambda i: rows["sa"][r0 + i], "name": lambda i: rows["names"][r0 + i]}
+
+
+def _fetch_view(g):
+    """What fetch derives from gathered rows: per name, in first-SA-row order, the de-duplicated SA entries in file
+    order (ibg:145-151) and l_seq of the first row with flag < 256 (ibg:142-143)."""
+    sa, rl, order = {}, {}, []
+    for k, name in enumerate(g["names"]):
+        if g["flag"][k] < 256 and name not in rl:
+            rl[name] = int(g["l_seq"][k])
+        a, b = int(g["text_off"][k]), int(g["text_off"][k + 1])
+        if b > a:
+            if name not in sa:
+                sa[name] = []
+                order.append(name)
+            for ent in g["text"][a:b].tobytes().decode()[:-1].split(";"):
+                if ent not in sa[name]:
+                    sa[name].append(ent)
+    return [(n, sa[n], rl.get(n)) for n in order]
+
+
+def _reference_view(rows):
+    """The same thing straight from the whole file, the way the reference's loop does it."""
+    sa, rl, order = {}, {}, []
+    for k, name in enumerate(rows["names"]):
+        if rows["flag"][k] < 256 and name not in rl:
+            rl[name] = int(rows["l_seq"][k])
+        if rows["sa"][k] is not None:
+            if name not in sa:
+                sa[name] = []
+                order.append(name)
+            for ent in rows["sa"][k].decode()[:-1].split(";"):
+                if ent not in sa[name]:
+                    sa[name].append(ent)
+    return [(n, sa[n], rl.get(n)) for n in order]
+
+
+@pytest.fixture(scope="module")
+def c5_rows(tmp_path_factory):
+    from sim import configs
+    from sim.generate import simulate, write_dataset
+    data = simulate(configs.CONFIGS["C5"](scale=0.004))
+    paths = write_dataset(data, str(tmp_path_factory.mktemp("shard_c5")))
+    return _file_rows(paths["bam"]), paths
+
+
+def _run_threads(world, fn):
+    comms = sharded.ThreadComm.make(world)
+    out, err = [None] * world, []
+
+    def body(r):
+        try:
+            out[r] = fn(comms[r])
+        except Exception as ex:      # noqa
+            err.append(ex)
+            comms[r]._s.barrier.abort()
+    th = [threading.Thread(target=body, args=(r,)) for r in range(world)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not err, err
+    return out
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 5])
+def test_fetch_exchange_is_cut_invariant(c5_rows, world):
+    rows, _ = c5_rows
+    n = len(rows["names"])
+    want = _reference_view(rows)
+    assert len(want) > 50                                  # chimeric reads exist, many across chromosomes
+    cuts = [n * r // world for r in range(world + 1)]
+    got = _run_threads(world, lambda c: sharded.exchange_fetch_rows(c, _local(rows, cuts[c.rank], cuts[c.rank + 1])))
+    for g in got:
+        assert _fetch_view(g) == want
+        assert len(g["names"]) == len(g["flag"]) == len(g["text_off"]) - 1
+
+
+def test_shard_ranges_cover_and_balance():
+    off = np.concatenate([[0], np.cumsum(np.random.default_rng(1).integers(1, 400, 1000) * 16)]).astype(np.uint64)
+    for world in (1, 2, 3, 8):
+        rg = sharded.shard_ranges(off, world)
+        assert rg[0][0] == 0 and rg[-1][1] == 1000 and all(rg[k][1] == rg[k + 1][0] for k in range(world - 1))
+        sizes = [int(off[b]) - int(off[a]) for a, b in rg]
+        assert max(sizes) - min(sizes) <= 2 * 400 * 16
+    assert sharded.shard_ranges(np.zeros(1, np.uint64), 4) == [(0, 0)] * 4
+
+
+def test_member_handles_equal_low_words():
+    set_lo = np.array([5, 5, 7], np.uint64); set_hi = np.array([1, 9, 2], np.uint64)
+    lo = np.array([5, 5, 5, 7, 8], np.uint64); hi = np.array([9, 1, 3, 2, 0], np.uint64)
+    assert sharded._member(lo, hi, set_lo, set_hi).tolist() == [True, True, False, True, False]
+
+
+def test_smalldel_and_concordant_merges():
+    rows = [[("a", 0, 1, 2, 3, 4, 60), ("b", 1, 1, 2, 3, 4, 60)], [("c", 0, 5, 6, 7, 8, 30), ("d", 1, 5, 6, 7, 8, 30)]]
+    got = _run_threads(2, lambda c: sharded.merge_smalldel_rows(c, rows[c.rank]))
+    assert got[0] == got[1] == [rows[0][0], rows[1][0], rows[0][1], rows[1][1]]
+    # read r1 covers p / p+1 on shard 0 and the two flanks on shard 1: only the OR of its records passes the 4-point test
+    conc = [[(0, "r1", 3), (0, "r2", 15), (0, "r3", 15)], [(0, "r1", 12), (0, "r4", 4)]]
+    got = _run_threads(2, lambda c: sharded.combine_concordant(c, 1, conc[c.rank], [{"r3"}]))
+    assert got[0] == got[1] == ([2], [{"r1", "r2", "r3"}])
+
+
+def _gloo_worker(rank, world, port, bam, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        comm = sharded.TorchComm()
+        rows = _file_rows(bam)
+        n = len(rows["names"])
+        cuts = [n * r // world for r in range(world + 1)]
+        g = sharded.exchange_fetch_rows(comm, _local(rows, cuts[rank], cuts[rank + 1]))
+        tot = comm.all_reduce_sum(np.array([rank + 1, 10 * (rank + 1)], np.int64))
+        merged = sharded.merge_smalldel_rows(comm, [("r%d" % rank, 1 - rank, 0, 0, 0, 0, 0)])
+        q.put((rank, _fetch_view(g) == _reference_view(rows), tot.tolist(), [m[0] for m in merged]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_exchange_over_gloo_world2(c5_rows):
+    import torch.multiprocessing as mp
+    _, paths = c5_rows
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + os.getpid() % 2000
+    ps = [ctx.Process(target=_gloo_worker, args=(r, 2, port, paths["bam"], q)) for r in range(2)]
+    [p.start() for p in ps]
+    res = sorted(q.get(timeout=300) for _ in range(2))
+    [p.join(60) for p in ps]
+    assert all(p.exitcode == 0 for p in ps)
+    for rank, same, tot, merged in res:
+        assert same and tot == [3, 30] and merged == ["r1", "r0"]
