@@ -174,6 +174,7 @@ def build_plan(eng, cn_seg):
     b = batches[0]
     plan["seq_edges"] = ([r[0] for r in b], [r[1] for r in b], [r[2] for r in b])
     plan["conc"] = ([u[0] for u in uniq], [u[1] for u in uniq], rb_edge, rb_rec)
+    plan["uniq"], plan["rbps"] = uniq, rbps
     plan["cutoff"] = eng.min_cluster_cutoff
     eng.assign_cov()
     return plan
@@ -194,6 +195,35 @@ def device_pass(ctx, plan, gpu_ops):
         out["cl2"] = gpu_ops.cluster_arrays(ctx, cand, plan["cutoff"], 2000, plan["cutoff"], 100)
     out["seq"] = ctx.region_coverage(*plan["seq_edges"])
     out["conc"] = ctx.concordant(*plan["conc"])
+    return out
+
+
+SHARD_MS = {}
+
+
+def sharded_device_pass(eng, plan, gpu_ops):
+    """The same pass on one shard of the file, with the exchanges of SURVEY.md §8e inside (all ranks in lockstep)."""
+    ctx = eng._ctx
+    out = {}
+    t = [time.perf_counter()]
+
+    def lap(name):
+        t.append(time.perf_counter())
+        SHARD_MS[name] = SHARD_MS.get(name, 0.0) + (t[-1] - t[-2]) * 1e3
+    ctx.rescan(); lap("scan")
+    out["normal"] = eng._region_counts(*plan["normal"]); lap("normal_cov+allreduce")
+    out["fetch"], _ = eng._run_fetch(); lap("fetch_exchange")
+    out["smalldel"] = eng._smalldel_rows(*plan["intervals"]); lap("smalldel+gather")
+    c = plan["smalldel_cand"]
+    if len(c["chr1"]):
+        out["cl1"] = gpu_ops.cluster_arrays(ctx, c, plan["cutoff"], 2000, plan["cutoff"], 100)
+    cand = eng._chim_ctx.candidates_l(*plan["intervals"])
+    if cand["n"]:
+        out["cl2"] = gpu_ops.cluster_arrays(ctx, cand, plan["cutoff"], 2000, plan["cutoff"], 100)
+    lap("candidates+cluster")
+    out["seq"] = eng._region_counts(*plan["seq_edges"]); lap("seq_cov+allreduce")
+    cnt = eng._concordant_counts(plan["uniq"], plan["rbps"])[0]        # local stab rows, combined by name hash (NCCL)
+    out["conc"] = cnt.cpu().numpy(); lap("concordant+gather")
     return out
 
 
@@ -242,7 +272,19 @@ def main():
     from coral_b200.records import RecordSet
     import tempfile
 
-    cfg = workload_config(a.scale, seed_shift=rank)      # weak scaling: one C2-sized sample per GPU
+    comm = None
+    if world > 1:
+        # weak scaling: rank r holds a C2-shaped sample on its own three chromosomes of one 24-contig file, i.e. the
+        # r-th contiguous genomic-bin shard of ONE coordinate-sorted BAM (sim/configs.py::c2_shard)
+        import types
+        from sim import configs
+        from coral_b200 import sharded
+        cfg, all_cn, all_seeds = configs.c2_shard(rank, world, scale=a.scale)
+        cfg_files = types.SimpleNamespace(cn_rows=all_cn, seeds=all_seeds)
+        comm = sharded.TorchComm(device=torch.device("cuda", local))
+    else:
+        cfg = workload_config(a.scale)
+        cfg_files = cfg
     pinned = {}
 
     def alloc(nbytes):
@@ -253,7 +295,12 @@ def main():
     n_rec = data.n_records
     nbytes = int(data.rec_off[-1])
     recs = RecordSet([c for c, _ in cfg.refs], data.rec, data.rec_off, rec_slack=64)
-    cns, seed = write_inputs(cfg, tempfile.mkdtemp(prefix="coral_bench_%d_" % rank))
+    cns, seed = write_inputs(cfg_files, tempfile.mkdtemp(prefix="coral_bench_%d_" % rank))
+
+    def make_engine(placement):
+        if world > 1:
+            return sharded.make_sharded_engine(recs, seed, comm, device=local, placement=placement, presharded=True)
+        return bam_to_breakpoint_nanopore(None, seed, device=local, records=recs, placement=placement)
     alg_bytes = record_field_bytes(data.rec, data.rec_off)
 
     if a.only == "scan":
@@ -276,7 +323,7 @@ def main():
 
     def e2e_pass():
         t = time.perf_counter()
-        eng = bam_to_breakpoint_nanopore(None, seed, device=local, records=recs, placement=a.e2e_placement)
+        eng = make_engine(a.e2e_placement)
         for name, fn, args in (("load+scan", None, ()), ("read_cns", eng.read_cns, (cns,)), ("fetch", eng.fetch, ()),
                                ("hash", eng.hash_alignment_to_seg, ()), ("intervals", eng.find_amplicon_intervals, ()),
                                ("smalldel", eng.find_smalldel_breakpoints, ()), ("breakpoints", eng.find_breakpoints, ()),
@@ -286,23 +333,31 @@ def main():
             t2 = time.perf_counter()
             e2e_stage[name] = (t2 - t) * 1e3
             t = t2
-        eng._ctx.close()
+        eng.closebam()
         return eng
 
     # plan + resident context
-    eng0 = bam_to_breakpoint_nanopore(None, seed, device=local, records=recs, placement="copy")
+    eng0 = make_engine("copy")
     plan = build_plan(eng0, cns)
     ctx = eng0._ctx
     tab = ctx.record_table()
     aligned = int(tab["aligned_bases"].sum())
     n_bp = len(eng0.new_bp_list)
+    def one_pass():
+        if world > 1:
+            return sharded_device_pass(eng0, plan, gpu_ops)
+        return device_pass(ctx, plan, gpu_ops)
+
+    def n_launches():
+        return ctx.launch_count + (eng0._cctx.launch_count if world > 1 else 0)
+
     for _ in range(warm):
-        out = device_pass(ctx, plan, gpu_ops)
+        out = one_pass()
     d2h = result_bytes(out)
     if a.profile:
         torch.cuda.synchronize()
         torch.cuda.cudart().cudaProfilerStart()
-        device_pass(ctx, plan, gpu_ops)
+        one_pass()
         torch.cuda.synchronize()
         torch.cuda.cudart().cudaProfilerStop()
         print(json.dumps({"profile": "one device pass", "records": n_rec}), flush=True)
@@ -316,17 +371,17 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    l0 = ctx.launch_count
+    l0 = n_launches()
     barrier()
     t0 = time.perf_counter()
     scan_ms, stage_ms = [], np.zeros(8)
     for _ in range(a.steps):
-        device_pass(ctx, plan, gpu_ops)
+        one_pass()
         scan_ms.append(ctx.stage_ms(0))
         stage_ms += np.array([max(ctx.stage_ms(s), 0.0) for s in range(8)])
     barrier()
     dt = time.perf_counter() - t0
-    launches = ctx.launch_count - l0
+    launches = n_launches() - l0
     # e2e through the public class, from pinned host records
     e2e_pass()
     barrier()
@@ -340,9 +395,12 @@ def main():
     sampler.join(timeout=2)
 
     tt = torch.tensor([dt, dt_e2e], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([n_rec, aligned, launches], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     dt, dt_e2e = float(tt[0]), float(tt[1])
+    n_rec_all, aligned_all, launches_all = int(tot[0]), int(tot[1]), int(tot[2])
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -353,26 +411,33 @@ def main():
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     names = ["scan", "coverage", "fetch", "smalldel", "candidates", "cluster", "bpc2bp", "concordant"]
     out = {
-        "metric": METRIC, "value": n_rec * world * a.steps / dt, "unit": "records/s",
+        "metric": METRIC, "value": n_rec_all * a.steps / dt, "unit": "records/s",
         "n_gpus": world, "steps": a.steps, "warmup": warm, "ms_per_step": dt / a.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8/int32/int64 (f64 stats)", "data": "synthetic",
         "config": {"workload": "C2 multi-segment ecDNA: 3 seeds/6 Mb, CN 40, 50x ONT 30 kb", "scale": a.scale,
                    "records_per_gpu": n_rec, "record_bytes_per_gpu": nbytes, "aligned_gbases_per_gpu": aligned / 1e9,
-                   "breakpoints_found": n_bp, "sharding": "one independent sample per GPU, no collective",
+                   "breakpoints_found": n_bp,
+                   "sharding": ("single GPU" if world == 1 else
+                                "rank r = r-th contiguous genomic-bin shard (its own 3 chromosomes, C2-shaped) of one "
+                                "24-contig file; NCCL all-gather of chimeric fetch rows / small-del rows / concordant "
+                                "rows and all-reduce of coverage sums inside every step"),
                    "l2_policy": "inputs (%.2f GB of record fields per pass) larger than the 126 MB L2" % (alg_bytes / 1e9)},
-        "aligned_gbases_per_s": aligned * world * a.steps / dt / 1e9,
-        "e2e": {"value": n_rec * world * e2e_steps / dt_e2e, "unit": "records/s", "ms_per_step": dt_e2e / e2e_steps * 1e3,
+        "aligned_gbases_per_s": aligned_all * a.steps / dt / 1e9,
+        "e2e": {"value": n_rec_all * e2e_steps / dt_e2e, "unit": "records/s", "ms_per_step": dt_e2e / e2e_steps * 1e3,
                 "h2d_bytes_per_step": (alg_bytes - 76 * n_rec if a.e2e_placement == "mapped" else nbytes) + 8 * (n_rec + 1),
                 "d2h_bytes_per_step": d2h, "placement": a.e2e_placement, "stage_ms": e2e_stage},
-        "gpu_launches": int(launches),
+        "gpu_launches": int(launches_all),
         "roofline": {"bound": "hbm", "kernel": "k_scan_records", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None,
+                     "frac": achieved / peak, "traffic": 5.621e9 if (world == 1 and a.scale == 1.0) else None,
+                     "traffic_source": "ncu --set full dram__bytes_read+write of one launch at this config (profiles/r1_scan_full.txt)",
                      "peak_source": "MEASURED_PEAKS.json (of measured)" if peaks else "fallback 6650 (of fallback)",
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": k_ms},
         "stage_ms_per_step": {n: float(stage_ms[i] / a.steps) for i, n in enumerate(names)},
         "clocks": sampler.summary(),
     }
+    if world > 1:
+        out["sharded_stage_ms_per_step"] = {k: v / (a.steps + warm) for k, v in SHARD_MS.items()}
     if rank == 0:
         if world == 1:
             try:

@@ -188,6 +188,18 @@ class Context(object):
         self._check(self._L.coral_load_rows(self._h, ctypes.c_int64(n), _p(text), ctypes.c_uint64(text.nbytes), _p(text_off),
                                             *[_p(x) for x in a]))
 
+    def device_view(self):
+        """Device addresses (recs, offsets, name_lo, name_hi, flag_mapq, l_seq, nm, sa_off, sa_len)."""
+        ptrs = (ctypes.c_uint64 * 9)()
+        self._check(self._L.coral_device_view(self._h, ptrs, 9))
+        return [int(x) for x in ptrs]
+
+    def load_rows_dev(self, n, text_ptr, text_bytes, off_ptr, lo_ptr, hi_ptr, fm_ptr, lseq_ptr, nm_ptr, sa_off_ptr, sa_len_ptr):
+        vp = ctypes.c_void_p
+        self._check(self._L.coral_load_rows_dev(self._h, ctypes.c_int64(n), vp(text_ptr), ctypes.c_uint64(text_bytes), vp(off_ptr),
+                                                vp(lo_ptr), vp(hi_ptr), vp(fm_ptr), vp(lseq_ptr), vp(nm_ptr), vp(sa_off_ptr),
+                                                vp(sa_len_ptr)))
+
     def rescan(self):
         self._check(self._L.coral_rescan(self._h))
 

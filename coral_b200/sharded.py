@@ -222,8 +222,10 @@ class _ShardView(object):
         pass
 
 
-def make_sharded_engine(records, seedfile, comm, device=0, placement="auto"):
-    """Factory (keeps the CUDA-bound import out of the CPU tests of the exchange logic)."""
+def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", presharded=False):
+    """Factory (keeps the CUDA-bound import out of the CPU tests of the exchange logic).
+    `records`: the whole file (every rank then takes its range of shard_ranges) or, with presharded=True, this rank's
+    own shard — ranks must hold increasing, contiguous ranges of one coordinate-sorted file."""
     from . import _abi
     from .infer_breakpoint_graph import bam_to_breakpoint_nanopore
 
@@ -233,12 +235,17 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto"):
 
         def __init__(self):
             self._comm = comm
-            r0, r1 = shard_ranges(records.rec_off, comm.world)[comm.rank]
-            view = _ShardView(records, r0, r1)
+            if presharded:
+                view = records
+            else:
+                r0, r1 = shard_ranges(records.rec_off, comm.world)[comm.rank]
+                view = _ShardView(records, r0, r1)
             bam_to_breakpoint_nanopore.__init__(self, None, seedfile, device=device, records=view, placement=placement)
             self._cctx = _abi.Context(device)          # rows-only ctx: the gathered fetch rows live here
             self._cctx.set_references(view.references)
-            self._row_names = []
+            self._row_names = None
+            self._rows = None
+            self._name_hash = {}     # read name -> 128-bit hash as two int64 (for the rbps rows of the concordant combine)
 
         @property
         def _chim_ctx(self):
@@ -250,52 +257,115 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto"):
             tot = self._comm.all_reduce_sum(np.concatenate([bs, rc]).astype(np.int64))
             return tot[:len(bs)], tot[len(bs):]
 
-        # a1: the exchange
+        # ---- tensor views of this shard's device tables (exchange.py runs on them) ---------------------------------
+        def _views(self):
+            import torch
+            from . import exchange
+            ctx = self._ctx
+            p = ctx.device_view()
+            n = ctx.n_records
+            nb = int(self.lr_bamfh.rec_off[-1]) if n else 0
+            dev = torch.device("cuda", device)
+            v = exchange.view
+            return {"recs": v(p[0], nb, "|u1", dev), "off": v(p[1], n + 1 if n else 0, "<i8", dev),
+                    "name_lo": v(p[2], n, "<i8", dev), "name_hi": v(p[3], n, "<i8", dev), "flag_mapq": v(p[4], n, "<i4", dev),
+                    "l_seq": v(p[5], n, "<i4", dev), "nm": v(p[6], n, "<i4", dev), "sa_off": v(p[7], n, "<i4", dev),
+                    "sa_len": v(p[8], n, "<i4", dev)}
+
+        # a1: the exchange, on the GPU: rows selected, all-gathered (NCCL) and loaded without visiting the host
         def _run_fetch(self):
-            ctx, fh = self._ctx, self.lr_bamfh
-            keys = ctx.record_keys()
-            tab = ctx.record_table()
-            rec, off = fh.rec, fh.rec_off
-
-            def sa_text(i):
-                b = int(off[i]) + int(keys["sa_off"][i])
-                return rec[b:b + int(keys["sa_len"][i])].tobytes()
-
-            rows = exchange_fetch_rows(self._comm, {
-                "name_lo": keys["name_lo"], "name_hi": keys["name_hi"], "has_sa": keys["sa_off"] != 0,
-                "flag": tab["flag"].astype(np.uint32), "mapq": tab["mapq"].astype(np.uint32),
-                "l_seq": tab["l_seq"].astype(np.uint32), "nm": keys["nm"], "sa_text": sa_text, "name": fh.query_name})
-            self._row_names = rows["names"]
-            self._cctx.load_rows(rows["text"], rows["text_off"], rows["name_lo"], rows["name_hi"], rows["flag"],
-                                 rows["mapq"], rows["l_seq"], rows["nm"])
+            import torch
+            from . import exchange
+            tc = exchange.TensorComm(self._comm)
+            tv = self._views()
+            rows = exchange.fetch_exchange(tc, tv)
+            s1, s2, nn, zd = self._ctx.nm_partials()
+            parts = torch.cat(tc.all_gather(torch.tensor([[s1, s2, float(nn), float(zd)]], dtype=torch.float64,
+                                                         device=rows["text"].device)), 0).cpu().numpy()
+            torch.cuda.current_stream().synchronize()
+            m = int(rows["name_lo"].shape[0])
+            keep = [rows[k].contiguous() for k in ("text", "text_off", "name_lo", "name_hi", "flag_mapq", "l_seq", "nm",
+                                                   "sa_off", "sa_len")]
+            self._cctx.load_rows_dev(m, keep[0].data_ptr(), int(keep[0].shape[0]), *[t.data_ptr() for t in keep[1:]])
             f = self._cctx.fetch()
-            # nm_stats (ibg:153-157) run over ALL records: all-reduce the shard partials (f64 sum order differs from
-            # the 1-GPU order: within 1e-9 relative, unused downstream)
-            s1, s2, nn, zd = ctx.nm_partials()
-            parts = self._comm.all_gather((s1, s2, nn, zd))
-            f["nm_sum"] = float(sum(p[0] for p in parts)); f["nm_sumsq"] = float(sum(p[1] for p in parts))
-            f["nm_n"] = int(sum(p[2] for p in parts)); f["nm_zero_div"] = int(sum(p[3] for p in parts))
-            return f, (lambda r: self._row_names[r])
+            # nm_stats (ibg:153-157) run over ALL records: the shard partials are summed in rank order (the f64 sum
+            # order differs from the 1-GPU order: within 1e-9 relative, unused downstream)
+            f["nm_sum"] = float(parts[:, 0].sum()); f["nm_sumsq"] = float(parts[:, 1].sum())
+            f["nm_n"] = int(parts[:, 2].sum()); f["nm_zero_div"] = int(parts[:, 3].sum())
+            self._rows, self._row_names = rows, None
+
+            def name_of(r):
+                if self._row_names is None:         # one D2H of the gathered text, only when names are materialised
+                    self._row_names = exchange.row_names(self._rows)
+                    lo = self._rows["name_lo"].cpu().numpy(); hi = self._rows["name_hi"].cpu().numpy()
+                    for k, nm in enumerate(self._row_names):
+                        self._name_hash[nm] = (int(lo[k]), int(hi[k]))
+                return self._row_names[r]
+            return f, name_of
 
         def find_breakpoints(self):
             self._cctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
             bam_to_breakpoint_nanopore.find_breakpoints(self)
 
-        # a3: local gap rows, merged in emission order
+        # a3: local gap rows (+ the name hash of each), merged in emission order
         def _smalldel_rows(self, t, s, e):
-            return merge_smalldel_rows(self._comm, bam_to_breakpoint_nanopore._smalldel_rows(self, t, s, e))
-
-        # a11: name-level set algebra across shards
-        def _concordant_support(self, uniq, rbps):
-            _, rows = self._ctx.concordant([u[0] for u in uniq], [u[1] for u in uniq], [], [])
-            name_of = {}
-            out = []
-            for e, r, m in zip(rows["edge"].tolist(), rows["rec"].tolist(), rows["mask"].tolist()):
-                nm = name_of.get(r)
+            rows = self._ctx.smalldel(t, s, e)
+            recs = rows["rec"].astype(np.int64)
+            lo = hi = np.zeros(0, np.int64)
+            if len(recs):
+                import torch
+                tv = self._views()
+                idx = torch.as_tensor(recs, device=tv["name_lo"].device)
+                lo, hi = tv["name_lo"][idx].cpu().numpy(), tv["name_hi"][idx].cpu().numpy()
+            names = {}
+            local = []
+            cols = [rows[k].tolist() for k in ("ai", "next_start", "prev_end", "first_start", "last_end", "mapq")]
+            for k, rec in enumerate(recs.tolist()):
+                nm = names.get(rec)
                 if nm is None:
-                    nm = name_of[r] = self.lr_bamfh.query_name(r)
-                out.append((e, nm, m))
-            return combine_concordant(self._comm, len(uniq), out, rbps)
+                    nm = names[rec] = self.lr_bamfh.query_name(rec)
+                local.append((nm, cols[0][k], cols[1][k], cols[2][k], cols[3][k], cols[4][k], cols[5][k], int(lo[k]), int(hi[k])))
+            merged = merge_smalldel_rows(self._comm, local)
+            for r in merged:
+                self._name_hash[r[0]] = (r[7], r[8])
+            return [r[:7] for r in merged]
+
+        # a11: name-level set algebra across shards, on name hashes
+        def _concordant_counts(self, uniq, rbps):
+            import torch
+            from . import exchange
+            _, rows = self._ctx.concordant([u[0] for u in uniq], [u[1] for u in uniq], [], [])
+            tv = self._views()
+            dev = tv["name_lo"].device
+            rec = torch.as_tensor(rows["rec"].astype(np.int64), device=dev)
+            edge = torch.as_tensor(rows["edge"].astype(np.int64), device=dev)
+            mask = torch.as_tensor(rows["mask"].astype(np.int64), device=dev)
+            rb = [(k, ) + self._name_hash[nm] for k, names in enumerate(rbps) for nm in names if nm in self._name_hash]
+            rbt = torch.as_tensor(np.array(rb, np.int64).reshape(-1, 3), device=dev)
+            cnt, keys, m = exchange.concordant_combine(exchange.TensorComm(self._comm), len(uniq), edge, tv["name_lo"][rec],
+                                                       tv["name_hi"][rec], mask, rbt[:, 0], rbt[:, 1], rbt[:, 2])
+            return cnt, keys, m, (rec, mask, tv)
+
+        def _concordant_support(self, uniq, rbps):
+            import torch
+            from . import exchange
+            cnt, keys, m, (rec, mask, tv) = self._concordant_counts(uniq, rbps)
+            # ce[9] wants the read NAMES covering p or p+1: every rank contributes the names of its own records
+            urec = torch.unique(rec[(mask & 3) != 0])
+            base = tv["off"][urec]
+            ln = tv["recs"][base + 12].to(torch.int64)
+            blob = exchange._gather_bytes(tv["recs"], base + 36, ln).cpu().numpy().tobytes()
+            mine = (tv["name_lo"][urec].cpu().numpy(), tv["name_hi"][urec].cpu().numpy(), blob.split(b"\0")[:len(urec)])
+            table = {}
+            for lo, hi, names in self._comm.all_gather(mine):
+                for a, b, nm in zip(lo.tolist(), hi.tolist(), names):
+                    table[(a, b)] = nm.decode()
+            sel = (m & 3) != 0
+            kk = keys[sel].cpu().numpy()
+            out = [set() for _ in uniq]
+            for e, a, b in kk.tolist():
+                out[e].add(table[(a, b)])
+            return [int(x) for x in cnt.cpu().numpy()], out
 
         def closebam(self):
             self._cctx.close()

@@ -164,6 +164,16 @@ int coral_load_rows(coral_ctx* ctx, int64_t n_rows, const uint8_t* text, uint64_
                     const uint64_t* name_lo, const uint64_t* name_hi, const uint32_t* flag, const uint32_t* mapq,
                     const uint32_t* l_seq, const int32_t* nm);
 
+/* Device-side form of the same exchange: coral_device_view hands out the device addresses of the record buffer,
+ * the offsets and the table columns (recs, offsets, name_lo, name_hi, flag|mapq<<16, l_seq, nm, sa_off, sa_len — valid
+ * until the next load / rescan, read-only), so the caller can select and all-gather the rows on the GPU (NCCL);
+ * coral_load_rows_dev takes the gathered arrays from device memory (slot i of d_text holds the row's SA text at
+ * d_sa_off[i], 0 = no SA tag). */
+int coral_device_view(coral_ctx* ctx, uint64_t* ptrs, int32_t n_ptrs);
+int coral_load_rows_dev(coral_ctx* ctx, int64_t n_rows, const uint8_t* d_text, uint64_t text_bytes, const uint64_t* d_text_off,
+                        const uint64_t* d_name_lo, const uint64_t* d_name_hi, const uint32_t* d_flag_mapq,
+                        const uint32_t* d_l_seq, const int32_t* d_nm, const uint32_t* d_sa_off, const uint32_t* d_sa_len);
+
 /* Operator form of cigar_parsing.alignment_from_satags / cigar2pos* (cigar_parsing.py:17-269) on SA text the
  * caller supplies: `text` holds the entries, read r owns entries [ent_ptr[r], ent_ptr[r+1]) whose bytes are
  * text[ent_beg[k] : ent_end[k]].  Per read: status as in coral_fetch; per entry, in the read's stable

@@ -130,5 +130,36 @@ def c5_whole_genome(scale=1.0, seed=20240215 + 5, cov=30.0, n_seeds=20, chroms=N
                      cycles=cycles, read_mean=20000, model="ont", noise_frac=0.005, seed=seed)
 
 
+ALL_CHROMS = ['chr%d' % i for i in range(1, 23)] + ['chrX', 'chrY']
+
+
+def c2_shard(rank, world, scale=1.0, seed=20240215 + 2, cov=50.0, bg_pad=6 * MB):
+    """Weak-scaling form of C2 for the multi-GPU bench: rank r carries a full C2-shaped sample (3 seeds / 6 Mb,
+    CN 40, 12 junctions, ONT 30 kb) on its own three chromosomes, ALL_CHROMS[3r : 3r + 3], against the common
+    24-contig header — so the ranks' record sets, taken in rank order, are the contiguous genomic-bin shards of ONE
+    coordinate-sorted file.  Returns (this rank's SimConfig, cn rows of all ranks, seeds of all ranks)."""
+    assert 1 <= world <= 8
+    refs = [(c, CHR_SIZES[c]) for c in ALL_CHROMS]
+    lay = [(0, 0, 700_000, '+'), (1, 0, 600_000, '-'), (0, 1_200_000, 1_800_000, '+'), (2, 0, 500_000, '+'),
+           (1, 1_000_000, 1_500_000, '+'), (2, 1_200_000, 1_700_000, '-'), (0, 800_000, 1_100_000, '-'),
+           (1, 650_000, 950_000, '+'), (2, 600_000, 1_100_000, '+'), (0, 1_850_000, 2_000_000, '+'),
+           (1, 1_550_000, 2_000_000, '-'), (2, 1_750_000, 2_000_000, '+')]
+    base = 20 * MB
+    all_cn, all_seeds, mine = [], [], None
+    for r in range(world):
+        ch = ALL_CHROMS[3 * r:3 * r + 3]
+        segs = [(ch[k], base + a, base + b, o) for (k, a, b, o) in lay]
+        cn_rows, bg, seeds = [], [], []
+        for c in ch:
+            lo, hi = base - bg_pad, base + 2 * MB + bg_pad
+            cn_rows += _tile_cn(c, lo, hi, [(base, base + 2 * MB, 40.0)], step=3 * MB)
+            bg.append((c, lo, hi)); seeds.append((c, base, base + 2 * MB - 1))
+        all_cn += cn_rows; all_seeds += seeds
+        if r == rank:
+            mine = SimConfig(name="C2", refs=refs, cn_rows=cn_rows, seeds=seeds, background=bg, cov=cov * scale,
+                             cycles=[Cycle(segs, 40.0)], read_mean=30000, model="ont", seed=seed + 1000 * r)
+    return mine, all_cn, all_seeds
+
+
 CONFIGS = {"C1": c1_single_ecdna, "C2": c2_multi_segment, "C3": c3_smalldel_heavy, "C4": c4_complex,
            "C5": c5_whole_genome}

@@ -171,3 +171,112 @@ def test_exchange_over_gloo_world2(c5_rows):
     assert all(p.exitcode == 0 for p in ps)
     for rank, same, tot, merged in res:
         assert same and tot == [3, 30] and merged == ["r1", "r0"]
+
+
+# ---- tensor form of the exchanges (coral_b200/exchange.py) on CPU tensors ------------------------------------------
+def _tensor_view(rows, r0, r1):
+    """Synthetic record bytes for rows [r0, r1): 36-byte core with l_read_name at +12, the name, then the SA text."""
+    import torch
+    buf, off, sa_off, sa_len = bytearray(), [0], [], []
+    for k in range(r0, r1):
+        name = rows["names"][k].encode() + b"\0"
+        core = bytearray(36); core[12] = len(name)
+        sa = rows["sa"][k] or b""
+        sa_off.append(36 + len(name) if sa else 0); sa_len.append(len(sa))
+        rec = bytes(core) + name + sa
+        rec += b"\0" * (-len(rec) % 16)
+        buf += rec; off.append(len(buf))
+    i32 = lambda a: torch.as_tensor(np.asarray(a, np.int64).astype(np.int32))
+    return {"recs": torch.as_tensor(np.frombuffer(bytes(buf), np.uint8).copy()), "off": torch.as_tensor(np.array(off, np.int64)),
+            "name_lo": torch.as_tensor(rows["name_lo"][r0:r1].view(np.int64).copy()),
+            "name_hi": torch.as_tensor(rows["name_hi"][r0:r1].view(np.int64).copy()),
+            "flag_mapq": i32(rows["flag"][r0:r1].astype(np.int64) | (rows["mapq"][r0:r1].astype(np.int64) << 16)),
+            "l_seq": i32(rows["l_seq"][r0:r1]), "nm": i32(rows["nm"][r0:r1]), "sa_off": i32(sa_off), "sa_len": i32(sa_len)}
+
+
+def _tensor_rows_as_numpy(g):
+    from coral_b200 import exchange
+    off = g["text_off"].numpy(); ln = g["name_len"].numpy(); text = g["text"].numpy()
+    sa_text, sa_off = [], [0]
+    for i in range(len(ln)):
+        sa_text.append(text[int(off[i]) + int(ln[i]):int(off[i + 1])].tobytes())
+        sa_off.append(sa_off[-1] + len(sa_text[-1]))
+    return {"names": exchange.row_names(g), "flag": (g["flag_mapq"].numpy().astype(np.int64) & 0xffff),
+            "l_seq": g["l_seq"].numpy(), "text": np.frombuffer(b"".join(sa_text), np.uint8), "text_off": np.array(sa_off)}
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+def test_tensor_fetch_exchange_matches_reference(c5_rows, world):
+    from coral_b200 import exchange
+    rows, _ = c5_rows
+    n = len(rows["names"])
+    want = _reference_view(rows)
+    cuts = [n * r // world for r in range(world + 1)]
+    got = _run_threads(world, lambda c: exchange.fetch_exchange(exchange.TensorComm(c), _tensor_view(rows, cuts[c.rank], cuts[c.rank + 1])))
+    for g in got:
+        assert _fetch_view(_tensor_rows_as_numpy(g)) == want
+        has = g["sa_len"].numpy() > 0
+        assert np.array_equal(g["sa_off"].numpy()[has], g["name_len"].numpy()[has]) and not g["sa_off"].numpy()[~has].any()
+
+
+def test_tensor_concordant_combine_matches_numpy():
+    import torch
+    from coral_b200 import exchange
+    rng = np.random.default_rng(5)
+    names = ["r%d" % i for i in range(300)]
+    h = {nm: (int(rng.integers(-2**62, 2**62)), int(rng.integers(-2**62, 2**62))) for nm in names}
+    n_edges, world = 6, 3
+    local = [[(int(rng.integers(n_edges)), names[int(rng.integers(300))], int(rng.integers(1, 16))) for _ in range(2000)]
+             for _ in range(world)]
+    rbps = [set(names[int(j)] for j in rng.integers(0, 300, 20)) for _ in range(n_edges)]
+    want = _run_threads(world, lambda c: sharded.combine_concordant(c, n_edges, local[c.rank], rbps))[0]
+
+    def run(c):
+        rows = local[c.rank]
+        t = lambda a: torch.as_tensor(np.array(a, np.int64))
+        rb = [(e, ) + h[nm] for e, s in enumerate(rbps) for nm in s]
+        rbt = t(rb).reshape(-1, 3)
+        return exchange.concordant_combine(exchange.TensorComm(c), n_edges, t([r[0] for r in rows]), t([h[r[1]][0] for r in rows]),
+                                           t([h[r[1]][1] for r in rows]), t([r[2] for r in rows]), rbt[:, 0], rbt[:, 1], rbt[:, 2])
+    inv = {v: k for k, v in h.items()}
+    for cnt, keys, m in run_all(world, run):
+        assert cnt.tolist() == want[0]
+        got_names = [set() for _ in range(n_edges)]
+        for (e, a, b), mm in zip(keys.tolist(), m.tolist()):
+            if mm & 3:
+                got_names[e].add(inv[(a, b)])
+        assert got_names == want[1]
+
+
+def run_all(world, fn):
+    return _run_threads(world, fn)
+
+
+def _gloo_tensor_worker(rank, world, port, bam, q):
+    import torch.distributed as dist
+    from coral_b200 import exchange
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        tc = exchange.TensorComm(sharded.TorchComm())
+        rows = _file_rows(bam)
+        n = len(rows["names"])
+        cuts = [n * r // world for r in range(world + 1)]
+        g = exchange.fetch_exchange(tc, _tensor_view(rows, cuts[rank], cuts[rank + 1]))
+        q.put((rank, _fetch_view(_tensor_rows_as_numpy(g)) == _reference_view(rows)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_tensor_exchange_over_gloo_world2(c5_rows):
+    import torch.multiprocessing as mp
+    _, paths = c5_rows
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31500 + os.getpid() % 2000
+    ps = [ctx.Process(target=_gloo_tensor_worker, args=(r, 2, port, paths["bam"], q)) for r in range(2)]
+    [p.start() for p in ps]
+    res = sorted(q.get(timeout=300) for _ in range(2))
+    [p.join(60) for p in ps]
+    assert all(p.exitcode == 0 for p in ps) and all(ok for _, ok in res)
