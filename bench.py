@@ -223,7 +223,7 @@ def sharded_device_pass(eng, plan, gpu_ops):
     lap("candidates+cluster")
     out["seq"] = eng._region_counts(*plan["seq_edges"]); lap("seq_cov+allreduce")
     cnt = eng._concordant_counts(plan["uniq"], plan["rbps"])[0]        # local stab rows, combined by name hash (NCCL)
-    out["conc"] = cnt.cpu().numpy(); lap("concordant+gather")
+    out["conc"] = cnt; lap("concordant+gather")
     return out
 
 

@@ -188,6 +188,20 @@ class Context(object):
         self._check(self._L.coral_load_rows(self._h, ctypes.c_int64(n), _p(text), ctypes.c_uint64(text.nbytes), _p(text_off),
                                             *[_p(x) for x in a]))
 
+    def concordant_device_rows(self):
+        """Device addresses (edge, rec, mask: uint32 arrays) and row count of the last concordant() call."""
+        ptrs = (ctypes.c_uint64 * 3)()
+        n = ctypes.c_int64()
+        self._check(self._L.coral_concordant_device_rows(self._h, ptrs, ctypes.byref(n)))
+        return [int(x) for x in ptrs], int(n.value)
+
+    def count_name_rows(self, n_edges, n, edge_ptr, lo_ptr, hi_ptr, mask_ptr):
+        vp = ctypes.c_void_p
+        cnt = np.zeros(max(n_edges, 1), np.int64)
+        self._check(self._L.coral_count_name_rows(self._h, int(n_edges), ctypes.c_int64(n), vp(edge_ptr), vp(lo_ptr), vp(hi_ptr),
+                                                  vp(mask_ptr), _p(cnt)))
+        return cnt[:n_edges]
+
     def device_view(self):
         """Device addresses (recs, offsets, name_lo, name_hi, flag_mapq, l_seq, nm, sa_off, sa_len)."""
         ptrs = (ctypes.c_uint64 * 9)()
@@ -314,7 +328,7 @@ class Context(object):
                 _p(out["row_pos2"]), _p(out["row_nb"]), _p(out["row_first"]), _p(out["row_stats"])))
         return out
 
-    def concordant(self, tid, p, rb_edge, rb_rec):
+    def concordant(self, tid, p, rb_edge, rb_rec, fetch_rows=True):
         """Edges sorted by (tid, p).  -> (lr_count int64[n], rows dict(edge, rec, mask))."""
         tid = np.ascontiguousarray(tid, dtype=np.int32)
         p = np.ascontiguousarray(p, dtype=np.int32)
@@ -327,7 +341,7 @@ class Context(object):
                                              _p(cnt), ctypes.byref(nr)))
         nr = nr.value
         rows = {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
-        if nr:
+        if nr and fetch_rows:
             self._check(self._L.coral_get_concordant_rows(self._h, _p(rows["edge"]), _p(rows["rec"]), _p(rows["mask"])))
         return cnt, rows
 

@@ -101,6 +101,31 @@ __global__ void k_stab_count(int64_t n, const uint32_t* __restrict__ perm, const
     if ((m & 15u) == 15u && !(m & 16u)) atomicAdd(count + e, 1ull);
 }
 
+// ---- the same count on explicit (edge, name hash, mask) rows: the multi-GPU combine --------------------------------
+__global__ void k_rows_key(int64_t n, const uint32_t* __restrict__ perm, const uint64_t* __restrict__ a, uint64_t* __restrict__ key) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) key[i] = a[perm[i]];
+}
+__global__ void k_rows_count(int64_t n, const uint32_t* __restrict__ perm, const uint64_t* __restrict__ edge,
+                             const uint64_t* __restrict__ lo, const uint64_t* __restrict__ hi, const uint64_t* __restrict__ mask,
+                             unsigned long long* __restrict__ count, int64_t n_edges) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t r = perm[i];
+    const uint64_t e = edge[r], l = lo[r], h = hi[r];
+    if (i > 0) {
+        const uint32_t q = perm[i - 1];
+        if (edge[q] == e && lo[q] == l && hi[q] == h) return;  // not a head
+    }
+    uint64_t m = 0;
+    for (int64_t j = i; j < n; j++) {
+        const uint32_t q = perm[j];
+        if (edge[q] != e || lo[q] != l || hi[q] != h) break;
+        m |= mask[q];
+    }
+    if ((m & 15u) == 15u && !(m & 16u) && (int64_t)e < n_edges) atomicAdd(count + e, 1ull);
+}
+
 }  // namespace coral
 
 #define LAUNCH_1D(kern, n, ...)                                                          \
@@ -195,5 +220,46 @@ extern "C" int coral_get_concordant_rows(coral_ctx* c, uint32_t* edge, uint32_t*
     if (rec) CORAL_TRY(d2h(c, rec, c->sw[4].p, n));
     if (mask) CORAL_TRY(d2h(c, mask, c->sw[5].p, n));
     CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    return CORAL_OK;
+}
+
+// Device addresses of the rows left by the last coral_concordant (edge, rec, mask: uint32 each), so a multi-GPU caller
+// can all-gather them (as (edge, name hash, mask)) without a host round trip.
+extern "C" int coral_concordant_device_rows(coral_ctx* c, uint64_t* ptrs, int64_t* n_rows) {
+    if (!c || !ptrs || !n_rows) return CORAL_E_ARG;
+    if (!c->stab_valid) { c->err = "coral_concordant_device_rows before coral_concordant"; return CORAL_E_STATE; }
+    for (int k = 0; k < 3; k++) ptrs[k] = (uint64_t)reinterpret_cast<uintptr_t>(c->sw[3 + k].p);
+    *n_rows = c->stab_n;
+    return CORAL_OK;
+}
+
+// ce[8] from explicit rows, all arrays on this ctx's device (uint64 each): per (edge, name hash) the masks are OR-ed;
+// a name counts for its edge when bits 0..3 are all set and bit 4 (rbps member, ibg:1047-1053) is not.
+extern "C" int coral_count_name_rows(coral_ctx* c, int32_t n_edges, int64_t n, const uint64_t* d_edge, const uint64_t* d_lo,
+                                     const uint64_t* d_hi, const uint64_t* d_mask, int64_t* lr_count) {
+    using namespace coral;
+    if (!c || n_edges < 0 || n < 0 || !lr_count) return CORAL_E_ARG;
+    cudaSetDevice(c->device);
+    for (int32_t i = 0; i < n_edges; i++) lr_count[i] = 0;
+    if (n == 0 || n_edges == 0) return CORAL_OK;
+    if (n >= ((int64_t)1 << 32)) { c->err = "too many rows"; return CORAL_E_ARG; }
+    DevBuf* w = c->sw;
+    CORAL_CUDA(c, w[7].ensure((size_t)n * 24 + 64 + (size_t)n_edges * 8));
+    uint64_t* keyA = w[7].as<uint64_t>(); uint64_t* keyB = keyA + n;
+    uint32_t* pa = reinterpret_cast<uint32_t*>(keyB + n); uint32_t* pb = pa + n;
+    unsigned long long* d_count = reinterpret_cast<unsigned long long*>(pb + n);   // byte offset 24 n: 8-byte aligned
+    CORAL_CUDA(c, cudaMemsetAsync(d_count, 0, (size_t)n_edges * 8, c->stream));
+    LAUNCH_1D(k_stab_iota, n, n, pa);
+    LAUNCH_1D(k_rows_key, n, n, pa, d_lo, keyA);
+    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pa, pb, n));
+    LAUNCH_1D(k_rows_key, n, n, pb, d_hi, keyA);
+    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pb, pa, n));
+    LAUNCH_1D(k_rows_key, n, n, pa, d_edge, keyA);
+    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pa, pb, n, 0, 32));
+    LAUNCH_1D(k_rows_count, n, n, pb, d_edge, d_lo, d_hi, d_mask, d_count, (int64_t)n_edges);
+    std::vector<unsigned long long> h((size_t)n_edges);
+    CORAL_TRY(d2h(c, h.data(), d_count, (size_t)n_edges));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (int32_t i = 0; i < n_edges; i++) lr_count[i] = (int64_t)h[i];
     return CORAL_OK;
 }

@@ -148,14 +148,26 @@ def row_names(rows):
     return [text[int(off[i]):int(off[i]) + int(ln[i]) - 1].decode() for i in range(len(ln))]
 
 
+def _lexsort_rows(keys):
+    """Row order that sorts `keys` [n, c] lexicographically (stable radix passes, last column first)."""
+    o = torch.arange(keys.shape[0], device=keys.device)
+    for c in range(keys.shape[1] - 1, -1, -1):
+        o = o[torch.sort(keys[o, c], stable=True)[1]]
+    return o
+
+
 def _or_reduce(keys, mask):
-    """Unique rows of `keys` with the bitwise OR (4 bits) of their masks."""
-    uniq, inv = torch.unique(keys, dim=0, return_inverse=True)
-    out = torch.zeros(uniq.shape[0], dtype=torch.int64, device=keys.device)
+    """Unique rows of `keys` (sorted) with the bitwise OR (4 bits) of their masks."""
+    o = _lexsort_rows(keys)
+    k, m = keys[o], mask[o]
+    head = torch.ones(k.shape[0], dtype=torch.bool, device=k.device)
+    head[1:] = (k[1:] != k[:-1]).any(1)
+    seg = torch.cumsum(head.to(torch.int64), 0) - 1
+    n = int(seg[-1]) + 1
+    out = torch.zeros(n, dtype=torch.int64, device=k.device)
     for b in range(4):
-        bit = torch.zeros_like(out).scatter_reduce(0, inv, (mask >> b) & 1, "amax")
-        out |= bit << b
-    return uniq, out
+        out |= torch.zeros_like(out).scatter_reduce(0, seg, (m >> b) & 1, "amax") << b
+    return k[head], out
 
 
 def concordant_combine(tc, n_edges, edge, lo, hi, mask, rb_edge, rb_lo, rb_hi):
@@ -174,11 +186,19 @@ def concordant_combine(tc, n_edges, edge, lo, hi, mask, rb_edge, rb_lo, rb_hi):
         keys, mask = g[:, :3], g[:, 3]
     full = mask == 15
     if rb_edge.shape[0] and keys.shape[0]:
-        both = torch.cat([keys, torch.stack([rb_edge, rb_lo, rb_hi], 1)], 0)
-        _, inv = torch.unique(both, dim=0, return_inverse=True)
+        # membership of every key in the rbps rows: sort both together, a key is hit when an rbps row shares its run
         nk = keys.shape[0]
-        hit = torch.zeros(int(inv.max()) + 1, dtype=torch.bool, device=dev)
-        hit[inv[nk:]] = True
-        full = full & ~hit[inv[:nk]]
+        both = torch.cat([keys, torch.stack([rb_edge, rb_lo, rb_hi], 1)], 0)
+        is_rb = torch.zeros(both.shape[0], dtype=torch.int64, device=dev)
+        is_rb[nk:] = 1
+        o = _lexsort_rows(both)
+        b = both[o]
+        head = torch.ones(b.shape[0], dtype=torch.bool, device=dev)
+        head[1:] = (b[1:] != b[:-1]).any(1)
+        seg = torch.cumsum(head.to(torch.int64), 0) - 1
+        seg_hit = torch.zeros(int(seg[-1]) + 1, dtype=torch.int64, device=dev).scatter_reduce(0, seg, is_rb[o], "amax")
+        hit = torch.zeros(both.shape[0], dtype=torch.bool, device=dev)
+        hit[o] = seg_hit[seg] > 0
+        full = full & ~hit[:nk]
     cnt = torch.bincount(keys[:, 0][full], minlength=n_edges) if keys.shape[0] else torch.zeros(n_edges, dtype=torch.int64, device=dev)
     return cnt, keys, mask

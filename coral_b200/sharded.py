@@ -245,6 +245,7 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             self._cctx.set_references(view.references)
             self._row_names = None
             self._rows = None
+            self._rbt = None
             self._name_hash = {}     # read name -> 128-bit hash as two int64 (for the rbps rows of the concordant combine)
 
         @property
@@ -330,26 +331,31 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
                 self._name_hash[r[0]] = (r[7], r[8])
             return [r[:7] for r in merged]
 
-        # a11: name-level set algebra across shards, on name hashes
+        # a11: name-level set algebra across shards, on name hashes: local stab rows stay on the device, are
+        # all-gathered as (edge, name hash, mask) and counted by the same sort + OR-reduce kernel on every rank
         def _concordant_counts(self, uniq, rbps):
             import torch
             from . import exchange
-            _, rows = self._ctx.concordant([u[0] for u in uniq], [u[1] for u in uniq], [], [])
+            ctx = self._ctx
+            ctx.concordant([u[0] for u in uniq], [u[1] for u in uniq], [], [], fetch_rows=False)
+            ptrs, n = ctx.concordant_device_rows()
             tv = self._views()
             dev = tv["name_lo"].device
-            rec = torch.as_tensor(rows["rec"].astype(np.int64), device=dev)
-            edge = torch.as_tensor(rows["edge"].astype(np.int64), device=dev)
-            mask = torch.as_tensor(rows["mask"].astype(np.int64), device=dev)
-            rb = [(k, ) + self._name_hash[nm] for k, names in enumerate(rbps) for nm in names if nm in self._name_hash]
-            rbt = torch.as_tensor(np.array(rb, np.int64).reshape(-1, 3), device=dev)
-            cnt, keys, m = exchange.concordant_combine(exchange.TensorComm(self._comm), len(uniq), edge, tv["name_lo"][rec],
-                                                       tv["name_hi"][rec], mask, rbt[:, 0], rbt[:, 1], rbt[:, 2])
-            return cnt, keys, m, (rec, mask, tv)
+            v = exchange.view
+            edge, rec, mask = (v(ptrs[k], n, "<i4", dev).to(torch.int64) for k in range(3))
+            if self._rbt is None or self._rbt[0] is not rbps:      # (edge, name hash, 16) rows of rbps: built once per graph
+                rb = [(k, ) + self._name_hash[nm] + (16, ) for k, names in enumerate(rbps) for nm in names if nm in self._name_hash]
+                self._rbt = (rbps, torch.as_tensor(np.array(rb, np.int64).reshape(-1, 4), device=dev))
+            mine = torch.stack([edge, tv["name_lo"][rec], tv["name_hi"][rec], mask], 1)
+            g = torch.cat(exchange.TensorComm(self._comm).all_gather(mine) + [self._rbt[1]], 0).t().contiguous()
+            torch.cuda.current_stream().synchronize()
+            cnt = ctx.count_name_rows(len(uniq), int(g.shape[1]), g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(), g[3].data_ptr())
+            return cnt, g, (rec, mask, tv)
 
         def _concordant_support(self, uniq, rbps):
             import torch
             from . import exchange
-            cnt, keys, m, (rec, mask, tv) = self._concordant_counts(uniq, rbps)
+            cnt, g, (rec, mask, tv) = self._concordant_counts(uniq, rbps)
             # ce[9] wants the read NAMES covering p or p+1: every rank contributes the names of its own records
             urec = torch.unique(rec[(mask & 3) != 0])
             base = tv["off"][urec]
@@ -360,12 +366,12 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             for lo, hi, names in self._comm.all_gather(mine):
                 for a, b, nm in zip(lo.tolist(), hi.tolist(), names):
                     table[(a, b)] = nm.decode()
-            sel = (m & 3) != 0
-            kk = keys[sel].cpu().numpy()
+            sel = (g[3] & 3) != 0
+            kk = g[:3, sel].t().cpu().numpy()
             out = [set() for _ in uniq]
             for e, a, b in kk.tolist():
                 out[e].add(table[(a, b)])
-            return [int(x) for x in cnt.cpu().numpy()], out
+            return [int(x) for x in cnt], out
 
         def closebam(self):
             self._cctx.close()

@@ -249,6 +249,13 @@ int coral_concordant(coral_ctx* ctx, const int32_t* tid, const int32_t* p, int32
                      const uint32_t* rb_edge, const uint32_t* rb_rec, int64_t* lr_count, int64_t* n_rows);
 int coral_get_concordant_rows(coral_ctx* ctx, uint32_t* edge, uint32_t* rec, uint32_t* mask);
 
+/* Multi-GPU form: the rows of the last coral_concordant stay on the device (edge, rec, mask: uint32
+ * each; coral_concordant_device_rows), the caller all-gathers them as (edge, name hash, mask) and every rank counts
+ * ce[8] on the gathered rows + the rbps rows (mask 16) with coral_count_name_rows (device arrays, uint64 each). */
+int coral_concordant_device_rows(coral_ctx* ctx, uint64_t* ptrs, int64_t* n_rows);
+int coral_count_name_rows(coral_ctx* ctx, int32_t n_edges, int64_t n_rows, const uint64_t* d_edge, const uint64_t* d_lo,
+                          const uint64_t* d_hi, const uint64_t* d_mask, int64_t* lr_count);
+
 #ifdef __cplusplus
 }
 #endif
