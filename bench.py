@@ -249,6 +249,7 @@ def main():
     ap.add_argument("--e2e-placement", default="mapped", choices=["mapped", "copy"],
                     help="e2e arm: kernels read the pinned host records in place over PCIe (mapped) or after a full H2D copy")
     ap.add_argument("--only", default="", help="'scan': time the record-scan kernel alone (development aid)")
+    ap.add_argument("--cprofile", action="store_true", help="cProfile of 20 device passes on rank 0 (development aid)")
     ap.add_argument("--profile", action="store_true",
                     help="bracket ONE device pass with cudaProfilerStart/Stop and exit (for ncu --profile-from-start off)")
     a = ap.parse_args()
@@ -354,6 +355,20 @@ def main():
     for _ in range(warm):
         out = one_pass()
     d2h = result_bytes(out)
+    if a.cprofile:
+        import cProfile
+        import pstats
+        pr = cProfile.Profile()
+        e2e_pass()
+        pr.enable()
+        for _ in range(20 if a.only != "e2e" else 3):
+            one_pass() if a.only != "e2e" else e2e_pass()
+        pr.disable()
+        if rank == 0:
+            pstats.Stats(pr).sort_stats("cumulative").print_stats(45)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     if a.profile:
         torch.cuda.synchronize()
         torch.cuda.cudart().cudaProfilerStart()

@@ -85,6 +85,10 @@ class BamFile(object):
         ln = int(self.rec[o + 12])
         return self.rec[o + 36:o + 36 + ln - 1].tobytes().decode()
 
+    def query_names(self, idx):
+        from .records import query_names
+        return query_names(self.rec, self.rec_off, idx)
+
     def close(self):
         if self._h is not None:
             self.rec = None

@@ -8,6 +8,8 @@ bpc2bp) come from ``self._ops`` — the CUDA-backed drop-ins in the product, the
 Citations: ``ibg`` = reference ``src/infer_breakpoint_graph.py``.
 """
 import bisect
+import contextlib
+import gc
 import logging
 import sys
 import time
@@ -45,6 +47,19 @@ class SegmentIndex(object):
                 out.add(self._iv[k])
             k -= 1
         return out
+
+
+@contextlib.contextmanager
+def gc_paused():
+    """The host steps build hundreds of thousands of small acyclic lists; the cyclic collector finds nothing in
+    them and costs more than the building itself, so it is paused while they are built."""
+    on = gc.isenabled()
+    gc.disable()
+    try:
+        yield
+    finally:
+        if on:
+            gc.enable()
 
 
 def _t():
@@ -142,7 +157,21 @@ class HostSteps(object):
         return self.cns_tree[chr][pos]
 
     # ---- ibg:181-210 ------------------------------------------------------------------------------------
-    def hash_alignment_to_seg(self):
+    def _cni_tables(self):
+        """Per chromosome (begins, ends, data) arrays of the CN segments when they do not overlap, else None
+        (then every lookup goes through pos2cni, which keeps the reference's assertion on double hits)."""
+        tabs = {}
+        for chrom, tree in self.cns_tree.items():
+            if not isinstance(tree, SegmentIndex):
+                return None
+            b = np.asarray(tree._b, dtype=np.int64)
+            e = np.asarray([h.end for h in tree._iv], dtype=np.int64)
+            if len(b) > 1 and bool((e[:-1] > b[1:]).any()):
+                return None
+            tabs[chrom] = (b, e, np.asarray([h.data for h in tree._iv], dtype=np.int64))
+        return tabs
+
+    def _hash_alignment_to_seg_scalar(self):
         for read, ca in self.chimeric_alignments.items():
             for rint in ca[1]:
                 if rint[0] not in self.cns_tree:
@@ -156,6 +185,50 @@ class HostSteps(object):
                     cniset.remove(-1)
                 rint.append(cniset)
                 by_seg = self.chimeric_alignments_seg.setdefault(rint[0], {})
+                for cni in cniset:
+                    if cni != -1:
+                        by_seg.setdefault(cni, []).append(read)
+
+    def hash_alignment_to_seg(self):
+        """CN-segment indices of both ends of every alignment.  Lookups are batched per chromosome (binary search
+        over the non-overlapping segments); the sets and chimeric_alignments_seg are then filled in read order,
+        exactly as the per-alignment loop of the reference does."""
+        tabs = self._cni_tables()
+        if tabs is None:
+            return self._hash_alignment_to_seg_scalar()
+        flat = [rint for ca in self.chimeric_alignments.values() for rint in ca[1]]
+        n = len(flat)
+        chrom = [r[0] for r in flat]
+        p1 = np.fromiter((r[1] for r in flat), dtype=np.int64, count=n)
+        p2 = np.fromiter((r[2] for r in flat), dtype=np.int64, count=n)
+        plo, phi = np.minimum(p1, p2), np.maximum(p1, p2)
+        lo = np.full(n, -2, dtype=np.int64)          # -2: chromosome without CN segments
+        hi = np.full(n, -2, dtype=np.int64)
+        names, inv = np.unique(np.asarray(chrom, dtype=object), return_inverse=True) if n else ([], None)
+        for ci, c in enumerate(names):
+            if c not in tabs:
+                continue
+            b, e, d = tabs[c]
+            sel = np.nonzero(inv == ci)[0]
+            for pos, out in ((plo[sel], lo), (phi[sel], hi)):
+                k = np.searchsorted(b, pos, side="right") - 1
+                kk = np.maximum(k, 0)
+                out[sel] = np.where((k >= 0) & (e[kk] > pos), d[kk], -1)
+        lo, hi = lo.tolist(), hi.tolist()
+        seg = self.chimeric_alignments_seg
+        k = 0
+        for read, ca in self.chimeric_alignments.items():
+            for rint in ca[1]:
+                a, z = lo[k], hi[k]
+                k += 1
+                if a == -2:
+                    rint.append(set([-1]))
+                    continue
+                cniset = set([a, z])
+                if len(cniset) > 1 and -1 in cniset:
+                    cniset.remove(-1)
+                rint.append(cniset)
+                by_seg = seg.setdefault(rint[0], {})
                 for cni in cniset:
                     if cni != -1:
                         by_seg.setdefault(cni, []).append(read)

@@ -6,6 +6,7 @@ find_breakpoints -> build_graph -> assign_cov``, reference ``reconstruct_graph``
 The hot methods run on the GPU through the C ABI (``_abi.Context``); this file only converts result tables
 into the reference's Python containers.  Without a CUDA device the constructor raises — there is no CPU path.
 """
+import functools
 import logging
 import math
 import time
@@ -14,7 +15,15 @@ import numpy as np
 
 from . import _abi, breakpoint_utilities, global_names, gpu_ops
 from .breakpoint_graph import output_breakpoint_graph_lr, output_breakpoint_info_lr
-from .host_steps import HostSteps, _t
+from .host_steps import HostSteps, _t, gc_paused
+
+
+def _gc_paused(fn):
+    @functools.wraps(fn)
+    def run(*a, **k):
+        with gc_paused():
+            return fn(*a, **k)
+    return run
 
 
 class bam_to_breakpoint_nanopore(HostSteps):
@@ -72,39 +81,50 @@ class bam_to_breakpoint_nanopore(HostSteps):
 
     # ---- a1/a2: ibg:139-174 ------------------------------------------------------------------------------
     def _run_fetch(self):
-        """Device fetch -> (table dict, record index -> read name).  The sharded engine overrides this with the
+        """Device fetch -> (table dict, record indices -> read names).  The sharded engine overrides this with the
         exchange of SURVEY.md §8e (rows all-gathered, fetch on the gathered rows)."""
-        return self._ctx.fetch(), self.lr_bamfh.query_name
+        return self._ctx.fetch(), self._names_of
 
     @property
     def _chim_ctx(self):
         """The ctx that holds the chimeric table (the shard's own ctx, or the gathered-rows ctx when sharded)."""
         return self._ctx
 
+    @_gc_paused
     def fetch(self):
-        f, name_of = self._run_fetch()
+        f, names_of = self._run_fetch()
         if f["nm_zero_div"] or f["nm_n"] == 0:
             raise ZeroDivisionError("division by zero")              # ibg:154 / ibg:159
         mean = f["nm_sum"] / f["nm_n"]
         self.nm_stats = [mean, math.sqrt(f["nm_sumsq"] / f["nm_n"] - mean ** 2), f["nm_n"]]
         refs = self.lr_bamfh.references
-        ap = f["aln_ptr"]
-        qs, qe, tid, rs, re = f["qs"].tolist(), f["qe"].tolist(), f["tid"].tolist(), f["rstart"].tolist(), f["rend"].tolist()
-        strand, mapq, nm = f["strand"].tolist(), f["mapq"].tolist(), f["nm"].tolist()
-        logging.info(_t() + "Fetched %d chimeric reads." % f["n_reads"])
-        self._read_names = []
-        for r in range(f["n_reads"]):
-            rec = int(f["read_first_rec"][r])
-            name = name_of(rec)
-            self._read_names.append(name)
+        n_reads = f["n_reads"]
+        ap = f["aln_ptr"].tolist() if n_reads else [0]
+        logging.info(_t() + "Fetched %d chimeric reads." % n_reads)
+        # flat Python lists built once (the per-read work below is slicing only)
+        d = (f["qe"].astype(np.int64) - f["qs"].astype(np.int64))
+        zero = np.nonzero(d == 0)[0]
+        nmn_all = (f["nm"].astype(np.float64) / np.where(d == 0, 1, d)).tolist()          # cp:268
+        qint_all = [[a_, b_] for a_, b_ in zip(f["qs"].tolist(), f["qe"].tolist())]
+        rint_all = [[refs[t_], a_, b_, '-' if s_ else '+'] for t_, a_, b_, s_ in
+                    zip(f["tid"].tolist(), f["rstart"].tolist(), f["rend"].tolist(), f["strand"].tolist())]
+        mapq_all = f["mapq"].tolist()
+        first_rec = f["read_first_rec"].astype(np.int64) if n_reads else np.zeros(0, np.int64)
+        names = names_of(first_rec)
+        status = f["read_status"].tolist() if n_reads else []
+        rlen = f["read_len"].tolist() if n_reads else []
+        recs = first_rec.tolist()
+        self._read_names = names
+        for r in range(n_reads):
+            name = names[r]
             self._read_index[name] = r
-            self._name_rec[name] = rec
-            st = int(f["read_status"][r])
+            self._name_rec[name] = recs[r]
+            st = status[r]
             if st == 1:      # ibg:164-169
                 logging.warning(_t() + "Found chimeric read without primary alignment.")
                 logging.warning(_t() + "\tRead name: %s; Read length: N/A." % name)
                 continue
-            self.read_length[name] = int(f["read_len"][r])
+            self.read_length[name] = rlen[r]
             if st == 2:      # cp:248-253
                 logging.warning(_t() + "Found chimeric alignment without match or soft clips.")
                 self.chimeric_alignments[name] = ([], [], [])
@@ -113,12 +133,10 @@ class bam_to_breakpoint_nanopore(HostSteps):
                 raise KeyError("CIGAR signature of an SA entry of read %s is not in cigar2pos_ops" % name)
             if st != 0:
                 raise ValueError("malformed SA entry on read %s" % name)
-            a, b = int(ap[r]), int(ap[r + 1])
-            qint = [[qs[k], qe[k]] for k in range(a, b)]
-            rint = [[refs[tid[k]], rs[k], re[k], '-' if strand[k] else '+'] for k in range(a, b)]
-            qual = mapq[a:b]
-            nmn = [float(nm[k]) / (qe[k] - qs[k]) for k in range(a, b)]   # cp:268
-            self.chimeric_alignments[name] = (qint, rint, qual, nmn)
+            a, b = ap[r], ap[r + 1]
+            if len(zero) and np.searchsorted(zero, a) != np.searchsorted(zero, b):
+                raise ZeroDivisionError("float division by zero")      # cp:268 with qe == qs
+            self.chimeric_alignments[name] = (qint_all[a:b], rint_all[a:b], mapq_all[a:b], nmn_all[a:b])
         logging.info(_t() + "Computed alignment intervals on all chimeric reads.")
 
     # ---- shared tail of ibg:691-718 and ibg:775-802 -------------------------------------------------------
@@ -159,6 +177,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
         return [self._tid[a[0]] for a in ivs], [a[1] for a in ivs], [a[2] for a in ivs]
 
     # ---- a3: ibg:721-802 ------------------------------------------------------------------------------------
+    @_gc_paused
     def find_smalldel_breakpoints(self):
         t, s, e = self._interval_arrays()
         self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
@@ -172,18 +191,14 @@ class bam_to_breakpoint_nanopore(HostSteps):
         """Rows (name, interval index, next_start, prev_end, first_start, last_end, mapq) in the reference's
         emission order: interval list order, file order, block order (ibg:750-762)."""
         rows = self._ctx.smalldel(t, s, e)
-        names = {}
-        recs = rows["rec"].tolist()
-        ai, ns, pe, fs, le, mq = (rows[k].tolist() for k in ("ai", "next_start", "prev_end", "first_start", "last_end", "mapq"))
-        out = []
-        for k in range(rows["n"]):
-            rec = recs[k]
-            name = names.get(rec)
-            if name is None:
-                name = names[rec] = self.lr_bamfh.query_name(rec)
-                self._name_rec.setdefault(name, rec)
-            out.append((name, ai[k], ns[k], pe[k], fs[k], le[k], mq[k]))
-        return out
+        if rows["n"] == 0:
+            return []
+        urec, inv = np.unique(rows["rec"].astype(np.int64), return_inverse=True)
+        unames = self._names_of(urec)
+        for nm, rc in zip(unames, urec.tolist()):
+            self._name_rec.setdefault(nm, rc)
+        names = [unames[k] for k in inv.tolist()]
+        return list(zip(names, *(rows[k].tolist() for k in ("ai", "next_start", "prev_end", "first_start", "last_end", "mapq"))))
 
     def _smalldel_candidates(self):
         tuples, chrs, p1, p2 = [], [], [], []
@@ -201,6 +216,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
         return cand, tuples
 
     # ---- a4/a5: ibg:676-718 ---------------------------------------------------------------------------------
+    @_gc_paused
     def find_breakpoints(self):
         t, s, e = self._interval_arrays()
         self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
@@ -217,9 +233,20 @@ class bam_to_breakpoint_nanopore(HostSteps):
                                       [intrvl1[2], intrvl2[2]])
         refs = self.lr_bamfh.references
         names = self._read_names
-        return [[refs[c["chr1"][k]], int(c["pos1"][k]), '+-'[c["o1"][k]], refs[c["chr2"][k]], int(c["pos2"][k]),
-                 '+-'[c["o2"][k]], (names[c["read"][k]], int(c["i"][k]), int(c["j"][k])), int(c["rgap"][k]), int(c["flag"][k]),
-                 int(c["mq1"][k]), int(c["mq2"][k])] for k in range(c["n"])]
+        L = {k: c[k].tolist() for k in ("chr1", "pos1", "o1", "chr2", "pos2", "o2", "read", "i", "j", "rgap", "flag", "mq1", "mq2")}
+        rows = [[refs[c1], p1, '+-'[o1], refs[c2], p2, '+-'[o2], (names[rd], i, j), rg, fl, m1, m2]
+                for c1, p1, o1, c2, p2, o2, rd, i, j, rg, fl, m1, m2 in
+                zip(L["chr1"], L["pos1"], L["o1"], L["chr2"], L["pos2"], L["o2"], L["read"], L["i"], L["j"], L["rgap"], L["flag"],
+                    L["mq1"], L["mq2"])]
+        return gpu_ops.BpList(rows, c)      # keeps the device table: cluster_bp_list / bpc2bp need no re-flattening
+
+    @_gc_paused
+    def hash_alignment_to_seg(self):
+        return HostSteps.hash_alignment_to_seg(self)
+
+    @_gc_paused
+    def find_amplicon_intervals(self):
+        return HostSteps.find_amplicon_intervals(self)
 
     # ---- a10/a11: ibg:1019-1056 -----------------------------------------------------------------------------
     def _edge_queries(self):
@@ -260,6 +287,13 @@ class bam_to_breakpoint_nanopore(HostSteps):
             rbps.append(seen)
         return batches, uniq, owners, rbps
 
+    def _names_of(self, recs):
+        """Read names of local records, in bulk when the BAM handle can (one pass over the host buffer)."""
+        fh = self.lr_bamfh
+        if hasattr(fh, "query_names"):
+            return fh.query_names(recs)
+        return [fh.query_name(int(r)) for r in recs]
+
     def _rbps_rows(self, rbps):
         """rbps name sets -> (edge index, a local record of that read) rows for coral_concordant."""
         rb_edge, rb_rec = [], []
@@ -282,18 +316,13 @@ class bam_to_breakpoint_nanopore(HostSteps):
         o = np.argsort(r_edge, kind="stable")
         r_edge, r_rec = r_edge[o], r_rec[o]
         bounds = np.searchsorted(r_edge, np.arange(len(uniq) + 1))
-        name_of = {}
-        out = []
-        for k in range(len(uniq)):
-            names = set()
-            for rec in r_rec[bounds[k]:bounds[k + 1]].tolist():
-                nm = name_of.get(rec)
-                if nm is None:
-                    nm = name_of[rec] = self.lr_bamfh.query_name(rec)
-                names.add(nm)
-            out.append(names)
+        urec, inv = np.unique(r_rec, return_inverse=True)
+        unames = self._names_of(urec)
+        row_names = [unames[i] for i in inv.tolist()]
+        out = [set(row_names[bounds[k]:bounds[k + 1]]) for k in range(len(uniq))]
         return [int(x) for x in cnt], out
 
+    @_gc_paused
     def assign_cov(self):
         batches, uniq, owners, rbps = self._edge_queries()
         for batch in batches:

@@ -2,6 +2,18 @@
 import numpy as np
 
 
+def query_names(rec, rec_off, idx):
+    """Read names of records `idx` in one pass over the host buffer (the per-record form is query_name)."""
+    idx = np.asarray(idx, dtype=np.int64)
+    if len(idx) == 0:
+        return []
+    base = np.asarray(rec_off, dtype=np.uint64)[idx].astype(np.int64)
+    ln = rec[base + 12].astype(np.int64)                      # l_read_name, NUL included
+    offs = np.cumsum(ln) - ln
+    pos = np.repeat(base + 36 - offs, ln) + np.arange(int(ln.sum()), dtype=np.int64)
+    return rec[pos].tobytes().decode().split("\0")[:len(idx)]
+
+
 class RecordSet(object):
     def __init__(self, references, rec, rec_off, lengths=None, rec_slack=0):
         self.rec_slack = int(rec_slack)   # bytes guaranteed readable behind `rec` (64 enables the mapped placement)
@@ -15,6 +27,9 @@ class RecordSet(object):
         o = int(self.rec_off[i])
         ln = int(self.rec[o + 12])
         return self.rec[o + 36:o + 36 + ln - 1].tobytes().decode()
+
+    def query_names(self, idx):
+        return query_names(self.rec, self.rec_off, idx)
 
     def close(self):
         pass

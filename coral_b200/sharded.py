@@ -218,6 +218,10 @@ class _ShardView(object):
     def query_name(self, i):
         return self._parent.query_name(self.g0 + i)
 
+    def query_names(self, idx):
+        from .records import query_names
+        return query_names(self.rec, self.rec_off, idx)
+
     def close(self):
         pass
 
@@ -295,14 +299,13 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             f["nm_n"] = int(parts[:, 2].sum()); f["nm_zero_div"] = int(parts[:, 3].sum())
             self._rows, self._row_names = rows, None
 
-            def name_of(r):
+            def names_of(recs):
                 if self._row_names is None:         # one D2H of the gathered text, only when names are materialised
                     self._row_names = exchange.row_names(self._rows)
-                    lo = self._rows["name_lo"].cpu().numpy(); hi = self._rows["name_hi"].cpu().numpy()
-                    for k, nm in enumerate(self._row_names):
-                        self._name_hash[nm] = (int(lo[k]), int(hi[k]))
-                return self._row_names[r]
-            return f, name_of
+                    lo = self._rows["name_lo"].cpu().tolist(); hi = self._rows["name_hi"].cpu().tolist()
+                    self._name_hash.update(zip(self._row_names, zip(lo, hi)))
+                return [self._row_names[int(r)] for r in recs]
+            return f, names_of
 
         def find_breakpoints(self):
             self._cctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
