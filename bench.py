@@ -271,6 +271,7 @@ def main():
     from coral_b200 import _abi, gpu_ops
     from coral_b200.infer_breakpoint_graph import bam_to_breakpoint_nanopore
     from coral_b200.records import RecordSet
+    from coral_b200.host_steps import gc_paused
     import tempfile
 
     comm = None
@@ -323,6 +324,13 @@ def main():
     e2e_stage = {}
 
     def e2e_pass():
+        with gc_paused():           # as reconstruct_graph() does
+            eng = _e2e_pass()
+            t = time.perf_counter()
+            del eng                 # released by reference count inside the timed region
+            e2e_stage["release"] = (time.perf_counter() - t) * 1e3
+
+    def _e2e_pass():
         t = time.perf_counter()
         eng = make_engine(a.e2e_placement)
         for name, fn, args in (("load+scan", None, ()), ("read_cns", eng.read_cns, (cns,)), ("fetch", eng.fetch, ()),
@@ -335,6 +343,7 @@ def main():
             e2e_stage[name] = (t2 - t) * 1e3
             t = t2
         eng.closebam()
+        e2e_stage["closebam"] = (time.perf_counter() - t) * 1e3
         return eng
 
     # plan + resident context

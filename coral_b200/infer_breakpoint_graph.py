@@ -350,8 +350,10 @@ class bam_to_breakpoint_nanopore(HostSteps):
 BamToBreakpointNanopore = bam_to_breakpoint_nanopore   # name used by BASELINE.json's north_star
 
 
+@_gc_paused
 def reconstruct_graph(args):
-    """Reference :1333-1395 up to (not including) compute_cn_lr, which stays on the reference's cvxopt code."""
+    """Reference :1333-1395 up to (not including) compute_cn_lr, which stays on the reference's cvxopt code.
+    The cyclic collector is paused for the whole pass (see host_steps.gc_paused)."""
     global_names.TSTART = time.time()
     b2bn = bam_to_breakpoint_nanopore(args.lr_bam, args.cnv_seed)
     b2bn.min_bp_cov_factor = args.min_bp_support
