@@ -173,7 +173,8 @@ def build_plan(eng, cn_seg):
     rb_edge, rb_rec = eng._rbps_rows(rbps)
     b = batches[0]
     plan["seq_edges"] = ([r[0] for r in b], [r[1] for r in b], [r[2] for r in b])
-    plan["conc"] = ([u[0] for u in uniq], [u[1] for u in uniq], rb_edge, rb_rec)
+    plan["conc"] = (np.array([u[0] for u in uniq], np.int32), np.array([u[1] for u in uniq], np.int32),
+                    np.array(rb_edge, np.uint32), np.array(rb_rec, np.uint32))
     plan["uniq"], plan["rbps"] = uniq, rbps
     plan["cutoff"] = eng.min_cluster_cutoff
     eng.assign_cov()

@@ -29,27 +29,8 @@ def default_context():
     return ctx
 
 
-_COLS = ("chr1", "pos1", "o1", "chr2", "pos2", "o2", "rgap", "flag", "mq1", "mq2")
-
-
-class BpList(list):
-    """A list of reference-layout breakpoint records that still carries the device table it was built from
-    (`arrays`: dict of parallel numpy columns, row k <-> self[k]), so the module-level operators do not have to
-    re-flatten the Python lists.  Behaves as a plain list for every caller."""
-
-    def __init__(self, rows, arrays):
-        list.__init__(self, rows)
-        self.arrays = arrays
-
-    def take(self, idx):
-        idx = np.asarray(idx, dtype=np.int64)
-        return BpList([self[int(i)] for i in idx], {k: self.arrays[k][idx] for k in _COLS})
-
-
 def flatten_bp_list(bp_list):
     """[[chr1,pos1,o1,chr2,pos2,o2,r,rgap,flag,mq1,mq2], ...] -> dict of arrays (chr -> local ids)."""
-    if isinstance(bp_list, BpList) and len(bp_list.arrays["chr1"]) == len(bp_list):
-        return bp_list.arrays
     ids = {}
     n = len(bp_list)
     a = {k: np.zeros(n, np.int32) for k in ("chr1", "pos1", "chr2", "pos2", "rgap", "mq1", "mq2")}
@@ -86,8 +67,6 @@ def cluster_bp_list(bp_list, min_cluster_size, bp_distance_cutoff, ctx=None):
     ctx = ctx or default_context()
     r = cluster_arrays(ctx, flatten_bp_list(bp_list), min_cluster_size, bp_distance_cutoff, float("inf"), 100)
     order, ptr = r["order"], r["cluster_ptr"]
-    if isinstance(bp_list, BpList):
-        return [bp_list.take(order[ptr[c]:ptr[c + 1]]) for c in range(r["n_clusters"])]
     return [[bp_list[int(i)] for i in order[ptr[c]:ptr[c + 1]]] for c in range(r["n_clusters"])]
 
 
@@ -108,10 +87,7 @@ def bpc2bp(bp_cluster, bp_distance_cutoff, ctx=None):
         return bp, [], [0, 0, 0, 0, 0, 0], []
     sub = r["sub_of"]
     bpr = [bp_cluster[i][6] for i in range(len(bp_cluster)) if sub[i] == 0]
-    if isinstance(bp_cluster, BpList):
-        rest = bp_cluster.take(np.nonzero(sub != 0)[0])
-    else:
-        rest = [bp_cluster[i] for i in range(len(bp_cluster)) if sub[i] != 0]
+    rest = [bp_cluster[i] for i in range(len(bp_cluster)) if sub[i] != 0]
     return bp, bpr, stats_row(r["row_stats"][0]), rest
 
 

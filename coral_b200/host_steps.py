@@ -441,6 +441,18 @@ class HostSteps(object):
             out += self._ops.alignment2bp(r, self.chimeric_alignments[r], self.min_bp_match_cutoff_, 20, intrvl1, intrvl2)
         return out
 
+    def _called_breakpoints(self, cands):
+        """(bp, bpr, bp_stats) of every sub-cluster peeled off every cluster of `cands`, in the reference's order
+        (ibg:436-446: cluster_bp_list, then bpc2bp on the remainder while it keeps min_cluster_cutoff members).
+        The CUDA engine overrides this with one device call per candidate list."""
+        ops = self._ops
+        for c in ops.cluster_bp_list(cands, self.min_cluster_cutoff, self.max_breakpoint_distance_cutoff):
+            if len(c) >= self.min_cluster_cutoff:
+                rest = c
+                while len(rest) >= self.min_cluster_cutoff:
+                    bp, bpr, bp_stats_, rest = ops.bpc2bp(rest, self.min_bp_match_cutoff_)
+                    yield bp, bpr, bp_stats_
+
     def find_interval_i(self, ai, ccid):
         ops = self._ops
         by = self.cns_intervals_by_chr
@@ -500,17 +512,13 @@ class HostSteps(object):
                     # NOTE: iteration order of a set of read names (ibg:432) — process-dependent in the reference too
                     cands = self._pair_candidates(list(nint_[-1]), [nint_[0], ns, ne], self.amplicon_intervals[ai_])
                     kept_bp = []
-                    for c in ops.cluster_bp_list(cands, self.min_cluster_cutoff, self.max_breakpoint_distance_cutoff):
-                        if len(c) >= self.min_cluster_cutoff:
-                            num_subcluster = 0     # never incremented here (ibg:442-457)
-                            rest = c
-                            while len(rest) >= self.min_cluster_cutoff:
-                                bp, bpr, bp_stats_, rest = ops.bpc2bp(rest, self.min_bp_match_cutoff_)
-                                if (num_subcluster == 0 and len(set(bpr)) >= self.min_cluster_cutoff) or \
-                                        (len(set(bpr)) >= max(self.normal_cov * self.min_bp_cov_factor, 3.0)):
-                                    bpi = self.addbp(bp, set(bpr), bp_stats_, ccid)
-                                    if bpi not in kept_bp:
-                                        kept_bp.append(bpi)
+                    num_subcluster = 0     # never incremented in the reference (ibg:442-457)
+                    for bp, bpr, bp_stats_ in self._called_breakpoints(cands):
+                        if (num_subcluster == 0 and len(set(bpr)) >= self.min_cluster_cutoff) or \
+                                (len(set(bpr)) >= max(self.normal_cov * self.min_bp_cov_factor, 3.0)):
+                            bpi = self.addbp(bp, set(bpr), bp_stats_, ccid)
+                            if bpi not in kept_bp:
+                                kept_bp.append(bpi)
 
                     segs, segs_ = [], []
                     if len(kept_bp) > 0:

@@ -227,18 +227,41 @@ class bam_to_breakpoint_nanopore(HostSteps):
         self._call_clusters(c, tuples)
 
     def _pair_candidates(self, reads, intrvl1, intrvl2):
-        """One batched launch of alignment2bp over the device chimeric table (ibg:432-434)."""
+        """One batched launch of alignment2bp over the device chimeric table (ibg:432-434).  The candidates stay a
+        column table (chr ids = BAM tids); _called_breakpoints clusters and calls them in one device call."""
         idx = [self._read_index[r] for r in reads]
-        c = self._chim_ctx.candidates_pair(idx, [self._tid[intrvl1[0]], self._tid[intrvl2[0]]], [intrvl1[1], intrvl2[1]],
-                                      [intrvl1[2], intrvl2[2]])
+        return self._chim_ctx.candidates_pair(idx, [self._tid[intrvl1[0]], self._tid[intrvl2[0]]], [intrvl1[1], intrvl2[1]],
+                                              [intrvl1[2], intrvl2[2]])
+
+    def _called_breakpoints(self, cand):
+        """cluster_bp_list + the bpc2bp peel loop of find_interval_i (ibg:436-446) as one coral_cluster_call."""
+        if cand["n"] == 0:
+            return
         refs = self.lr_bamfh.references
         names = self._read_names
-        L = {k: c[k].tolist() for k in ("chr1", "pos1", "o1", "chr2", "pos2", "o2", "read", "i", "j", "rgap", "flag", "mq1", "mq2")}
-        rows = [[refs[c1], p1, '+-'[o1], refs[c2], p2, '+-'[o2], (names[rd], i, j), rg, fl, m1, m2]
-                for c1, p1, o1, c2, p2, o2, rd, i, j, rg, fl, m1, m2 in
-                zip(L["chr1"], L["pos1"], L["o1"], L["chr2"], L["pos2"], L["o2"], L["read"], L["i"], L["j"], L["rgap"], L["flag"],
-                    L["mq1"], L["mq2"])]
-        return gpu_ops.BpList(rows, c)      # keeps the device table: cluster_bp_list / bpc2bp need no re-flattening
+        cutoff = self.min_cluster_cutoff
+        r = gpu_ops.cluster_arrays(self._ctx, cand, cutoff, self.max_breakpoint_distance_cutoff, cutoff,
+                                   self.min_bp_match_cutoff_)
+        order, ptr, sub_of = r["order"], r["cluster_ptr"], r["sub_of"]
+        rd, ii, jj = cand["read"], cand["i"], cand["j"]
+
+        def tup(m):
+            return (names[rd[m]], int(ii[m]), int(jj[m]))
+        for c in range(r["n_clusters"]):
+            b, e = int(ptr[c]), int(ptr[c + 1])
+            if e - b < cutoff:
+                continue
+            members = order[b:e]
+            subs = sub_of[members]
+            for k in range(int(r["n_sub"][c])):
+                row = b + k
+                f0 = int(r["row_first"][row])
+                bp = [refs[cand["chr1"][f0]], int(r["row_pos1"][row]), '+-'[cand["o1"][f0]], refs[cand["chr2"][f0]],
+                      int(r["row_pos2"][row]), '+-'[cand["o2"][f0]], tup(f0), int(cand["rgap"][f0]), int(cand["flag"][f0])]
+                if r["row_nb"][row] == 0:        # bpc2bp with no member near the called position (bu:352-353)
+                    yield bp, [], [0, 0, 0, 0, 0, 0]
+                    continue
+                yield bp, [tup(int(m)) for m in members[subs == k]], gpu_ops.stats_row(r["row_stats"][row])
 
     @_gc_paused
     def hash_alignment_to_seg(self):
@@ -296,11 +319,12 @@ class bam_to_breakpoint_nanopore(HostSteps):
 
     def _rbps_rows(self, rbps):
         """rbps name sets -> (edge index, a local record of that read) rows for coral_concordant."""
+        name_rec = self._name_rec
         rb_edge, rb_rec = [], []
         for k, names in enumerate(rbps):
-            for nm in names:
-                if nm in self._name_rec:   # a read with no loaded record cannot cover any point
-                    rb_edge.append(k); rb_rec.append(self._name_rec[nm])
+            hit = [name_rec[nm] for nm in names if nm in name_rec]   # a read with no loaded record cannot cover any point
+            rb_rec.extend(hit)
+            rb_edge.extend([k] * len(hit))
         return rb_edge, rb_rec
 
     def _region_counts(self, tid, start, stop):
