@@ -376,6 +376,7 @@ def main():
         pr.disable()
         if rank == 0:
             pstats.Stats(pr).sort_stats("cumulative").print_stats(45)
+            pstats.Stats(pr).sort_stats("tottime").print_stats(40)
         if world > 1:
             dist.destroy_process_group()
         return
@@ -481,4 +482,10 @@ def main():
 
 
 if __name__ == "__main__":
+    # stdout carries the JSON line only: libraries that write to fd 1 (NCCL prints its version there) go to stderr
+    sys.stdout.flush()
+    _json_fd = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(_json_fd, "w")
     main()
+    sys.stdout.flush()

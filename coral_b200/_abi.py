@@ -192,18 +192,42 @@ class Context(object):
         self._check(self._L.coral_load_rows(self._h, ctypes.c_int64(n), _p(text), ctypes.c_uint64(text.nbytes), _p(text_off),
                                             *[_p(x) for x in a]))
 
-    def concordant_device_rows(self):
-        """Device addresses (edge, rec, mask: uint32 arrays) and row count of the last concordant() call."""
-        ptrs = (ctypes.c_uint64 * 3)()
-        n = ctypes.c_int64()
-        self._check(self._L.coral_concordant_device_rows(self._h, ptrs, ctypes.byref(n)))
-        return [int(x) for x in ptrs], int(n.value)
+    # ---- packed device-side exchange (csrc/exchange.cu, csrc/stab.cu); addresses are device addresses ----------
+    def pack_sa_rows(self):
+        """-> (device address, bytes) of message 1 of the fetch exchange."""
+        ptr = ctypes.c_uint64(); nb = ctypes.c_uint64()
+        self._check(self._L.coral_pack_sa_rows(self._h, ctypes.byref(ptr), ctypes.byref(nb)))
+        return int(ptr.value), int(nb.value)
 
-    def count_name_rows(self, n_edges, n, edge_ptr, lo_ptr, hi_ptr, mask_ptr):
-        vp = ctypes.c_void_p
+    def pack_extra_rows(self, buf_ptr, starts):
+        """Gathered messages 1 (device buffer + per-rank start offsets) -> (device address, bytes) of message 2."""
+        st = np.ascontiguousarray(starts, dtype=np.uint64)
+        ptr = ctypes.c_uint64(); nb = ctypes.c_uint64()
+        self._check(self._L.coral_pack_extra_rows(self._h, len(st), ctypes.c_void_p(buf_ptr), _p(st), ctypes.byref(ptr),
+                                                  ctypes.byref(nb)))
+        return int(ptr.value), int(nb.value)
+
+    def unpack_rows(self, buf1_ptr, starts1, buf2_ptr, starts2):
+        """Both gathered message sets -> this (rows-only) ctx.  -> (n_rows, nm partial sums per rank: 4 arrays)."""
+        s1 = np.ascontiguousarray(starts1, dtype=np.uint64); s2 = np.ascontiguousarray(starts2, dtype=np.uint64)
+        w = len(s1)
+        a = np.zeros(w, np.float64); b = np.zeros(w, np.float64); cn = np.zeros(w, np.int64); zd = np.zeros(w, np.int64)
+        n = ctypes.c_int64()
+        self._check(self._L.coral_unpack_rows(self._h, w, ctypes.c_void_p(buf1_ptr), _p(s1), ctypes.c_void_p(buf2_ptr), _p(s2),
+                                              _p(a), _p(b), _p(cn), _p(zd), ctypes.byref(n)))
+        return int(n.value), (a, b, cn, zd)
+
+    def concordant_pack(self):
+        """-> (device address, bytes) of the (edge, name hash, mask) message of the last concordant() call."""
+        ptr = ctypes.c_uint64(); nb = ctypes.c_uint64()
+        self._check(self._L.coral_concordant_pack(self._h, ctypes.byref(ptr), ctypes.byref(nb)))
+        return int(ptr.value), int(nb.value)
+
+    def count_name_msgs(self, n_edges, buf_ptr, starts, sizes, rb_ptr, n_rb):
+        st = np.ascontiguousarray(starts, dtype=np.uint64); sz = np.ascontiguousarray(sizes, dtype=np.uint64)
         cnt = np.zeros(max(n_edges, 1), np.int64)
-        self._check(self._L.coral_count_name_rows(self._h, int(n_edges), ctypes.c_int64(n), vp(edge_ptr), vp(lo_ptr), vp(hi_ptr),
-                                                  vp(mask_ptr), _p(cnt)))
+        self._check(self._L.coral_count_name_msgs(self._h, int(n_edges), len(st), ctypes.c_void_p(buf_ptr), _p(st), _p(sz),
+                                                  ctypes.c_void_p(rb_ptr), ctypes.c_int64(n_rb), _p(cnt)))
         return cnt[:n_edges]
 
     def device_view(self):
@@ -211,12 +235,6 @@ class Context(object):
         ptrs = (ctypes.c_uint64 * 9)()
         self._check(self._L.coral_device_view(self._h, ptrs, 9))
         return [int(x) for x in ptrs]
-
-    def load_rows_dev(self, n, text_ptr, text_bytes, off_ptr, lo_ptr, hi_ptr, fm_ptr, lseq_ptr, nm_ptr, sa_off_ptr, sa_len_ptr):
-        vp = ctypes.c_void_p
-        self._check(self._L.coral_load_rows_dev(self._h, ctypes.c_int64(n), vp(text_ptr), ctypes.c_uint64(text_bytes), vp(off_ptr),
-                                                vp(lo_ptr), vp(hi_ptr), vp(fm_ptr), vp(lseq_ptr), vp(nm_ptr), vp(sa_off_ptr),
-                                                vp(sa_len_ptr)))
 
     def rescan(self):
         self._check(self._L.coral_rescan(self._h))
@@ -332,6 +350,24 @@ class Context(object):
                 _p(out["row_pos2"]), _p(out["row_nb"]), _p(out["row_first"]), _p(out["row_stats"])))
         return out
 
+    def concordant_rows_only(self, tid, p):
+        """The (edge, record, mask) rows of this ctx's records stay on the device (concordant_pack); no count."""
+        tid = np.ascontiguousarray(tid, dtype=np.int32)
+        p = np.ascontiguousarray(p, dtype=np.int32)
+        nr = ctypes.c_int64()
+        self._check(self._L.coral_concordant(self._h, _p(tid), _p(p), len(tid), ctypes.c_int64(0), None, None, None,
+                                             ctypes.byref(nr)))
+        self._stab_n = int(nr.value)
+        return self._stab_n
+
+    def concordant_rows(self):
+        """(edge, record, mask) rows of the last concordant / concordant_rows_only call, read back to the host."""
+        nr = self._stab_n
+        rows = {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
+        if nr:
+            self._check(self._L.coral_get_concordant_rows(self._h, _p(rows["edge"]), _p(rows["rec"]), _p(rows["mask"])))
+        return rows
+
     def concordant(self, tid, p, rb_edge, rb_rec, fetch_rows=True):
         """Edges sorted by (tid, p).  -> (lr_count int64[n], rows dict(edge, rec, mask))."""
         tid = np.ascontiguousarray(tid, dtype=np.int32)
@@ -343,11 +379,10 @@ class Context(object):
         nr = ctypes.c_int64()
         self._check(self._L.coral_concordant(self._h, _p(tid), _p(p), n, ctypes.c_int64(len(rb_edge)), _p(rb_edge), _p(rb_rec),
                                              _p(cnt), ctypes.byref(nr)))
-        nr = nr.value
-        rows = {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
-        if nr and fetch_rows:
-            self._check(self._L.coral_get_concordant_rows(self._h, _p(rows["edge"]), _p(rows["rec"]), _p(rows["mask"])))
-        return cnt, rows
+        self._stab_n = nr = nr.value
+        if fetch_rows:
+            return cnt, self.concordant_rows()
+        return cnt, {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
 
     def sa_text(self, text, ent_ptr, ent_beg, ent_end, read_len):
         n_reads = len(read_len)

@@ -118,6 +118,7 @@ struct coral_ctx {
     DevBuf cw[32];   // cluster / peel work buffers and results
     int64_t cl_n = 0, cl_n_clusters = 0;
     bool cl_valid = false;
+    DevBuf xmsg[3];  // packed exchange messages (SA rows, extra primaries, concordant rows): live until the next pack
     DevBuf status;  // int32[8] device status words (format errors etc.)
 
     // scratch

@@ -111,7 +111,7 @@ int coral_load_rows(coral_ctx* c, int64_t n, const uint8_t* text, uint64_t text_
 
 }  // extern "C"
 
-// ---- device-side views: the exchange itself runs on the GPU (torch / NCCL on the caller's side) ------------------
+// ---- device-side views (the packed device-side exchange is in exchange.cu) ---------------------------------------
 extern "C" {
 
 // Device addresses of the record buffer, the offsets and the table columns the exchange reads (valid until the next
@@ -123,48 +123,6 @@ int coral_device_view(coral_ctx* c, uint64_t* ptrs, int32_t n_ptrs) {
     RecordTable& t = c->rt;
     const void* v[9] = {c->d_recs, c->d_off.p, t.name_lo.p, t.name_hi.p, t.flag_mapq.p, t.lseq.p, t.nm.p, t.sa_off.p, t.sa_len.p};
     for (int i = 0; i < 9; i++) ptrs[i] = (uint64_t)reinterpret_cast<uintptr_t>(v[i]);
-    return CORAL_OK;
-}
-
-// coral_load_rows with every array already on this ctx's device (the all-gathered rows never visit the host).
-// Slot i of `d_text` = bytes [d_text_off[i], d_text_off[i+1]); its SA text sits at d_sa_off[i] within the slot
-// (0 = the row has no SA tag), d_sa_len[i] bytes long.  flag_mapq = flag | mapq << 16.
-int coral_load_rows_dev(coral_ctx* c, int64_t n, const uint8_t* d_text, uint64_t text_bytes, const uint64_t* d_text_off,
-                        const uint64_t* d_name_lo, const uint64_t* d_name_hi, const uint32_t* d_flag_mapq,
-                        const uint32_t* d_l_seq, const int32_t* d_nm, const uint32_t* d_sa_off, const uint32_t* d_sa_len) {
-    if (!c || n < 0) return CORAL_E_ARG;
-    cudaSetDevice(c->device);
-    c->loaded = false;
-    c->rows_only = true;
-    CORAL_CUDA(c, c->recs_owned.ensure(text_bytes + 64));
-    if (text_bytes) CORAL_CUDA(c, cudaMemcpyAsync(c->recs_owned.p, d_text, text_bytes, cudaMemcpyDeviceToDevice, c->stream));
-    CORAL_CUDA(c, cudaMemsetAsync((uint8_t*)c->recs_owned.p + text_bytes, 0, 64, c->stream));
-    c->d_recs = c->recs_owned.as<uint8_t>();
-    c->nbytes = text_bytes;
-    c->nrec = n;
-    RecordTable& t = c->rt;
-    const size_t n4 = (size_t)n * 4, n8 = (size_t)n * 8;
-    struct { DevBuf* b; const void* src; size_t bytes; } cp[] = {
-        {&c->d_off, d_text_off, n8 + 8}, {&t.name_lo, d_name_lo, n8}, {&t.name_hi, d_name_hi, n8},
-        {&t.flag_mapq, d_flag_mapq, n4}, {&t.lseq, d_l_seq, n4}, {&t.nm, d_nm, n4}, {&t.sa_off, d_sa_off, n4},
-        {&t.sa_len, d_sa_len, n4}};
-    for (auto& x : cp) {
-        CORAL_CUDA(c, x.b->ensure(std::max<size_t>(x.bytes, 8)));
-        if (n > 0 || x.b == &c->d_off) CORAL_CUDA(c, cudaMemcpyAsync(x.b->p, x.src, x.bytes, cudaMemcpyDeviceToDevice, c->stream));
-    }
-    CORAL_CUDA(c, t.tid.ensure(std::max<size_t>(n4, 4)));
-    CORAL_CUDA(c, cudaMemsetAsync(t.tid.p, 0xFF, std::max<size_t>(n4, 4), c->stream));
-    DevBuf* zero4[] = {&t.pos, &t.endpos, &t.ncig, &t.infer, &t.mbases, &t.nonacgt, &t.fbs, &t.lbe, &t.ngap};
-    for (DevBuf* b : zero4) {
-        CORAL_CUDA(c, b->ensure(std::max<size_t>(n4, 4)));
-        CORAL_CUDA(c, cudaMemsetAsync(b->p, 0, std::max<size_t>(n4, 4), c->stream));
-    }
-    c->gaps.n = 0;
-    CORAL_CUDA(c, c->status.ensure(64));
-    CORAL_CUDA(c, cudaMemsetAsync(c->status.p, 0, 64, c->stream));
-    CORAL_CUDA(c, c->gaps.counter.ensure(16));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->loaded = true;
     return CORAL_OK;
 }
 

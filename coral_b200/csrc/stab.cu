@@ -6,12 +6,16 @@
 //   ce[8] = len((names(p) & names(p+1) & names(p-d-1) & names(p+1+d)) - rbps)
 // with rbps = names of the reads on discordant edges incident to either node.  Here every record emits a
 // (edge, record, 4-bit mask) row for the edges whose points it covers, rbps members emit a row with bit 16,
-// rows are sorted by (edge, name hash) and the masks OR-ed per name, so two records of one read can jointly
-// satisfy the test exactly as the name sets do.
+// rows are bucketed by a 24-bit hash of (edge, name hash) (one 3-pass radix sort), equal (edge, name) triples are
+// found by exact comparison inside a bucket and their masks OR-ed, so two records of one read can jointly satisfy
+// the test exactly as the name sets do.  The multi-GPU form packs the local rows as one message per rank
+// (coral_concordant_pack), the caller all-gathers the messages, and coral_count_name_msgs runs the same count on
+// the gathered rows.
 #include <vector>
 
 #include "ctx.h"
 #include "dev_util.cuh"
+#include "msg.cuh"
 #include "relops.cuh"
 
 namespace coral {
@@ -64,67 +68,58 @@ __global__ void k_stab_rbps(int64_t n_rb, const uint32_t* __restrict__ rb_edge, 
     row_mask[base + i] = 16u;
 }
 
-__global__ void k_stab_iota(int64_t n, uint32_t* p) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) p[i] = (uint32_t)i;
-}
-
-__global__ void k_stab_key(int64_t n, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ row_rec,
-                           const uint32_t* __restrict__ row_edge, const uint64_t* __restrict__ name, int which,
-                           uint64_t* __restrict__ key) {
+// ---- concordant exchange: (edge, name, mask) rows counted per edge -----------------------------------------
+__global__ void k_name_rows(int64_t n, const uint32_t* __restrict__ edge, const uint32_t* __restrict__ rec,
+                            const uint32_t* __restrict__ mask, const uint64_t* __restrict__ lo, const uint64_t* __restrict__ hi,
+                            NameRow* __restrict__ out) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint32_t r = perm[i];
-    key[i] = which == 2 ? (uint64_t)row_edge[r] : name[row_rec[r]];
+    const uint32_t r = rec[i];
+    out[i] = NameRow{edge[i], lo[r], hi[r], mask[i]};
 }
 
-// one thread per (edge, name) segment head: OR the masks, count full support outside rbps
-__global__ void k_stab_count(int64_t n, const uint32_t* __restrict__ perm, const uint32_t* __restrict__ row_edge,
-                             const uint32_t* __restrict__ row_rec, const uint32_t* __restrict__ row_mask,
-                             const uint64_t* __restrict__ nlo, const uint64_t* __restrict__ nhi,
-                             unsigned long long* __restrict__ count) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t r = perm[i];
-    const uint32_t e = row_edge[r];
-    const uint64_t lo = nlo[row_rec[r]], hi = nhi[row_rec[r]];
-    if (i > 0) {
-        const uint32_t q = perm[i - 1];
-        if (row_edge[q] == e && nlo[row_rec[q]] == lo && nhi[row_rec[q]] == hi) return;  // not a head
-    }
-    uint32_t m = 0;
-    for (int64_t j = i; j < n; j++) {
-        const uint32_t q = perm[j];
-        if (row_edge[q] != e || nlo[row_rec[q]] != lo || nhi[row_rec[q]] != hi) break;
-        m |= row_mask[q];
-    }
-    if ((m & 15u) == 15u && !(m & 16u)) atomicAdd(count + e, 1ull);
+struct NameSet {
+    const uint8_t* base[17];   // messages of the ranks, then the caller's rbps rows (no header)
+    uint64_t row0[18];
+    int n;                     // entries in base[]
+    int n_msgs;                // the first n_msgs carry a MsgHdr
+};
+
+__device__ __forceinline__ NameRow name_row(const NameSet& s, uint64_t g) {
+    int r = 0;
+    while (r + 1 < s.n && g >= s.row0[r + 1]) r++;
+    const uint8_t* b = s.base[r] + (r < s.n_msgs ? sizeof(MsgHdr) : 0);
+    return reinterpret_cast<const NameRow*>(b)[g - s.row0[r]];
 }
 
-// ---- the same count on explicit (edge, name hash, mask) rows: the multi-GPU combine --------------------------------
-__global__ void k_rows_key(int64_t n, const uint32_t* __restrict__ perm, const uint64_t* __restrict__ a, uint64_t* __restrict__ key) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) key[i] = a[perm[i]];
+// 32-bit bucket of (edge, name); equal triples share a bucket, the count kernel compares triples exactly
+__global__ void k_name_keys(NameSet s, NameRow* __restrict__ rows, uint64_t* __restrict__ key, uint32_t* __restrict__ idx) {
+    const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= s.row0[s.n]) return;
+    const NameRow r = name_row(s, g);
+    rows[g] = r;
+    key[g] = mix64(r.lo ^ mix64(r.hi + 0x9e3779b97f4a7c15ull * (r.edge + 1))) >> 40;   // 24 bits: 3 radix passes
+    idx[g] = (uint32_t)g;
 }
-__global__ void k_rows_count(int64_t n, const uint32_t* __restrict__ perm, const uint64_t* __restrict__ edge,
-                             const uint64_t* __restrict__ lo, const uint64_t* __restrict__ hi, const uint64_t* __restrict__ mask,
-                             unsigned long long* __restrict__ count, int64_t n_edges) {
+
+__global__ void k_name_count(int64_t n, const uint64_t* __restrict__ skey, const uint32_t* __restrict__ sidx,
+                             const NameRow* __restrict__ rows, unsigned long long* __restrict__ count, int64_t n_edges) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint32_t r = perm[i];
-    const uint64_t e = edge[r], l = lo[r], h = hi[r];
-    if (i > 0) {
-        const uint32_t q = perm[i - 1];
-        if (edge[q] == e && lo[q] == l && hi[q] == h) return;  // not a head
+    const uint64_t k = skey[i];
+    const NameRow me = rows[sidx[i]];
+    for (int64_t j = i - 1; j >= 0 && skey[j] == k; j--) {     // a head has no equal triple before it in its bucket
+        const NameRow q = rows[sidx[j]];
+        if (q.edge == me.edge && q.lo == me.lo && q.hi == me.hi) return;
     }
-    uint64_t m = 0;
-    for (int64_t j = i; j < n; j++) {
-        const uint32_t q = perm[j];
-        if (edge[q] != e || lo[q] != l || hi[q] != h) break;
-        m |= mask[q];
+    uint64_t m = me.mask;
+    for (int64_t j = i + 1; j < n && skey[j] == k; j++) {
+        const NameRow q = rows[sidx[j]];
+        if (q.edge == me.edge && q.lo == me.lo && q.hi == me.hi) m |= q.mask;
     }
-    if ((m & 15u) == 15u && !(m & 16u) && (int64_t)e < n_edges) atomicAdd(count + e, 1ull);
+    if ((m & 15u) == 15u && !(m & 16u) && (int64_t)me.edge < n_edges) atomicAdd(count + me.edge, 1ull);
 }
+
 
 }  // namespace coral
 
@@ -137,6 +132,35 @@ __global__ void k_rows_count(int64_t n, const uint32_t* __restrict__ perm, const
         }                                                                                \
     } while (0)
 
+namespace {
+using namespace coral;
+
+// lr_count[e] = names of edge e whose OR-ed mask has bits 0..3 and not bit 4, over the rows of `set`
+int count_names(coral_ctx* c, const NameSet& set, int32_t n_edges, int64_t* lr_count) {
+    for (int32_t i = 0; i < n_edges; i++) lr_count[i] = 0;
+    const int64_t n = (int64_t)set.row0[set.n];
+    if (n == 0 || n_edges == 0) return CORAL_OK;
+    if (n >= ((int64_t)1 << 32)) { c->err = "too many rows"; return CORAL_E_ARG; }
+    DevBuf* w = c->sw;
+    CORAL_CUDA(c, w[6].ensure((size_t)n * 56 + 64 + (size_t)n_edges * 8));
+    NameRow* rows = w[6].as<NameRow>();
+    uint64_t* keyA = reinterpret_cast<uint64_t*>(rows + n); uint64_t* keyB = keyA + n;
+    unsigned long long* d_count = reinterpret_cast<unsigned long long*>(keyB + n);
+    uint32_t* pa = reinterpret_cast<uint32_t*>(d_count + n_edges); uint32_t* pb = pa + n;
+    CORAL_CUDA(c, cudaMemsetAsync(d_count, 0, (size_t)n_edges * 8, c->stream));
+    LAUNCH_1D(k_name_keys, n, set, rows, keyA, pa);
+    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pa, pb, n, 0, 24));
+    LAUNCH_1D(k_name_count, n, n, keyB, pb, rows, d_count, (int64_t)n_edges);
+    std::vector<unsigned long long> h((size_t)n_edges);
+    CORAL_TRY(d2h(c, h.data(), d_count, (size_t)n_edges));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (int32_t i = 0; i < n_edges; i++) lr_count[i] = (int64_t)h[i];
+    return CORAL_OK;
+}
+
+}  // namespace
+
+// lr_count == NULL: only the stab rows are produced (the sharded path counts on the gathered rows).
 extern "C" int coral_concordant(coral_ctx* c, const int32_t* tid, const int32_t* p, int32_t n_edges, int64_t n_rbps,
                                 const uint32_t* rb_edge, const uint32_t* rb_rec, int64_t* lr_count, int64_t* n_union_rows) {
     using namespace coral;
@@ -162,9 +186,8 @@ extern "C" int coral_concordant(coral_ctx* c, const int32_t* tid, const int32_t*
     CORAL_TRY(h2d(c, d_e, tid, (size_t)n_edges));
     CORAL_TRY(h2d(c, d_e + n_edges, p, (size_t)n_edges));
     Edges E{d_e, d_e + n_edges, n_edges, c->prm.min_bp_match_cutoff};
-    CORAL_CUDA(c, w[1].ensure((size_t)n_edges * 8 + 16));
-    unsigned long long* d_count = w[1].as<unsigned long long>();
-    unsigned long long* d_nrows = d_count + n_edges;
+    CORAL_CUDA(c, w[1].ensure(16));
+    unsigned long long* d_nrows = w[1].as<unsigned long long>();
     CORAL_CUDA(c, w[2].ensure((size_t)std::max<int64_t>(n_rbps, 1) * 8));
     uint32_t* d_rb = w[2].as<uint32_t>();
     CORAL_TRY(h2d(c, d_rb, rb_edge, (size_t)n_rbps));
@@ -175,7 +198,7 @@ extern "C" int coral_concordant(coral_ctx* c, const int32_t* tid, const int32_t*
     for (int attempt = 0; attempt < 2; attempt++) {
         const size_t tot = (size_t)(cap + n_rbps);
         CORAL_CUDA(c, w[3].ensure(tot * 4)); CORAL_CUDA(c, w[4].ensure(tot * 4)); CORAL_CUDA(c, w[5].ensure(tot * 4));
-        CORAL_CUDA(c, cudaMemsetAsync(d_count, 0, (size_t)n_edges * 8 + 8, c->stream));
+        CORAL_CUDA(c, cudaMemsetAsync(d_nrows, 0, 8, c->stream));
         LAUNCH_1D(k_stab_rows, c->nrec, c->nrec, rt.tid.as<int32_t>(), rt.pos.as<int32_t>(), rt.endpos.as<int32_t>(), E,
                   w[3].as<uint32_t>(), w[4].as<uint32_t>(), w[5].as<uint32_t>(), d_nrows, cap);
         CORAL_TRY(d2h(c, &n_rows, d_nrows, 1));
@@ -186,28 +209,23 @@ extern "C" int coral_concordant(coral_ctx* c, const int32_t* tid, const int32_t*
     uint32_t* row_edge = w[3].as<uint32_t>(); uint32_t* row_rec = w[4].as<uint32_t>(); uint32_t* row_mask = w[5].as<uint32_t>();
     LAUNCH_1D(k_stab_rbps, n_rbps, n_rbps, d_rb, d_rb + n_rbps, row_edge, row_rec, row_mask, (int64_t)n_rows);
     const int64_t n = (int64_t)n_rows + n_rbps;
-    if (n > 0) {
-        CORAL_CUDA(c, w[6].ensure((size_t)n * 24 + 64));
-        uint64_t* keyA = w[6].as<uint64_t>(); uint64_t* keyB = keyA + n;
-        uint32_t* pa = reinterpret_cast<uint32_t*>(keyB + n); uint32_t* pb = pa + n;
-        LAUNCH_1D(k_stab_iota, n, n, pa);
-        LAUNCH_1D(k_stab_key, n, n, pa, row_rec, row_edge, rt.name_lo.as<uint64_t>(), 0, keyA);
-        CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pa, pb, n));
-        LAUNCH_1D(k_stab_key, n, n, pb, row_rec, row_edge, rt.name_hi.as<uint64_t>(), 1, keyA);
-        CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pb, pa, n));
-        LAUNCH_1D(k_stab_key, n, n, pa, row_rec, row_edge, rt.name_lo.as<uint64_t>(), 2, keyA);
-        CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pa, pb, n, 0, 32));
-        LAUNCH_1D(k_stab_count, n, n, pb, row_edge, row_rec, row_mask, rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(), d_count);
-    }
-    c->stage_end(CORAL_STAGE_STAB);
-    std::vector<unsigned long long> h((size_t)n_edges);
-    CORAL_TRY(d2h(c, h.data(), d_count, (size_t)n_edges));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
-    for (int32_t i = 0; i < n_edges; i++) lr_count[i] = (int64_t)h[i];
     c->stab_n = (int64_t)n_rows;
     c->stab_valid = true;
     if (n_union_rows) *n_union_rows = (int64_t)n_rows;
-    return CORAL_OK;
+    int rc = CORAL_OK;
+    if (lr_count) {
+        // the local rows (+ rbps rows, mask 16) as one headerless NameRow array, counted like a gathered set
+        CORAL_CUDA(c, w[7].ensure((size_t)std::max<int64_t>(n, 1) * sizeof(NameRow)));
+        LAUNCH_1D(k_name_rows, n, n, row_edge, row_rec, row_mask, rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(),
+                  w[7].as<NameRow>());
+        NameSet set;
+        set.n = 1; set.n_msgs = 0;
+        set.base[0] = w[7].as<uint8_t>();
+        set.row0[0] = 0; set.row0[1] = (uint64_t)n;
+        rc = count_names(c, set, n_edges, lr_count);
+    }
+    c->stage_end(CORAL_STAGE_STAB);
+    return rc;
 }
 
 extern "C" int coral_get_concordant_rows(coral_ctx* c, uint32_t* edge, uint32_t* rec, uint32_t* mask) {
@@ -216,6 +234,7 @@ extern "C" int coral_get_concordant_rows(coral_ctx* c, uint32_t* edge, uint32_t*
     if (!c->stab_valid) { c->err = "coral_get_concordant_rows before coral_concordant"; return CORAL_E_STATE; }
     cudaSetDevice(c->device);
     const size_t n = (size_t)c->stab_n;
+    if (n == 0) return CORAL_OK;
     if (edge) CORAL_TRY(d2h(c, edge, c->sw[3].p, n));
     if (rec) CORAL_TRY(d2h(c, rec, c->sw[4].p, n));
     if (mask) CORAL_TRY(d2h(c, mask, c->sw[5].p, n));
@@ -223,43 +242,51 @@ extern "C" int coral_get_concordant_rows(coral_ctx* c, uint32_t* edge, uint32_t*
     return CORAL_OK;
 }
 
-// Device addresses of the rows left by the last coral_concordant (edge, rec, mask: uint32 each), so a multi-GPU caller
-// can all-gather them (as (edge, name hash, mask)) without a host round trip.
-extern "C" int coral_concordant_device_rows(coral_ctx* c, uint64_t* ptrs, int64_t* n_rows) {
-    if (!c || !ptrs || !n_rows) return CORAL_E_ARG;
-    if (!c->stab_valid) { c->err = "coral_concordant_device_rows before coral_concordant"; return CORAL_E_STATE; }
-    for (int k = 0; k < 3; k++) ptrs[k] = (uint64_t)reinterpret_cast<uintptr_t>(c->sw[3 + k].p);
-    *n_rows = c->stab_n;
+// ---- multi-GPU form ----------------------------------------------------------------------------
+// The rows of the last coral_concordant as one message: MsgHdr + n NameRow (edge, name hash, mask), on the device.
+extern "C" int coral_concordant_pack(coral_ctx* c, uint64_t* d_msg, uint64_t* nbytes) {
+    using namespace coral;
+    if (!c || !d_msg || !nbytes) return CORAL_E_ARG;
+    if (!c->stab_valid) { c->err = "coral_concordant_pack before coral_concordant"; return CORAL_E_STATE; }
+    cudaSetDevice(c->device);
+    const int64_t n = c->stab_n;
+    const uint64_t total = sizeof(MsgHdr) + (uint64_t)n * sizeof(NameRow);
+    DevBuf& msg = c->xmsg[2];
+    CORAL_CUDA(c, msg.ensure(total));
+    MsgHdr h{};
+    h.n_rows = (uint64_t)n; h.kind = MSG_NAMES;
+    CORAL_CUDA(c, cudaMemcpyAsync(msg.p, &h, sizeof h, cudaMemcpyHostToDevice, c->stream));
+    RecordTable& rt = c->rt;
+    LAUNCH_1D(k_name_rows, n, n, c->sw[3].as<uint32_t>(), c->sw[4].as<uint32_t>(), c->sw[5].as<uint32_t>(),
+              rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(), reinterpret_cast<NameRow*>(msg.as<uint8_t>() + sizeof(MsgHdr)));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    *d_msg = (uint64_t)reinterpret_cast<uintptr_t>(msg.p);
+    *nbytes = total;
     return CORAL_OK;
 }
 
-// ce[8] from explicit rows, all arrays on this ctx's device (uint64 each): per (edge, name hash) the masks are OR-ed;
-// a name counts for its edge when bits 0..3 are all set and bit 4 (rbps member, ibg:1047-1053) is not.
-extern "C" int coral_count_name_rows(coral_ctx* c, int32_t n_edges, int64_t n, const uint64_t* d_edge, const uint64_t* d_lo,
-                                     const uint64_t* d_hi, const uint64_t* d_mask, int64_t* lr_count) {
+// ce[8] on the gathered messages of all ranks (message r = d_buf[starts[r] : starts[r] + sizes[r]), host arrays) + the
+// caller's rbps rows (d_rb_rows: n_rb NameRow on this device, mask 16, ibg:1047-1053).
+extern "C" int coral_count_name_msgs(coral_ctx* c, int32_t n_edges, int32_t n_ranks, const uint8_t* d_buf, const uint64_t* starts,
+                                     const uint64_t* sizes, const uint64_t* d_rb_rows, int64_t n_rb, int64_t* lr_count) {
     using namespace coral;
-    if (!c || n_edges < 0 || n < 0 || !lr_count) return CORAL_E_ARG;
+    if (!c || n_edges < 0 || !d_buf || !starts || !sizes || n_rb < 0 || !lr_count) return CORAL_E_ARG;
+    if (n_ranks < 1 || n_ranks > 16) { c->err = "1..16 ranks per exchange"; return CORAL_E_ARG; }
     cudaSetDevice(c->device);
-    for (int32_t i = 0; i < n_edges; i++) lr_count[i] = 0;
-    if (n == 0 || n_edges == 0) return CORAL_OK;
-    if (n >= ((int64_t)1 << 32)) { c->err = "too many rows"; return CORAL_E_ARG; }
-    DevBuf* w = c->sw;
-    CORAL_CUDA(c, w[7].ensure((size_t)n * 24 + 64 + (size_t)n_edges * 8));
-    uint64_t* keyA = w[7].as<uint64_t>(); uint64_t* keyB = keyA + n;
-    uint32_t* pa = reinterpret_cast<uint32_t*>(keyB + n); uint32_t* pb = pa + n;
-    unsigned long long* d_count = reinterpret_cast<unsigned long long*>(pb + n);   // byte offset 24 n: 8-byte aligned
-    CORAL_CUDA(c, cudaMemsetAsync(d_count, 0, (size_t)n_edges * 8, c->stream));
-    LAUNCH_1D(k_stab_iota, n, n, pa);
-    LAUNCH_1D(k_rows_key, n, n, pa, d_lo, keyA);
-    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pa, pb, n));
-    LAUNCH_1D(k_rows_key, n, n, pb, d_hi, keyA);
-    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pb, pa, n));
-    LAUNCH_1D(k_rows_key, n, n, pa, d_edge, keyA);
-    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pa, pb, n, 0, 32));
-    LAUNCH_1D(k_rows_count, n, n, pb, d_edge, d_lo, d_hi, d_mask, d_count, (int64_t)n_edges);
-    std::vector<unsigned long long> h((size_t)n_edges);
-    CORAL_TRY(d2h(c, h.data(), d_count, (size_t)n_edges));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
-    for (int32_t i = 0; i < n_edges; i++) lr_count[i] = (int64_t)h[i];
-    return CORAL_OK;
+    NameSet set;
+    set.n = n_ranks + (n_rb > 0 ? 1 : 0);
+    set.n_msgs = n_ranks;
+    set.row0[0] = 0;
+    for (int r = 0; r < n_ranks; r++) {
+        if ((starts[r] & 15) || sizes[r] < sizeof(MsgHdr) || (sizes[r] - sizeof(MsgHdr)) % sizeof(NameRow)) {
+            c->err = "bad name-row message"; return CORAL_E_ARG;
+        }
+        set.base[r] = d_buf + starts[r];
+        set.row0[r + 1] = set.row0[r] + (sizes[r] - sizeof(MsgHdr)) / sizeof(NameRow);
+    }
+    if (n_rb > 0) {
+        set.base[n_ranks] = reinterpret_cast<const uint8_t*>(d_rb_rows);
+        set.row0[n_ranks + 1] = set.row0[n_ranks] + (uint64_t)n_rb;
+    }
+    return count_names(c, set, n_edges, lr_count);
 }

@@ -181,6 +181,30 @@ def merge_smalldel_rows(comm, rows):
     return allr
 
 
+def pack_smalldel(rows):
+    """rows: list of (name, ai, next_start, prev_end, first_start, last_end, mapq, name_lo, name_hi) -> one int64
+    message: [n, name bytes] + n x 8 columns + the NUL-separated names (padded to 8 bytes)."""
+    n = len(rows)
+    blob = b"".join(r[0].encode() + b"\0" for r in rows)
+    nb = (len(blob) + 7) // 8
+    out = np.zeros(2 + 8 * n + nb, np.int64)
+    out[0], out[1] = n, len(blob)
+    if n:
+        out[2:2 + 8 * n] = np.array([r[1:9] for r in rows], np.int64).reshape(-1)
+        out[2 + 8 * n:].view(np.uint8)[:len(blob)] = np.frombuffer(blob, np.uint8)
+    return out
+
+
+def unpack_smalldel(msg):
+    """Inverse of pack_smalldel on the bytes of one message (uint8 array, possibly padded at the end)."""
+    a = np.ascontiguousarray(msg).view(np.uint8)
+    head = a[:16].view(np.int64)
+    n, nbytes = int(head[0]), int(head[1])
+    cols = a[16:16 + 64 * n].view(np.int64).reshape(n, 8)
+    names = a[16 + 64 * n:16 + 64 * n + nbytes].tobytes().split(b"\0")[:n]
+    return [(names[k].decode(), ) + tuple(int(x) for x in cols[k]) for k in range(n)]
+
+
 def combine_concordant(comm, n_edges, rows, rbps):
     """rows: this rank's (edge, read name, mask) for every local record covering one of the four points of an edge
     (mask bit0 = p, bit1 = p+1, bit2 = p-d-1, bit3 = p+1+d).  The reference works on NAME sets (ibg:1043-1055), so
@@ -248,13 +272,26 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             self._cctx = _abi.Context(device)          # rows-only ctx: the gathered fetch rows live here
             self._cctx.set_references(view.references)
             self._row_names = None
-            self._rows = None
             self._rbt = None
+            self._edge_arrays = None
             self._name_hash = {}     # read name -> 128-bit hash as two int64 (for the rbps rows of the concordant combine)
+            self._tc = None
 
         @property
         def _chim_ctx(self):
             return self._cctx
+
+        def _tcomm(self):
+            if self._tc is None:
+                from . import exchange
+                self._tc = exchange.TensorComm(self._comm)
+            return self._tc
+
+        def _gather(self, ptr, nbytes):
+            """All-gather of a device message the CUDA side packed -> (buffer, starts, sizes)."""
+            import torch
+            from . import exchange
+            return self._tcomm().gather_msgs(exchange.view(ptr, nbytes, "|u1", torch.device("cuda", device)))
 
         # a12 / a10: additive over records -> integer all-reduce of the shard sums
         def _region_counts(self, tid, start, stop):
@@ -262,47 +299,41 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             tot = self._comm.all_reduce_sum(np.concatenate([bs, rc]).astype(np.int64))
             return tot[:len(bs)], tot[len(bs):]
 
-        # ---- tensor views of this shard's device tables (exchange.py runs on them) ---------------------------------
         def _views(self):
+            """Tensor views of this shard's name-hash columns (device memory owned by the ctx)."""
             import torch
             from . import exchange
-            ctx = self._ctx
-            p = ctx.device_view()
-            n = ctx.n_records
-            nb = int(self.lr_bamfh.rec_off[-1]) if n else 0
+            p = self._ctx.device_view()
+            n = self._ctx.n_records
             dev = torch.device("cuda", device)
-            v = exchange.view
-            return {"recs": v(p[0], nb, "|u1", dev), "off": v(p[1], n + 1 if n else 0, "<i8", dev),
-                    "name_lo": v(p[2], n, "<i8", dev), "name_hi": v(p[3], n, "<i8", dev), "flag_mapq": v(p[4], n, "<i4", dev),
-                    "l_seq": v(p[5], n, "<i4", dev), "nm": v(p[6], n, "<i4", dev), "sa_off": v(p[7], n, "<i4", dev),
-                    "sa_len": v(p[8], n, "<i4", dev)}
+            return {"name_lo": exchange.view(p[2], n, "<i8", dev), "name_hi": exchange.view(p[3], n, "<i8", dev)}
 
-        # a1: the exchange, on the GPU: rows selected, all-gathered (NCCL) and loaded without visiting the host
+        # a1: the exchange, on the GPU.  Two packed messages per rank (csrc/exchange.cu), two all-gathers, and the
+        # gathered rows are unpacked straight into the rows-only ctx: nothing visits the host.
         def _run_fetch(self):
-            import torch
-            from . import exchange
-            tc = exchange.TensorComm(self._comm)
-            tv = self._views()
-            rows = exchange.fetch_exchange(tc, tv)
-            s1, s2, nn, zd = self._ctx.nm_partials()
-            parts = torch.cat(tc.all_gather(torch.tensor([[s1, s2, float(nn), float(zd)]], dtype=torch.float64,
-                                                         device=rows["text"].device)), 0).cpu().numpy()
-            torch.cuda.current_stream().synchronize()
-            m = int(rows["name_lo"].shape[0])
-            keep = [rows[k].contiguous() for k in ("text", "text_off", "name_lo", "name_hi", "flag_mapq", "l_seq", "nm",
-                                                   "sa_off", "sa_len")]
-            self._cctx.load_rows_dev(m, keep[0].data_ptr(), int(keep[0].shape[0]), *[t.data_ptr() for t in keep[1:]])
-            f = self._cctx.fetch()
+            ctx, cctx = self._ctx, self._cctx
+            buf1, st1, _ = self._gather(*ctx.pack_sa_rows())
+            buf2, st2, _ = self._gather(*ctx.pack_extra_rows(buf1.data_ptr(), st1))
+            _, (s1, s2, nn, zd) = cctx.unpack_rows(buf1.data_ptr(), st1, buf2.data_ptr(), st2)
+            f = cctx.fetch()
             # nm_stats (ibg:153-157) run over ALL records: the shard partials are summed in rank order (the f64 sum
             # order differs from the 1-GPU order: within 1e-9 relative, unused downstream)
-            f["nm_sum"] = float(parts[:, 0].sum()); f["nm_sumsq"] = float(parts[:, 1].sum())
-            f["nm_n"] = int(parts[:, 2].sum()); f["nm_zero_div"] = int(parts[:, 3].sum())
-            self._rows, self._row_names = rows, None
+            f["nm_sum"] = float(s1.sum()); f["nm_sumsq"] = float(s2.sum())
+            f["nm_n"] = int(nn.sum()); f["nm_zero_div"] = int(zd.sum())
+            self._row_names = None
 
             def names_of(recs):
                 if self._row_names is None:         # one D2H of the gathered text, only when names are materialised
-                    self._row_names = exchange.row_names(self._rows)
-                    lo = self._rows["name_lo"].cpu().tolist(); hi = self._rows["name_hi"].cpu().tolist()
+                    import torch
+                    from . import exchange
+                    dev = torch.device("cuda", device)
+                    p = cctx.device_view()
+                    n = cctx.n_records
+                    off = exchange.view(p[1], n + 1, "<i8", dev).cpu().numpy()
+                    text = exchange.view(p[0], int(off[-1]), "|u1", dev).cpu().numpy()
+                    self._row_names = exchange.row_names(text, off[:-1])
+                    lo = exchange.view(p[2], n, "<i8", dev).cpu().tolist()
+                    hi = exchange.view(p[3], n, "<i8", dev).cpu().tolist()
                     self._name_hash.update(zip(self._row_names, zip(lo, hi)))
                 return [self._row_names[int(r)] for r in recs]
             return f, names_of
@@ -311,69 +342,67 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             self._cctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
             bam_to_breakpoint_nanopore.find_breakpoints(self)
 
-        # a3: local gap rows (+ the name hash of each), merged in emission order
+        # a3: local gap rows (+ the name hash of each) as one host-built message per rank, merged in emission order
         def _smalldel_rows(self, t, s, e):
+            import torch
+            from . import exchange
             rows = self._ctx.smalldel(t, s, e)
-            recs = rows["rec"].astype(np.int64)
-            lo = hi = np.zeros(0, np.int64)
-            if len(recs):
-                import torch
+            local = []
+            if rows["n"]:
+                recs = rows["rec"].astype(np.int64)
                 tv = self._views()
                 idx = torch.as_tensor(recs, device=tv["name_lo"].device)
-                lo, hi = tv["name_lo"][idx].cpu().numpy(), tv["name_hi"][idx].cpu().numpy()
-            names = {}
-            local = []
-            cols = [rows[k].tolist() for k in ("ai", "next_start", "prev_end", "first_start", "last_end", "mapq")]
-            for k, rec in enumerate(recs.tolist()):
-                nm = names.get(rec)
-                if nm is None:
-                    nm = names[rec] = self.lr_bamfh.query_name(rec)
-                local.append((nm, cols[0][k], cols[1][k], cols[2][k], cols[3][k], cols[4][k], cols[5][k], int(lo[k]), int(hi[k])))
-            merged = merge_smalldel_rows(self._comm, local)
+                lo, hi = tv["name_lo"][idx].cpu().tolist(), tv["name_hi"][idx].cpu().tolist()
+                urec, inv = np.unique(recs, return_inverse=True)
+                unames = self._names_of(urec)
+                names = [unames[k] for k in inv.tolist()]
+                local = list(zip(names, *(rows[k].tolist() for k in ("ai", "next_start", "prev_end", "first_start", "last_end",
+                                                                      "mapq")), lo, hi))
+            dev = torch.device("cuda", device)
+            buf, st, sz = self._tcomm().gather_msgs(exchange.host_msg(pack_smalldel(local), dev))
+            raw = buf.cpu().numpy()
+            merged = [r for a, n in zip(st, sz) for r in unpack_smalldel(raw[a:a + n])]
+            merged.sort(key=lambda r: r[1])           # stable: interval order, then rank (= file) order, then block order
             for r in merged:
                 self._name_hash[r[0]] = (r[7], r[8])
             return [r[:7] for r in merged]
 
-        # a11: name-level set algebra across shards, on name hashes: local stab rows stay on the device, are
-        # all-gathered as (edge, name hash, mask) and counted by the same sort + OR-reduce kernel on every rank
+        # a11: name-level set algebra across shards, on name hashes: the local stab rows are packed on the device as
+        # (edge, name hash, mask), all-gathered, and counted by the same kernels on every rank
         def _concordant_counts(self, uniq, rbps):
             import torch
-            from . import exchange
             ctx = self._ctx
-            ctx.concordant([u[0] for u in uniq], [u[1] for u in uniq], [], [], fetch_rows=False)
-            ptrs, n = ctx.concordant_device_rows()
-            tv = self._views()
-            dev = tv["name_lo"].device
-            v = exchange.view
-            edge, rec, mask = (v(ptrs[k], n, "<i4", dev).to(torch.int64) for k in range(3))
+            if self._edge_arrays is None or self._edge_arrays[0] is not uniq:
+                self._edge_arrays = (uniq, np.array([u[0] for u in uniq], np.int32), np.array([u[1] for u in uniq], np.int32))
+            ctx.concordant_rows_only(self._edge_arrays[1], self._edge_arrays[2])
             if self._rbt is None or self._rbt[0] is not rbps:      # (edge, name hash, 16) rows of rbps: built once per graph
                 rb = [(k, ) + self._name_hash[nm] + (16, ) for k, names in enumerate(rbps) for nm in names if nm in self._name_hash]
-                self._rbt = (rbps, torch.as_tensor(np.array(rb, np.int64).reshape(-1, 4), device=dev))
-            mine = torch.stack([edge, tv["name_lo"][rec], tv["name_hi"][rec], mask], 1)
-            g = torch.cat(exchange.TensorComm(self._comm).all_gather(mine) + [self._rbt[1]], 0).t().contiguous()
-            torch.cuda.current_stream().synchronize()
-            cnt = ctx.count_name_rows(len(uniq), int(g.shape[1]), g[0].data_ptr(), g[1].data_ptr(), g[2].data_ptr(), g[3].data_ptr())
-            return cnt, g, (rec, mask, tv)
+                self._rbt = (rbps, torch.as_tensor(np.array(rb, np.int64).reshape(-1, 4), device=torch.device("cuda", device)))
+                torch.cuda.current_stream().synchronize()
+            gathered = self._gather(*ctx.concordant_pack())
+            rbt = self._rbt[1]
+            cnt = ctx.count_name_msgs(len(uniq), gathered[0].data_ptr(), gathered[1], gathered[2], rbt.data_ptr(), int(rbt.shape[0]))
+            return cnt, gathered
 
         def _concordant_support(self, uniq, rbps):
-            import torch
-            from . import exchange
-            cnt, g, (rec, mask, tv) = self._concordant_counts(uniq, rbps)
+            cnt, (buf, st, sz) = self._concordant_counts(uniq, rbps)
             # ce[9] wants the read NAMES covering p or p+1: every rank contributes the names of its own records
-            urec = torch.unique(rec[(mask & 3) != 0])
-            base = tv["off"][urec]
-            ln = tv["recs"][base + 12].to(torch.int64)
-            blob = exchange._gather_bytes(tv["recs"], base + 36, ln).cpu().numpy().tobytes()
-            mine = (tv["name_lo"][urec].cpu().numpy(), tv["name_hi"][urec].cpu().numpy(), blob.split(b"\0")[:len(urec)])
+            # (its message rows are in the order of its stab rows)
+            raw = buf.cpu().numpy()
+            rows = self._ctx.concordant_rows()
+            mine = raw[st[self._comm.rank] + 64:st[self._comm.rank] + sz[self._comm.rank]].view(np.int64).reshape(-1, 4)
+            sel = np.nonzero((rows["mask"] & 3) != 0)[0]
+            urec, first = np.unique(rows["rec"][sel], return_index=True)
+            keys = mine[sel[first]]
             table = {}
-            for lo, hi, names in self._comm.all_gather(mine):
-                for a, b, nm in zip(lo.tolist(), hi.tolist(), names):
-                    table[(a, b)] = nm.decode()
-            sel = (g[3] & 3) != 0
-            kk = g[:3, sel].t().cpu().numpy()
+            for part in self._comm.all_gather((keys[:, 1].tolist(), keys[:, 2].tolist(), self._names_of(urec.astype(np.int64)))):
+                table.update(zip(zip(part[0], part[1]), part[2]))
             out = [set() for _ in uniq]
-            for e, a, b in kk.tolist():
-                out[e].add(table[(a, b)])
+            for a, n in zip(st, sz):
+                g = raw[a + 64:a + n].view(np.int64).reshape(-1, 4)
+                g = g[(g[:, 3] & 3) != 0]
+                for e, lo, hi in g[:, :3].tolist():
+                    out[e].add(table[(lo, hi)])
             return [int(x) for x in cnt], out
 
         def closebam(self):

@@ -164,15 +164,28 @@ int coral_load_rows(coral_ctx* ctx, int64_t n_rows, const uint8_t* text, uint64_
                     const uint64_t* name_lo, const uint64_t* name_hi, const uint32_t* flag, const uint32_t* mapq,
                     const uint32_t* l_seq, const int32_t* nm);
 
-/* Device-side form of the same exchange: coral_device_view hands out the device addresses of the record buffer,
- * the offsets and the table columns (recs, offsets, name_lo, name_hi, flag|mapq<<16, l_seq, nm, sa_off, sa_len — valid
- * until the next load / rescan, read-only), so the caller can select and all-gather the rows on the GPU (NCCL);
- * coral_load_rows_dev takes the gathered arrays from device memory (slot i of d_text holds the row's SA text at
- * d_sa_off[i], 0 = no SA tag). */
+/* Device-side form of the same exchange (what the multi-GPU engine uses; the rows never visit the host).  Every rank
+ * packs what it contributes into ONE byte message in its own HBM, the caller all-gathers the messages (NCCL) into a
+ * buffer on this ctx's device — message r = d_buf[starts[r] : ...], starts 16-byte aligned, host array — and hands
+ * the gathered buffer to the next call:
+ *   coral_pack_sa_rows    : message 1 = this shard's SA-bearing records (name hash, flag, MAPQ, l_seq, NM, record
+ *                           index, read name + SA text), file order;
+ *   coral_pack_extra_rows : given every rank's message 1: message 2 = the first local record with flag < 256 of each
+ *                           chimeric name that carries no SA tag itself (ibg:142-143), + this shard's nm_stats
+ *                           partial sums (ibg:153-157) in its header;
+ *   coral_unpack_rows     : both gathered sets -> a rows-only ctx (rows in global file order); nm_* [n_ranks]
+ *                           receive the shards' partial sums (may be NULL).
+ * *d_msg / *nbytes: device address and size of the message, valid until the next pack call of the same kind.
+ * At most 16 ranks per exchange.  coral_device_view: device addresses of the record buffer, offsets and table
+ * columns (recs, offsets, name_lo, name_hi, flag|mapq<<16, l_seq, nm, sa_off, sa_len; valid until the next load /
+ * rescan / unpack, read-only). */
 int coral_device_view(coral_ctx* ctx, uint64_t* ptrs, int32_t n_ptrs);
-int coral_load_rows_dev(coral_ctx* ctx, int64_t n_rows, const uint8_t* d_text, uint64_t text_bytes, const uint64_t* d_text_off,
-                        const uint64_t* d_name_lo, const uint64_t* d_name_hi, const uint32_t* d_flag_mapq,
-                        const uint32_t* d_l_seq, const int32_t* d_nm, const uint32_t* d_sa_off, const uint32_t* d_sa_len);
+int coral_pack_sa_rows(coral_ctx* ctx, uint64_t* d_msg, uint64_t* nbytes);
+int coral_pack_extra_rows(coral_ctx* ctx, int32_t n_ranks, const uint8_t* d_buf, const uint64_t* starts, uint64_t* d_msg,
+                          uint64_t* nbytes);
+int coral_unpack_rows(coral_ctx* ctx, int32_t n_ranks, const uint8_t* d_buf1, const uint64_t* starts1, const uint8_t* d_buf2,
+                      const uint64_t* starts2, double* nm_sum, double* nm_sumsq, int64_t* nm_n, int64_t* nm_zero_div,
+                      int64_t* n_rows);
 
 /* Operator form of cigar_parsing.alignment_from_satags / cigar2pos* (cigar_parsing.py:17-269) on SA text the
  * caller supplies: `text` holds the entries, read r owns entries [ent_ptr[r], ent_ptr[r+1]) whose bytes are
@@ -249,12 +262,14 @@ int coral_concordant(coral_ctx* ctx, const int32_t* tid, const int32_t* p, int32
                      const uint32_t* rb_edge, const uint32_t* rb_rec, int64_t* lr_count, int64_t* n_rows);
 int coral_get_concordant_rows(coral_ctx* ctx, uint32_t* edge, uint32_t* rec, uint32_t* mask);
 
-/* Multi-GPU form: the rows of the last coral_concordant stay on the device (edge, rec, mask: uint32
- * each; coral_concordant_device_rows), the caller all-gathers them as (edge, name hash, mask) and every rank counts
- * ce[8] on the gathered rows + the rbps rows (mask 16) with coral_count_name_rows (device arrays, uint64 each). */
-int coral_concordant_device_rows(coral_ctx* ctx, uint64_t* ptrs, int64_t* n_rows);
-int coral_count_name_rows(coral_ctx* ctx, int32_t n_edges, int64_t n_rows, const uint64_t* d_edge, const uint64_t* d_lo,
-                          const uint64_t* d_hi, const uint64_t* d_mask, int64_t* lr_count);
+/* Multi-GPU form: coral_concordant with lr_count == NULL only produces the rows of this shard;
+ * coral_concordant_pack turns them into one message (64-byte header + n rows of 4 x uint64: edge, name hash lo, hi,
+ * mask) in this ctx's HBM; the caller all-gathers the messages; coral_count_name_msgs counts ce[8] on the gathered
+ * messages (message r = d_buf[starts[r] : starts[r] + sizes[r]), host arrays) + the rbps rows (d_rb_rows: n_rb rows
+ * of the same 4 x uint64 layout on this device, mask 16).  Same result on every rank. */
+int coral_concordant_pack(coral_ctx* ctx, uint64_t* d_msg, uint64_t* nbytes);
+int coral_count_name_msgs(coral_ctx* ctx, int32_t n_edges, int32_t n_ranks, const uint8_t* d_buf, const uint64_t* starts,
+                          const uint64_t* sizes, const uint64_t* d_rb_rows, int64_t n_rb, int64_t* lr_count);
 
 #ifdef __cplusplus
 }

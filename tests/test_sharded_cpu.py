@@ -173,109 +173,80 @@ def test_exchange_over_gloo_world2(c5_rows):
         assert same and tot == [3, 30] and merged == ["r1", "r0"]
 
 
-# ---- tensor form of the exchanges (coral_b200/exchange.py) on CPU tensors ------------------------------------------
-def _tensor_view(rows, r0, r1):
-    """Synthetic record bytes for rows [r0, r1): 36-byte core with l_read_name at +12, the name, then the SA text."""
+# ---- transport of the packed device messages (coral_b200/exchange.py) on CPU tensors ---------------------------------
+def _msg(rank, nbytes):
     import torch
-    buf, off, sa_off, sa_len = bytearray(), [0], [], []
-    for k in range(r0, r1):
-        name = rows["names"][k].encode() + b"\0"
-        core = bytearray(36); core[12] = len(name)
-        sa = rows["sa"][k] or b""
-        sa_off.append(36 + len(name) if sa else 0); sa_len.append(len(sa))
-        rec = bytes(core) + name + sa
-        rec += b"\0" * (-len(rec) % 16)
-        buf += rec; off.append(len(buf))
-    i32 = lambda a: torch.as_tensor(np.asarray(a, np.int64).astype(np.int32))
-    return {"recs": torch.as_tensor(np.frombuffer(bytes(buf), np.uint8).copy()), "off": torch.as_tensor(np.array(off, np.int64)),
-            "name_lo": torch.as_tensor(rows["name_lo"][r0:r1].view(np.int64).copy()),
-            "name_hi": torch.as_tensor(rows["name_hi"][r0:r1].view(np.int64).copy()),
-            "flag_mapq": i32(rows["flag"][r0:r1].astype(np.int64) | (rows["mapq"][r0:r1].astype(np.int64) << 16)),
-            "l_seq": i32(rows["l_seq"][r0:r1]), "nm": i32(rows["nm"][r0:r1]), "sa_off": i32(sa_off), "sa_len": i32(sa_len)}
-
-
-def _tensor_rows_as_numpy(g):
-    from coral_b200 import exchange
-    off = g["text_off"].numpy(); ln = g["name_len"].numpy(); text = g["text"].numpy()
-    sa_text, sa_off = [], [0]
-    for i in range(len(ln)):
-        sa_text.append(text[int(off[i]) + int(ln[i]):int(off[i + 1])].tobytes())
-        sa_off.append(sa_off[-1] + len(sa_text[-1]))
-    return {"names": exchange.row_names(g), "flag": (g["flag_mapq"].numpy().astype(np.int64) & 0xffff),
-            "l_seq": g["l_seq"].numpy(), "text": np.frombuffer(b"".join(sa_text), np.uint8), "text_off": np.array(sa_off)}
+    return torch.as_tensor(((np.arange(nbytes) * 7 + rank * 13) % 251).astype(np.uint8))
 
 
 @pytest.mark.parametrize("world", [1, 2, 4])
-def test_tensor_fetch_exchange_matches_reference(c5_rows, world):
+def test_gather_msgs_thread_ranks(world):
     from coral_b200 import exchange
-    rows, _ = c5_rows
-    n = len(rows["names"])
-    want = _reference_view(rows)
-    cuts = [n * r // world for r in range(world + 1)]
-    got = _run_threads(world, lambda c: exchange.fetch_exchange(exchange.TensorComm(c), _tensor_view(rows, cuts[c.rank], cuts[c.rank + 1])))
-    for g in got:
-        assert _fetch_view(_tensor_rows_as_numpy(g)) == want
-        has = g["sa_len"].numpy() > 0
-        assert np.array_equal(g["sa_off"].numpy()[has], g["name_len"].numpy()[has]) and not g["sa_off"].numpy()[~has].any()
+    sizes = [16 * (3 + 5 * r) for r in range(world)]
+    got = _run_threads(world, lambda c: exchange.TensorComm(c).gather_msgs(_msg(c.rank, sizes[c.rank])))
+    for buf, st, sz in got:
+        assert sz == sizes and all(s % 16 == 0 for s in st)
+        for r in range(world):
+            assert np.array_equal(buf[st[r]:st[r] + sz[r]].numpy(), _msg(r, sizes[r]).numpy())
 
 
-def test_tensor_concordant_combine_matches_numpy():
+def test_smalldel_message_round_trip():
+    rows = [("read/%d" % k, k % 3, 1000 + k, 900 + k, 10, 5000, 60, -(2 ** 62) + k, 2 ** 62 - k) for k in range(7)]
+    for part in ([], rows[:1], rows):
+        msg = sharded.pack_smalldel(part)
+        padded = np.concatenate([msg.view(np.uint8), np.zeros(8, np.uint8)])     # transport pads to 16 bytes
+        assert sharded.unpack_smalldel(padded) == part
+
+
+def test_row_names_from_text_slots():
+    from coral_b200 import exchange
+    slots = [b"readA\0chr1,5,+,10M,60,0;", b"b\0", b"read/long/name\0chr2,7,-,5S5M,3,1;chr3,1,+,5M5S,0,0;"]
+    text = np.frombuffer(b"".join(slots), np.uint8)
+    off = np.cumsum([0] + [len(x) for x in slots])[:-1]
+    assert exchange.row_names(text, off) == ["readA", "b", "read/long/name"]
+    assert exchange.row_names(text, off[[2, 0, 1]]) == ["read/long/name", "readA", "b"]       # any slot order
+    assert exchange.row_names(text, off[:0]) == []
+
+
+def _gloo_msg_worker(rank, world, port, q):
     import torch
-    from coral_b200 import exchange
-    rng = np.random.default_rng(5)
-    names = ["r%d" % i for i in range(300)]
-    h = {nm: (int(rng.integers(-2**62, 2**62)), int(rng.integers(-2**62, 2**62))) for nm in names}
-    n_edges, world = 6, 3
-    local = [[(int(rng.integers(n_edges)), names[int(rng.integers(300))], int(rng.integers(1, 16))) for _ in range(2000)]
-             for _ in range(world)]
-    rbps = [set(names[int(j)] for j in rng.integers(0, 300, 20)) for _ in range(n_edges)]
-    want = _run_threads(world, lambda c: sharded.combine_concordant(c, n_edges, local[c.rank], rbps))[0]
-
-    def run(c):
-        rows = local[c.rank]
-        t = lambda a: torch.as_tensor(np.array(a, np.int64))
-        rb = [(e, ) + h[nm] for e, s in enumerate(rbps) for nm in s]
-        rbt = t(rb).reshape(-1, 3)
-        return exchange.concordant_combine(exchange.TensorComm(c), n_edges, t([r[0] for r in rows]), t([h[r[1]][0] for r in rows]),
-                                           t([h[r[1]][1] for r in rows]), t([r[2] for r in rows]), rbt[:, 0], rbt[:, 1], rbt[:, 2])
-    inv = {v: k for k, v in h.items()}
-    for cnt, keys, m in run_all(world, run):
-        assert cnt.tolist() == want[0]
-        got_names = [set() for _ in range(n_edges)]
-        for (e, a, b), mm in zip(keys.tolist(), m.tolist()):
-            if mm & 3:
-                got_names[e].add(inv[(a, b)])
-        assert got_names == want[1]
-
-
-def run_all(world, fn):
-    return _run_threads(world, fn)
-
-
-def _gloo_tensor_worker(rank, world, port, bam, q):
     import torch.distributed as dist
     from coral_b200 import exchange
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        tc = exchange.TensorComm(sharded.TorchComm())
-        rows = _file_rows(bam)
-        n = len(rows["names"])
-        cuts = [n * r // world for r in range(world + 1)]
-        g = exchange.fetch_exchange(tc, _tensor_view(rows, cuts[rank], cuts[rank + 1]))
-        q.put((rank, _fetch_view(_tensor_rows_as_numpy(g)) == _reference_view(rows)))
+        comm = sharded.TorchComm()
+        ok = True
+        # eager round only / a message larger than the eager slot (second, exact round) / an empty-payload header
+        for eager, sizes in ((4096, [160, 48]), (256, [64, 1024]), (256, [1024, 2048]), (4096, [16, 16])):
+            tc = exchange.TensorComm(comm, eager=eager)
+            buf, st, sz = tc.gather_msgs(_msg(rank, sizes[rank]))
+            ok = ok and sz == sizes and all(s % 16 == 0 for s in st)
+            for r in range(world):
+                ok = ok and np.array_equal(buf[st[r]:st[r] + sz[r]].numpy(), _msg(r, sizes[r]).numpy())
+            ok = ok and tc.n_collectives == (1 if max(sizes) <= eager - 16 else 2)
+        # small-deletion rows: host-built messages merged in (interval, rank, block) order
+        mine = [("r%d_%d" % (rank, k), (k + rank) % 2, k, k, 0, 9, 60, rank, k) for k in range(3)]
+        tc = exchange.TensorComm(comm)
+        buf, st, sz = tc.gather_msgs(exchange.host_msg(sharded.pack_smalldel(mine), torch.device("cpu")))
+        raw = buf.numpy()
+        merged = [r for a, n in zip(st, sz) for r in sharded.unpack_smalldel(raw[a:a + n])]
+        merged.sort(key=lambda r: r[1])
+        want = [("r%d_%d" % (rk, k), (k + rk) % 2, k, k, 0, 9, 60, rk, k) for rk in range(world) for k in range(3)]
+        want.sort(key=lambda r: r[1])
+        ok = ok and merged == want
+        q.put((rank, ok))
     finally:
         dist.destroy_process_group()
 
 
-def test_tensor_exchange_over_gloo_world2(c5_rows):
+def test_gather_msgs_over_gloo_world2():
     import torch.multiprocessing as mp
-    _, paths = c5_rows
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 31500 + os.getpid() % 2000
-    ps = [ctx.Process(target=_gloo_tensor_worker, args=(r, 2, port, paths["bam"], q)) for r in range(2)]
+    ps = [ctx.Process(target=_gloo_msg_worker, args=(r, 2, port, q)) for r in range(2)]
     [p.start() for p in ps]
     res = sorted(q.get(timeout=300) for _ in range(2))
     [p.join(60) for p in ps]
