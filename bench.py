@@ -364,6 +364,7 @@ def main():
 
     for _ in range(warm):
         out = one_pass()
+    SHARD_MS.clear()
     d2h = result_bytes(out)
     if a.cprofile:
         import cProfile
@@ -463,7 +464,7 @@ def main():
         "clocks": sampler.summary(),
     }
     if world > 1:
-        out["sharded_stage_ms_per_step"] = {k: v / (a.steps + warm) for k, v in SHARD_MS.items()}
+        out["sharded_stage_ms_per_step"] = {k: v / a.steps for k, v in SHARD_MS.items()}
     if rank == 0:
         if world == 1:
             try:
