@@ -236,6 +236,9 @@ class Context(object):
         self._check(self._L.coral_device_view(self._h, ptrs, 9))
         return [int(x) for x in ptrs]
 
+    def set_option(self, name, value):
+        self._check(self._L.coral_set_option(self._h, name.encode(), ctypes.c_int64(int(value))))
+
     def rescan(self):
         self._check(self._L.coral_rescan(self._h))
 

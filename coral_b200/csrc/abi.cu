@@ -67,6 +67,13 @@ int coral_set_params(coral_ctx* c, const coral_params* p) {
     return CORAL_OK;
 }
 
+int coral_set_option(coral_ctx* c, const char* name, int64_t value) {
+    if (!c || !name) return CORAL_E_ARG;
+    if (std::string(name) == "full_name_sort") { c->force_full_name_sort = value != 0; return CORAL_OK; }
+    c->err = std::string("unknown option: ") + name;
+    return CORAL_E_ARG;
+}
+
 int coral_set_references(coral_ctx* c, const char* names, int32_t n, const int32_t* chr_rank) {
     if (!c || !names || n < 0 || !chr_rank) return CORAL_E_ARG;
     cudaSetDevice(c->device);

@@ -99,34 +99,44 @@ __global__ void k_region_cov_slow(const uint8_t* __restrict__ recs, const uint64
         int32_t refpos = pos;
         int64_t qpos = 0;
         unsigned long long total = 0;
-        for (uint32_t base = 0; base < n_cig; base += 32) {
-            const uint32_t k = base + lane;
-            uint32_t v = (k < n_cig) ? ld_u32_any(cig + 4ull * k) : 0xFu;
-            const uint32_t op = v & 15u;
-            const int32_t len = (int32_t)(v >> 4);
-            const bool is_m = (op == 0 || op == 7 || op == 8);
-            const int32_t rlen = (is_m || op == 2 || op == 3) ? len : 0;
-            const int32_t qlen = (is_m || op == 1 || op == 4) ? len : 0;
-            const int32_t ri_incl = warp_incl_sum_i32(rlen);
-            const int32_t qi_incl = warp_incl_sum_i32(qlen);
-            if (is_m) {
-                const int32_t s = refpos + ri_incl - rlen;
-                const int32_t a = max(s, rs), b = min(s + len, re);
-                if (b > a) {
-                    total += (unsigned long long)(b - a);
-                    if (check_seq) {
-                        int64_t q0 = qpos + (qi_incl - qlen) + (a - s);
-                        for (int32_t x = 0; x < b - a; x++) {
-                            int64_t q = q0 + x;
-                            uint32_t by = seq[q >> 1];
-                            uint32_t nib = (q & 1) ? (by & 15u) : (by >> 4);
-                            if (!(nib == 1 || nib == 2 || nib == 4 || nib == 8)) total -= 1;
+        // 4 chunks of 32 ops per trip: the four loads are issued together (the walk is latency-bound), and the walk
+        // stops once the region's end is behind the reference position
+        for (uint32_t base = 0; base < n_cig && refpos < re; base += 128) {
+            uint32_t vv[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const uint32_t k = base + 32u * u + lane;
+                vv[u] = (k < n_cig) ? ld_u32_any(cig + 4ull * k) : 0xFu;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const uint32_t v = vv[u];
+                const uint32_t op = v & 15u;
+                const int32_t len = (int32_t)(v >> 4);
+                const bool is_m = (op == 0 || op == 7 || op == 8);
+                const int32_t rlen = (is_m || op == 2 || op == 3) ? len : 0;
+                const int32_t qlen = (is_m || op == 1 || op == 4) ? len : 0;
+                const int32_t ri_incl = warp_incl_sum_i32(rlen);
+                const int32_t qi_incl = warp_incl_sum_i32(qlen);
+                if (is_m) {
+                    const int32_t s = refpos + ri_incl - rlen;
+                    const int32_t a = max(s, rs), b = min(s + len, re);
+                    if (b > a) {
+                        total += (unsigned long long)(b - a);
+                        if (check_seq) {
+                            int64_t q0 = qpos + (qi_incl - qlen) + (a - s);
+                            for (int32_t x = 0; x < b - a; x++) {
+                                int64_t q = q0 + x;
+                                uint32_t by = seq[q >> 1];
+                                uint32_t nib = (q & 1) ? (by & 15u) : (by >> 4);
+                                if (!(nib == 1 || nib == 2 || nib == 4 || nib == 8)) total -= 1;
+                            }
                         }
                     }
                 }
+                refpos += __shfl_sync(FULL_MASK, ri_incl, 31);
+                qpos += __shfl_sync(FULL_MASK, qi_incl, 31);
             }
-            refpos += __shfl_sync(FULL_MASK, ri_incl, 31);
-            qpos += __shfl_sync(FULL_MASK, qi_incl, 31);
         }
         total = warp_sum_u64(total);
         if (lane == 0 && total) atomicAdd(base_sum + ri, total);

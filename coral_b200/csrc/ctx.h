@@ -105,6 +105,7 @@ struct coral_ctx {
     int64_t nrec = 0;
     bool loaded = false;
     bool has_ordinal = false;
+    bool force_full_name_sort = false;   // test hook: take the 128-bit name sort of coral_fetch (its fallback path)
     bool rows_only = false;   // ctx was filled by coral_load_rows: only fetch / candidates / cluster are valid
 
     RecordTable rt;

@@ -172,13 +172,19 @@ __global__ void k_iota(int64_t n, uint32_t* p) {
     if (i < n) p[i] = (uint32_t)i;
 }
 // head[i] = 1 when sorted position i starts a new read name
+// head[i] = entry i (in sorted order) starts a new read name.  The entries were sorted on `key_mask` bits of the low
+// hash word only: if two different names share those bits their entries may interleave, which shows as an adjacent
+// pair with equal masked keys and different names -> *mixed is set and the caller re-sorts on all 128 bits.
 __global__ void k_heads(int64_t n, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
-                        const uint64_t* __restrict__ nlo, const uint64_t* __restrict__ nhi, uint32_t* __restrict__ head) {
+                        const uint64_t* __restrict__ nlo, const uint64_t* __restrict__ nhi, uint64_t key_mask,
+                        uint32_t* __restrict__ head, uint32_t* __restrict__ mixed) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     if (i == 0) { head[0] = 1; return; }
     const uint32_t a = ent[perm[i]].rec, b = ent[perm[i - 1]].rec;
-    head[i] = (nlo[a] != nlo[b] || nhi[a] != nhi[b]) ? 1u : 0u;
+    const bool differ = nlo[a] != nlo[b] || nhi[a] != nhi[b];
+    head[i] = differ ? 1u : 0u;
+    if (differ && ((nlo[a] ^ nlo[b]) & key_mask) == 0) *mixed = 1u;
 }
 // seg_id (0-based) from inclusive scan of heads; records segment starts; marks duplicates within a segment
 __global__ void k_segments(int64_t n, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
@@ -205,10 +211,11 @@ __global__ void k_mark_dups(int64_t n, const SaEntry* __restrict__ ent, const ui
 }
 
 // ---- 5. ------------------------------------------------------------------------------------------
-// names of the segments, sorted by (hi, lo) because the sort was LSD lo-then-hi; binary search join.
+// names of the segments: sorted by the masked low word (key_mask != 0; distinct per segment, k_heads checked it), or by
+// (hi, lo) after the full LSD lo-then-hi sort (key_mask == 0); binary search join.
 __global__ void k_first_primary(int64_t n_rec, const uint32_t* __restrict__ flag_mapq, const uint64_t* __restrict__ nlo,
                                 const uint64_t* __restrict__ nhi, int64_t n_seg, const uint64_t* __restrict__ seg_lo,
-                                const uint64_t* __restrict__ seg_hi, uint32_t* __restrict__ first_primary) {
+                                const uint64_t* __restrict__ seg_hi, uint64_t key_mask, uint32_t* __restrict__ first_primary) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_rec) return;
     if ((flag_mapq[i] & 0xffffu) >= 256u) return;
@@ -216,7 +223,8 @@ __global__ void k_first_primary(int64_t n_rec, const uint32_t* __restrict__ flag
     int64_t lo = 0, hi = n_seg;
     while (lo < hi) {
         int64_t mid = (lo + hi) >> 1;
-        bool less = seg_hi[mid] < hi_k || (seg_hi[mid] == hi_k && seg_lo[mid] < lo_k);
+        bool less = key_mask ? (seg_lo[mid] & key_mask) < (lo_k & key_mask)
+                             : (seg_hi[mid] < hi_k || (seg_hi[mid] == hi_k && seg_lo[mid] < lo_k));
         if (less) lo = mid + 1; else hi = mid;
     }
     if (lo < n_seg && seg_hi[lo] == hi_k && seg_lo[lo] == lo_k) atomicMin(&first_primary[lo], (uint32_t)i);
@@ -447,32 +455,47 @@ int coral_run_fetch(coral_ctx* c) {
     LAUNCH_1D(k_parse_entries, (int64_t)n_ent, recs, off, (int64_t)n_ent, e_rec, e_beg, e_end, c->d_ref_hash.as<uint64_t>(),
               (int32_t)c->ref_names.size(), ent);
 
-    // 4. stable sort of entry indices by name (lo then hi)
+    // 4. stable sort of entry indices by name.  One 5-pass sort on 40 bits of the low hash word groups the names unless
+    // two names share those bits (p ~ n^2 / 2^41); k_heads detects that exactly and the full 128-bit sort runs instead.
     CORAL_CUDA(c, c->s5.ensure((size_t)n_ent * 24 + 64));
     uint64_t* key_a = c->s5.as<uint64_t>();
     uint64_t* key_b = key_a + n_ent;
     uint32_t* perm_a = reinterpret_cast<uint32_t*>(key_b + n_ent);
     uint32_t* perm_b = perm_a + n_ent;
-    LAUNCH_1D(k_iota, (int64_t)n_ent, (int64_t)n_ent, perm_a);
-    LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, (const uint32_t*)nullptr, rt.name_lo.as<uint64_t>(), key_a);
-    CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_a, perm_b, n_ent));
-    LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, perm_b, rt.name_hi.as<uint64_t>(), key_a);
-    CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_b, perm_a, n_ent));
-    const uint32_t* perm = perm_a;
-
-    // segments
-    CORAL_CUDA(c, c->s6.ensure((size_t)n_ent * 13 + 64));
+    CORAL_CUDA(c, c->s6.ensure((size_t)n_ent * 13 + 64 + 16));
     uint32_t* head = c->s6.as<uint32_t>();
     uint32_t* seg_of = head + n_ent;
     uint32_t* seg_start = seg_of + n_ent;
     uint8_t* keep = reinterpret_cast<uint8_t*>(seg_start + n_ent);
-    LAUNCH_1D(k_heads, (int64_t)n_ent, (int64_t)n_ent, ent, perm, rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(), head);
-    CORAL_TRY(inclusive_sum_u32(c, head, head, n_ent));
+    uint32_t* d_mixed = reinterpret_cast<uint32_t*>(c->s6.as<uint8_t>() + (((size_t)n_ent * 13 + 64 + 3) & ~(size_t)3));
+    const uint32_t* perm = nullptr;
     uint32_t n_seg = 0;
-    CORAL_TRY(d2h(c, &n_seg, head + n_ent - 1, 1));
+    uint64_t name_key_mask = 0;
+    for (int full = c->force_full_name_sort ? 1 : 0; full < 2; full++) {
+        name_key_mask = full ? 0 : ((1ull << 40) - 1);
+        LAUNCH_1D(k_iota, (int64_t)n_ent, (int64_t)n_ent, perm_a);
+        LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, (const uint32_t*)nullptr, rt.name_lo.as<uint64_t>(), key_a);
+        if (!full) {
+            CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_a, perm_b, n_ent, 0, 40));
+            perm = perm_b;
+        } else {
+            CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_a, perm_b, n_ent));
+            LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, perm_b, rt.name_hi.as<uint64_t>(), key_a);
+            CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_b, perm_a, n_ent));
+            perm = perm_a;
+        }
+        CORAL_CUDA(c, cudaMemsetAsync(d_mixed, 0, 4, c->stream));
+        LAUNCH_1D(k_heads, (int64_t)n_ent, (int64_t)n_ent, ent, perm, rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(),
+                  full ? ~0ull : name_key_mask, head, d_mixed);
+        CORAL_TRY(inclusive_sum_u32(c, head, head, n_ent));
+        uint32_t mixed = 0;
+        CORAL_TRY(d2h(c, &n_seg, head + n_ent - 1, 1));
+        CORAL_TRY(d2h(c, &mixed, d_mixed, 1));
+        CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (!mixed) break;
+    }
     LAUNCH_1D(k_segments, (int64_t)n_ent, (int64_t)n_ent, ent, perm, head, seg_start, seg_of);
     LAUNCH_1D(k_mark_dups, (int64_t)n_ent, (int64_t)n_ent, ent, perm, seg_of, seg_start, keep);
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
 
     // 5. per-read names, first primary
     CORAL_CUDA(c, c->s7.ensure((size_t)n_seg * 48 + 64));
@@ -487,7 +510,7 @@ int coral_run_fetch(coral_ctx* c) {
     LAUNCH_1D(k_seg_names, (int64_t)n_seg, (int64_t)n_seg, ent, perm, seg_start, rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(),
               seg_lo, seg_hi, seg_emit, first_primary);
     LAUNCH_1D(k_first_primary, n, n, rt.flag_mapq.as<uint32_t>(), rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(), (int64_t)n_seg,
-              seg_lo, seg_hi, first_primary);
+              seg_lo, seg_hi, name_key_mask, first_primary);
 
     // 6-7. counts, read order, CSR
     CORAL_CUDA(c, T.read_first_rec.ensure((size_t)n_seg * 4));
@@ -499,7 +522,7 @@ int coral_run_fetch(coral_ctx* c) {
     uint32_t* cnt_ranked = seg_cnt + n_seg;
     LAUNCH_1D(k_read_counts, (int64_t)n_seg, (int64_t)n_seg, (int64_t)n_ent, ent, perm, seg_start, keep, first_primary, seg_status, seg_cnt);
     LAUNCH_1D(k_iota, (int64_t)n_seg, (int64_t)n_seg, seg_idx);
-    CORAL_TRY(sort_pairs_u64(c, seg_emit, seg_emit_sorted, seg_idx, order, n_seg));
+    CORAL_TRY(sort_pairs_u64(c, seg_emit, seg_emit_sorted, seg_idx, order, n_seg, 0, 32));   // keys are entry indices
     LAUNCH_1D(k_gather_u32, (int64_t)n_seg, (int64_t)n_seg, order, seg_cnt, cnt_ranked);
     CORAL_TRY(exclusive_sum_u32(c, cnt_ranked, T.aln_ptr.as<uint32_t>(), n_seg));
     uint32_t last_ptr = 0, last_cnt = 0;

@@ -54,6 +54,10 @@ int coral_create(int device, coral_ctx** out);
 void coral_destroy(coral_ctx* ctx);
 const char* coral_last_error(const coral_ctx* ctx);
 int coral_set_params(coral_ctx* ctx, const coral_params* p);
+/* Named switches that do not change any result.  "full_name_sort" = 1: coral_fetch groups SA entries by a full
+ * 128-bit name sort instead of the 40-bit sort it normally tries first (the path it falls back to when two read
+ * names share those bits; exposed so that tests can cover it).  Unknown names return CORAL_E_ARG. */
+int coral_set_option(coral_ctx* ctx, const char* name, int64_t value);
 
 /* Reference sequence table (BAM header order).  `names` = n NUL-terminated strings back to back.
  * `chr_rank[tid]` = global_names.chr_idx value (global_names.py:13-18) or -1 when the contig is not

@@ -54,4 +54,12 @@ def test_fetch_matches_oracle(built_lib, dataset, name, kw):
     assert n == ora.nm_stats[2]
     assert abs(mean - ora.nm_stats[0]) <= 1e-9 * abs(ora.nm_stats[0])
     assert abs(std - ora.nm_stats[1]) <= 1e-9 * abs(ora.nm_stats[1])
+    # the 128-bit name sort (what fetch falls back to when two names share the 40 bits it sorts on first): same table
+    ctx.set_option("full_name_sort", 1)
+    f2 = ctx.fetch()
+    assert f2["n_reads"] == f["n_reads"]
+    for k in ("read_first_rec", "read_len", "read_status", "aln_ptr", "qs", "qe", "tid", "rstart", "rend", "strand", "mapq", "nm"):
+        assert np.array_equal(f2[k], f[k]), k
+    with pytest.raises(RuntimeError):
+        ctx.set_option("no_such_option", 1)
     ctx.close(); bam.close()
