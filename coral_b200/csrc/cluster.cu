@@ -492,6 +492,9 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     uint32_t* cstart = w[W_CSTART].as<uint32_t>(); uint32_t* label = w[W_LABEL].as<uint32_t>();
 
     c->stage_begin(CORAL_STAGE_CLUSTER);
+    // every sort key below is (an id < n) << 32 | 32 payload bits: only the id bits that can be set are sorted on
+    int bits_n = 1;
+    while (((int64_t)1 << bits_n) < n + 1) bits_n++;
     // groups (first-appearance order is carried by gfirst)
     LAUNCH_1D(k_group_key, n, n, C, keyA, idxA);
     CORAL_TRY(sort_pairs_u64(c, keyA, keyB, idxA, idxB, n, 0, 40));
@@ -504,13 +507,13 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     LAUNCH_1D(k_group_big, (int64_t)n_groups, (int64_t)n_groups, gstart, n, min_cluster_size, gbig);
     // runs along pos1 within a group (idxB is grouped by gid already; sort by (gid, pos1))
     LAUNCH_1D(k_seg_pos_key, n, n, idxB, gid, C.pos1, keyA);
-    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, idxB, idxA, n));
+    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, idxB, idxA, n, 0, 32 + bits_n));
     LAUNCH_1D(k_gap_heads, n, n, keyB, idxA, gid, gbig, bp_distance_cutoff, head);
     CORAL_TRY(inclusive_sum_u32(c, head, head, n));
     LAUNCH_1D(k_scatter_seg, n, n, idxA, head, seg);
     // components along pos2 within a run
     LAUNCH_1D(k_seg_pos_key, n, n, idxA, seg, C.pos2, keyA);
-    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, idxA, idxB, n));
+    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, idxA, idxB, n, 0, 32 + bits_n));
     LAUNCH_1D(k_gap_heads, n, n, keyB, idxB, gid, gbig, bp_distance_cutoff, head);
     CORAL_TRY(inclusive_sum_u32(c, head, head, n));
     uint32_t n_comp = 0;
@@ -518,7 +521,7 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     LAUNCH_1D(k_scatter_seg, n, n, idxB, head, seg);
     // members of each component in input order
     LAUNCH_1D(k_seg_idx_key, n, n, seg, keyA, idxA);
-    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, idxA, idxB, n));
+    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, idxA, idxB, n, 0, 32 + bits_n));
     CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
     LAUNCH_1D(k_seg_starts, n, n, keyB, cstart, n_comp);
     k_component_cluster<<<n_comp, CL_THREADS, 0, c->stream>>>(cstart, idxB, C, gid, gbig, bp_distance_cutoff, label,
@@ -529,7 +532,7 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     uint32_t* order = w[W_ORDER].as<uint32_t>();
     uint32_t* cptr = w[W_CPTR].as<uint32_t>();
     LAUNCH_1D(k_cluster_key, n, n, gid, gfirst, label, keyA, idxA);
-    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, idxA, order, n));
+    CORAL_TRY(sort_pairs_u64(c, keyA, keyB, idxA, order, n, 0, 32 + bits_n));
     LAUNCH_1D(k_key_heads, n, n, keyB, head);
     CORAL_TRY(inclusive_sum_u32(c, head, head, n));
     uint32_t n_cl = 0;
