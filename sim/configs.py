@@ -157,7 +157,8 @@ def c2_shard(rank, world, scale=1.0, seed=20240215 + 2, cov=50.0, bg_pad=6 * MB)
         all_cn += cn_rows; all_seeds += seeds
         if r == rank:
             mine = SimConfig(name="C2", refs=refs, cn_rows=cn_rows, seeds=seeds, background=bg, cov=cov * scale,
-                             cycles=[Cycle(segs, 40.0)], read_mean=30000, model="ont", seed=seed + 1000 * r)
+                             cycles=[Cycle(segs, 40.0)], read_mean=30000, model="ont", seed=seed + 1000 * r,
+                             name_style=2 + r)       # read names are unique across the file: a letter per shard
     return mine, all_cn, all_seeds
 
 

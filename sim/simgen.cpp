@@ -73,7 +73,7 @@ struct SimParams {
     int32_t hard_clip_supp;      // 1: supplementary records use H clips (minimap2 default)
     int32_t record_align;        // pad record starts to this many bytes (1 = as on disk)
     int32_t n_threads;
-    int32_t name_style;          // 0: "r<id>", 1: 36-char uuid-like
+    int32_t name_style;          // 0: "r<id>", 1: 36-char uuid-like, 2 + k: "<letter k><id>" (same length as style 0)
 };
 
 }  // extern "C"
@@ -168,6 +168,8 @@ std::string read_name(int32_t id, const SimParams& prm) {
         uint64_t a = mix(prm.seed ^ 0xABCDEF, (uint64_t)id), c = mix(a, 77);
         snprintf(b, sizeof b, "%08x-%04x-%04x-%04x-%012llx", (uint32_t)(a >> 32), (uint32_t)(a >> 16) & 0xffff,
                  (uint32_t)a & 0xffff, (uint32_t)(c >> 48) & 0xffff, (unsigned long long)(c & 0xffffffffffffull));
+    } else if (prm.name_style >= 2) {      // shards of one file generated separately: a distinct letter per shard
+        snprintf(b, sizeof b, "%c%d", (char)('a' + (prm.name_style - 2) % 26), id);
     } else {
         snprintf(b, sizeof b, "r%d", id);
     }
