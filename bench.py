@@ -365,6 +365,8 @@ def main():
     for _ in range(warm):
         out = one_pass()
     SHARD_MS.clear()
+    if world > 1:
+        eng0.fetch_laps.clear()
     d2h = result_bytes(out)
     if a.cprofile:
         import cProfile
@@ -465,6 +467,7 @@ def main():
     }
     if world > 1:
         out["sharded_stage_ms_per_step"] = {k: v / a.steps for k, v in SHARD_MS.items()}
+        out["fetch_exchange_ms_per_step"] = {k: v / a.steps for k, v in eng0.fetch_laps.items()}
     if rank == 0:
         if world == 1:
             try:

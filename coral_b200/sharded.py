@@ -276,6 +276,7 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             self._edge_arrays = None
             self._name_hash = {}     # read name -> 128-bit hash as two int64 (for the rbps rows of the concordant combine)
             self._tc = None
+            self.fetch_laps = {}
 
         @property
         def _chim_ctx(self):
@@ -311,11 +312,19 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
         # a1: the exchange, on the GPU.  Two packed messages per rank (csrc/exchange.cu), two all-gathers, and the
         # gathered rows are unpacked straight into the rows-only ctx: nothing visits the host.
         def _run_fetch(self):
+            import time
             ctx, cctx = self._ctx, self._cctx
-            buf1, st1, _ = self._gather(*ctx.pack_sa_rows())
-            buf2, st2, _ = self._gather(*ctx.pack_extra_rows(buf1.data_ptr(), st1))
-            _, (s1, s2, nn, zd) = cctx.unpack_rows(buf1.data_ptr(), st1, buf2.data_ptr(), st2)
-            f = cctx.fetch()
+            t = [time.perf_counter()]
+
+            def lap(name):      # host wall time of the steps of the exchange (bench.py reports them)
+                t.append(time.perf_counter())
+                self.fetch_laps[name] = self.fetch_laps.get(name, 0.0) + (t[-1] - t[-2]) * 1e3
+            m1 = ctx.pack_sa_rows(); lap("pack_sa_rows")
+            buf1, st1, _ = self._gather(*m1); lap("gather_1")
+            m2 = ctx.pack_extra_rows(buf1.data_ptr(), st1); lap("pack_extra_rows")
+            buf2, st2, _ = self._gather(*m2); lap("gather_2")
+            _, (s1, s2, nn, zd) = cctx.unpack_rows(buf1.data_ptr(), st1, buf2.data_ptr(), st2); lap("unpack_rows")
+            f = cctx.fetch(); lap("fetch_on_gathered_rows")
             # nm_stats (ibg:153-157) run over ALL records: the shard partials are summed in rank order (the f64 sum
             # order differs from the 1-GPU order: within 1e-9 relative, unused downstream)
             f["nm_sum"] = float(s1.sum()); f["nm_sumsq"] = float(s2.sum())

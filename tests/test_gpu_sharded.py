@@ -101,3 +101,65 @@ def test_packed_fetch_exchange_matches_the_file(built_lib, world, tmp_path_facto
     _, _, whole = _packed_rows([(rec, off)], names)
     assert int(parts[2].sum()) == int(whole[2].sum()) and int(parts[3].sum()) == int(whole[3].sum())
     assert abs(float(parts[0].sum()) - float(whole[0].sum())) <= 1e-9 * max(1.0, abs(float(whole[0].sum())))
+
+
+def test_packed_exchange_edge_cases(built_lib, tmp_path_factory):
+    """An empty shard in the middle, a shard without any SA record, and the argument checks of the entry points."""
+    import numpy as np
+    import torch
+    import test_sharded_cpu as S
+    from coral_b200 import _abi, exchange
+    from sim import configs
+    from sim.bgzf import write_bam
+    from sim.generate import simulate
+    data = simulate(configs.CONFIGS["C2"](scale=0.01))
+    rec, off = data.rec, np.asarray(data.rec_off, dtype=np.uint64)
+    refs = data.cfg.refs
+    names = [r[0] for r in refs]
+    n = len(off) - 1
+    path = str(tmp_path_factory.mktemp("packed_edge") / "reads.bam")
+    write_bam(path, refs, rec, off)
+    want = S._reference_view(S._file_rows(path))
+    assert len(want) > 0
+    # cuts: [0, a) | empty | [a, b) | [b, n); the first shard is short enough to hold no SA record on most data
+    a, b = n // 50, n // 2
+    cuts = [(0, a), (a, a), (a, b), (b, n)]
+    shards = [(rec[int(off[x]):int(off[y])], off[x:y + 1] - off[x]) for x, y in cuts]
+    g, extras, parts = _packed_rows(shards, names)
+    assert S._fetch_view(g) == want
+    assert int(parts[2][1]) == 0 and float(parts[0][1]) == 0.0          # the empty shard contributes nothing
+    # argument checks
+    dev = torch.device("cuda", 0)
+    c = _abi.Context(0)
+    c.set_references(names)
+    with pytest.raises(RuntimeError):
+        c.pack_sa_rows()                                  # no records loaded
+    c.load_records(*shards[2])
+    ptr, nb = c.pack_sa_rows()
+    assert nb % 16 == 0 and nb >= 64
+    msg = exchange.view(ptr, nb, "|u1", dev).clone()
+    with pytest.raises(RuntimeError):
+        c.pack_extra_rows(msg.data_ptr(), [8])            # misaligned message start
+    with pytest.raises(RuntimeError):
+        c.pack_extra_rows(msg.data_ptr(), [0] * 17)       # more than 16 ranks
+    xptr, xnb = c.pack_extra_rows(msg.data_ptr(), [0])
+    x = exchange.view(xptr, xnb, "|u1", dev).clone()
+    cc = _abi.Context(0)
+    cc.set_references(names)
+    with pytest.raises(RuntimeError):
+        cc.unpack_rows(x.data_ptr(), [0], msg.data_ptr(), [0])          # message kinds swapped
+    nrows, _ = cc.unpack_rows(msg.data_ptr(), [0], x.data_ptr(), [0])
+    assert nrows == cc.n_records
+    for call in (cc.rescan, lambda: cc.region_coverage([0], [0], [10]), cc.pack_sa_rows, lambda: cc.concordant_rows_only([0], [1000])):
+        with pytest.raises(RuntimeError):
+            call()                                         # a rows-only ctx holds no records
+    # concordant messages: a bad size is refused, an empty message counts nothing
+    c.set_params(min_bp_match_cutoff=100)
+    c.concordant_rows_only([0], [1000])
+    mptr, mnb = c.concordant_pack()
+    m = exchange.view(mptr, mnb, "|u1", dev).clone()
+    with pytest.raises(RuntimeError):
+        c.count_name_msgs(1, m.data_ptr(), [0], [mnb + 8], 0, 0)
+    cnt = c.count_name_msgs(1, m.data_ptr(), [0], [mnb], 0, 0)
+    assert cnt.shape == (1,) and int(cnt[0]) >= 0
+    c.close(); cc.close()
