@@ -73,3 +73,53 @@ def run_pipeline(eng, cn_seg, stop_after=None):
 def jsonify(x):
     import json
     return json.loads(json.dumps(x))
+
+
+# ---- hand-made BAM records for the edge-case tests -------------------------------------------------------------
+_OPS = "MIDNSHP=X"
+_SEQ = "=ACMGRSVTWYHKDBN"
+
+
+def make_record(name, tid, pos, mapq, flag, cigar, seq=None, aux=b"", l_seq=None):
+    """One BAM alignment record (block_size .. aux) as bytes.  cigar: [(op char, length)]; seq: base string, or None
+    for '*' (then l_seq gives the stored length, default 0 — QUAL is then 0xFF bytes of that length with no SEQ only
+    when l_seq is 0, as htslib writes it)."""
+    import struct
+    nm = name.encode() + b"\0"
+    cg = b"".join(struct.pack("<I", (ln << 4) | _OPS.index(op)) for op, ln in cigar)
+    if seq is None:
+        ls = 0 if l_seq is None else l_seq
+        sq = bytes((ls + 1) // 2)
+        ql = b"\xff" * ls
+    else:
+        ls = len(seq)
+        codes = [_SEQ.index(c) for c in seq] + ([0] if ls & 1 else [])
+        sq = bytes((codes[2 * k] << 4) | codes[2 * k + 1] for k in range(len(codes) // 2))
+        ql = bytes([30]) * ls
+    body = struct.pack("<iiBBHHHIiii", tid, pos, len(nm), mapq, 4680, len(cigar), flag, ls, -1, -1, 0) + nm + cg + sq + ql + aux
+    return struct.pack("<i", len(body)) + body
+
+
+def frame_records(records, align=16):
+    """Concatenate records with 16-byte aligned starts -> (uint8 array, uint64 offsets[n+1]); offsets[n] is the end of
+    the last record's padded frame, as the host reader produces them."""
+    import numpy as np
+    buf, off = bytearray(), [0]
+    for r in records:
+        buf += r
+        buf += b"\0" * (-len(buf) % align)
+        off.append(len(buf))
+    return np.frombuffer(bytes(buf), np.uint8).copy(), np.array(off, np.uint64)
+
+
+def aux_tag(tag, ty, value):
+    import struct
+    t = tag.encode() + ty.encode()
+    if ty in "ZH":
+        return t + value.encode() + b"\0"
+    if ty == "A":
+        return t + value.encode()
+    if ty == "B":
+        sub, vals = value
+        return t + sub.encode() + struct.pack("<i", len(vals)) + b"".join(struct.pack("<" + {"c": "b", "C": "B", "s": "h", "S": "H", "i": "i", "I": "I", "f": "f"}[sub], v) for v in vals)
+    return t + struct.pack("<" + {"c": "b", "C": "B", "s": "h", "S": "H", "i": "i", "I": "I", "f": "f"}[ty], value)
