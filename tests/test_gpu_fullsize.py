@@ -1,0 +1,107 @@
+"""Size-independent properties at BASELINE.json's full size (C2: 260 k records, 13 GB of decoded BAM, 7.2 aligned
+Gbases), where the CPU oracle would take hours: sums against the generator's own counts, additivity of coverage,
+idempotence of the scan, equality of the two record placements, structural invariants of the chimeric table."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def c2_full():
+    from sim import configs
+    from sim.generate import simulate
+    cfg = configs.CONFIGS["C2"](scale=1.0)
+    return cfg, simulate(cfg)
+
+
+def _load(cfg, data, placement):
+    from coral_b200 import _abi
+    c = _abi.Context(0)
+    c.set_references([r[0] for r in cfg.refs])
+    if placement == "mapped":
+        nb = int(data.rec_off[-1])
+        buf = np.empty(nb + 64, np.uint8)
+        buf[:nb] = data.rec[:nb]
+        buf[nb:] = 0
+        c.load_records(buf[:nb], data.rec_off, placement="mapped", slack=64)
+    else:
+        c.load_records(data.rec, data.rec_off)
+    return c
+
+
+def test_full_size_properties(built_lib, c2_full):
+    cfg, data = c2_full
+    names = [r[0] for r in cfg.refs]
+    c = _load(cfg, data, "copy")
+    t = c.record_table()
+    assert c.n_records == data.n_records == len(t["tid"])
+    # against the generator's plan: every kept piece is one record with that placement and reference span
+    kept = data.pieces[data.pieces["dropped"] == 0]
+    trip = lambda a, b, c_: np.sort((a.astype(np.int64) << 48) | (b.astype(np.int64) << 20) | c_.astype(np.int64))    # noqa: E731
+    assert np.array_equal(trip(t["tid"], t["pos"], t["endpos"] - t["pos"]), trip(kept["tid"], kept["ref_start"], kept["ref_len"]))
+    # CIGAR sums of a random sample of records, recomputed from the record bytes
+    off = np.asarray(data.rec_off, dtype=np.int64)
+    for i in np.random.default_rng(1).choice(data.n_records, 300, replace=False).tolist():
+        o = int(off[i])
+        ncig = int(data.rec[o + 16]) | int(data.rec[o + 17]) << 8
+        cg = np.frombuffer(data.rec[o + 36 + int(data.rec[o + 12]):][:4 * ncig].tobytes(), "<u4")
+        op, ln = cg & 15, (cg >> 4).astype(np.int64)
+        assert int(t["aligned_bases"][i]) == int(ln[(op == 0) | (op == 7) | (op == 8)].sum())
+        assert int(t["infer_len"][i]) == int(ln[np.isin(op, (0, 1, 4, 5, 7, 8))].sum())
+        assert int(t["endpos"][i] - t["pos"][i]) == int(ln[np.isin(op, (0, 2, 3, 7, 8))].sum())
+        assert int(t["n_cigar"][i]) == ncig
+    assert int(t["non_acgt"].sum()) == 0
+    assert bool((t["endpos"] > t["pos"]).all()) and bool((t["infer_len"] >= t["l_seq"]).all())
+    # file order = coordinate order
+    key = t["tid"].astype(np.int64) << 32 | t["pos"].astype(np.int64)
+    assert bool((np.diff(key) >= 0).all())
+    # scan is idempotent
+    c.rescan()
+    t2 = c.record_table()
+    for k in t:
+        assert np.array_equal(t[k], t2[k]), k
+    # coverage: a region covering a whole contig's records sums their aligned bases; splitting it anywhere keeps the sum
+    rng = np.random.default_rng(5)
+    for (chrom, lo, hi) in cfg.background:
+        tid = names.index(chrom)
+        on = t["tid"] == tid
+        a, b = int(t["pos"][on].min()), int(t["endpos"][on].max())
+        whole, cnt = c.region_coverage([tid], [a], [b])
+        assert int(whole[0]) == int(t["aligned_bases"][on].sum()) and int(cnt[0]) == int(on.sum())
+        cuts = np.unique(np.concatenate([[a, b], rng.integers(a + 1, b, 40)]))
+        parts, pcnt = c.region_coverage([tid] * (len(cuts) - 1), cuts[:-1], cuts[1:])
+        assert int(parts.sum()) == int(whole[0])
+        assert int(pcnt.sum()) >= int(cnt[0])                   # a record straddling a cut is counted on both sides
+        # record counts against the interval rule of fetch(): pos < stop and endpos > start
+        for k in range(0, len(cuts) - 1, 7):
+            want = int((on & (t["pos"] < cuts[k + 1]) & (t["endpos"] > cuts[k])).sum())
+            assert int(pcnt[k]) == want
+    # chimeric table: reads = distinct names among SA-bearing records; alignments sorted by (qs, qe) inside a read
+    keys = c.record_keys()
+    sa = keys["sa_off"] != 0
+    pairs = np.stack([keys["name_lo"][sa], keys["name_hi"][sa]], 1)
+    f = c.fetch()
+    assert f["n_reads"] == len(np.unique(pairs, axis=0))
+    assert set(np.unique(f["read_status"]).tolist()) <= {0, 1, 2}
+    ap = f["aln_ptr"].astype(np.int64)
+    assert int(ap[-1]) == f["n_aln"] == len(f["qs"])
+    inside = np.ones(f["n_aln"], bool)
+    inside[ap[:-1][ap[:-1] < f["n_aln"]]] = False              # first alignment of each read
+    q = f["qs"].astype(np.int64) << 32 | f["qe"].astype(np.int64)
+    assert bool((np.diff(q)[inside[1:]] >= 0).all())
+    assert bool((f["qe"] > f["qs"]).all())
+    # read_first_rec is a record of the read, and no two reads share a name
+    fr = f["read_first_rec"].astype(np.int64)
+    assert bool((fr < c.n_records).all())
+    assert len(np.unique(np.stack([keys["name_lo"][fr], keys["name_hi"][fr]], 1), axis=0)) == f["n_reads"]
+    # both placements see the same bytes
+    m = _load(cfg, data, "mapped")
+    tm = m.record_table()
+    for k in t:
+        assert np.array_equal(t[k], tm[k]), k
+    fm = m.fetch()
+    for k in ("read_first_rec", "read_len", "read_status", "aln_ptr", "qs", "qe", "tid", "rstart", "rend", "strand", "mapq", "nm"):
+        assert np.array_equal(f[k], fm[k]), k
+    assert (fm["nm_sum"], fm["nm_sumsq"], fm["nm_n"]) == (f["nm_sum"], f["nm_sumsq"], f["nm_n"])
+    m.close(); c.close()
