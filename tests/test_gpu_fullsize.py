@@ -105,3 +105,44 @@ def test_full_size_properties(built_lib, c2_full):
         assert np.array_equal(f[k], fm[k]), k
     assert (fm["nm_sum"], fm["nm_sumsq"], fm["nm_n"]) == (f["nm_sum"], f["nm_sumsq"], f["nm_n"])
     m.close(); c.close()
+
+
+def test_full_size_sharded_equals_single(built_lib, c2_full, tmp_path_factory):
+    """The full C2 file cut into 3 shards (thread ranks on one device, real kernels and messages) ends every stage in
+    the state of the 1-GPU run, graph.txt included."""
+    import threading
+    import bench
+    import util
+    from coral_b200 import sharded
+    from coral_b200.infer_breakpoint_graph import bam_to_breakpoint_nanopore
+    from coral_b200.records import RecordSet
+    cfg, data = c2_full
+    cns, seed = bench.write_inputs(cfg, str(tmp_path_factory.mktemp("c2_full_inputs")))
+    rs = RecordSet([r[0] for r in cfg.refs], data.rec, data.rec_off)
+    one = util.jsonify(util.run_pipeline(bam_to_breakpoint_nanopore(None, seed, records=rs, placement="copy"), cns))
+    assert len(one["find_breakpoints"]["new_bp_list"]) == 12          # C2 is built from 12 junctions
+    world = 3
+    comms = sharded.ThreadComm.make(world)
+    out, err = [None] * world, []
+
+    def body(r):
+        try:
+            eng = sharded.make_sharded_engine(rs, seed, comms[r], device=0, placement="copy")
+            out[r] = util.jsonify(util.run_pipeline(eng, cns))
+            eng.closebam()
+        except Exception as ex:      # noqa
+            import traceback
+            traceback.print_exc()
+            err.append(ex)
+            comms[r]._s.barrier.abort()
+    th = [threading.Thread(target=body, args=(r,)) for r in range(world)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not err, err
+    for r in range(world):
+        for stage in one:
+            a, b = dict(one[stage]), dict(out[r][stage])
+            if stage == "fetch":          # f64 partial sums are added in another order: 1e-9 relative
+                na, nb = a.pop("nm_stats"), b.pop("nm_stats")
+                assert na[2] == nb[2] and all(abs(x - y) <= 1e-9 * abs(x) for x, y in zip(na[:2], nb[:2]))
+            assert a == b, (r, stage)
