@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcoral_b200.so")
+LIB_PATH = os.environ.get("CORAL_B200_LIB") or os.path.join(_HERE, "libcoral_b200.so")   # override: kernel tuning runs
 
 CHR_IDX = {('chr%d' % (i + 1)): i for i in range(22)}
 CHR_IDX.update({'chrX': 22, 'chrY': 23, 'chrM': 24})
