@@ -243,10 +243,8 @@ class bam_to_breakpoint_nanopore(HostSteps):
         r = gpu_ops.cluster_arrays(self._ctx, cand, cutoff, self.max_breakpoint_distance_cutoff, cutoff,
                                    self.min_bp_match_cutoff_)
         order, ptr, sub_of = r["order"], r["cluster_ptr"], r["sub_of"]
-        rd, ii, jj = cand["read"], cand["i"], cand["j"]
-
-        def tup(m):
-            return (names[rd[m]], int(ii[m]), int(jj[m]))
+        tups = list(zip([names[x] for x in cand["read"].tolist()], cand["i"].tolist(), cand["j"].tolist()))
+        tup = tups.__getitem__
         for c in range(r["n_clusters"]):
             b, e = int(ptr[c]), int(ptr[c + 1])
             if e - b < cutoff:
@@ -261,7 +259,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
                 if r["row_nb"][row] == 0:        # bpc2bp with no member near the called position (bu:352-353)
                     yield bp, [], [0, 0, 0, 0, 0, 0]
                     continue
-                yield bp, [tup(int(m)) for m in members[subs == k]], gpu_ops.stats_row(r["row_stats"][row])
+                yield bp, [tups[m] for m in members[subs == k].tolist()], gpu_ops.stats_row(r["row_stats"][row])
 
     @_gc_paused
     def hash_alignment_to_seg(self):
