@@ -9,8 +9,10 @@ the records of a chimeric read live on several shards.  Every rank exports one s
 the rows are all-gathered in rank (= file) order, and every rank runs the same deterministic fetch on the
 gathered rows (coral_load_rows), so candidates and clustering are replicated and identical to the 1-GPU result.
 
-This module holds the communicators and the host-side exchange logic (pure numpy: covered by world_size-2 gloo
-tests on CPU); `ShardedEngine` at the bottom binds it to the CUDA contexts.
+This module holds the communicators, the engine that binds the exchanges to the CUDA contexts (`ShardedEngine`, at
+the bottom: packed device messages, csrc/exchange.cu + exchange.py) and — in plain numpy — the statement of what each
+exchange must deliver (`exchange_fetch_rows`, `merge_smalldel_rows`, `combine_concordant`): the CPU tests run those
+over thread ranks and world_size-2 gloo, and the GPU tests check the device messages against the same file view.
 """
 import threading
 
