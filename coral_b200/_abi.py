@@ -387,6 +387,29 @@ class Context(object):
             return cnt, self.concordant_rows()
         return cnt, {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
 
+    def alignment_paths(self, iv_tid, iv_start, iv_stop, se_tid, se_l, se_r, name_rec=(), name_lo=(), name_hi=(),
+                        min_overlap=500, min_mapq=20):
+        """Concordant-read pass of compute_path_constraints (ibg:1303-1310).  Intervals [start, stop) in list order,
+        sequence edges [l, r] sorted by (tid, l) and disjoint, the name set through records carrying the names and / or
+        128-bit name hashes.  -> dict(n, rec, iv, first, last): rows in (interval, file) order."""
+        i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+        iv_tid, iv_start, iv_stop, se_tid, se_l, se_r = map(i32, (iv_tid, iv_start, iv_stop, se_tid, se_l, se_r))
+        name_rec = np.ascontiguousarray(name_rec, dtype=np.uint32)
+        name_lo = np.ascontiguousarray(name_lo, dtype=np.uint64)
+        name_hi = np.ascontiguousarray(name_hi, dtype=np.uint64)
+        assert len(name_lo) == len(name_hi) and len(iv_tid) == len(iv_start) == len(iv_stop) and len(se_tid) == len(se_l) == len(se_r)
+        n = ctypes.c_int64()
+        self._check(self._L.coral_alignment_paths(
+            self._h, _p(iv_tid), _p(iv_start), _p(iv_stop), ctypes.c_int32(len(iv_tid)), _p(se_tid), _p(se_l), _p(se_r),
+            ctypes.c_int32(len(se_tid)), _p(name_rec), ctypes.c_int64(len(name_rec)), _p(name_lo), _p(name_hi),
+            ctypes.c_int64(len(name_lo)), ctypes.c_int32(min_overlap), ctypes.c_int32(min_mapq), ctypes.byref(n)))
+        n = int(n.value)
+        out = {"n": n, "rec": np.zeros(n, np.uint32), "iv": np.zeros(n, np.int32), "first": np.zeros(n, np.int32),
+               "last": np.zeros(n, np.int32)}
+        if n:
+            self._check(self._L.coral_get_alignment_paths(self._h, _p(out["rec"]), _p(out["iv"]), _p(out["first"]), _p(out["last"])))
+        return out
+
     def sa_text(self, text, ent_ptr, ent_beg, ent_end, read_len):
         n_reads = len(read_len)
         ne = int(ent_ptr[-1])

@@ -50,6 +50,14 @@ void coral_destroy(coral_ctx* c) {
                      &c->chim.read_first_rec, &c->chim.read_len, &c->chim.read_status, &c->chim.aln_ptr, &c->chim.qs,
                      &c->chim.qe, &c->chim.tid, &c->chim.rs, &c->chim.re, &c->chim.strand, &c->chim.mapq, &c->chim.nm};
     for (DevBuf* b : all) b->release();
+    for (DevBuf& b : c->sw) b.release();
+    for (DevBuf& b : c->cw) b.release();
+    for (DevBuf& b : c->pw) b.release();
+    DevBuf* tables[] = {&c->paths.rec, &c->paths.iv, &c->paths.first, &c->paths.last,
+                        &c->sdel.rec, &c->sdel.ai, &c->sdel.next_start, &c->sdel.prev_end, &c->sdel.first_start, &c->sdel.last_end, &c->sdel.mapq,
+                        &c->cand.read, &c->cand.i, &c->cand.j, &c->cand.chr1, &c->cand.pos1, &c->cand.chr2, &c->cand.pos2, &c->cand.rgap,
+                        &c->cand.mq1, &c->cand.mq2, &c->cand.o1, &c->cand.o2, &c->cand.flag};
+    for (DevBuf* b : tables) b->release();
     coral_release_tables(c);
     for (int i = 0; i < CORAL_N_STAGES; i++) {
         if (c->ev_beg[i]) cudaEventDestroy(c->ev_beg[i]);

@@ -85,6 +85,13 @@ struct CandTable {
     bool valid = false;
 };
 
+// Rows of coral_alignment_paths in emission order (interval list order, then file order), ibg:1303-1321.
+struct PathTable {
+    DevBuf rec, iv, first, last;
+    int64_t n = 0;
+    bool valid = false;
+};
+
 struct coral_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -119,6 +126,8 @@ struct coral_ctx {
     DevBuf cw[32];   // cluster / peel work buffers and results
     int64_t cl_n = 0, cl_n_clusters = 0;
     bool cl_valid = false;
+    PathTable paths;
+    DevBuf pw[11];   // alignment-path (compute_path_constraints) work buffers
     DevBuf xmsg[3];  // packed exchange messages (SA rows, extra primaries, concordant rows): live until the next pack
     DevBuf status;  // int32[8] device status words (format errors etc.)
 

@@ -19,6 +19,7 @@ import numpy as np
 
 from . import global_names
 from .breakpoint_graph import BreakpointGraph
+from .path_steps import PathConstraintSteps
 
 _Hit = namedtuple("_Hit", ["begin", "end", "data"])
 
@@ -66,7 +67,7 @@ def _t():
     return "#TIME " + '%.4f\t' % (time.time() - global_names.TSTART)
 
 
-class HostSteps(object):
+class HostSteps(PathConstraintSteps):
     # class constants of the reference (ibg:25-33)
     max_seq_len = 2000000
     cn_gain = 5.0

@@ -50,6 +50,8 @@ class bam_to_breakpoint_nanopore(HostSteps):
         self._name_rec = {}     # read name -> index of one record carrying it (for concordant-edge rbps)
         self._read_names = []   # chimeric read order of the device table
         self._read_index = {}
+        self._ce_recs = None    # (names, a record of each) over all concordant-edge name sets of the last assign_cov
+        self._ce_rec_of = None
         self._read_seeds(seedfile)
 
     # ---- a12: ibg:75-136 ---------------------------------------------------------------------------------
@@ -340,6 +342,8 @@ class bam_to_breakpoint_nanopore(HostSteps):
         bounds = np.searchsorted(r_edge, np.arange(len(uniq) + 1))
         urec, inv = np.unique(r_rec, return_inverse=True)
         unames = self._names_of(urec)
+        self._ce_recs = (unames, urec)          # a record per name of every ce[9]: compute_path_constraints' name set
+        self._ce_rec_of = None
         row_names = [unames[i] for i in inv.tolist()]
         out = [set(row_names[bounds[k]:bounds[k + 1]]) for k in range(len(uniq))]
         return [int(x) for x in cnt], out
@@ -363,6 +367,49 @@ class bam_to_breakpoint_nanopore(HostSteps):
                 ce = self.lr_graph[gi].concordant_edges[ci]
                 ce[9] = set(names_of[k]) if len(own) > 1 else names_of[k]
                 ce[8] = cnt[k]
+
+    # ---- §8f-2: concordant-read pass of compute_path_constraints (ibg:1303-1321) -----------------------------------
+    def _sorted_sequence_edges(self, g):
+        """Sequence edges of one graph as device columns sorted by (tid, l) + the map back to graph edge ids."""
+        se = g.sequence_edges
+        perm = sorted(range(len(se)), key=lambda k: (self._tid[se[k][0]], se[k][1]))
+        return ([self._tid[se[k][0]] for k in perm], [se[k][1] for k in perm], [se[k][2] for k in perm],
+                np.array(perm, np.int64))
+
+    def _name_set_records(self, concordant_reads):
+        """A local record per read name of the set (names come from the ce[9] sets assign_cov built)."""
+        if self._ce_rec_of is None:
+            unames, urec = self._ce_recs if self._ce_recs is not None else ([], np.zeros(0, np.int64))
+            self._ce_rec_of = dict(zip(unames, urec.tolist()))
+        rec_of, other = self._ce_rec_of, self._name_rec
+        return [rec_of[nm] if nm in rec_of else other[nm] for nm in concordant_reads]
+
+    @staticmethod
+    def _distinct_runs(first, last):
+        """Rows in emission order -> [(first, last, count)] in first-seen order."""
+        if len(first) == 0:
+            return []
+        key = (first.astype(np.int64) << 32) | last.astype(np.int64)
+        uk, idx, cnt = np.unique(key, return_index=True, return_counts=True)
+        o = np.argsort(idx, kind="stable")
+        return [(int(uk[k] >> 32), int(uk[k] & 0xffffffff), int(cnt[k])) for k in o]
+
+    def _path_rows(self, g, intervals, **name_set):
+        t, l, r, perm = self._sorted_sequence_edges(g)
+        rows = self._ctx.alignment_paths([self._tid[a[0]] for a in intervals], [a[1] for a in intervals],
+                                         [a[2] + 1 for a in intervals], t, l, r, **name_set)
+        return rows["iv"], perm[rows["first"]], perm[rows["last"]]
+
+    def _concordant_read_runs(self, amplicon_idx, intervals, concordant_reads):
+        if not intervals or not concordant_reads:
+            return []
+        _, first, last = self._path_rows(self.lr_graph[amplicon_idx], intervals,
+                                         name_rec=self._name_set_records(concordant_reads))
+        return self._distinct_runs(first, last)
+
+    @_gc_paused
+    def compute_path_constraints(self):
+        return HostSteps.compute_path_constraints(self)
 
     def closebam(self):
         self.lr_bamfh.close()

@@ -408,6 +408,7 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             table = {}
             for part in self._comm.all_gather((keys[:, 1].tolist(), keys[:, 2].tolist(), self._names_of(urec.astype(np.int64)))):
                 table.update(zip(zip(part[0], part[1]), part[2]))
+            self._ce_hash = table          # (hash lo, hi) -> name over every ce[9]: compute_path_constraints' name set
             out = [set() for _ in uniq]
             for a, n in zip(st, sz):
                 g = raw[a + 64:a + n].view(np.int64).reshape(-1, 4)
@@ -415,6 +416,21 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
                 for e, lo, hi in g[:, :3].tolist():
                     out[e].add(table[(lo, hi)])
             return [int(x) for x in cnt], out
+
+        # §8f-2: the name set spans shards, so it travels as name hashes; every rank runs the pass on its own records,
+        # the rows are gathered in rank (= file) order and put back in (interval, file) order
+        def _concordant_read_runs(self, amplicon_idx, intervals, concordant_reads):
+            if not intervals or not concordant_reads:
+                return []
+            hash_of = {nm: h for h, nm in getattr(self, "_ce_hash", {}).items()}
+            hash_of.update({nm: h for nm, h in self._name_hash.items() if nm not in hash_of})
+            keys = np.array([hash_of[nm] for nm in concordant_reads], np.int64).reshape(-1, 2)
+            iv, first, last = self._path_rows(self.lr_graph[amplicon_idx], intervals, name_lo=keys[:, 0].view(np.uint64),
+                                              name_hi=keys[:, 1].view(np.uint64))
+            parts = self._comm.all_gather((iv, first, last))
+            iv = np.concatenate([p[0] for p in parts])
+            o = np.argsort(iv, kind="stable")
+            return self._distinct_runs(np.concatenate([p[1] for p in parts])[o], np.concatenate([p[2] for p in parts])[o])
 
         def closebam(self):
             self._cctx.close()

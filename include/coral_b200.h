@@ -115,7 +115,8 @@ int coral_rescan(coral_ctx* ctx);
 #define CORAL_STAGE_CLUSTER 5
 #define CORAL_STAGE_BPC2BP 6
 #define CORAL_STAGE_STAB 7
-#define CORAL_N_STAGES 8
+#define CORAL_STAGE_PATHS 8
+#define CORAL_N_STAGES 9
 float coral_stage_ms(coral_ctx* ctx, int stage);
 
 /* Per-record scan table copied to host arrays (any pointer may be NULL to skip that column). */
@@ -274,6 +275,22 @@ int coral_get_concordant_rows(coral_ctx* ctx, uint32_t* edge, uint32_t* rec, uin
 int coral_concordant_pack(coral_ctx* ctx, uint64_t* d_msg, uint64_t* nbytes);
 int coral_count_name_msgs(coral_ctx* ctx, int32_t n_edges, int32_t n_ranks, const uint8_t* d_buf, const uint64_t* starts,
                           const uint64_t* sizes, const uint64_t* d_rb_rows, int64_t n_rb, int64_t* lr_count);
+
+/* ---- subpath constraints: the concordant-read pass ------------------------------------------------------ *
+ * replaces the record loop of compute_path_constraints (ibg:1303-1310: fetch(interval) + `q >= 20 and rn in
+ * concordant_reads` + path_constraints.py:48-84 alignment_to_path up to the graph walk).  Intervals are
+ * [start, stop) in the caller's list order; sequence edges [l, r] inclusive, sorted by (tid, l) and disjoint (what
+ * build_graph + sort_edges produce).  The name set ("concordant_reads") is given through
+ * records of this ctx that carry the names (name_rec) and / or as 128-bit name hashes (name_lo, name_hi: the hash of
+ * coral_get_record_keys; the multi-GPU form, where the set spans shards); either may be empty.
+ * One row per (interval, record) pair whose trimmed run keeps >= 3 edges: (record, interval index, first edge, last
+ * edge), in the reference's order — interval list order, then file order.  A record of the set whose reference_end
+ * pysam reports as None (unmapped flag or no CIGAR) makes the reference raise TypeError: CORAL_E_FORMAT. */
+int coral_alignment_paths(coral_ctx* ctx, const int32_t* iv_tid, const int32_t* iv_start, const int32_t* iv_stop,
+                          int32_t n_iv, const int32_t* se_tid, const int32_t* se_l, const int32_t* se_r, int32_t n_se,
+                          const uint32_t* name_rec, int64_t n_name_rec, const uint64_t* name_lo, const uint64_t* name_hi,
+                          int64_t n_name_hash, int32_t min_overlap, int32_t min_mapq, int64_t* n_rows);
+int coral_get_alignment_paths(coral_ctx* ctx, uint32_t* rec, int32_t* iv, int32_t* first, int32_t* last);
 
 #ifdef __cplusplus
 }

@@ -402,6 +402,42 @@ class OracleHotPath(object):
                 ce[8] = len((rls & rrs & rls1 & rrs1) - rbps)
 
 
+    # -- §8f-2: concordant-read pass of compute_path_constraints (ibg:1303-1310) --------------------------
+    def _concordant_read_runs(self, amplicon_idx, intervals, concordant_reads):
+        """Every record of the amplicon's intervals (list order, file order) with MAPQ >= 20 and a name in
+        `concordant_reads` -> its run of sequence edges (path_constraints.py:60-84); distinct runs with their record
+        counts in first-seen order.  The graph walk that spells a run out as a path is shared host code."""
+        g = self.lr_graph[amplicon_idx]
+        runs = {}
+        for aint in intervals:
+            for read in self.lr_bamfh.fetch(aint[0], aint[1], aint[2] + 1):
+                if read.mapq >= 20 and read.query_name in concordant_reads:
+                    ids = alignment_run(g, [read.reference_name, read.reference_start, read.reference_end])
+                    if ids:
+                        key = (ids[0], ids[-1])
+                        runs[key] = runs.get(key, 0) + 1
+        return [(a, b, n) for (a, b), n in runs.items()]
+
+
+def alignment_run(g, rint, min_overlap=500):
+    """path_constraints.py:60-84: sequence edges touched by [chr, start, end], by start; the first / last edge is
+    dropped when the alignment shares < min_overlap with it, then edges shorter than min_overlap are dropped from
+    that end (never the last one left); runs of fewer than three edges give no path."""
+    lst = [i for i, sseg in enumerate(g.sequence_edges) if interval_overlap(rint, sseg)]
+    if len(lst) == 0:
+        return []
+    lst = sorted(lst, key=lambda i: g.sequence_edges[i][1])
+
+    def shared(i):
+        return min(g.sequence_edges[i][2], rint[2]) - max(g.sequence_edges[i][1], rint[1])
+    for end in (0, -1):
+        if len(lst) > 1 and shared(lst[end]) < min_overlap:
+            del lst[end]
+        while len(lst) > 1 and g.sequence_edges[lst[end]][7] < min_overlap:
+            del lst[end]
+    return lst if len(lst) > 2 else []
+
+
 # ---- remaining interval helpers used by the host steps (bu:18-34, :54-67) ---------------------------------
 def interval_adjacent(a, b):
     """bu:25-34."""

@@ -53,6 +53,22 @@ def canon_chimeric(ca):
     return out
 
 
+def canon_path(path):
+    """A subpath and its reverse are the same constraint (ibg:1282-1287); which orientation is stored depends on the
+    iteration order of a set of read tuples (ibg:1070, 1086), so the canonical form is the smaller of the two."""
+    fwd = [list(x) for x in path]
+    return min(fwd, fwd[::-1], key=repr)
+
+
+def canon_path_constraints(pc):
+    """{amplicon index: [paths, counts, amplicon ids]} -> per amplicon the sorted [canonical path, count, amplicon id]."""
+    out = []
+    for ai in sorted(pc):
+        paths, counts, amps = pc[ai]
+        out.append(sorted(([canon_path(p), int(c), int(a)] for p, c, a in zip(paths, counts, amps)), key=repr))
+    return out
+
+
 def graph_text(g, writer):
     import tempfile
     fd, p = tempfile.mkstemp(suffix=".txt")
@@ -135,6 +151,11 @@ def run(bam, cn_seg, seed, min_bp_support=1.0, stop_after=None, log=None):
             "graph_txt": graph_text(g, bg.output_breakpoint_graph_lr),
         })
     st["stages"]["assign_cov"] = {"graphs": graphs}
+    if stop_after == "assign_cov":
+        return st
+    # the step after the path (cycle_decomposition.py:2067): reads -> subpath constraints (ibg:1059-1323)
+    timed("compute_path_constraints", b.compute_path_constraints)
+    st["stages"]["compute_path_constraints"] = {"path_constraints": canon_path_constraints(b.path_constraints)}
     return st
 
 

@@ -67,6 +67,11 @@ def run_pipeline(eng, cn_seg, stop_after=None):
             "discordant_edges": [list(de[:10]) + [sorted([list(t) for t in de[10]])] + [de[11]] for de in g.discordant_edges],
             "graph_txt": txt})
     st["assign_cov"] = {"graphs": graphs}
+    if stop_after == "assign_cov":
+        return st
+    from oracle.ref_runner import canon_path_constraints
+    eng.compute_path_constraints()
+    st["compute_path_constraints"] = {"path_constraints": canon_path_constraints(eng.path_constraints)}
     return st
 
 
