@@ -122,7 +122,8 @@ def reference_arm(a, rank, world):
         for name, fn, args in (("read_cns", eng.read_cns, (paths["cn_seg"],)), ("fetch", eng.fetch, ()),
                                ("hash", eng.hash_alignment_to_seg, ()), ("intervals", eng.find_amplicon_intervals, ()),
                                ("smalldel", eng.find_smalldel_breakpoints, ()), ("breakpoints", eng.find_breakpoints, ()),
-                               ("graph", eng.build_graph, ()), ("assign_cov", eng.assign_cov, ())):
+                               ("graph", eng.build_graph, ()), ("assign_cov", eng.assign_cov, ()),
+                               ("path_constraints", eng.compute_path_constraints, ())):     # SURVEY 8f-2, not in the sum
             t0 = time.perf_counter()
             fn(*args)
             t[name] = time.perf_counter() - t0
@@ -422,6 +423,25 @@ def main():
     dt_e2e = time.perf_counter() - t1
     sampler.stop_flag = True
     sampler.join(timeout=2)
+    # SURVEY 8f-2 (the step after the path): compute_path_constraints through the public class, on its own clock
+    pc_info = None
+    if world == 1:
+        eng = make_engine("copy")
+        with gc_paused():
+            for fn, args in ((eng.read_cns, (cns,)), (eng.fetch, ()), (eng.hash_alignment_to_seg, ()),
+                             (eng.find_amplicon_intervals, ()), (eng.find_smalldel_breakpoints, ()),
+                             (eng.find_breakpoints, ()), (eng.build_graph, ()), (eng.assign_cov, ())):
+                fn(*args)
+            eng.compute_path_constraints()
+            l1 = eng._ctx.launch_count
+            t2 = time.perf_counter()
+            eng.compute_path_constraints()
+            pc_ms = (time.perf_counter() - t2) * 1e3
+        pc_info = {"ms_through_the_class": pc_ms, "kernel_ms": eng._ctx.stage_ms(8), "launches": int(eng._ctx.launch_count - l1),
+                   "constraints": int(sum(len(v[0]) for v in eng.path_constraints.values())),
+                   "sequence_edges": int(sum(len(g.sequence_edges) for g in eng.lr_graph)),
+                   "note": "not part of value / e2e; the CPU port's time for the same step is cpu_baseline.stage_s.path_constraints"}
+        eng.closebam()
 
     tt = torch.tensor([dt, dt_e2e], dtype=torch.float64, device="cuda")
     tot = torch.tensor([n_rec, aligned, launches], dtype=torch.float64, device="cuda")
@@ -465,6 +485,8 @@ def main():
         "stage_ms_per_step": {n: float(stage_ms[i] / a.steps) for i, n in enumerate(names)},
         "clocks": sampler.summary(),
     }
+    if pc_info is not None:
+        out["path_constraints_step"] = pc_info
     if world > 1:
         out["sharded_stage_ms_per_step"] = {k: v / a.steps for k, v in SHARD_MS.items()}
         out["fetch_exchange_ms_per_step"] = {k: v / a.steps for k, v in eng0.fetch_laps.items()}
