@@ -387,6 +387,15 @@ class Context(object):
             return cnt, self.concordant_rows()
         return cnt, {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
 
+    def cn_segment_index(self, seg_tid, seg_begin, seg_end, seg_idx, n_aln):
+        """hash_alignment_to_seg lookups (ibg:181-210) for every alignment of the chimeric table -> (lo, hi) int32."""
+        i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
+        seg_tid, seg_begin, seg_end, seg_idx = map(i32, (seg_tid, seg_begin, seg_end, seg_idx))
+        lo, hi = np.zeros(n_aln, np.int32), np.zeros(n_aln, np.int32)
+        self._check(self._L.coral_cn_segment_index(self._h, _p(seg_tid), _p(seg_begin), _p(seg_end), _p(seg_idx),
+                                                   ctypes.c_int32(len(seg_tid)), _p(lo), _p(hi)))
+        return lo, hi
+
     def alignment_paths(self, iv_tid, iv_start, iv_stop, se_tid, se_l, se_r, name_rec=(), name_lo=(), name_hi=(),
                         min_overlap=500, min_mapq=20):
         """Concordant-read pass of compute_path_constraints (ibg:1303-1310).  Intervals [start, stop) in list order,

@@ -190,13 +190,10 @@ class HostSteps(PathConstraintSteps):
                     if cni != -1:
                         by_seg.setdefault(cni, []).append(read)
 
-    def hash_alignment_to_seg(self):
-        """CN-segment indices of both ends of every alignment.  Lookups are batched per chromosome (binary search
-        over the non-overlapping segments); the sets and chimeric_alignments_seg are then filled in read order,
-        exactly as the per-alignment loop of the reference does."""
-        tabs = self._cni_tables()
-        if tabs is None:
-            return self._hash_alignment_to_seg_scalar()
+    def _cn_segment_ends(self, tabs):
+        """(lo, hi) lists over the alignments of chimeric_alignments in dict order: CN-segment index holding the lower /
+        higher end, -1 = none, -2 = chromosome without CN segments.  numpy form (the test oracle's engine); the product
+        overrides it with the device lookup (csrc/segments.cu)."""
         flat = [rint for ca in self.chimeric_alignments.values() for rint in ca[1]]
         n = len(flat)
         chrom = [r[0] for r in flat]
@@ -215,7 +212,16 @@ class HostSteps(PathConstraintSteps):
                 k = np.searchsorted(b, pos, side="right") - 1
                 kk = np.maximum(k, 0)
                 out[sel] = np.where((k >= 0) & (e[kk] > pos), d[kk], -1)
-        lo, hi = lo.tolist(), hi.tolist()
+        return lo.tolist(), hi.tolist()
+
+    def hash_alignment_to_seg(self):
+        """CN-segment indices of both ends of every alignment.  Lookups are batched per chromosome (binary search
+        over the non-overlapping segments); the sets and chimeric_alignments_seg are then filled in read order,
+        exactly as the per-alignment loop of the reference does."""
+        tabs = self._cni_tables()
+        if tabs is None:
+            return self._hash_alignment_to_seg_scalar()
+        lo, hi = self._cn_segment_ends(tabs)
         seg = self.chimeric_alignments_seg
         k = 0
         for read, ca in self.chimeric_alignments.items():

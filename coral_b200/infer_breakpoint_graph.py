@@ -50,6 +50,8 @@ class bam_to_breakpoint_nanopore(HostSteps):
         self._name_rec = {}     # read name -> index of one record carrying it (for concordant-edge rbps)
         self._read_names = []   # chimeric read order of the device table
         self._read_index = {}
+        self._aln_ptr = np.zeros(1, np.uint32)
+        self._read_kept = np.zeros(0, bool)
         self._ce_recs = None    # (names, a record of each) over all concordant-edge name sets of the last assign_cov
         self._ce_rec_of = None
         self._read_seeds(seedfile)
@@ -113,6 +115,8 @@ class bam_to_breakpoint_nanopore(HostSteps):
         mapq_all = f["mapq"].tolist()
         first_rec = f["read_first_rec"].astype(np.int64) if n_reads else np.zeros(0, np.int64)
         names = names_of(first_rec)
+        self._aln_ptr = f["aln_ptr"] if n_reads else np.zeros(1, np.uint32)
+        self._read_kept = np.zeros(n_reads, bool)     # reads whose alignments entered chimeric_alignments (table order)
         status = f["read_status"].tolist() if n_reads else []
         rlen = f["read_len"].tolist() if n_reads else []
         recs = first_rec.tolist()
@@ -139,6 +143,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
             if len(zero) and np.searchsorted(zero, a) != np.searchsorted(zero, b):
                 raise ZeroDivisionError("float division by zero")      # cp:268 with qe == qs
             self.chimeric_alignments[name] = (qint_all[a:b], rint_all[a:b], mapq_all[a:b], nmn_all[a:b])
+            self._read_kept[r] = True
         logging.info(_t() + "Computed alignment intervals on all chimeric reads.")
 
     # ---- shared tail of ibg:691-718 and ibg:775-802 -------------------------------------------------------
@@ -262,6 +267,20 @@ class bam_to_breakpoint_nanopore(HostSteps):
                     yield bp, [], [0, 0, 0, 0, 0, 0]
                     continue
                 yield bp, [tups[m] for m in members[subs == k].tolist()], gpu_ops.stats_row(r["row_stats"][row])
+
+    def _cn_segment_ends(self, tabs):
+        """The lookups of hash_alignment_to_seg (ibg:181-210) on the device chimeric table (coral_cn_segment_index)."""
+        rows = sorted((self._tid[c], b, e, d) for c, (bs, es, ds) in tabs.items() if c in self._tid
+                      for b, e, d in zip(bs.tolist(), es.tolist(), ds.tolist()))
+        n_aln = int(self._aln_ptr[-1])
+        lo, hi = self._chim_ctx.cn_segment_index([r[0] for r in rows], [r[1] for r in rows], [r[2] for r in rows],
+                                                 [r[3] for r in rows], n_aln)
+        per_read = np.diff(self._aln_ptr.astype(np.int64))
+        keep = np.repeat(self._read_kept, per_read)
+        n_py = sum(len(ca[1]) for ca in self.chimeric_alignments.values())
+        if int(keep.sum()) != n_py:
+            raise RuntimeError("chimeric_alignments no longer matches the device table fetch() built")
+        return lo[keep].tolist(), hi[keep].tolist()
 
     @_gc_paused
     def hash_alignment_to_seg(self):

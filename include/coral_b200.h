@@ -276,6 +276,14 @@ int coral_concordant_pack(coral_ctx* ctx, uint64_t* d_msg, uint64_t* nbytes);
 int coral_count_name_msgs(coral_ctx* ctx, int32_t n_edges, int32_t n_ranks, const uint8_t* d_buf, const uint64_t* starts,
                           const uint64_t* sizes, const uint64_t* d_rb_rows, int64_t n_rb, int64_t* lr_count);
 
+/* ---- CN-segment hashing of the chimeric alignments ---------------------------------------------------------- *
+ * replaces the lookups of hash_alignment_to_seg (ibg:181-210: pos2cni on the lower and the higher end of every local
+ * alignment).  CN segments [begin, end) sorted by (tid, begin), not overlapping, seg_idx = the caller's segment ids.
+ * lo_idx / hi_idx (one entry per alignment of the chimeric table, table order): the id of the segment holding that
+ * end, -1 when no segment of the contig holds it, -2 when the contig has no CN segment at all (ibg:184-186). */
+int coral_cn_segment_index(coral_ctx* ctx, const int32_t* seg_tid, const int32_t* seg_begin, const int32_t* seg_end,
+                           const int32_t* seg_idx, int32_t n_seg, int32_t* lo_idx, int32_t* hi_idx);
+
 /* ---- subpath constraints: the concordant-read pass ------------------------------------------------------ *
  * replaces the record loop of compute_path_constraints (ibg:1303-1310: fetch(interval) + `q >= 20 and rn in
  * concordant_reads` + path_constraints.py:48-84 alignment_to_path up to the graph walk).  Intervals are

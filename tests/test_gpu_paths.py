@@ -186,3 +186,61 @@ def test_alignment_paths_thresholds_and_errors(built_lib):
         _gpu_rows(ctx, refs, intervals, edges, name_rec=[0, 1])
     assert ei.value.code == -4 and "TypeError" in str(ei.value)
     ctx.close()
+
+
+@pytest.mark.parametrize("name,kw", [("C2", dict(scale=0.03)), ("C5", dict(scale=0.08, n_seeds=3, chroms=['chr20', 'chr21', 'chr22']))])
+def test_cn_segment_index_matches_interval_lookup(built_lib, dataset, name, kw):
+    """coral_cn_segment_index (the lookups of hash_alignment_to_seg, ibg:181-210) against the oracle's interval index
+    on random non-overlapping CN segments: ends inside a segment, in a hole, before the first / after the last segment,
+    exactly on begin / end - 1 / end, and a contig without any segment."""
+    from coral_b200 import _abi
+    from oracle.intervaltree_shim import IntervalTree
+    ds = dataset(name, **kw)
+    bam = _abi.BamFile(ds["paths"]["bam"], 4)
+    ctx = _abi.Context(0)
+    ctx.set_references(bam.references)
+    ctx.load_records(bam.rec, bam.rec_off)
+    f = ctx.fetch()
+    n_aln = int(f["aln_ptr"][-1])
+    assert n_aln > 50
+    rng = np.random.default_rng(9)
+    tids = np.unique(f["tid"])
+    skip = int(tids[-1]) if len(tids) > 1 else -1            # this contig gets no CN segment
+    ends = np.concatenate([f["rstart"], f["rend"]]).astype(np.int64)
+    rows, trees, idx = [], {}, 0
+    for t in tids.tolist():
+        if t == skip:
+            continue
+        mine = ends[np.concatenate([f["tid"], f["tid"]]) == t]
+        lo, hi = int(mine.min()), int(mine.max())
+        cuts = np.unique(np.concatenate([rng.integers(lo - 1000, hi + 1000, 60), rng.choice(mine, 20), rng.choice(mine, 20) + 1]))
+        tree = trees.setdefault(t, IntervalTree())
+        for k in range(len(cuts) - 1):
+            if rng.random() < 0.25:          # a hole
+                continue
+            b, e = int(cuts[k]), int(cuts[k + 1])
+            tree[b:e] = idx
+            rows.append((t, b, e, idx))
+            idx += 1
+    got_lo, got_hi = ctx.cn_segment_index([r[0] for r in rows], [r[1] for r in rows], [r[2] for r in rows],
+                                          [r[3] for r in rows], n_aln)
+
+    def want(t, p):
+        if t not in trees:
+            return -2
+        hit = trees[t][p]
+        assert len(hit) <= 1
+        return list(hit)[0].data if hit else -1
+    seen = set()
+    for k in range(n_aln):
+        t, a, b = int(f["tid"][k]), int(f["rstart"][k]), int(f["rend"][k])
+        w = (want(t, min(a, b)), want(t, max(a, b)))
+        assert (int(got_lo[k]), int(got_hi[k])) == w, (k, t, a, b)
+        seen.update(w)
+    assert -1 in seen and (skip < 0 or -2 in seen) and len(seen) > 10
+    # overlapping or unsorted segments are refused
+    with pytest.raises(_abi.CoralError):
+        ctx.cn_segment_index([0, 0], [100, 150], [200, 300], [0, 1], n_aln)
+    with pytest.raises(_abi.CoralError):
+        ctx.cn_segment_index([0, 0], [500, 100], [600, 200], [0, 1], n_aln)
+    ctx.close(); bam.close()
