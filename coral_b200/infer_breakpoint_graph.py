@@ -50,11 +50,14 @@ class bam_to_breakpoint_nanopore(HostSteps):
         self._name_rec = {}     # read name -> index of one record carrying it (for concordant-edge rbps)
         self._read_names = []   # chimeric read order of the device table
         self._read_index = {}
+        self._nm_stats_required = True   # hsr.fetch (the second caller of this pass) keeps no NM statistics
+        self._warn_no_primary = True
         self._aln_ptr = np.zeros(1, np.uint32)
         self._read_kept = np.zeros(0, bool)
         self._ce_recs = None    # (names, a record of each) over all concordant-edge name sets of the last assign_cov
         self._ce_rec_of = None
-        self._read_seeds(seedfile)
+        if seedfile is not None:
+            self._read_seeds(seedfile)
 
     # ---- a12: ibg:75-136 ---------------------------------------------------------------------------------
     def read_cns(self, cns):
@@ -97,10 +100,11 @@ class bam_to_breakpoint_nanopore(HostSteps):
     @_gc_paused
     def fetch(self):
         f, names_of = self._run_fetch()
-        if f["nm_zero_div"] or f["nm_n"] == 0:
-            raise ZeroDivisionError("division by zero")              # ibg:154 / ibg:159
-        mean = f["nm_sum"] / f["nm_n"]
-        self.nm_stats = [mean, math.sqrt(f["nm_sumsq"] / f["nm_n"] - mean ** 2), f["nm_n"]]
+        if self._nm_stats_required:
+            if f["nm_zero_div"] or f["nm_n"] == 0:
+                raise ZeroDivisionError("division by zero")              # ibg:154 / ibg:159
+            mean = f["nm_sum"] / f["nm_n"]
+            self.nm_stats = [mean, math.sqrt(f["nm_sumsq"] / f["nm_n"] - mean ** 2), f["nm_n"]]
         refs = self.lr_bamfh.references
         n_reads = f["n_reads"]
         ap = f["aln_ptr"].tolist() if n_reads else [0]
@@ -127,8 +131,9 @@ class bam_to_breakpoint_nanopore(HostSteps):
             self._name_rec[name] = recs[r]
             st = status[r]
             if st == 1:      # ibg:164-169
-                logging.warning(_t() + "Found chimeric read without primary alignment.")
-                logging.warning(_t() + "\tRead name: %s; Read length: N/A." % name)
+                if self._warn_no_primary:
+                    logging.warning(_t() + "Found chimeric read without primary alignment.")
+                    logging.warning(_t() + "\tRead name: %s; Read length: N/A." % name)
                 continue
             self.read_length[name] = rlen[r]
             if st == 2:      # cp:248-253
