@@ -248,8 +248,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--scale", type=float, default=float(os.environ.get("CORAL_BENCH_SCALE", "1.0")))
-    ap.add_argument("--e2e-placement", default="mapped", choices=["mapped", "copy"],
-                    help="e2e arm: kernels read the pinned host records in place over PCIe (mapped) or after a full H2D copy")
+    ap.add_argument("--e2e-placement", default="auto", choices=["auto", "mapped_async", "mapped", "copy"],
+                    help="e2e arm: kernels read the pinned host records in place over PCIe (mapped; mapped_async = fetch and "
+                         "the host steps after it run next to the scan; auto = mapped_async on 1 GPU, mapped on N) or after "
+                         "a full H2D copy")
     ap.add_argument("--only", default="", help="'scan': time the record-scan kernel alone (development aid)")
     ap.add_argument("--cprofile", action="store_true", help="cProfile of 20 device passes on rank 0 (development aid)")
     ap.add_argument("--profile", action="store_true",
@@ -261,6 +263,8 @@ def main():
     if a.impl == "reference":
         reference_arm(a, rank, world)
         return
+    if a.e2e_placement == "auto":
+        a.e2e_placement = "mapped_async" if world == 1 else "mapped"
     warm = max(a.warmup, 3)
 
     import torch
@@ -336,7 +340,8 @@ def main():
         t = time.perf_counter()
         eng = make_engine(a.e2e_placement)
         for name, fn, args in (("load+scan", None, ()), ("read_cns", eng.read_cns, (cns,)), ("fetch", eng.fetch, ()),
-                               ("hash", eng.hash_alignment_to_seg, ()), ("intervals", eng.find_amplicon_intervals, ()),
+                               ("hash", eng.hash_alignment_to_seg, ()), ("scan_join", eng._ctx.wait_scan, ()),
+                               ("intervals", eng.find_amplicon_intervals, ()),
                                ("smalldel", eng.find_smalldel_breakpoints, ()), ("breakpoints", eng.find_breakpoints, ()),
                                ("graph", eng.build_graph, ()), ("assign_cov", eng.assign_cov, ())):
             if fn is not None:
@@ -474,7 +479,7 @@ def main():
                    "l2_policy": "inputs (%.2f GB of record fields per pass) larger than the 126 MB L2" % (alg_bytes / 1e9)},
         "aligned_gbases_per_s": aligned_all * a.steps / dt / 1e9,
         "e2e": {"value": n_rec_all * e2e_steps / dt_e2e, "unit": "records/s", "ms_per_step": dt_e2e / e2e_steps * 1e3,
-                "h2d_bytes_per_step": (alg_bytes - 76 * n_rec if a.e2e_placement == "mapped" else nbytes) + 8 * (n_rec + 1),
+                "h2d_bytes_per_step": (alg_bytes - 76 * n_rec if a.e2e_placement.startswith("mapped") else nbytes) + 8 * (n_rec + 1),
                 "d2h_bytes_per_step": d2h, "placement": a.e2e_placement, "stage_ms": e2e_stage},
         "gpu_launches": int(launches_all),
         "roofline": {"bound": "hbm", "kernel": "k_scan_records", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -148,19 +148,25 @@ class Context(object):
     def load_records(self, rec, rec_off, global_ordinal=None, placement="copy", slack=0):
         """rec: uint8 array (host) of framed records; rec_off: uint64[n+1].
         placement "copy": records are copied to HBM; "mapped": they stay in (page-locked) host memory and the
-        kernels read them in place over PCIe — `rec` must then extend >= 64 bytes past rec_off[-1] and stay alive."""
+        kernels read them in place over PCIe — `rec` must then extend >= 64 bytes past rec_off[-1] and stay alive;
+        "mapped_async": as "mapped", but the call returns after the pre-scan (what fetch needs) while the full scan keeps
+        running; entry points that need it join it (wait_scan)."""
         rec = np.ascontiguousarray(rec, dtype=np.uint8)
         rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
         n = len(rec_off) - 1
         go = None if global_ordinal is None else np.ascontiguousarray(global_ordinal, dtype=np.uint64)
-        mode = {"copy": 0, "mapped": 2}[placement]
+        mode = {"copy": 0, "mapped": 2, "mapped_async": 3}[placement]
         nbytes = int(rec_off[-1]) if n >= 0 and len(rec_off) else 0
-        if mode == 2:
+        if mode >= 2:
             if rec.nbytes + int(slack) < nbytes + 64:     # `slack`: bytes the caller guarantees behind the view
                 raise ValueError("mapped placement needs 64 bytes of slack after the last record")
             self._keep = [rec]
         self._check(self._L.coral_load_records(self._h, _p(rec), ctypes.c_uint64(nbytes), _p(rec_off), ctypes.c_int64(n),
                                                _p(go), mode))
+
+    def wait_scan(self):
+        """Join the scan a "mapped_async" load left running (no-op otherwise); its format errors surface here."""
+        self._check(self._L.coral_wait_scan(self._h))
 
     def load_records_device(self, dev_ptr, nbytes, rec_off, global_ordinal=None):
         rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)

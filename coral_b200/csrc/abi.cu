@@ -39,9 +39,11 @@ int coral_create(int device, coral_ctx** out) {
 void coral_destroy(coral_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
+    if (c->scan_stream) { cudaStreamSynchronize(c->scan_stream); cudaStreamDestroy(c->scan_stream); }
+    c->scan_pending = false;
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->host_registered) cudaHostUnregister(c->host_registered);
-    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status, &c->xmsg[0], &c->xmsg[1], &c->xmsg[2],
+    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status, &c->scan_status, &c->xmsg[0], &c->xmsg[1], &c->xmsg[2],
                      &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->s6, &c->s7, &c->cub_tmp,
                      &c->rt.tid, &c->rt.pos, &c->rt.endpos, &c->rt.flag_mapq, &c->rt.lseq, &c->rt.ncig, &c->rt.infer,
                      &c->rt.mbases, &c->rt.nonacgt, &c->rt.fbs, &c->rt.lbe, &c->rt.name_lo, &c->rt.name_hi,
@@ -103,6 +105,10 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
                        const uint64_t* global_ordinal, int on_device) {
     if (!c || n < 0 || (n > 0 && (!recs || !offsets))) return CORAL_E_ARG;
     cudaSetDevice(c->device);
+    if (c->scan_pending) {                 // a previous asynchronous load is still scanning: join it first
+        c->scan_pending = false;
+        cudaStreamSynchronize(c->scan_stream);
+    }
     c->loaded = false;
     c->rows_only = false;
     for (int64_t i = 0; i < n; i++) {
@@ -121,7 +127,7 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     if (on_device == CORAL_RECORDS_DEVICE) {
         if (reinterpret_cast<uintptr_t>(recs) & 15) { c->err = "device record buffer must be 16-byte aligned"; return CORAL_E_ARG; }
         c->d_recs = recs;
-    } else if (on_device == CORAL_RECORDS_HOST_MAPPED) {
+    } else if (on_device == CORAL_RECORDS_HOST_MAPPED || on_device == CORAL_RECORDS_HOST_MAPPED_ASYNC) {
         // Records stay in page-locked host memory; every kernel reads them in place over PCIe (the scan only
         // fetches the fields it needs, so QUAL never crosses the link).
         if (reinterpret_cast<uintptr_t>(recs) & 15) { c->err = "host record buffer must be 16-byte aligned"; return CORAL_E_ARG; }
@@ -155,7 +161,8 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
         CORAL_CUDA(c, c->d_ordinal.ensure((size_t)n * 8));
         CORAL_CUDA(c, cudaMemcpyAsync(c->d_ordinal.p, global_ordinal, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
     }
-    CORAL_TRY(coral_run_scan(c));
+    if (on_device == CORAL_RECORDS_HOST_MAPPED_ASYNC) CORAL_TRY(coral_start_scan_async(c));
+    else CORAL_TRY(coral_run_scan(c));
     c->loaded = true;
     return CORAL_OK;
 }

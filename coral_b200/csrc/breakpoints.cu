@@ -237,6 +237,7 @@ extern "C" int coral_smalldel(coral_ctx* c, const int32_t* tid, const int32_t* s
     using namespace coral;
     if (!c || n_intervals < 0) return CORAL_E_ARG;
     if (!c->loaded || c->rows_only) { c->err = "coral_smalldel before coral_load_records"; return CORAL_E_STATE; }
+    CORAL_TRY(coral_wait_scan(c));
     if (n_intervals >= 65536) { c->err = "more than 65535 amplicon intervals"; return CORAL_E_ARG; }
     cudaSetDevice(c->device);
     SmallDelTable& T = c->sdel;

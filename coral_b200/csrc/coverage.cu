@@ -149,6 +149,7 @@ int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t*
                               int32_t n, int64_t* base_sum, int64_t* rec_count) {
     using namespace coral;
     if (!ctx->loaded) { ctx->err = "coral_region_coverage before coral_load_records"; return CORAL_E_STATE; }
+    CORAL_TRY(coral_wait_scan(ctx));
     if (n < 0) { ctx->err = "negative region count"; return CORAL_E_ARG; }
     if (n == 0) return CORAL_OK;
     for (int32_t i = 0; i < n; i++) {

@@ -292,6 +292,7 @@ extern "C" {
 int coral_pack_sa_rows(coral_ctx* c, uint64_t* d_msg, uint64_t* nbytes) {
     if (!c) return CORAL_E_ARG;
     if (!c->loaded || c->rows_only) { c->err = "coral_pack_sa_rows needs a ctx with records"; return CORAL_E_STATE; }
+    CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
     const int64_t n = c->nrec;
     CORAL_CUDA(c, c->s0.ensure((size_t)std::max<int64_t>(n, 1) * 4));
@@ -307,6 +308,7 @@ int coral_pack_extra_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf, c
                           uint64_t* nbytes) {
     if (!c || !d_buf || !starts) return CORAL_E_ARG;
     if (!c->loaded || c->rows_only) { c->err = "coral_pack_extra_rows needs a ctx with records"; return CORAL_E_STATE; }
+    CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
     MsgSet set;
     std::vector<MsgHdr> hdrs;

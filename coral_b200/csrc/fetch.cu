@@ -553,6 +553,7 @@ extern "C" int coral_nm_partials(coral_ctx* c, double* nm_sum, double* nm_sumsq,
     using namespace coral;
     if (!c) return CORAL_E_ARG;
     if (!c->loaded || c->rows_only) { c->err = "coral_nm_partials before coral_load_records"; return CORAL_E_STATE; }
+    CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
     const int64_t n = c->nrec;
     const int64_t nblk = (n + NM_BLOCK - 1) / NM_BLOCK;

@@ -170,6 +170,7 @@ extern "C" int coral_alignment_paths(coral_ctx* c, const int32_t* iv_tid, const 
     using namespace coral;
     if (!c || n_iv < 0 || n_se < 0 || n_name_rec < 0 || n_name_hash < 0 || !n_rows_out) return CORAL_E_ARG;
     if (!c->loaded || c->rows_only) { c->err = "coral_alignment_paths before coral_load_records"; return CORAL_E_STATE; }
+    CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
     PathTable& pt = c->paths;
     pt.n = 0; pt.valid = false;

@@ -36,6 +36,7 @@ int coral_get_record_keys(coral_ctx* c, uint64_t* name_lo, uint64_t* name_hi, ui
                           int32_t* nm) {
     if (!c) return CORAL_E_ARG;
     if (!c->loaded) { c->err = "coral_get_record_keys before coral_load_records"; return CORAL_E_STATE; }
+    CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
     const size_t n = (size_t)c->nrec;
     if (n == 0) return CORAL_OK;
@@ -55,6 +56,7 @@ int coral_load_rows(coral_ctx* c, int64_t n, const uint8_t* text, uint64_t text_
     using namespace coral;
     if (!c || n < 0 || (n > 0 && (!text_off || !name_lo || !name_hi || !flag || !mapq || !l_seq || !nm))) return CORAL_E_ARG;
     cudaSetDevice(c->device);
+    CORAL_TRY(coral_wait_scan(c));
     c->loaded = false;
     c->rows_only = true;
     for (int64_t i = 0; i < n; i++)
@@ -120,6 +122,7 @@ extern "C" {
 int coral_device_view(coral_ctx* c, uint64_t* ptrs, int32_t n_ptrs) {
     if (!c || !ptrs || n_ptrs < 9) return CORAL_E_ARG;
     if (!c->loaded) { c->err = "coral_device_view before coral_load_records"; return CORAL_E_STATE; }
+    CORAL_TRY(coral_wait_scan(c));
     RecordTable& t = c->rt;
     const void* v[9] = {c->d_recs, c->d_off.p, t.name_lo.p, t.name_hi.p, t.flag_mapq.p, t.lseq.p, t.nm.p, t.sa_off.p, t.sa_len.p};
     for (int i = 0; i < 9; i++) ptrs[i] = (uint64_t)reinterpret_cast<uintptr_t>(v[i]);

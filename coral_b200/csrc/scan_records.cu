@@ -358,7 +358,7 @@ __device__ __noinline__ uint32_t gen_next(uint32_t ctl, uint32_t s, const uint8_
 
 __global__ void __launch_bounds__(SC_WARPS * 32, 4)
 k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off, uint32_t n, int32_t min_del_len,
-               ScanCols o, ScanEvents ev, int32_t* __restrict__ status, unsigned int* __restrict__ queue) {
+               ScanCols o, ScanEvents ev, int32_t* __restrict__ status, unsigned int* __restrict__ queue, uint32_t write_aux) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t lane = lane_id();
     const uint32_t warp = threadIdx.x >> 5;
@@ -441,7 +441,9 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
                 o.ncig[rec] = n_cig;
                 o.name_lo[rec] = h1;
                 o.name_hi[rec] = h2;
-                o.sa_off[rec] = 0; o.sa_len[rec] = 0; o.nm[rec] = 0;     // overwritten by the aux walk
+                // overwritten by the aux walk; in the asynchronous mode the pre-scan owns these columns and fetch may
+                // already be reading them, so they are left alone
+                if (write_aux) { o.sa_off[rec] = 0; o.sa_len[rec] = 0; o.nm[rec] = 0; }
                 if (rec_bad) atomicAdd(&status[1], 1);
             }
             __syncwarp();
@@ -616,7 +618,7 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
         }
 
         // ---- aux block -------------------------------------------------------------------------------------------
-        if (fl & (SF_AUX | SF_AUXG)) {
+        if ((fl & (SF_AUX | SF_AUXG)) && write_aux) {
             const uint32_t rec_size = rc1.y, aux_beg = rc1.x + rc0.y;
             AuxOut a;
             if (fl & SF_AUX) {
@@ -657,10 +659,65 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
     }
 }
 
+// Pre-scan of the asynchronous mode: the columns `fetch` needs (core fields, name hash, SA / NM location) for every
+// record, from the record core, the read name and the aux block only — a few hundred bytes per record, so it is done
+// in about a millisecond even over PCIe, and fetch + the host steps that follow it can run while the full scan is
+// still pulling CIGAR and SEQ bytes.  Same values as k_scan_records writes into the same columns.
+__global__ void k_prescan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off, uint32_t n, ScanCols o,
+                                  int32_t* __restrict__ status) {
+    const uint32_t lane = lane_id();
+    const uint32_t nw = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t rec = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; rec < n; rec += nw) {
+        const uint64_t o0 = __ldg(off + rec), o1 = __ldg(off + rec + 1);
+        const uint8_t* r = recs + o0;
+        const uint32_t len16 = (uint32_t)(o1 - o0);
+        const uint32_t cw = lane < 9 ? __ldg(reinterpret_cast<const uint32_t*>(r) + lane) : 0u;
+        const uint32_t block_size = __shfl_sync(FULL_MASK, cw, 0);
+        const uint32_t tid = __shfl_sync(FULL_MASK, cw, 1);
+        const uint32_t pos_ = __shfl_sync(FULL_MASK, cw, 2);
+        const uint32_t w3 = __shfl_sync(FULL_MASK, cw, 3), w4 = __shfl_sync(FULL_MASK, cw, 4);
+        uint32_t l_seq = __shfl_sync(FULL_MASK, cw, 5);
+        const uint32_t l_name = w3 & 255u;
+        uint32_t n_cig = w4 & 0xffffu;
+        const uint32_t flag = w4 >> 16;
+        const uint64_t seq_end = 36ull + l_name + 4ull * n_cig + ((uint64_t)l_seq + 1) / 2;
+        const uint64_t aux_beg = seq_end + l_seq, rec_size = 4ull + block_size;
+        const bool rec_bad = aux_beg > rec_size || rec_size > len16;     // the framing test of gen_next
+        if (rec_bad) { n_cig = 0; l_seq = 0; }
+        const uint32_t nl = (l_name && !rec_bad) ? l_name - 1 : 0;
+        uint64_t h1 = 0, h2 = 0;
+        for (uint32_t i = lane; i < nl; i += 32) {
+            const uint32_t b = r[36 + i];
+            h1 += hterm1(i, b);
+            h2 += hterm2(i, b);
+        }
+        h1 = warp_sum_u64(h1) + mix64(nl);
+        h2 = warp_sum_u64(h2) + mix64(nl ^ 0xABCDull);
+        AuxOut a{0, 0, 0, 0, 0};
+        if (!rec_bad && aux_beg < rec_size) a = aux_walk_global(r + aux_beg, r + rec_size, (uint32_t)aux_beg, lane);
+        if (lane == 0) {
+            o.tid[rec] = (int32_t)tid;
+            o.pos[rec] = (int32_t)pos_;
+            o.flag_mapq[rec] = flag | (((w3 >> 8) & 255u) << 16);
+            o.lseq[rec] = l_seq;
+            o.ncig[rec] = n_cig;
+            o.name_lo[rec] = h1;
+            o.name_hi[rec] = h2;
+            o.sa_off[rec] = a.have_sa ? a.sa_off : 0u;
+            o.sa_len[rec] = a.sa_len;
+            o.nm[rec] = a.nm;
+            if (rec_bad) atomicAdd(&status[1], 1);
+            if (a.bad) atomicAdd(&status[0], 1);
+        }
+    }
+}
+
 }  // namespace coral
 
-int coral_run_scan(coral_ctx* ctx) {
-    using namespace coral;
+namespace {
+using namespace coral;
+
+int scan_ensure_tables(coral_ctx* ctx) {
     const int64_t n = ctx->nrec;
     RecordTable& t = ctx->rt;
     const size_t n4 = (size_t)(n > 0 ? n : 1) * 4, n8 = (size_t)(n > 0 ? n : 1) * 8;
@@ -669,27 +726,126 @@ int coral_run_scan(coral_ctx* ctx) {
     for (DevBuf* b : c4) CORAL_CUDA(ctx, b->ensure(n4));
     CORAL_CUDA(ctx, t.name_lo.ensure(n8));
     CORAL_CUDA(ctx, t.name_hi.ensure(n8));
-    CORAL_CUDA(ctx, ctx->status.ensure(64));
+    CORAL_CUDA(ctx, ctx->scan_status.ensure(64));
     CORAL_CUDA(ctx, ctx->gaps.counter.ensure(16));
     if (ctx->gaps.capacity == 0) ctx->gaps.capacity = std::max<int64_t>(1 << 16, n / 2);
+    GapEvents& g = ctx->gaps;
+    CORAL_CUDA(ctx, g.rec.ensure((size_t)g.capacity * 4));
+    CORAL_CUDA(ctx, g.k.ensure((size_t)g.capacity * 4));
+    CORAL_CUDA(ctx, g.next_start.ensure((size_t)g.capacity * 4));
+    CORAL_CUDA(ctx, g.prev_end.ensure((size_t)g.capacity * 4));
     static bool attr_set = false;
     if (!attr_set) {
         CORAL_CUDA(ctx, cudaFuncSetAttribute(k_scan_records, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SC_SMEM_TOTAL));
         attr_set = true;
     }
+    return CORAL_OK;
+}
+
+ScanCols scan_cols(coral_ctx* ctx) {
+    RecordTable& t = ctx->rt;
+    return ScanCols{t.tid.as<int32_t>(), t.pos.as<int32_t>(), t.endpos.as<int32_t>(), t.fbs.as<int32_t>(),
+                    t.lbe.as<int32_t>(), t.nm.as<int32_t>(), t.flag_mapq.as<uint32_t>(), t.lseq.as<uint32_t>(),
+                    t.ncig.as<uint32_t>(), t.infer.as<uint32_t>(), t.mbases.as<uint32_t>(), t.nonacgt.as<uint32_t>(),
+                    t.sa_off.as<uint32_t>(), t.sa_len.as<uint32_t>(), t.ngap.as<uint32_t>(),
+                    t.name_lo.as<uint64_t>(), t.name_hi.as<uint64_t>()};
+}
+
+// counters + status of a finished scan -> CORAL_OK, an error, or 1 = gap-event buffer too small (capacity was raised)
+int scan_verdict(coral_ctx* ctx, cudaStream_t st) {
+    GapEvents& g = ctx->gaps;
+    unsigned long long total = 0;
+    int32_t sw[2] = {0, 0};
+    CORAL_CUDA(ctx, cudaMemcpyAsync(&total, g.counter.p, 8, cudaMemcpyDeviceToHost, st));
+    CORAL_CUDA(ctx, cudaMemcpyAsync(sw, ctx->scan_status.p, 8, cudaMemcpyDeviceToHost, st));
+    CORAL_CUDA(ctx, cudaStreamSynchronize(st));
+    if (sw[1] != 0) {
+        ctx->err = "record framing inconsistent with the record core in " + std::to_string(sw[1]) + " record(s)";
+        return CORAL_E_FORMAT;
+    }
+    if (sw[0] != 0) {
+        ctx->err = "malformed aux field in " + std::to_string(sw[0]) + " record(s)";
+        return CORAL_E_FORMAT;
+    }
+    if ((int64_t)total <= g.capacity) {
+        g.n = (int64_t)total;
+        return CORAL_OK;
+    }
+    g.capacity = (int64_t)total + (int64_t)total / 8 + 1024;  // rescan with room for every event
+    return 1;
+}
+
+}  // namespace
+
+// Asynchronous form of the load-time scan (CORAL_RECORDS_HOST_MAPPED_ASYNC): the pre-scan runs to completion, the
+// full scan is left running on its own stream with one block per SM (the link, not the SMs, bounds it, and the
+// kernels of fetch need room next to it); coral_wait_scan() joins it.
+int coral_start_scan_async(coral_ctx* ctx) {
+    using namespace coral;
+    const int64_t n = ctx->nrec;
+    CORAL_TRY(scan_ensure_tables(ctx));
+    if (!ctx->scan_stream) CORAL_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->scan_stream, cudaStreamNonBlocking));
+    GapEvents& g = ctx->gaps;
+    CORAL_CUDA(ctx, cudaMemsetAsync(g.counter.p, 0, 16, ctx->stream));
+    CORAL_CUDA(ctx, cudaMemsetAsync(ctx->scan_status.p, 0, 64, ctx->stream));
+    if (n == 0) { g.n = 0; return CORAL_OK; }
+    ScanCols o = scan_cols(ctx);
+    const int pre_blocks = (int)std::min<int64_t>((n + 7) / 8, (int64_t)ctx->sm_count * 8);
+    k_prescan_records<<<pre_blocks, 256, 0, ctx->stream>>>(ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, o,
+                                                          ctx->scan_status.as<int32_t>());
+    ctx->n_launches++;
+    CORAL_CUDA(ctx, cudaGetLastError());
+    int32_t sw[2] = {0, 0};
+    CORAL_CUDA(ctx, cudaMemcpyAsync(sw, ctx->scan_status.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CORAL_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (sw[1] != 0) {
+        ctx->err = "record framing inconsistent with the record core in " + std::to_string(sw[1]) + " record(s)";
+        return CORAL_E_FORMAT;
+    }
+    if (sw[0] != 0) {
+        ctx->err = "malformed aux field in " + std::to_string(sw[0]) + " record(s)";
+        return CORAL_E_FORMAT;
+    }
+    ScanEvents e{g.rec.as<uint32_t>(), g.k.as<uint32_t>(), g.next_start.as<int32_t>(), g.prev_end.as<int32_t>(),
+                 g.counter.as<unsigned long long>(), g.capacity};
+    const int64_t want = (n + SC_WARPS - 1) / SC_WARPS;
+    const int blocks = (int)std::min<int64_t>(want, (int64_t)ctx->sm_count);
+    if (!ctx->ev_beg[CORAL_STAGE_SCAN]) { cudaEventCreate(&ctx->ev_beg[CORAL_STAGE_SCAN]); cudaEventCreate(&ctx->ev_end[CORAL_STAGE_SCAN]); }
+    cudaEventRecord(ctx->ev_beg[CORAL_STAGE_SCAN], ctx->scan_stream);
+    k_scan_records<<<blocks, SC_WARPS * 32, SC_SMEM_TOTAL, ctx->scan_stream>>>(
+        ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, ctx->prm.min_del_len, o, e, ctx->scan_status.as<int32_t>(),
+        reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1), 0u);
+    cudaEventRecord(ctx->ev_end[CORAL_STAGE_SCAN], ctx->scan_stream);
+    ctx->ev_valid[CORAL_STAGE_SCAN] = true;
+    ctx->n_launches++;
+    CORAL_CUDA(ctx, cudaGetLastError());
+    ctx->scan_pending = true;
+    return CORAL_OK;
+}
+
+extern "C" int coral_wait_scan(coral_ctx* ctx) {
+    if (!ctx) return CORAL_E_ARG;
+    if (!ctx->scan_pending) return CORAL_OK;
+    cudaSetDevice(ctx->device);
+    ctx->scan_pending = false;
+    const int v = scan_verdict(ctx, ctx->scan_stream);
+    if (v == 1) return coral_run_scan(ctx);      // more gap events than the buffer held: synchronous rescan with room
+    return v;
+}
+
+int coral_run_scan(coral_ctx* ctx) {
+    using namespace coral;
+    const int64_t n = ctx->nrec;
+    if (ctx->scan_pending) {                    // join an asynchronous scan before starting over
+        ctx->scan_pending = false;
+        CORAL_CUDA(ctx, cudaStreamSynchronize(ctx->scan_stream));
+    }
     for (int attempt = 0; attempt < 2; attempt++) {
+        CORAL_TRY(scan_ensure_tables(ctx));
         GapEvents& g = ctx->gaps;
-        CORAL_CUDA(ctx, g.rec.ensure((size_t)g.capacity * 4));
-        CORAL_CUDA(ctx, g.k.ensure((size_t)g.capacity * 4));
-        CORAL_CUDA(ctx, g.next_start.ensure((size_t)g.capacity * 4));
-        CORAL_CUDA(ctx, g.prev_end.ensure((size_t)g.capacity * 4));
         CORAL_CUDA(ctx, cudaMemsetAsync(g.counter.p, 0, 16, ctx->stream));     // [0] event count, [1] record queue
-        CORAL_CUDA(ctx, cudaMemsetAsync(ctx->status.p, 0, 64, ctx->stream));
-        ScanCols o{t.tid.as<int32_t>(), t.pos.as<int32_t>(), t.endpos.as<int32_t>(), t.fbs.as<int32_t>(),
-                   t.lbe.as<int32_t>(), t.nm.as<int32_t>(), t.flag_mapq.as<uint32_t>(), t.lseq.as<uint32_t>(),
-                   t.ncig.as<uint32_t>(), t.infer.as<uint32_t>(), t.mbases.as<uint32_t>(), t.nonacgt.as<uint32_t>(),
-                   t.sa_off.as<uint32_t>(), t.sa_len.as<uint32_t>(), t.ngap.as<uint32_t>(),
-                   t.name_lo.as<uint64_t>(), t.name_hi.as<uint64_t>()};
+        CORAL_CUDA(ctx, cudaMemsetAsync(ctx->scan_status.p, 0, 64, ctx->stream));
+        ScanCols o = scan_cols(ctx);
         ScanEvents e{g.rec.as<uint32_t>(), g.k.as<uint32_t>(), g.next_start.as<int32_t>(), g.prev_end.as<int32_t>(),
                      g.counter.as<unsigned long long>(), g.capacity};
         if (n > 0) {
@@ -700,30 +856,14 @@ int coral_run_scan(coral_ctx* ctx) {
             const int blocks = (int)std::min<int64_t>(want, (int64_t)ctx->sm_count * per_sm);   // persistent: one wave
             ctx->stage_begin(CORAL_STAGE_SCAN);
             k_scan_records<<<blocks, SC_WARPS * 32, SC_SMEM_TOTAL, ctx->stream>>>(
-                ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, ctx->prm.min_del_len, o, e, ctx->status.as<int32_t>(),
-                reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1));
+                ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, ctx->prm.min_del_len, o, e, ctx->scan_status.as<int32_t>(),
+                reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1), 1u);
             ctx->stage_end(CORAL_STAGE_SCAN);
             ctx->n_launches++;
             CORAL_CUDA(ctx, cudaGetLastError());
         }
-        unsigned long long total = 0;
-        int32_t st[2] = {0, 0};
-        CORAL_CUDA(ctx, cudaMemcpyAsync(&total, g.counter.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-        CORAL_CUDA(ctx, cudaMemcpyAsync(st, ctx->status.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-        CORAL_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        if (st[1] != 0) {
-            ctx->err = "record framing inconsistent with the record core in " + std::to_string(st[1]) + " record(s)";
-            return CORAL_E_FORMAT;
-        }
-        if (st[0] != 0) {
-            ctx->err = "malformed aux field in " + std::to_string(st[0]) + " record(s)";
-            return CORAL_E_FORMAT;
-        }
-        if ((int64_t)total <= g.capacity) {
-            g.n = (int64_t)total;
-            return CORAL_OK;
-        }
-        g.capacity = (int64_t)total + (int64_t)total / 8 + 1024;  // rescan with room for every event
+        const int v = scan_verdict(ctx, ctx->stream);
+        if (v != 1) return v;
     }
     ctx->err = "gap-event buffer overflow after rescan";
     return CORAL_E_NOMEM;

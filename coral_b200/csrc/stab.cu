@@ -166,6 +166,7 @@ extern "C" int coral_concordant(coral_ctx* c, const int32_t* tid, const int32_t*
     using namespace coral;
     if (!c || n_edges < 0 || n_rbps < 0) return CORAL_E_ARG;
     if (!c->loaded || c->rows_only) { c->err = "coral_concordant before coral_load_records"; return CORAL_E_STATE; }
+    CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
     c->stab_n = 0; c->stab_valid = false;
     if (n_union_rows) *n_union_rows = 0;

@@ -42,6 +42,7 @@ extern "C" int coral_get_record_table(coral_ctx* c, int32_t* tid, int32_t* pos, 
                                       int64_t* aligned_bases, int64_t* non_acgt) {
     if (!c) return CORAL_E_ARG;
     if (!c->loaded) { c->err = "no records loaded"; return CORAL_E_STATE; }
+    CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
     const int64_t n = c->nrec;
     std::vector<uint8_t> tmp;

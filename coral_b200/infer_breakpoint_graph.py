@@ -29,12 +29,17 @@ def _gc_paused(fn):
 class bam_to_breakpoint_nanopore(HostSteps):
     _ops = breakpoint_utilities
 
+    _normal_pending = None      # (class default: _init_state assigns the properties before __init__ sets it)
+
     def __init__(self, lr_bamfile, seedfile, device=0, n_threads=0, records=None, placement="auto"):
         """`records` (optional): an object with .references, .rec (uint8 host buffer of framed records), .rec_off and
         .query_name(i) — lets a caller that already holds decompressed records skip the BAM file.
         `placement`: "copy" (records copied to HBM), "mapped" (kernels read the page-locked host buffer in place; the
-        scan runs once per BAM, so only the fields it needs cross PCIe) or "auto" (mapped when the buffer has the
-        64 bytes of slack that mode needs)."""
+        scan runs once per BAM, so only the fields it needs cross PCIe), "mapped_async" (as "mapped", and the
+        constructor returns after a pre-scan of the fields `fetch` needs: `fetch` and `hash_alignment_to_seg` then run
+        while the full scan is still pulling CIGAR / SEQ bytes over the link; `read_cns`'s coverage sum is evaluated
+        when `normal_cov` / `min_cluster_cutoff` are first read) or "auto" (mapped_async on one GPU when the buffer
+        has the 64 bytes of slack the mapped modes need, else copy)."""
         self._init_state()
         self.lr_bamfh = records if records is not None else _abi.BamFile(lr_bamfile, n_threads)   # replaces pysam (ibg:65)
         self._ctx = _abi.Context(device)
@@ -45,6 +50,10 @@ class bam_to_breakpoint_nanopore(HostSteps):
         if placement == "auto":
             nb = int(rec_off[-1]) if len(rec_off) else 0
             placement = "mapped" if nb > 0 and getattr(rec, "nbytes", 0) + slack >= nb + 64 else "copy"
+            if placement == "mapped" and getattr(self, "_comm", None) is None:
+                placement = "mapped_async"       # one GPU: fetch and the host steps after it run next to the scan
+        self._scan_async = placement == "mapped_async"
+        self._normal_pending = None              # read_cns's coverage call, deferred while the scan is still running
         self._ctx.load_records(rec, rec_off, placement=placement, slack=slack)
         self._tid = {c: i for i, c in enumerate(self.lr_bamfh.references)}
         self._name_rec = {}     # read name -> index of one record carrying it (for concordant-edge rbps)
@@ -64,10 +73,41 @@ class bam_to_breakpoint_nanopore(HostSteps):
         self._parse_cns(cns)
         segs, total = self._median_cn_segments()
         order = sorted(range(len(segs)), key=lambda k: (self._tid[segs[k][0]], segs[k][1]))
-        nnc = self._coverage_sum([segs[k] for k in order])
-        self.normal_cov = nnc * 1.0 / total
-        logging.info(_t() + "LR normal cov = %f." % (self.normal_cov))
-        self.min_cluster_cutoff = max(self.min_cluster_cutoff, self.min_bp_cov_factor * self.normal_cov)
+        self._normal_pending = ([segs[k] for k in order], total)
+        if not self._scan_async:
+            self._resolve_normal_cov()
+
+    def _resolve_normal_cov(self):
+        """ibg:129-135.  With an asynchronous scan this runs when normal_cov / min_cluster_cutoff are first read (the
+        coverage sum needs the whole scan; fetch and hash_alignment_to_seg, which the reference calls next, do not)."""
+        pending, self._normal_pending = self._normal_pending, None
+        if pending is None:
+            return
+        segs, total = pending
+        nnc = self._coverage_sum(segs)
+        self._normal_cov = nnc * 1.0 / total
+        logging.info(_t() + "LR normal cov = %f." % (self._normal_cov))
+        self._min_cluster_cutoff = max(self._min_cluster_cutoff, self.min_bp_cov_factor * self._normal_cov)
+
+    @property
+    def normal_cov(self):
+        if self._normal_pending is not None:
+            self._resolve_normal_cov()
+        return self._normal_cov
+
+    @normal_cov.setter
+    def normal_cov(self, v):
+        self._normal_cov = v
+
+    @property
+    def min_cluster_cutoff(self):
+        if self._normal_pending is not None:
+            self._resolve_normal_cov()
+        return self._min_cluster_cutoff
+
+    @min_cluster_cutoff.setter
+    def min_cluster_cutoff(self, v):
+        self._min_cluster_cutoff = v
 
     def _coverage_sum(self, segs):
         """Sum of count_coverage over inclusive segments; overlapping requests are issued in disjoint batches."""
@@ -436,8 +476,14 @@ class bam_to_breakpoint_nanopore(HostSteps):
         return HostSteps.compute_path_constraints(self)
 
     def closebam(self):
+        self._ctx.close()            # first: joins a scan that may still be reading the record buffer
         self.lr_bamfh.close()
-        self._ctx.close()
+
+    def __del__(self):
+        try:                         # an engine dropped without closebam(): the ctx goes before the records it reads
+            self._ctx.close()
+        except Exception:
+            pass
 
 
 BamToBreakpointNanopore = bam_to_breakpoint_nanopore   # name used by BASELINE.json's north_star

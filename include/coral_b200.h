@@ -95,6 +95,13 @@ const uint64_t* coral_bam_offsets(const coral_bam* b);                     /* n_
 #define CORAL_RECORDS_HOST_COPY 0
 #define CORAL_RECORDS_DEVICE 1
 #define CORAL_RECORDS_HOST_MAPPED 2
+/*   CORAL_RECORDS_HOST_MAPPED_ASYNC  as HOST_MAPPED, but the call returns once a pre-scan (record core, read name and
+ *                              aux block only: what coral_fetch needs) is done; the full scan keeps running on its
+ *                              own stream while the caller already runs coral_fetch / coral_candidates_* /
+ *                              coral_cluster_call / coral_cn_segment_index.  Every other entry point joins the scan
+ *                              first (coral_wait_scan), where its errors (malformed record -> CORAL_E_FORMAT) surface. */
+#define CORAL_RECORDS_HOST_MAPPED_ASYNC 3
+int coral_wait_scan(coral_ctx* ctx);
 int coral_load_records(coral_ctx* ctx, const uint8_t* recs, uint64_t nbytes, const uint64_t* offsets,
                        int64_t n_records, const uint64_t* global_ordinal, int on_device);
 int64_t coral_n_records(const coral_ctx* ctx);

@@ -53,8 +53,11 @@ def main():
             eng = util.oracle_engine(bam, seed)
         else:
             from coral_b200.infer_breakpoint_graph import bam_to_breakpoint_nanopore
-            eng = bam_to_breakpoint_nanopore(bam, seed)
-        st = util.run_pipeline(eng, cn_seg)
+            eng = bam_to_breakpoint_nanopore(bam, seed, placement={"cuda": "auto", "cuda-lazy": "auto", "cuda-sync": "mapped",
+                                                                    "cuda-copy": "copy"}[kind])
+            if kind in ("cuda", "cuda-lazy"):
+                assert eng._scan_async           # BamFile buffers carry the slack: the asynchronous placement is in use
+        st = util.run_pipeline(eng, cn_seg, defer_cov=(kind == "cuda-lazy"))
     with open(out, "w") as fp:
         json.dump(st, fp)
 

@@ -71,10 +71,18 @@ def _ctx(rec, off, placement="copy"):
     from coral_b200 import _abi
     c = _abi.Context(0)
     c.set_references([r[0] for r in REFS])
-    if placement == "mapped":
+    if placement.startswith("mapped"):
         buf = np.zeros(len(rec) + 64, np.uint8)
         buf[:len(rec)] = rec
-        c.load_records(buf[:len(rec)], off, placement="mapped", slack=64)
+        c.load_records(buf[:len(rec)], off, placement=placement, slack=64)
+        if placement == "mapped_async":
+            # what the pre-scan wrote (the columns fetch reads while the full scan is in flight) against what the full
+            # scan writes into the same columns; fetch must not wait for the scan and must give the same table
+            f0 = c.fetch()
+            c.wait_scan()
+            f1 = c.fetch()
+            for k in f0:
+                assert np.array_equal(f0[k], f1[k]), k
     else:
         c.load_records(rec, off)
     return c
@@ -86,7 +94,7 @@ def _table_matches(t, ora):
         assert np.array_equal(t[k], want), k
 
 
-@pytest.mark.parametrize("placement", ["copy", "mapped"])
+@pytest.mark.parametrize("placement", ["copy", "mapped", "mapped_async"])
 def test_edge_records_scan_table(built_lib, edge, placement):
     c = _ctx(edge["rec"], edge["off"], placement)
     ora = edge["ora"]

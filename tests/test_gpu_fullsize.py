@@ -19,12 +19,12 @@ def _load(cfg, data, placement):
     from coral_b200 import _abi
     c = _abi.Context(0)
     c.set_references([r[0] for r in cfg.refs])
-    if placement == "mapped":
+    if placement.startswith("mapped"):
         nb = int(data.rec_off[-1])
         buf = np.empty(nb + 64, np.uint8)
         buf[:nb] = data.rec[:nb]
         buf[nb:] = 0
-        c.load_records(buf[:nb], data.rec_off, placement="mapped", slack=64)
+        c.load_records(buf[:nb], data.rec_off, placement=placement, slack=64)
     else:
         c.load_records(data.rec, data.rec_off)
     return c
@@ -104,6 +104,19 @@ def test_full_size_properties(built_lib, c2_full):
     for k in ("read_first_rec", "read_len", "read_status", "aln_ptr", "qs", "qe", "tid", "rstart", "rend", "strand", "mapq", "nm"):
         assert np.array_equal(f[k], fm[k]), k
     assert (fm["nm_sum"], fm["nm_sumsq"], fm["nm_n"]) == (f["nm_sum"], f["nm_sumsq"], f["nm_n"])
+    m.close()
+    # asynchronous placement: fetch right after the pre-scan, while the full scan is still pulling 5.5 GB over the link
+    m = _load(cfg, data, "mapped_async")
+    fa = m.fetch()
+    for k in ("read_first_rec", "read_len", "read_status", "aln_ptr", "qs", "qe", "tid", "rstart", "rend", "strand", "mapq", "nm"):
+        assert np.array_equal(f[k], fa[k]), k
+    assert (fa["nm_sum"], fa["nm_sumsq"], fa["nm_n"]) == (f["nm_sum"], f["nm_sumsq"], f["nm_n"])
+    ta = m.record_table()                      # joins the scan
+    for k in t:
+        assert np.array_equal(t[k], ta[k]), k
+    ka = m.record_keys()
+    for k in keys:
+        assert np.array_equal(keys[k], ka[k]), k
     m.close(); c.close()
 
 

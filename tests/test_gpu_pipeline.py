@@ -18,3 +18,17 @@ def test_cuda_pipeline_matches_reference(built_lib, case, tmp_path_factory):
     assert G.compare_states(got, gold["stages"]) == []
     for g_got, g_ref in zip(got["assign_cov"]["graphs"], gold["stages"]["assign_cov"]["graphs"]):
         assert g_got["graph_txt"] == g_ref["graph_txt"]          # byte-identical graph.txt
+
+
+@pytest.mark.parametrize("case,kind", [("c2_small", "cuda-lazy"), ("c4_small", "cuda-lazy"), ("c3_small", "cuda-lazy"),
+                                       ("c5_mini", "cuda-lazy"), ("c4_small", "cuda-sync"), ("c3_small", "cuda-copy")])
+def test_cuda_pipeline_placements(built_lib, case, kind, tmp_path_factory):
+    """The same parity with the other record placements: "cuda-lazy" = asynchronous scan with fetch and
+    hash_alignment_to_seg running while it is in flight (normal_cov first read when find_amplicon_intervals needs
+    it), "cuda-sync" = mapped placement with the scan joined at load, "cuda-copy" = records copied to HBM."""
+    gold = G.load_golden(case)
+    cfg, data, paths = G.golden_dataset(case, tmp_path_factory)
+    got = G.run_engine(kind, paths, tmp_path_factory)
+    assert G.compare_states(got, gold["stages"]) == []
+    for g_got, g_ref in zip(got["assign_cov"]["graphs"], gold["stages"]["assign_cov"]["graphs"]):
+        assert g_got["graph_txt"] == g_ref["graph_txt"]

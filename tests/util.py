@@ -25,15 +25,20 @@ def oracle_engine(bam, seed):
     return OracleEngine(bam, seed)
 
 
-def run_pipeline(eng, cn_seg, stop_after=None):
-    """Drive an engine in the reference's call order; returns canonical per-stage state (ref_runner format)."""
+def run_pipeline(eng, cn_seg, stop_after=None, defer_cov=False):
+    """Drive an engine in the reference's call order; returns canonical per-stage state (ref_runner format).
+    defer_cov: do not look at normal_cov before find_amplicon_intervals needs it — with the asynchronous scan of the
+    product, fetch and hash_alignment_to_seg then really run while the record scan is still in flight."""
     from oracle.ref_runner import canon_chimeric, _bp_rows
     st = {}
     eng.read_cns(cn_seg)
-    st["read_cns"] = {"normal_cov": eng.normal_cov, "min_cluster_cutoff": eng.min_cluster_cutoff}
+    if not defer_cov:
+        st["read_cns"] = {"normal_cov": eng.normal_cov, "min_cluster_cutoff": eng.min_cluster_cutoff}
     eng.fetch()
     st["fetch"] = {"chimeric": canon_chimeric(eng.chimeric_alignments), "nm_stats": list(eng.nm_stats)}
     eng.hash_alignment_to_seg()
+    if defer_cov:
+        st["read_cns"] = {"normal_cov": eng.normal_cov, "min_cluster_cutoff": eng.min_cluster_cutoff}
     eng.find_amplicon_intervals()
     st["find_amplicon_intervals"] = {
         "amplicon_intervals": [list(a) for a in eng.amplicon_intervals],
