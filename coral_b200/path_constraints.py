@@ -11,6 +11,8 @@ step — every record of the amplicon intervals mapped onto its run of sequence 
 back here as distinct ``(first edge, last edge)`` runs to be spelled out by ``sequence_run_to_path``.
 """
 
+import bisect
+
 edge_type_to_index = {'s': 0, 'c': 1, 'd': 2}      # slot of each edge kind in g.nodes[node] (reference :7)
 
 
@@ -42,11 +44,36 @@ def valid_path(g, path):
 
 
 # ---- shared pieces ---------------------------------------------------------------------------------------------
+def _edge_index(g):
+    """Per contig: (starts, ends, ids) of the sequence edges by start, when ends then ascend too (disjoint edges, what
+    build_graph makes); None for a contig whose edges overlap.  Rebuilt when the edge list changes length."""
+    cache = getattr(g, "_se_lookup", None)
+    if cache is None or cache[0] != len(g.sequence_edges):
+        by_chr = {}
+        for k, e in enumerate(g.sequence_edges):
+            by_chr.setdefault(e[0], []).append((e[1], k, e[2]))
+        table = {}
+        for c, rows in by_chr.items():
+            rows.sort(key=lambda r: r[0])                     # stable: equal starts keep edge-id order
+            ends = [r[2] for r in rows]
+            ok = all(ends[i] < ends[i + 1] for i in range(len(ends) - 1))
+            table[c] = ([r[0] for r in rows], ends, [r[1] for r in rows]) if ok else None
+        cache = (len(g.sequence_edges), table)
+        g._se_lookup = cache
+    return cache[1]
+
+
 def _touching(g, chrom, lo, hi):
     """Sequence-edge ids with interval_overlap([chrom, lo, hi], edge) (breakpoint_utilities.py:11-15), by edge start."""
-    ids = [k for k, e in enumerate(g.sequence_edges) if e[0] == chrom and lo <= e[2] and e[1] <= hi]
-    ids.sort(key=lambda k: g.sequence_edges[k][1])
-    return ids
+    idx = _edge_index(g).get(chrom, ())
+    if idx is None:       # overlapping edges on this contig: the literal scan
+        ids = [k for k, e in enumerate(g.sequence_edges) if e[0] == chrom and lo <= e[2] and e[1] <= hi]
+        ids.sort(key=lambda k: g.sequence_edges[k][1])
+        return ids
+    if not idx:
+        return []
+    starts, ends, ids = idx
+    return ids[bisect.bisect_left(ends, lo):bisect.bisect_right(starts, hi)]
 
 
 def _shared(g, k, lo, hi):

@@ -27,10 +27,13 @@ class PathConstraintSteps(object):
         if not (len(path) > 5 and pc.valid_path(self.lr_graph[amplicon_idx], path)):
             return
         paths, counts, labels = self.path_constraints[amplicon_idx]
+        where = self._subpath_index.setdefault(amplicon_idx, {})       # tuple(path) -> position, in step with `paths`
         for cand in (path, path[::-1]):
-            if cand in paths:
-                counts[paths.index(cand)] += count
+            k = where.get(tuple(cand))
+            if k is not None:
+                counts[k] += count
                 return
+        where[tuple(path)] = len(paths)
         paths.append(path)
         counts.append(count)
         labels.append(amp_label)
@@ -148,6 +151,7 @@ class PathConstraintSteps(object):
 
     # ---- ibg:1059-1323 ---------------------------------------------------------------------------------------------
     def compute_path_constraints(self):
+        self._subpath_index = {}
         for amplicon_idx, g in enumerate(self.lr_graph):
             self.path_constraints[amplicon_idx] = [[], [], []]
             self.longest_path_constraints[amplicon_idx] = [[], [], []]
