@@ -325,6 +325,7 @@ extern "C" int coral_candidates_l(coral_ctx* c, const int32_t* tid, const int32_
     CORAL_CUDA(c, c->s1.ensure((size_t)(nr + 1) * 8 + 16));
     uint32_t* cnt = c->s1.as<uint32_t>();
     uint32_t* ptr = cnt + nr + 1;
+    CORAL_CUDA(c, c->status.ensure(64));
     CORAL_CUDA(c, cudaMemsetAsync(c->status.p, 0, 64, c->stream));
     CandCols none{};
     LAUNCH_1D(k_align2bp_l<false>, nr, nr, V, I, c->d_chr_rank.as<int32_t>(), c->prm.min_bp_match_cutoff, c->prm.min_mapq,
@@ -433,6 +434,7 @@ extern "C" int coral_candidates_pair(coral_ctx* c, const uint32_t* reads, int64_
     uint32_t* ptr = cnt + n_sel + 1;
     uint32_t* d_sel = ptr + n_sel + 1;
     CORAL_TRY(h2d(c, d_sel, reads, (size_t)n_sel));
+    CORAL_CUDA(c, c->status.ensure(64));
     CORAL_CUDA(c, cudaMemsetAsync(c->status.p, 0, 64, c->stream));
     CandCols none{};
     LAUNCH_1D(k_align2bp_pair<false>, n_sel, n_sel, d_sel, V, I, c->d_chr_rank.as<int32_t>(), c->prm.min_bp_match_cutoff,

@@ -727,6 +727,7 @@ int scan_ensure_tables(coral_ctx* ctx) {
     CORAL_CUDA(ctx, t.name_lo.ensure(n8));
     CORAL_CUDA(ctx, t.name_hi.ensure(n8));
     CORAL_CUDA(ctx, ctx->scan_status.ensure(64));
+    CORAL_CUDA(ctx, ctx->status.ensure(64));       // the status words of the other entry points
     CORAL_CUDA(ctx, ctx->gaps.counter.ensure(16));
     if (ctx->gaps.capacity == 0) ctx->gaps.capacity = std::max<int64_t>(1 << 16, n / 2);
     GapEvents& g = ctx->gaps;
