@@ -40,6 +40,7 @@ void coral_destroy(coral_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->scan_stream) { cudaStreamSynchronize(c->scan_stream); cudaStreamDestroy(c->scan_stream); }
+    if (c->scan_pending) coral_mem::scan_joined();
     c->scan_pending = false;
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->host_registered) cudaHostUnregister(c->host_registered);
@@ -108,6 +109,7 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     if (c->scan_pending) {                 // a previous asynchronous load is still scanning: join it first
         c->scan_pending = false;
         cudaStreamSynchronize(c->scan_stream);
+        coral_mem::scan_joined();
     }
     c->loaded = false;
     c->rows_only = false;

@@ -26,13 +26,32 @@
         if (r__ != CORAL_OK) return r__; \
     } while (0)
 
+// cudaFree waits for every kernel in flight on the device — including an asynchronous record scan, which is exactly
+// what the entry points running next to it must not wait for.  While such a scan is pending, freed blocks are parked
+// and released when it is joined.  (A ctx is single-threaded; the counters are only touched by asynchronous loads.)
+namespace coral_mem {
+inline int defer = 0;
+inline std::vector<void*> parked;
+inline void release(void* p) {
+    if (!p) return;
+    if (defer > 0) parked.push_back(p); else cudaFree(p);
+}
+inline void scan_started() { defer++; }
+inline void scan_joined() {
+    if (defer > 0 && --defer == 0) {
+        for (void* p : parked) cudaFree(p);
+        parked.clear();
+    }
+}
+}  // namespace coral_mem
+
 // Grow-only device buffer.
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
     cudaError_t ensure(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFree(p);
+        coral_mem::release(p);
         p = nullptr;
         size_t want = bytes + bytes / 8 + 256;
         cudaError_t e = cudaMalloc(&p, want);
@@ -40,7 +59,7 @@ struct DevBuf {
         return e;
     }
     void release() {
-        if (p) cudaFree(p);
+        coral_mem::release(p);
         p = nullptr;
         cap = 0;
     }

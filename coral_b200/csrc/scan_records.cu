@@ -821,6 +821,7 @@ int coral_start_scan_async(coral_ctx* ctx) {
     ctx->n_launches++;
     CORAL_CUDA(ctx, cudaGetLastError());
     ctx->scan_pending = true;
+    coral_mem::scan_started();
     return CORAL_OK;
 }
 
@@ -830,6 +831,7 @@ extern "C" int coral_wait_scan(coral_ctx* ctx) {
     cudaSetDevice(ctx->device);
     ctx->scan_pending = false;
     const int v = scan_verdict(ctx, ctx->scan_stream);
+    coral_mem::scan_joined();
     if (v == 1) return coral_run_scan(ctx);      // more gap events than the buffer held: synchronous rescan with room
     return v;
 }
@@ -839,7 +841,8 @@ int coral_run_scan(coral_ctx* ctx) {
     const int64_t n = ctx->nrec;
     if (ctx->scan_pending) {                    // join an asynchronous scan before starting over
         ctx->scan_pending = false;
-        CORAL_CUDA(ctx, cudaStreamSynchronize(ctx->scan_stream));
+        cudaStreamSynchronize(ctx->scan_stream);
+        coral_mem::scan_joined();
     }
     for (int attempt = 0; attempt < 2; attempt++) {
         CORAL_TRY(scan_ensure_tables(ctx));
