@@ -225,6 +225,17 @@ def combine_concordant(comm, n_edges, rows, rbps):
     return cnt, names
 
 
+def merge_path_rows(comm, iv, first, last):
+    """Concordant-read pass of compute_path_constraints across shards: every rank holds the rows (interval index, first
+    sequence edge, last sequence edge) of ITS records in (interval, file) order; ranks hold increasing file ranges, so
+    concatenating in rank order and stable-sorting by interval restores the reference's emission order
+    (ibg:1303-1310: interval list order, then file order).  -> (iv, first, last), the same on every rank."""
+    parts = comm.all_gather((np.asarray(iv, np.int64), np.asarray(first, np.int64), np.asarray(last, np.int64)))
+    iv = np.concatenate([p[0] for p in parts])
+    o = np.argsort(iv, kind="stable")
+    return iv[o], np.concatenate([p[1] for p in parts])[o], np.concatenate([p[2] for p in parts])[o]
+
+
 # ---- the engine --------------------------------------------------------------------------------------------------
 class _ShardView(object):
     """This rank's slice of a record set: the interface the drop-in class needs from its BAM handle."""
@@ -427,10 +438,8 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             keys = np.array([hash_of[nm] for nm in concordant_reads], np.int64).reshape(-1, 2)
             iv, first, last = self._path_rows(self.lr_graph[amplicon_idx], intervals, name_lo=keys[:, 0].view(np.uint64),
                                               name_hi=keys[:, 1].view(np.uint64))
-            parts = self._comm.all_gather((iv, first, last))
-            iv = np.concatenate([p[0] for p in parts])
-            o = np.argsort(iv, kind="stable")
-            return self._distinct_runs(np.concatenate([p[1] for p in parts])[o], np.concatenate([p[2] for p in parts])[o])
+            _, first, last = merge_path_rows(self._comm, iv, first, last)
+            return self._distinct_runs(first, last)
 
         def closebam(self):
             self._cctx.close()

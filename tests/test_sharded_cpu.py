@@ -236,9 +236,40 @@ def _gloo_msg_worker(rank, world, port, q):
         want = [("r%d_%d" % (rk, k), (k + rk) % 2, k, k, 0, 9, 60, rk, k) for rk in range(world) for k in range(3)]
         want.sort(key=lambda r: r[1])
         ok = ok and merged == want
+        # concordant-read rows of compute_path_constraints: (interval, file) order restored from per-rank rows
+        iv, first, last = _path_rows(rank)
+        m = sharded.merge_path_rows(comm, iv, first, last)
+        ok = ok and all(np.array_equal(a, b) for a, b in zip(m, _path_rows_whole(world)))
         q.put((rank, ok))
     finally:
         dist.destroy_process_group()
+
+
+def _path_rows(rank):
+    """Rows of rank `rank`: intervals 0..2, a few records each, edge runs that encode (interval, rank, k)."""
+    iv = np.repeat(np.arange(3), [2 + rank, 0 if rank == 1 else 3, 1])
+    k = np.arange(len(iv))
+    return iv, 100 * iv + 10 * rank, 100 * iv + 10 * rank + k
+
+
+def _path_rows_whole(world):
+    rows = [(int(i), int(f), int(l), r, n) for r in range(world) for n, (i, f, l) in enumerate(zip(*_path_rows(r)))]
+    rows.sort(key=lambda t: (t[0], t[3], t[4]))          # interval, then rank (= file) order, then row order
+    return tuple(np.array([t[c] for t in rows], np.int64) for c in range(3))
+
+
+@pytest.mark.parametrize("world", [1, 2, 3])
+def test_merge_path_rows_thread_ranks(world):
+    comms = sharded.ThreadComm.make(world)
+    out = [None] * world
+
+    def body(r):
+        out[r] = sharded.merge_path_rows(comms[r], *_path_rows(r))
+    th = [threading.Thread(target=body, args=(r,)) for r in range(world)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    for r in range(world):
+        assert all(np.array_equal(a, b) for a, b in zip(out[r], _path_rows_whole(world)))
 
 
 def test_gather_msgs_over_gloo_world2():
