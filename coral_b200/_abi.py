@@ -150,12 +150,13 @@ class Context(object):
         placement "copy": records are copied to HBM; "mapped": they stay in (page-locked) host memory and the
         kernels read them in place over PCIe — `rec` must then extend >= 64 bytes past rec_off[-1] and stay alive;
         "mapped_async": as "mapped", but the call returns after the pre-scan (what fetch needs) while the full scan keeps
-        running; entry points that need it join it (wait_scan)."""
+        running; entry points that need it join it (wait_scan); "mapped_lazy": only the pre-scan runs, the full scan
+        runs inside the first entry point that needs it."""
         rec = np.ascontiguousarray(rec, dtype=np.uint8)
         rec_off = np.ascontiguousarray(rec_off, dtype=np.uint64)
         n = len(rec_off) - 1
         go = None if global_ordinal is None else np.ascontiguousarray(global_ordinal, dtype=np.uint64)
-        mode = {"copy": 0, "mapped": 2, "mapped_async": 3}[placement]
+        mode = {"copy": 0, "mapped": 2, "mapped_async": 3, "mapped_lazy": 4}[placement]
         nbytes = int(rec_off[-1]) if n >= 0 and len(rec_off) else 0
         if mode >= 2:
             if rec.nbytes + int(slack) < nbytes + 64:     # `slack`: bytes the caller guarantees behind the view

@@ -129,7 +129,8 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     if (on_device == CORAL_RECORDS_DEVICE) {
         if (reinterpret_cast<uintptr_t>(recs) & 15) { c->err = "device record buffer must be 16-byte aligned"; return CORAL_E_ARG; }
         c->d_recs = recs;
-    } else if (on_device == CORAL_RECORDS_HOST_MAPPED || on_device == CORAL_RECORDS_HOST_MAPPED_ASYNC) {
+    } else if (on_device == CORAL_RECORDS_HOST_MAPPED || on_device == CORAL_RECORDS_HOST_MAPPED_ASYNC ||
+               on_device == CORAL_RECORDS_HOST_MAPPED_LAZY) {
         // Records stay in page-locked host memory; every kernel reads them in place over PCIe (the scan only
         // fetches the fields it needs, so QUAL never crosses the link).
         if (reinterpret_cast<uintptr_t>(recs) & 15) { c->err = "host record buffer must be 16-byte aligned"; return CORAL_E_ARG; }
@@ -163,7 +164,9 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
         CORAL_CUDA(c, c->d_ordinal.ensure((size_t)n * 8));
         CORAL_CUDA(c, cudaMemcpyAsync(c->d_ordinal.p, global_ordinal, (size_t)n * 8, cudaMemcpyHostToDevice, c->stream));
     }
-    if (on_device == CORAL_RECORDS_HOST_MAPPED_ASYNC) CORAL_TRY(coral_start_scan_async(c));
+    c->scan_lazy = false;
+    if (on_device == CORAL_RECORDS_HOST_MAPPED_ASYNC) CORAL_TRY(coral_start_scan_async(c, true));
+    else if (on_device == CORAL_RECORDS_HOST_MAPPED_LAZY) CORAL_TRY(coral_start_scan_async(c, false));
     else CORAL_TRY(coral_run_scan(c));
     c->loaded = true;
     return CORAL_OK;

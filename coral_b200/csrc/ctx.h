@@ -152,6 +152,7 @@ struct coral_ctx {
     DevBuf scan_status;   // the record scan's own status words (it may run next to other entry points)
     cudaStream_t scan_stream = nullptr;   // CORAL_RECORDS_HOST_MAPPED_ASYNC: the full scan runs here ...
     bool scan_pending = false;            // ... until coral_wait_scan() joins it
+    bool scan_lazy = false;               // CORAL_RECORDS_HOST_MAPPED_LAZY: pre-scan done, full scan not started yet
 
     // scratch
     DevBuf s0, s1, s2, s3, s4, s5, s6, s7;
@@ -176,7 +177,7 @@ struct coral_ctx {
 int coral_upload_ref_hashes(coral_ctx* ctx);
 void coral_release_tables(coral_ctx* ctx);
 int coral_run_scan(coral_ctx* ctx);
-int coral_start_scan_async(coral_ctx* ctx);
+int coral_start_scan_async(coral_ctx* ctx, bool launch_full_scan);
 int coral_run_fetch(coral_ctx* ctx);
 int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
                               int32_t n, int64_t* base_sum, int64_t* rec_count);

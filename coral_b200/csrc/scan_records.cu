@@ -781,7 +781,7 @@ int scan_verdict(coral_ctx* ctx, cudaStream_t st) {
 // Asynchronous form of the load-time scan (CORAL_RECORDS_HOST_MAPPED_ASYNC): the pre-scan runs to completion, the
 // full scan is left running on its own stream with one block per SM (the link, not the SMs, bounds it, and the
 // kernels of fetch need room next to it); coral_wait_scan() joins it.
-int coral_start_scan_async(coral_ctx* ctx) {
+int coral_start_scan_async(coral_ctx* ctx, bool launch_full_scan) {
     using namespace coral;
     const int64_t n = ctx->nrec;
     CORAL_TRY(scan_ensure_tables(ctx));
@@ -807,6 +807,10 @@ int coral_start_scan_async(coral_ctx* ctx) {
         ctx->err = "malformed aux field in " + std::to_string(sw[0]) + " record(s)";
         return CORAL_E_FORMAT;
     }
+    if (!launch_full_scan) {            // CORAL_RECORDS_HOST_MAPPED_LAZY: the full scan runs when an entry point asks for it
+        ctx->scan_lazy = true;
+        return CORAL_OK;
+    }
     ScanEvents e{g.rec.as<uint32_t>(), g.k.as<uint32_t>(), g.next_start.as<int32_t>(), g.prev_end.as<int32_t>(),
                  g.counter.as<unsigned long long>(), g.capacity};
     const int64_t want = (n + SC_WARPS - 1) / SC_WARPS;
@@ -827,6 +831,10 @@ int coral_start_scan_async(coral_ctx* ctx) {
 
 extern "C" int coral_wait_scan(coral_ctx* ctx) {
     if (!ctx) return CORAL_E_ARG;
+    if (ctx->scan_lazy) {
+        cudaSetDevice(ctx->device);
+        return coral_run_scan(ctx);
+    }
     if (!ctx->scan_pending) return CORAL_OK;
     cudaSetDevice(ctx->device);
     ctx->scan_pending = false;
@@ -839,6 +847,7 @@ extern "C" int coral_wait_scan(coral_ctx* ctx) {
 int coral_run_scan(coral_ctx* ctx) {
     using namespace coral;
     const int64_t n = ctx->nrec;
+    ctx->scan_lazy = false;
     if (ctx->scan_pending) {                    // join an asynchronous scan before starting over
         ctx->scan_pending = false;
         cudaStreamSynchronize(ctx->scan_stream);

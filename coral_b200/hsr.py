@@ -20,7 +20,10 @@ def fetch(lr_bamfh, device=0):
     """reference :21-49.  `lr_bamfh`: coral_b200._abi.BamFile (or any record set the engine accepts).
     -> (read_length of the chimeric reads, chimeric_alignments); reads without a primary record are dropped."""
     from .infer_breakpoint_graph import bam_to_breakpoint_nanopore
-    eng = bam_to_breakpoint_nanopore(None, None, device=device, records=lr_bamfh)
+    slack = int(getattr(lr_bamfh, "rec_slack", 0))
+    # only core / name / aux bytes are needed: the lazy placement never runs the CIGAR + SEQ scan for this caller
+    eng = bam_to_breakpoint_nanopore(None, None, device=device, records=lr_bamfh,
+                                     placement="mapped_lazy" if slack >= 64 and lr_bamfh.n_records else "copy")
     eng._nm_stats_required = False           # hsr.fetch keeps no NM statistics (and must not fail without them)
     eng._warn_no_primary = False
     eng.fetch()

@@ -52,7 +52,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
             placement = "mapped" if nb > 0 and getattr(rec, "nbytes", 0) + slack >= nb + 64 else "copy"
             if placement == "mapped" and getattr(self, "_comm", None) is None:
                 placement = "mapped_async"       # one GPU: fetch and the host steps after it run next to the scan
-        self._scan_async = placement == "mapped_async"
+        self._scan_async = placement in ("mapped_async", "mapped_lazy")
         self._normal_pending = None              # read_cns's coverage call, deferred while the scan is still running
         self._ctx.load_records(rec, rec_off, placement=placement, slack=slack)
         self._tid = {c: i for i, c in enumerate(self.lr_bamfh.references)}

@@ -101,6 +101,10 @@ const uint64_t* coral_bam_offsets(const coral_bam* b);                     /* n_
  *                              coral_cluster_call / coral_cn_segment_index.  Every other entry point joins the scan
  *                              first (coral_wait_scan), where its errors (malformed record -> CORAL_E_FORMAT) surface. */
 #define CORAL_RECORDS_HOST_MAPPED_ASYNC 3
+/*   CORAL_RECORDS_HOST_MAPPED_LAZY   only the pre-scan runs at load; the full scan runs (synchronously) inside the first
+ *                              entry point that needs it, or never — a caller that only wants coral_fetch (the HSR
+ *                              mode, hsr.py:21-49) moves a few hundred bytes per record instead of CIGAR and SEQ. */
+#define CORAL_RECORDS_HOST_MAPPED_LAZY 4
 int coral_wait_scan(coral_ctx* ctx);
 int coral_load_records(coral_ctx* ctx, const uint8_t* recs, uint64_t nbytes, const uint64_t* offsets,
                        int64_t n_records, const uint64_t* global_ordinal, int on_device);

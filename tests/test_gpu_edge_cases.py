@@ -75,7 +75,7 @@ def _ctx(rec, off, placement="copy"):
         buf = np.zeros(len(rec) + 64, np.uint8)
         buf[:len(rec)] = rec
         c.load_records(buf[:len(rec)], off, placement=placement, slack=64)
-        if placement == "mapped_async":
+        if placement in ("mapped_async", "mapped_lazy"):
             # what the pre-scan wrote (the columns fetch reads while the full scan is in flight) against what the full
             # scan writes into the same columns; fetch must not wait for the scan and must give the same table
             f0 = c.fetch()
@@ -94,7 +94,7 @@ def _table_matches(t, ora):
         assert np.array_equal(t[k], want), k
 
 
-@pytest.mark.parametrize("placement", ["copy", "mapped", "mapped_async"])
+@pytest.mark.parametrize("placement", ["copy", "mapped", "mapped_async", "mapped_lazy"])
 def test_edge_records_scan_table(built_lib, edge, placement):
     c = _ctx(edge["rec"], edge["off"], placement)
     ora = edge["ora"]
