@@ -248,10 +248,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--scale", type=float, default=float(os.environ.get("CORAL_BENCH_SCALE", "1.0")))
-    ap.add_argument("--e2e-placement", default="auto", choices=["auto", "mapped_async", "mapped", "copy"],
+    ap.add_argument("--e2e-placement", default="mapped", choices=["mapped", "mapped_async", "copy"],
                     help="e2e arm: kernels read the pinned host records in place over PCIe (mapped; mapped_async = fetch and "
-                         "the host steps after it run next to the scan; auto = mapped_async on 1 GPU, mapped on N) or after "
-                         "a full H2D copy")
+                         "the host steps after it run next to the scan — measured slower on C2, DESIGN.md 5) or after a full "
+                         "H2D copy")
     ap.add_argument("--only", default="", help="'scan': time the record-scan kernel alone (development aid)")
     ap.add_argument("--cprofile", action="store_true", help="cProfile of 20 device passes on rank 0 (development aid)")
     ap.add_argument("--profile", action="store_true",
@@ -263,8 +263,8 @@ def main():
     if a.impl == "reference":
         reference_arm(a, rank, world)
         return
-    if a.e2e_placement == "auto":
-        a.e2e_placement = "mapped_async" if world == 1 else "mapped"
+    if world > 1 and a.e2e_placement == "mapped_async":
+        a.e2e_placement = "mapped"
     warm = max(a.warmup, 3)
 
     import torch

@@ -38,8 +38,9 @@ class bam_to_breakpoint_nanopore(HostSteps):
         scan runs once per BAM, so only the fields it needs cross PCIe), "mapped_async" (as "mapped", and the
         constructor returns after a pre-scan of the fields `fetch` needs: `fetch` and `hash_alignment_to_seg` then run
         while the full scan is still pulling CIGAR / SEQ bytes over the link; `read_cns`'s coverage sum is evaluated
-        when `normal_cov` / `min_cluster_cutoff` are first read) or "auto" (mapped_async on one GPU when the buffer
-        has the 64 bytes of slack the mapped modes need, else copy)."""
+        when `normal_cov` / `min_cluster_cutoff` are first read; measured slower than "mapped" on C2),
+        "mapped_lazy" (pre-scan only; the full scan runs when a method needs it) or "auto" (mapped when the buffer has
+        the 64 bytes of slack the mapped modes need, else copy)."""
         self._init_state()
         self.lr_bamfh = records if records is not None else _abi.BamFile(lr_bamfile, n_threads)   # replaces pysam (ibg:65)
         self._ctx = _abi.Context(device)
@@ -50,8 +51,6 @@ class bam_to_breakpoint_nanopore(HostSteps):
         if placement == "auto":
             nb = int(rec_off[-1]) if len(rec_off) else 0
             placement = "mapped" if nb > 0 and getattr(rec, "nbytes", 0) + slack >= nb + 64 else "copy"
-            if placement == "mapped" and getattr(self, "_comm", None) is None:
-                placement = "mapped_async"       # one GPU: fetch and the host steps after it run next to the scan
         self._scan_async = placement in ("mapped_async", "mapped_lazy")
         self._normal_pending = None              # read_cns's coverage call, deferred while the scan is still running
         self._ctx.load_records(rec, rec_off, placement=placement, slack=slack)

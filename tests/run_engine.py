@@ -53,11 +53,10 @@ def main():
             eng = util.oracle_engine(bam, seed)
         else:
             from coral_b200.infer_breakpoint_graph import bam_to_breakpoint_nanopore
-            eng = bam_to_breakpoint_nanopore(bam, seed, placement={"cuda": "auto", "cuda-lazy": "auto", "cuda-sync": "mapped",
-                                                                    "cuda-copy": "copy"}[kind])
-            if kind in ("cuda", "cuda-lazy"):
-                assert eng._scan_async           # BamFile buffers carry the slack: the asynchronous placement is in use
-        st = util.run_pipeline(eng, cn_seg, defer_cov=(kind == "cuda-lazy"))
+            eng = bam_to_breakpoint_nanopore(bam, seed, placement={"cuda": "auto", "cuda-async": "mapped_async",
+                                                                    "cuda-lazy": "mapped_lazy", "cuda-copy": "copy"}[kind])
+            assert eng._scan_async == (kind in ("cuda-async", "cuda-lazy"))
+        st = util.run_pipeline(eng, cn_seg, defer_cov=(kind in ("cuda-async", "cuda-lazy")))
     with open(out, "w") as fp:
         json.dump(st, fp)
 
