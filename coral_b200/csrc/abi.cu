@@ -44,7 +44,7 @@ void coral_destroy(coral_ctx* c) {
     c->scan_pending = false;
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->host_registered) cudaHostUnregister(c->host_registered);
-    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status, &c->scan_status, &c->xmsg[0], &c->xmsg[1], &c->xmsg[2],
+    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status, &c->scan_status, &c->sa_side, &c->sa_side_off, &c->xmsg[0], &c->xmsg[1], &c->xmsg[2],
                      &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->s6, &c->s7, &c->cub_tmp,
                      &c->rt.tid, &c->rt.pos, &c->rt.endpos, &c->rt.flag_mapq, &c->rt.lseq, &c->rt.ncig, &c->rt.infer,
                      &c->rt.mbases, &c->rt.nonacgt, &c->rt.fbs, &c->rt.lbe, &c->rt.name_lo, &c->rt.name_hi,
@@ -113,6 +113,7 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     }
     c->loaded = false;
     c->rows_only = false;
+    c->sa_side_valid = false;
     for (int64_t i = 0; i < n; i++) {
         if (offsets[i] & 15) { c->err = "record offsets must be 16-byte aligned"; return CORAL_E_ARG; }
         if (offsets[i] + 36 > nbytes || offsets[i + 1] < offsets[i] + 36 || offsets[i + 1] > nbytes) {

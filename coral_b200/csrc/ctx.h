@@ -152,6 +152,8 @@ struct coral_ctx {
     DevBuf scan_status;   // the record scan's own status words (it may run next to other entry points)
     cudaStream_t scan_stream = nullptr;   // CORAL_RECORDS_HOST_MAPPED_ASYNC: the full scan runs here ...
     bool scan_pending = false;            // ... until coral_wait_scan() joins it
+    DevBuf sa_side, sa_side_off;          // SA strings copied to HBM by the pre-scan, and where each record's sits
+    bool sa_side_valid = false;
     bool scan_lazy = false;               // CORAL_RECORDS_HOST_MAPPED_LAZY: pre-scan done, full scan not started yet
 
     // scratch

@@ -398,8 +398,10 @@ int coral_run_fetch(coral_ctx* c) {
     T.valid = false; T.n_reads = 0; T.n_aln = 0;
     const int64_t n = c->nrec;
     RecordTable& rt = c->rt;
-    const uint8_t* recs = c->d_recs;
-    const uint64_t* off = c->d_off.as<uint64_t>();
+    // where the SA strings are read from: the records, or — after a pre-scan (asynchronous / lazy placements) — its
+    // side copy in HBM, addressed through per-record offsets chosen so that base + offset + sa_off is the copy
+    const uint8_t* recs = c->sa_side_valid ? c->sa_side.as<uint8_t>() : c->d_recs;
+    const uint64_t* off = c->sa_side_valid ? c->sa_side_off.as<uint64_t>() : c->d_off.as<uint64_t>();
     c->stage_begin(CORAL_STAGE_FETCH);
 
     // nm_stats partials

@@ -660,23 +660,40 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
 }
 
 // Pre-scan of the asynchronous mode: the columns `fetch` needs (core fields, name hash, SA / NM location) for every
-// record, from the record core, the read name and the aux block only — a few hundred bytes per record, so it is done
-// in about a millisecond even over PCIe, and fetch + the host steps that follow it can run while the full scan is
-// still pulling CIGAR and SEQ bytes.  Same values as k_scan_records writes into the same columns.
-__global__ void k_prescan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off, uint32_t n, ScanCols o,
-                                  int32_t* __restrict__ status) {
+// record, from the record core, the read name and the aux block only — a few hundred bytes per record — so that
+// fetch + the host steps that follow it can run while the full scan is still pulling CIGAR and SEQ bytes.  Same values
+// as k_scan_records writes into the same columns.  The records may sit behind PCIe, where every dependent access costs
+// microseconds: a warp makes two round trips per record — the first 128 bytes (core + name) as one coalesced load, then
+// the aux block as 16-byte loads into a shared-memory stage that the table-driven walk reads — and the SA text is
+// copied into a side buffer in HBM (`side`), so that the kernels of fetch never touch the link.
+constexpr uint32_t PS_STAGE = 2048;                  // aux bytes staged per warp; longer aux blocks are walked in place
+
+struct SideText {
+    uint8_t* text;                // SA strings back to back (16-byte slots), first slot at 64
+    unsigned long long* used;     // bump pointer
+    uint64_t cap;
+    uint64_t* rec_off;            // per record: slot position - sa_off (mod 2^64), so that text + rec_off + sa_off = slot
+};
+
+__global__ void __launch_bounds__(256)
+k_prescan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off, uint32_t n, ScanCols o, SideText side,
+                  int32_t* __restrict__ status) {
+    __shared__ __align__(16) uint8_t stage_mem[8][PS_STAGE + 32];
     const uint32_t lane = lane_id();
+    const uint32_t stage = smem_u32(stage_mem[threadIdx.x >> 5]);
     const uint32_t nw = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t rec = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; rec < n; rec += nw) {
         const uint64_t o0 = __ldg(off + rec), o1 = __ldg(off + rec + 1);
         const uint8_t* r = recs + o0;
         const uint32_t len16 = (uint32_t)(o1 - o0);
-        const uint32_t cw = lane < 9 ? __ldg(reinterpret_cast<const uint32_t*>(r) + lane) : 0u;
-        const uint32_t block_size = __shfl_sync(FULL_MASK, cw, 0);
-        const uint32_t tid = __shfl_sync(FULL_MASK, cw, 1);
-        const uint32_t pos_ = __shfl_sync(FULL_MASK, cw, 2);
-        const uint32_t w3 = __shfl_sync(FULL_MASK, cw, 3), w4 = __shfl_sync(FULL_MASK, cw, 4);
-        uint32_t l_seq = __shfl_sync(FULL_MASK, cw, 5);
+        const uint32_t* rw = reinterpret_cast<const uint32_t*>(r);
+        // round trip 1: the first 128 bytes (a frame holds at least the 36-byte core)
+        const uint32_t w0 = (4 * lane + 4 <= len16) ? __ldg(rw + lane) : 0u;
+        const uint32_t block_size = __shfl_sync(FULL_MASK, w0, 0);
+        const uint32_t tid = __shfl_sync(FULL_MASK, w0, 1);
+        const uint32_t pos_ = __shfl_sync(FULL_MASK, w0, 2);
+        const uint32_t w3 = __shfl_sync(FULL_MASK, w0, 3), w4 = __shfl_sync(FULL_MASK, w0, 4);
+        uint32_t l_seq = __shfl_sync(FULL_MASK, w0, 5);
         const uint32_t l_name = w3 & 255u;
         uint32_t n_cig = w4 & 0xffffu;
         const uint32_t flag = w4 >> 16;
@@ -686,15 +703,51 @@ __global__ void k_prescan_records(const uint8_t* __restrict__ recs, const uint64
         if (rec_bad) { n_cig = 0; l_seq = 0; }
         const uint32_t nl = (l_name && !rec_bad) ? l_name - 1 : 0;
         uint64_t h1 = 0, h2 = 0;
-        for (uint32_t i = lane; i < nl; i += 32) {
-            const uint32_t b = r[36 + i];
-            h1 += hterm1(i, b);
-            h2 += hterm2(i, b);
+        for (uint32_t wi = lane; 4 * wi < 36 + nl; wi += 32) {            // name bytes sit at record offsets 36 .. 36 + nl
+            const uint32_t w = wi < 32 ? w0 : __ldg(rw + wi);              // (names longer than 92 characters: one more trip)
+#pragma unroll
+            for (uint32_t b = 0; b < 4; b++) {
+                const uint32_t bo = 4 * wi + b;
+                if (bo >= 36 && bo < 36 + nl) {
+                    const uint32_t ch = (w >> (8 * b)) & 255u;
+                    h1 += hterm1(bo - 36, ch);
+                    h2 += hterm2(bo - 36, ch);
+                }
+            }
         }
         h1 = warp_sum_u64(h1) + mix64(nl);
         h2 = warp_sum_u64(h2) + mix64(nl ^ 0xABCDull);
         AuxOut a{0, 0, 0, 0, 0};
-        if (!rec_bad && aux_beg < rec_size) a = aux_walk_global(r + aux_beg, r + rec_size, (uint32_t)aux_beg, lane);
+        bool staged = false;
+        uint32_t a0 = 0;
+        if (!rec_bad && aux_beg < rec_size) {
+            a0 = (uint32_t)aux_beg & ~15u;
+            const uint32_t a1 = ((uint32_t)rec_size + 15u) & ~15u;       // <= len16: frames are 16-byte padded
+            if (a1 - a0 <= PS_STAGE) {
+                // round trip 2: the aux block, 16 bytes per lane per step
+                for (uint32_t c = 16 * lane; c < a1 - a0; c += 512)
+                    sts128(stage + c, __ldg(reinterpret_cast<const uint4*>(r + a0 + c)));
+                __syncwarp();
+                a = aux_walk_smem(stage + ((uint32_t)aux_beg - a0), stage + ((uint32_t)rec_size - a0), (uint32_t)aux_beg, lane);
+                staged = true;
+            } else {
+                a = aux_walk_global(r + aux_beg, r + rec_size, (uint32_t)aux_beg, lane);
+            }
+        }
+        if (a.have_sa && side.text) {          // SA text -> side buffer (16-byte slots)
+            unsigned long long slot = 0;
+            const uint32_t need = (a.sa_len + 16u) & ~15u;
+            if (lane == 0) slot = atomicAdd(side.used, (unsigned long long)need);
+            slot = __shfl_sync(FULL_MASK, slot, 0);
+            if (slot + need + 64 <= side.cap) {
+                for (uint32_t b = lane; b < a.sa_len; b += 32)
+                    side.text[slot + b] = staged ? (uint8_t)lds8(stage + (a.sa_off - a0) + b) : r[a.sa_off + b];
+                if (lane == 0) side.rec_off[rec] = (uint64_t)slot - (uint64_t)a.sa_off;
+            } else if (lane == 0) {
+                atomicExch(&status[2], 1);     // side buffer too small: fetch reads the records instead
+            }
+        }
+        __syncwarp();                          // the stage is reused by the next record
         if (lane == 0) {
             o.tid[rec] = (int32_t)tid;
             o.pos[rec] = (int32_t)pos_;
@@ -791,14 +844,25 @@ int coral_start_scan_async(coral_ctx* ctx, bool launch_full_scan) {
     CORAL_CUDA(ctx, cudaMemsetAsync(ctx->scan_status.p, 0, 64, ctx->stream));
     if (n == 0) { g.n = 0; return CORAL_OK; }
     ScanCols o = scan_cols(ctx);
+    // side buffer for the SA strings (fetch then never reads the records): 1/32 of the record bytes, at least 1 MB;
+    // a file with more SA text than that falls back to reading the records
+    const uint64_t side_cap = std::max<uint64_t>((uint64_t)1 << 20, ctx->nbytes / 32);
+    CORAL_CUDA(ctx, ctx->sa_side.ensure(side_cap));
+    CORAL_CUDA(ctx, ctx->sa_side_off.ensure((size_t)n * 8 + 16));
+    unsigned long long* d_used = reinterpret_cast<unsigned long long*>(ctx->sa_side_off.as<uint64_t>() + n);
+    const unsigned long long first_slot = 64;
+    CORAL_CUDA(ctx, cudaMemcpyAsync(d_used, &first_slot, 8, cudaMemcpyHostToDevice, ctx->stream));
+    SideText side{ctx->sa_side.as<uint8_t>(), d_used, side_cap, ctx->sa_side_off.as<uint64_t>()};
     const int pre_blocks = (int)std::min<int64_t>((n + 7) / 8, (int64_t)ctx->sm_count * 8);
-    k_prescan_records<<<pre_blocks, 256, 0, ctx->stream>>>(ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, o,
+    k_prescan_records<<<pre_blocks, 256, 0, ctx->stream>>>(ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, o, side,
                                                           ctx->scan_status.as<int32_t>());
     ctx->n_launches++;
     CORAL_CUDA(ctx, cudaGetLastError());
-    int32_t sw[2] = {0, 0};
-    CORAL_CUDA(ctx, cudaMemcpyAsync(sw, ctx->scan_status.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    int32_t sw[3] = {0, 0, 0};
+    CORAL_CUDA(ctx, cudaMemcpyAsync(sw, ctx->scan_status.p, 12, cudaMemcpyDeviceToHost, ctx->stream));
     CORAL_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->sa_side_valid = sw[2] == 0;
+    if (!ctx->sa_side_valid) CORAL_CUDA(ctx, cudaMemsetAsync(ctx->scan_status.as<int32_t>() + 2, 0, 4, ctx->stream));
     if (sw[1] != 0) {
         ctx->err = "record framing inconsistent with the record core in " + std::to_string(sw[1]) + " record(s)";
         return CORAL_E_FORMAT;
@@ -848,6 +912,7 @@ int coral_run_scan(coral_ctx* ctx) {
     using namespace coral;
     const int64_t n = ctx->nrec;
     ctx->scan_lazy = false;
+    ctx->sa_side_valid = false;
     if (ctx->scan_pending) {                    // join an asynchronous scan before starting over
         ctx->scan_pending = false;
         cudaStreamSynchronize(ctx->scan_stream);
