@@ -248,9 +248,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--scale", type=float, default=float(os.environ.get("CORAL_BENCH_SCALE", "1.0")))
-    ap.add_argument("--e2e-placement", default="mapped", choices=["mapped", "mapped_async", "copy"],
+    ap.add_argument("--e2e-placement", default="mapped_async", choices=["mapped", "mapped_async", "copy"],
                     help="e2e arm: kernels read the pinned host records in place over PCIe (mapped; mapped_async = fetch and "
-                         "the host steps after it run next to the scan — measured slower on C2, DESIGN.md 5) or after a full "
+                         "the host steps after it run next to the scan, the default at N=1: 172 vs 200 ms per C2 pass) or after a full "
                          "H2D copy")
     ap.add_argument("--only", default="", help="'scan': time the record-scan kernel alone (development aid)")
     ap.add_argument("--cprofile", action="store_true", help="cProfile of 20 device passes on rank 0 (development aid)")

@@ -29,6 +29,7 @@ def _gc_paused(fn):
 class bam_to_breakpoint_nanopore(HostSteps):
     _ops = breakpoint_utilities
 
+    _auto_mapped = "mapped_async"   # what placement="auto" means for a buffer with slack (the sharded engine joins at load)
     _normal_pending = None      # (class default: _init_state assigns the properties before __init__ sets it)
 
     def __init__(self, lr_bamfile, seedfile, device=0, n_threads=0, records=None, placement="auto"):
@@ -38,9 +39,9 @@ class bam_to_breakpoint_nanopore(HostSteps):
         scan runs once per BAM, so only the fields it needs cross PCIe), "mapped_async" (as "mapped", and the
         constructor returns after a pre-scan of the fields `fetch` needs: `fetch` and `hash_alignment_to_seg` then run
         while the full scan is still pulling CIGAR / SEQ bytes over the link; `read_cns`'s coverage sum is evaluated
-        when `normal_cov` / `min_cluster_cutoff` are first read; measured slower than "mapped" on C2),
-        "mapped_lazy" (pre-scan only; the full scan runs when a method needs it) or "auto" (mapped when the buffer has
-        the 64 bytes of slack the mapped modes need, else copy)."""
+        when `normal_cov` / `min_cluster_cutoff` are first read; 172 vs 200 ms per C2 pass),
+        "mapped_lazy" (pre-scan only; the full scan runs when a method needs it) or "auto" (mapped_async when the
+        buffer has the 64 bytes of slack the mapped modes need, else copy)."""
         self._init_state()
         self.lr_bamfh = records if records is not None else _abi.BamFile(lr_bamfile, n_threads)   # replaces pysam (ibg:65)
         self._ctx = _abi.Context(device)
@@ -50,7 +51,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
         slack = int(getattr(self.lr_bamfh, "rec_slack", 0))
         if placement == "auto":
             nb = int(rec_off[-1]) if len(rec_off) else 0
-            placement = "mapped" if nb > 0 and getattr(rec, "nbytes", 0) + slack >= nb + 64 else "copy"
+            placement = self._auto_mapped if nb > 0 and getattr(rec, "nbytes", 0) + slack >= nb + 64 else "copy"
         self._scan_async = placement in ("mapped_async", "mapped_lazy")
         self._normal_pending = None              # read_cns's coverage call, deferred while the scan is still running
         self._ctx.load_records(rec, rec_off, placement=placement, slack=slack)

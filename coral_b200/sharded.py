@@ -274,6 +274,8 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
         """bam_to_breakpoint_nanopore over one shard of the file + the exchanges of SURVEY.md §8e.  Same public
         methods, same call order; every rank ends with the same containers as the 1-GPU engine."""
 
+        _auto_mapped = "mapped"      # every shard's scan is joined at load: the exchanges need its columns at once
+
         def __init__(self):
             self._comm = comm
             if presharded:

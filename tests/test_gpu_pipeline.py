@@ -20,13 +20,14 @@ def test_cuda_pipeline_matches_reference(built_lib, case, tmp_path_factory):
         assert g_got["graph_txt"] == g_ref["graph_txt"]          # byte-identical graph.txt
 
 
-@pytest.mark.parametrize("case,kind", [("c2_small", "cuda-async"), ("c4_small", "cuda-async"), ("c3_small", "cuda-async"),
-                                       ("c5_mini", "cuda-async"), ("c4_small", "cuda-lazy"), ("c3_small", "cuda-copy")])
+@pytest.mark.parametrize("case,kind", [("c2_small", "cuda-async"), ("c4_small", "cuda-async"), ("c3_small", "cuda-sync"),
+                                       ("c5_mini", "cuda-sync"), ("c4_small", "cuda-lazy"), ("c3_small", "cuda-copy")])
 def test_cuda_pipeline_placements(built_lib, case, kind, tmp_path_factory):
-    """The same parity with the other record placements ("cuda" above = mapped, the scan joined at load):
-    "cuda-async" = asynchronous scan with fetch and hash_alignment_to_seg running while it is in flight (normal_cov
-    first read when find_amplicon_intervals needs it), "cuda-lazy" = pre-scan at load and the full scan inside the first
-    method that needs it, "cuda-copy" = records copied to HBM."""
+    """The same parity with every record placement.  "cuda" above = the default: asynchronous scan, with normal_cov read
+    right after read_cns as the harness does (which joins the scan there).  "cuda-async" = the same placement with the
+    reference's own access pattern: fetch and hash_alignment_to_seg run while the scan is in flight, normal_cov is
+    first read when find_amplicon_intervals needs it.  "cuda-sync" = mapped with the scan joined at load, "cuda-lazy" =
+    pre-scan at load and the full scan inside the first method that needs it, "cuda-copy" = records copied to HBM."""
     gold = G.load_golden(case)
     cfg, data, paths = G.golden_dataset(case, tmp_path_factory)
     got = G.run_engine(kind, paths, tmp_path_factory)
