@@ -56,8 +56,38 @@ class ClockSampler(threading.Thread):
         self.gpu = gpu
         self.rows = []
         self.stop_flag = False
+        self.source = "none"
 
     def run(self):
+        """Clocks and throttle reasons while the timed regions run.  NVML in-process (what nvidia-smi itself queries):
+        spawning nvidia-smi five times a second attaches a new driver client each time, which can stall the
+        cudaMalloc / cudaFree calls of the pass being timed; nvidia-smi is the fallback when pynvml is unusable."""
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self._nvml_index())
+            bits = [0x8, 0x40, 0x20, 0x4]      # hw_slowdown, hw_thermal_slowdown, sw_thermal_slowdown, sw_power_cap
+            sm_max = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+        except Exception:
+            return self._run_nvidia_smi()
+        self.source = "nvml"
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                why = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                self.rows.append([str(sm), str(sm_max)] + ["Active" if why & b else "Not Active" for b in bits])
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def _nvml_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        ids = [x for x in vis.split(",") if x.strip() != ""]
+        return int(ids[self.gpu]) if ids and all(x.strip().isdigit() for x in ids) and self.gpu < len(ids) else self.gpu
+
+    def _run_nvidia_smi(self):
+        self.source = "nvidia-smi"
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         while not self.stop_flag:
@@ -68,7 +98,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append([x.strip() for x in out.split(",")])
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(1.0)
 
     def summary(self):
         if not self.rows:
@@ -77,7 +107,8 @@ class ClockSampler(threading.Thread):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for k, n in enumerate(names) if any(len(r) > 2 + k and r[2 + k] == "Active" for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None,
-                "sm_max_mhz": int(self.rows[0][1]) if self.rows[0][1].isdigit() else None, "reasons": reasons}
+                "sm_max_mhz": int(self.rows[0][1]) if self.rows[0][1].isdigit() else None, "reasons": reasons,
+                "samples": len(self.rows), "source": self.source}
 
 
 def write_inputs(cfg, outdir):
@@ -252,7 +283,8 @@ def main():
                     help="e2e arm: kernels read the pinned host records in place over PCIe (mapped; mapped_async = fetch and "
                          "the host steps after it run next to the scan, the default at N=1: 172 vs 200 ms per C2 pass) or after a full "
                          "H2D copy")
-    ap.add_argument("--only", default="", help="'scan': time the record-scan kernel alone (development aid)")
+    ap.add_argument("--only", default="", help="'scan': time the record-scan kernel alone; 'e2e': per-pass stage times of "
+                                               "the e2e arm alone (development aids)")
     ap.add_argument("--cprofile", action="store_true", help="cProfile of 20 device passes on rank 0 (development aid)")
     ap.add_argument("--profile", action="store_true",
                     help="bracket ONE device pass with cudaProfilerStart/Stop and exit (for ncu --profile-from-start off)")
@@ -352,6 +384,19 @@ def main():
         eng.closebam()
         e2e_stage["closebam"] = (time.perf_counter() - t) * 1e3
         return eng
+
+    if a.only == "e2e":             # development aid: per-pass stage times of the e2e arm alone
+        rows = []
+        sampler = ClockSampler(local)
+        sampler.start()
+        for _ in range(warm + a.steps):
+            t = time.perf_counter()
+            e2e_pass()
+            rows.append(dict(e2e_stage, total=(time.perf_counter() - t) * 1e3))
+        sampler.stop_flag = True
+        sampler.join(timeout=2)
+        print(json.dumps({"only": "e2e", "placement": a.e2e_placement, "clocks": sampler.summary(), "passes": rows}), flush=True)
+        return
 
     # plan + resident context
     eng0 = make_engine("copy")
