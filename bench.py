@@ -466,9 +466,12 @@ def main():
     e2e_pass()
     barrier()
     t1 = time.perf_counter()
-    e2e_steps = max(1, min(a.steps, 3))
+    e2e_steps = max(1, min(a.steps, 5))
+    e2e_ms = []
     for _ in range(e2e_steps):
+        tp = time.perf_counter()
         e2e_pass()
+        e2e_ms.append((time.perf_counter() - tp) * 1e3)
     barrier()
     dt_e2e = time.perf_counter() - t1
     sampler.stop_flag = True
@@ -525,7 +528,8 @@ def main():
         "aligned_gbases_per_s": aligned_all * a.steps / dt / 1e9,
         "e2e": {"value": n_rec_all * e2e_steps / dt_e2e, "unit": "records/s", "ms_per_step": dt_e2e / e2e_steps * 1e3,
                 "h2d_bytes_per_step": (alg_bytes - 76 * n_rec if a.e2e_placement.startswith("mapped") else nbytes) + 8 * (n_rec + 1),
-                "d2h_bytes_per_step": d2h, "placement": a.e2e_placement, "stage_ms": e2e_stage},
+                "d2h_bytes_per_step": d2h, "placement": a.e2e_placement, "steps": e2e_steps,
+                "ms_per_pass": [round(x, 2) for x in e2e_ms], "stage_ms": e2e_stage},
         "gpu_launches": int(launches_all),
         "roofline": {"bound": "hbm", "kernel": "k_scan_records", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": 5.621e9 if (world == 1 and a.scale == 1.0) else None,
