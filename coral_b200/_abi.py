@@ -46,12 +46,66 @@ def lib():
         L.coral_bam_ref_name.restype = ctypes.c_char_p
         L.coral_bam_records.restype = ctypes.c_void_p
         L.coral_bam_offsets.restype = ctypes.c_void_p
+        L.coral_ingest_ref_name.restype = ctypes.c_char_p
+        L.coral_ingest_ref_len.restype = ctypes.c_int64
         _lib = L
     return _lib
 
 
 def _p(a):
     return None if a is None else a.ctypes.data_as(ctypes.c_void_p)
+
+
+def ingest_host_check(file_bytes, mode=0):
+    """CPU run of the device-side ingest's decoder and framing steps (coral_ingest_host_check; test hook).
+    -> dict(rec, rec_off, n_candidates, used_serial).  mode 1 forces the serial chase."""
+    L = lib()
+    fb = np.ascontiguousarray(file_bytes, dtype=np.uint8)
+    n, nb, ncand, ser = ctypes.c_int64(0), ctypes.c_uint64(0), ctypes.c_int64(0), ctypes.c_int32(0)
+    err = ctypes.create_string_buffer(512)
+    rc = L.coral_ingest_host_check(_p(fb), ctypes.c_uint64(len(fb)), int(mode), None, ctypes.c_uint64(0), None, ctypes.c_int64(-1),
+                                   ctypes.byref(n), ctypes.byref(nb), ctypes.byref(ncand), ctypes.byref(ser), err, 512)
+    if rc not in (0, -6):          # -6 = CORAL_E_NOMEM: sizing call
+        raise CoralError(rc, err.value.decode())
+    rec = np.zeros(nb.value + 64, np.uint8)
+    off = np.zeros(n.value + 1, np.uint64)
+    rc = L.coral_ingest_host_check(_p(fb), ctypes.c_uint64(len(fb)), int(mode), _p(rec), ctypes.c_uint64(nb.value), _p(off),
+                                   ctypes.c_int64(n.value), ctypes.byref(n), ctypes.byref(nb), ctypes.byref(ncand),
+                                   ctypes.byref(ser), err, 512)
+    if rc != 0:
+        raise CoralError(rc, err.value.decode())
+    return {"rec": rec[:nb.value], "rec_off": off, "n_candidates": int(ncand.value), "used_serial": int(ser.value)}
+
+
+class DeviceBam(object):
+    """Device-side ingest (csrc/ingest.cu): the .bam file's bytes are inflated and framed on the GPU of `ctx`, which
+    afterwards holds the records exactly as after load_records of a BamFile.  The handle offers what the drop-in class
+    needs from its BAM handle without a host copy of the records: references, n_records, query_names."""
+
+    def __init__(self, path, ctx):
+        self.path = path
+        self._ctx = ctx
+        self._bytes = np.fromfile(path, dtype=np.uint8)
+        self.references, self.lengths = ctx.ingest_open(self._bytes)
+        self.n_records = None
+        self.rec = None
+        self.rec_off = None
+        self.rec_slack = 0
+
+    def run(self):
+        """References must have been set on the ctx (set_references) before."""
+        self.n_records, self.framed_bytes = self._ctx.ingest_run()
+        self._bytes = None
+        return self.n_records
+
+    def query_name(self, i):
+        return self.query_names([i])[0]
+
+    def query_names(self, idx):
+        return self._ctx.read_names(idx)
+
+    def close(self):
+        self._bytes = None
 
 
 class BamFile(object):
@@ -402,6 +456,38 @@ class Context(object):
         self._check(self._L.coral_cn_segment_index(self._h, _p(seg_tid), _p(seg_begin), _p(seg_end), _p(seg_idx),
                                                    ctypes.c_int32(len(seg_tid)), _p(lo), _p(hi)))
         return lo, hi
+
+    def ingest_open(self, file_bytes):
+        """Device-side ingest, step 1 (host only): -> (reference names, lengths).  `file_bytes` must stay alive until
+        ingest_run."""
+        self._ingest_bytes = np.ascontiguousarray(file_bytes, dtype=np.uint8)
+        self._check(self._L.coral_ingest_open(self._h, _p(self._ingest_bytes), ctypes.c_uint64(len(self._ingest_bytes))))
+        n = self._L.coral_ingest_n_ref(self._h)
+        return (tuple(self._L.coral_ingest_ref_name(self._h, i).decode() for i in range(n)),
+                tuple(int(self._L.coral_ingest_ref_len(self._h, i)) for i in range(n)))
+
+    def ingest_run(self):
+        """Step 2: inflate + frame on the device, then the load-time scan.  -> (n_records, framed bytes)."""
+        n, nb = ctypes.c_int64(0), ctypes.c_uint64(0)
+        try:
+            self._check(self._L.coral_ingest_run(self._h, ctypes.byref(n), ctypes.byref(nb)))
+        finally:
+            self._ingest_bytes = None
+        return int(n.value), int(nb.value)
+
+    def ingest_used_serial_chase(self):
+        return int(self._L.coral_ingest_used_serial_chase(self._h))
+
+    def read_names(self, idx):
+        """Read names of records `idx` (any placement; the only way to them after a device-side ingest)."""
+        idx = np.ascontiguousarray(idx, dtype=np.uint32)
+        if len(idx) == 0:
+            return []
+        out = np.zeros(len(idx) * 256, np.uint8)
+        self._check(self._L.coral_get_read_names(self._h, _p(idx), ctypes.c_int64(len(idx)), _p(out)))
+        rows = out.reshape(len(idx), 256)
+        ln = (rows != 0).argmin(axis=1)          # first NUL (names are at most 254 characters + NUL)
+        return [rows[k, :ln[k]].tobytes().decode() for k in range(len(idx))]
 
     def alignment_paths(self, iv_tid, iv_start, iv_stop, se_tid, se_l, se_r, name_rec=(), name_lo=(), name_hi=(),
                         min_overlap=500, min_mapq=20):

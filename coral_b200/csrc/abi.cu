@@ -56,6 +56,8 @@ void coral_destroy(coral_ctx* c) {
     for (DevBuf& b : c->sw) b.release();
     for (DevBuf& b : c->cw) b.release();
     for (DevBuf& b : c->pw) b.release();
+    for (DevBuf& b : c->ing_w) b.release();
+    c->ing_comp.release(); c->ing_stream.release(); c->ing_recs.release();
     DevBuf* tables[] = {&c->paths.rec, &c->paths.iv, &c->paths.first, &c->paths.last,
                         &c->sdel.rec, &c->sdel.ai, &c->sdel.next_start, &c->sdel.prev_end, &c->sdel.first_start, &c->sdel.last_end, &c->sdel.mapq,
                         &c->cand.read, &c->cand.i, &c->cand.j, &c->cand.chr1, &c->cand.pos1, &c->cand.chr2, &c->cand.pos2, &c->cand.rgap,

@@ -45,6 +45,8 @@ inline void scan_joined() {
 }
 }  // namespace coral_mem
 
+struct IngestMember { uint64_t in_off, out_off; uint32_t in_len, out_len; };   // one BGZF member: CDATA in the file, place in the stream
+
 // Grow-only device buffer.
 struct DevBuf {
     void* p = nullptr;
@@ -147,6 +149,16 @@ struct coral_ctx {
     bool cl_valid = false;
     PathTable paths;
     DevBuf pw[11];   // alignment-path (compute_path_constraints) work buffers
+    // device-side BAM ingest (ingest.cu): state between coral_ingest_open and coral_ingest_run, and the framed records
+    std::vector<IngestMember> ing_members;
+    uint64_t ing_total = 0, ing_first = 0, ing_file_bytes = 0;
+    const uint8_t* ing_file = nullptr;
+    std::vector<std::string> ing_ref_names;
+    std::vector<int64_t> ing_ref_lens;
+    std::vector<uint64_t> ing_offsets;
+    bool ing_ready = false;
+    int ing_serial_chase = 0;      // 1 when the last ingest had to fall back to the serial chase
+    DevBuf ing_comp, ing_stream, ing_recs, ing_w[8];
     DevBuf xmsg[3];  // packed exchange messages (SA rows, extra primaries, concordant rows): live until the next pack
     DevBuf status;  // int32[8] device status words (format errors etc.)
     DevBuf scan_status;   // the record scan's own status words (it may run next to other entry points)

@@ -40,21 +40,32 @@ class bam_to_breakpoint_nanopore(HostSteps):
         constructor returns after a pre-scan of the fields `fetch` needs: `fetch` and `hash_alignment_to_seg` then run
         while the full scan is still pulling CIGAR / SEQ bytes over the link; `read_cns`'s coverage sum is evaluated
         when `normal_cov` / `min_cluster_cutoff` are first read; 172 vs 200 ms per C2 pass),
-        "mapped_lazy" (pre-scan only; the full scan runs when a method needs it) or "auto" (mapped_async when the
-        buffer has the 64 bytes of slack the mapped modes need, else copy)."""
+        "mapped_lazy" (pre-scan only; the full scan runs when a method needs it), "auto" (mapped_async when the
+        buffer has the 64 bytes of slack the mapped modes need, else copy) or "device_ingest" (opt-in: `lr_bamfile` is
+        inflated and framed on the GPU; CPU-verified only so far, see csrc/ingest.cu)."""
         self._init_state()
-        self.lr_bamfh = records if records is not None else _abi.BamFile(lr_bamfile, n_threads)   # replaces pysam (ibg:65)
-        self._ctx = _abi.Context(device)
-        gpu_ops.set_default_device(device)
-        self._ctx.set_references(self.lr_bamfh.references)
-        rec, rec_off = self.lr_bamfh.rec, self.lr_bamfh.rec_off
-        slack = int(getattr(self.lr_bamfh, "rec_slack", 0))
-        if placement == "auto":
-            nb = int(rec_off[-1]) if len(rec_off) else 0
-            placement = self._auto_mapped if nb > 0 and getattr(rec, "nbytes", 0) + slack >= nb + 64 else "copy"
-        self._scan_async = placement in ("mapped_async", "mapped_lazy")
         self._normal_pending = None              # read_cns's coverage call, deferred while the scan is still running
-        self._ctx.load_records(rec, rec_off, placement=placement, slack=slack)
+        if placement == "device_ingest":
+            # opt-in (SURVEY 8f rank 3, csrc/ingest.cu): the file's BGZF bytes go to the GPU as they are on disk and are
+            # inflated and framed there; no host copy of the records exists, read names come back through the ctx
+            self._ctx = _abi.Context(device)
+            gpu_ops.set_default_device(device)
+            self.lr_bamfh = _abi.DeviceBam(lr_bamfile, self._ctx)
+            self._ctx.set_references(self.lr_bamfh.references)
+            self.lr_bamfh.run()
+            self._scan_async = False
+        else:
+            self.lr_bamfh = records if records is not None else _abi.BamFile(lr_bamfile, n_threads)   # replaces pysam (ibg:65)
+            self._ctx = _abi.Context(device)
+            gpu_ops.set_default_device(device)
+            self._ctx.set_references(self.lr_bamfh.references)
+            rec, rec_off = self.lr_bamfh.rec, self.lr_bamfh.rec_off
+            slack = int(getattr(self.lr_bamfh, "rec_slack", 0))
+            if placement == "auto":
+                nb = int(rec_off[-1]) if len(rec_off) else 0
+                placement = self._auto_mapped if nb > 0 and getattr(rec, "nbytes", 0) + slack >= nb + 64 else "copy"
+            self._scan_async = placement in ("mapped_async", "mapped_lazy")
+            self._ctx.load_records(rec, rec_off, placement=placement, slack=slack)
         self._tid = {c: i for i, c in enumerate(self.lr_bamfh.references)}
         self._name_rec = {}     # read name -> index of one record carrying it (for concordant-edge rbps)
         self._read_names = []   # chimeric read order of the device table

@@ -311,6 +311,31 @@ int coral_alignment_paths(coral_ctx* ctx, const int32_t* iv_tid, const int32_t* 
                           int64_t n_name_hash, int32_t min_overlap, int32_t min_mapq, int64_t* n_rows);
 int coral_get_alignment_paths(coral_ctx* ctx, uint32_t* rec, int32_t* iv, int32_t* first, int32_t* last);
 
+/* ---- device-side BAM ingest (replaces pysam.AlignmentFile(path,'rb'), ibg:65, for callers
+ * that opt in) -----------------------------------------------------------------------------------------------------
+ * The whole .bam file (BGZF bytes) is handed over as it is on disk; members are inflated and the alignment records
+ * framed on the GPU (csrc/ingest.cu), so the host does no zlib work and only compressed bytes cross PCIe.
+ *   coral_ingest_open : host only — BGZF member table and BAM header; `file` must stay valid until coral_ingest_run.
+ *                       The caller then reads the reference table (coral_ingest_n_ref / _ref_name / _ref_len) and
+ *                       calls coral_set_references, as after coral_bam_read.
+ *   coral_ingest_run  : H2D of the compressed bytes, inflate, framing, then coral_load_records(CORAL_RECORDS_DEVICE)
+ *                       on the framed buffer (owned by the ctx) — the ctx is then in the same state as after a load
+ *                       of the host reader's records, with identical offsets.
+ *   coral_get_read_names : read names of the given records (any placement), 256 bytes per record, NUL padded — what
+ *                       a caller without a host copy of the records uses for pysam's query_name.
+ *   coral_ingest_host_check : the same decoder and framing steps run on the CPU (test hook; mode 1 forces the serial
+ *                       chase).  STATUS: CPU-verified; not yet run on a B200. */
+int coral_ingest_open(coral_ctx* ctx, const uint8_t* file, uint64_t n_bytes);
+int32_t coral_ingest_n_ref(const coral_ctx* ctx);
+const char* coral_ingest_ref_name(const coral_ctx* ctx, int32_t tid);
+int64_t coral_ingest_ref_len(const coral_ctx* ctx, int32_t tid);
+int coral_ingest_run(coral_ctx* ctx, int64_t* n_records, uint64_t* framed_bytes);
+int coral_ingest_used_serial_chase(const coral_ctx* ctx);
+int coral_get_read_names(coral_ctx* ctx, const uint32_t* rec, int64_t n, uint8_t* out);
+int coral_ingest_host_check(const uint8_t* file, uint64_t n_bytes, int mode, uint8_t* recs_out, uint64_t recs_cap,
+                            uint64_t* offsets_out, int64_t rec_cap, int64_t* n_records, uint64_t* framed_bytes,
+                            int64_t* n_candidates, int32_t* used_serial, char* err, size_t err_len);
+
 #ifdef __cplusplus
 }
 #endif

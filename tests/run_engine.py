@@ -55,7 +55,7 @@ def main():
             from coral_b200.infer_breakpoint_graph import bam_to_breakpoint_nanopore
             eng = bam_to_breakpoint_nanopore(bam, seed, placement={"cuda": "auto", "cuda-async": "mapped_async",
                                                                     "cuda-sync": "mapped", "cuda-lazy": "mapped_lazy",
-                                                                    "cuda-copy": "copy"}[kind])
+                                                                    "cuda-copy": "copy", "cuda-ingest": "device_ingest"}[kind])
             assert eng._scan_async == (kind in ("cuda", "cuda-async", "cuda-lazy"))
         st = util.run_pipeline(eng, cn_seg, defer_cov=(kind in ("cuda-async", "cuda-lazy")))
     with open(out, "w") as fp:
