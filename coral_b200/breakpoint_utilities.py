@@ -131,6 +131,72 @@ def alignment2bp(rn, chimeric_alignment, min_bp_match_cutoff, min_mapq, intrvl1,
     return _rows(c, [rn], names)
 
 
+# ---- edit-distance filtered candidate forms (reference :99-126, :189-249) ------------------------------------------
+# Reached only with bam_to_breakpoint_nanopore.nm_filter = True, which the reference never sets (ibg:40; ibg:1351 is
+# commented out): host Python, kept so that the module offers every callable of the reference's.
+def _query_gap(qint, a, b):
+    return int(qint[b][0]) - int(qint[a][1])
+
+
+def alignment2bp_nm(rn, chimeric_alignment, min_bp_match_cutoff, min_mapq, max_nm, intrvl1, intrvl2, gap_mapq=10):
+    """reference :99-126: alignment2bp with both alignments' NM rate below max_nm."""
+    qint, rint, mq, nm = chimeric_alignment[0], chimeric_alignment[1], chimeric_alignment[2], chimeric_alignment[3]
+    n = len(rint)
+
+    def usable(a, b):
+        return mq[a] >= min_mapq and mq[b] >= min_mapq and nm[a] < max_nm and nm[b] < max_nm
+
+    def across(a, b):        # one alignment on each interval, either way round
+        return (interval_overlap(rint[a], intrvl1) and interval_overlap(rint[b], intrvl2)) or \
+               (interval_overlap(rint[b], intrvl1) and interval_overlap(rint[a], intrvl2))
+
+    out, taken = [], [0] * max(n - 1, 0)
+    for i in range(n - 1):
+        g = _query_gap(qint, i, i + 1)
+        if g + min_bp_match_cutoff >= 0 and usable(i, i + 1) and across(i, i + 1):
+            out.append(interval2bp(rint[i], rint[i + 1], (rn, i, i + 1), g) + [mq[i], mq[i + 1]])
+            taken[i] = 1
+    for i in range(1, n - 1):
+        if not taken[i - 1] and not taken[i] and mq[i] < gap_mapq and usable(i - 1, i + 1) and across(i - 1, i + 1):
+            out.append(interval2bp(rint[i - 1], rint[i + 1], (rn, i - 1, i + 1), _query_gap(qint, i - 1, i + 1)) + [mq[i - 1], mq[i + 1]])
+    return out
+
+
+def alignment2bp_nm_l(rn, chimeric_alignment, min_bp_match_cutoff, min_mapq, max_nm, gap_, intrvls, gap_mapq=10):
+    """reference :189-249: alignment2bp_l with both alignments' NM rate below max_nm."""
+    qint, rint, mq, nm = chimeric_alignment[0], chimeric_alignment[1], chimeric_alignment[2], chimeric_alignment[3]
+    n = len(rint)
+
+    def usable(a, b):
+        return mq[a] >= min_mapq and mq[b] >= min_mapq and nm[a] < max_nm and nm[b] < max_nm
+
+    def junction(a, b):      # both on the same amplicon interval, and either a strand switch or a reference jump unlike the query's
+        io = interval_overlap_l(rint[a], intrvls)
+        if io < 0 or io != interval_overlap_l(rint[b], intrvls):
+            return False
+        if rint[b][3] != rint[a][3]:
+            return True
+        if rint[b][3] == '+':
+            ref_gap = int(rint[b][1]) - int(rint[a][2])
+        elif rint[b][3] == '-':
+            ref_gap = int(rint[a][2]) - int(rint[b][1])
+        else:
+            return False
+        g = _query_gap(qint, a, b)
+        return abs(g - ref_gap) > max(gap_, abs(g * 0.2))
+
+    out, taken = [], [0] * max(n - 1, 0)
+    for i in range(n - 1):
+        g = _query_gap(qint, i, i + 1)
+        if g + min_bp_match_cutoff >= 0 and usable(i, i + 1) and junction(i, i + 1):
+            out.append(interval2bp(rint[i], rint[i + 1], (rn, i, i + 1), g) + [mq[i], mq[i + 1]])
+            taken[i] = 1
+    for i in range(1, n - 1):
+        if not taken[i - 1] and not taken[i] and mq[i] < gap_mapq and usable(i - 1, i + 1) and junction(i - 1, i + 1):
+            out.append(interval2bp(rint[i - 1], rint[i + 1], (rn, i - 1, i + 1), _query_gap(qint, i - 1, i + 1)) + [mq[i - 1], mq[i + 1]])
+    return out
+
+
 def sort_chrom_names(chromlist):
     def key(x):
         v = x[3:] if x.startswith("chr") else x

@@ -152,6 +152,23 @@ def candidate_vectors(rng):
     return out
 
 
+def nm_vectors(rng):
+    """The edit-distance filtered forms (bu:99-126, :189-249; reached only with nm_filter = True, which the reference never
+    sets): the same alignments with per-alignment NM rates on both sides of max_nm."""
+    out = []
+    for t in range(120):
+        c = CHROMS[int(rng.integers(3))]
+        ivs = []
+        for _ in range(int(rng.integers(1, 4))):
+            a = int(rng.integers(10 ** 5, 10 ** 6))
+            ivs.append([c if rng.random() < 0.7 else "chr12", a, a + int(rng.integers(20000, 400000)), int(rng.integers(3))])
+        ca = rand_chimeric(rng, ivs)
+        ca[3] = [float(rng.choice([0.0, 0.01, 0.05, 0.0999, 0.1, 0.2])) for _ in ca[1]]
+        out.append({"fn": "alignment2bp_nm_l", "args": ["rn%d" % t, ca, 100, 20, 0.1, 100, ivs]})
+        out.append({"fn": "alignment2bp_nm", "args": ["rn%d" % t, ca, 100, 20, 0.1, ivs[0], ivs[-1]]})
+    return out
+
+
 def make_bp(k, c1, p1, o1, c2, p2, o2, rgap=0, flag=0, mq=(60, 60)):
     return [c1, int(p1), o1, c2, int(p2), o2, ["r%d" % k, k % 5, k % 5 + 1], int(rgap), int(flag), int(mq[0]), int(mq[1])]
 
@@ -272,7 +289,7 @@ def main():
     import cigar_parsing as cp
     rng = np.random.default_rng(20240215)
     vectors = cigar_vectors(rng) + satag_vectors(rng) + interval_vectors(rng) + candidate_vectors(rng) + \
-        cluster_vectors(rng) + bpc2bp_vectors(rng)
+        cluster_vectors(rng) + bpc2bp_vectors(rng) + nm_vectors(np.random.default_rng(20240216))
     counts = {}
     for v in vectors:
         v["out"] = run_vector((cp, bu), v)
@@ -283,7 +300,8 @@ def main():
     print(len(vectors), "vectors,", os.path.getsize(OUT) // 1024, "KB")
     for k in sorted(counts):
         print("  %-36s %d" % (k, counts[k]))
-    n_c = sum(1 for v in vectors if v["fn"].startswith("alignment2bp") and v["out"])
+    n_c = sum(1 for v in vectors if v["fn"].startswith("alignment2bp") and "_nm" not in v["fn"] and v["out"])
+    print("  alignment2bp_nm* vectors that emit candidates:", sum(1 for v in vectors if "_nm" in v["fn"] and v["out"]))
     print("  alignment2bp* vectors that emit candidates:", n_c)
 
 

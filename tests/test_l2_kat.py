@@ -72,6 +72,20 @@ def test_oracle_matches_reference_vectors():
     assert bad == [], bad[:3]
 
 
+HOST_ONLY = ("interval_overlap", "interval_overlap_l", "interval_include", "interval_include_l", "interval_adjacent",
+             "interval_exclusive", "interval2bp", "alignment2bp_nm", "alignment2bp_nm_l")
+
+
+def test_host_python_callables_of_the_dropin_match_reference_vectors():
+    """The callables of coral_b200.breakpoint_utilities that are plain host Python (predicates, interval2bp and the
+    nm-filtered candidate forms the reference never reaches) need no GPU."""
+    from coral_b200 import breakpoint_utilities as bu
+    vs = [v for v in vectors() if v["fn"] in HOST_ONLY]
+    assert len(vs) > 600 and sum(1 for v in vs if "_nm" in v["fn"] and v["out"]) >= 20
+    bad = mismatches((bu,), vs)
+    assert bad == [], bad[:3]
+
+
 @pytest.mark.gpu
 def test_dropin_modules_match_reference_vectors(built_lib):
     from coral_b200 import breakpoint_utilities as bu, cigar_parsing as cp
