@@ -333,7 +333,16 @@ class HostSteps(PathConstraintSteps):
             self.lr_graph[self.ccid2id[self.source_edge_ccids[srci]] - 1].add_source_edge(srce[3], srce[4], srce[5])
 
     # ---- ibg:213-323 ------------------------------------------------------------------------------------
+    def _no_nm_filter(self):
+        """nm_filter = True routes the reference through the edit-distance filtered candidate forms (ibg:427, :682, :728).
+        The reference never sets it (ibg:40; ibg:1351 is commented out) and this class does not build that route: say so
+        instead of silently returning the unfiltered result."""
+        if self.nm_filter:
+            raise NotImplementedError("nm_filter = True is not supported (dead in the reference, ibg:40 / :1351); the "
+                                      "alignment2bp_nm / alignment2bp_nm_l forms exist in breakpoint_utilities")
+
     def find_amplicon_intervals(self):
+        self._no_nm_filter()
         ops = self._ops
         d = self.interval_delta
         for iv in self.amplicon_intervals:  # seeds -> CN-segment bounds, padded when a segment exists there

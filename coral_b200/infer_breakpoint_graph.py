@@ -242,6 +242,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
     # ---- a3: ibg:721-802 ------------------------------------------------------------------------------------
     @_gc_paused
     def find_smalldel_breakpoints(self):
+        self._no_nm_filter()
         t, s, e = self._interval_arrays()
         self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
         lia = self.large_indel_alignments
@@ -281,6 +282,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
     # ---- a4/a5: ibg:676-718 ---------------------------------------------------------------------------------
     @_gc_paused
     def find_breakpoints(self):
+        self._no_nm_filter()
         t, s, e = self._interval_arrays()
         self._ctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
         c = self._chim_ctx.candidates_l(t, s, e)
@@ -498,6 +500,13 @@ class bam_to_breakpoint_nanopore(HostSteps):
 
 
 BamToBreakpointNanopore = bam_to_breakpoint_nanopore   # name used by BASELINE.json's north_star
+
+edge_type_to_index = {'s': 0, 'c': 1, 'd': 2}          # reference :17
+
+
+def print_complete_message():
+    """Reference :1398-1399 (called by CoRAL.py:30 after the run)."""
+    logging.info(_t() + "Total runtime.")
 
 
 @_gc_paused

@@ -266,3 +266,29 @@ def chimeric_alignment_to_path(g, rints, ai_list, bp_list):
                 out += chimeric_alignment_to_path_r(g, rints, a_out, far)
         last = far
     return out
+
+
+def longest_path_dict(path_constraints_):
+    """Reference :378-417 (called by cycle_decomposition.py:1512, the consumer of compute_path_constraints): every
+    path as its multiset of edges; a path whose multiset is contained in another path's is dropped — scanning from the
+    last path to the first, the container being the first other path that holds it — and hands its support to the
+    container when larger.  -> [edge multisets, indices of the surviving paths, supports]."""
+    bags = []
+    for path in path_constraints_[0]:
+        bag = {}
+        for edge in path[0::2]:
+            bag[edge] = bag.get(edge, 0) + 1
+        bags.append(bag)
+    ids = list(range(len(bags)))
+    support = list(path_constraints_[1][:len(bags)])
+    for i in range(len(bags) - 1, -1, -1):
+        mine = bags[i]
+        host = -1
+        for j, other in enumerate(bags):
+            if j != i and all(other.get(e, 0) >= c for e, c in mine.items()):
+                host = j
+                break
+        if host >= 0:
+            support[host] = max(support[host], support[i])
+            del bags[i], ids[i], support[i]
+    return [bags, ids, support]

@@ -83,3 +83,22 @@ def test_compute_path_constraints_matches_reference():
     assert n_ok > 100 and n_raise > 0 and n_paths > 100
     for k in ("one", "many", "del1", "deln", "mixed"):       # every read class ran and kept at least one path
         assert classes[k] > 20 and classes[k + "_kept"] > 0, classes
+
+
+def test_longest_path_dict_matches_reference_vectors():
+    """path_constraints.longest_path_dict (the hand-over to cycle decomposition) against vectors of the unmodified
+    reference: golden pipeline constraints + seeded walks with sub-walks, duplicates, repeated edges, empty paths."""
+    import gzip
+    import importlib.util
+    import json
+    import os
+    here = os.path.dirname(os.path.abspath(__file__))
+    spec = importlib.util.spec_from_file_location("make_lpd_kat", os.path.join(here, "golden", "make_lpd_kat.py"))
+    kat = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(kat)
+    from coral_b200 import path_constraints as pc
+    with gzip.open(os.path.join(here, "golden", "lpd_kat.json.gz"), "rt") as fp:
+        vectors = json.load(fp)
+    assert len(vectors) >= 60 and sum(len(v["paths"]) - len(v["out"]["ids"]) for v in vectors) > 100
+    for k, v in enumerate(vectors):
+        assert kat.run_vector(pc.longest_path_dict, v) == v["out"], k
