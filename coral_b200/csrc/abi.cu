@@ -142,7 +142,9 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
                       at.devicePointer != nullptr;
         cudaGetLastError();
         if (!mapped) {
-            if (n > 0) CORAL_CUDA(c, cudaHostRegister(const_cast<uint8_t*>(recs), nbytes, cudaHostRegisterMapped | cudaHostRegisterPortable));
+            // the ABI promises the kernels 64 readable bytes past `nbytes` (include/coral_b200.h): page-lock them too, else
+            // a record ending just before a page boundary leaves the slack on an unregistered page (device fault)
+            if (n > 0) CORAL_CUDA(c, cudaHostRegister(const_cast<uint8_t*>(recs), nbytes + 64, cudaHostRegisterMapped | cudaHostRegisterPortable));
             c->host_registered = const_cast<uint8_t*>(recs);
             if (n > 0) CORAL_CUDA(c, cudaPointerGetAttributes(&at, recs));
         }

@@ -18,7 +18,21 @@ from collections import namedtuple
 import numpy as np
 
 from . import global_names
-from .breakpoint_graph import BreakpointGraph
+from .breakpoint_graph import BreakpointGraph as _LocalBreakpointGraph
+
+
+def reference_graph_class():
+    """The reference's own ``breakpoint_graph.BreakpointGraph`` (reference ``breakpoint_graph.py:83-765``) when that
+    module is importable under its bare name — i.e. when the drop-in runs inside the reference (``src/`` on
+    ``sys.path``, cvxopt installed): the graphs handed to ``compute_cn_lr`` (``infer_breakpoint_graph.py:1388-1389``) and
+    to ``cycle_decomposition.reconstruct_cycles`` are then instances of the class those functions were written for.
+    None when it is not importable (the GPU box of this repo: no reference, no cvxopt)."""
+    try:
+        import breakpoint_graph as ref_bg           # bare name: the reference's module layout (ibg:10-14)
+    except Exception:                                # noqa  (ImportError, or cvxopt missing inside it)
+        return None
+    cls = getattr(ref_bg, "BreakpointGraph", None)
+    return cls if cls is not None and hasattr(cls, "compute_cn_lr") else None
 from .path_steps import PathConstraintSteps
 
 _Hit = namedtuple("_Hit", ["begin", "end", "data"])
@@ -76,6 +90,7 @@ class HostSteps(PathConstraintSteps):
     max_breakpoint_distance_cutoff = 2000
     min_del_len = 600
     nm_filter = False
+    graph_cls = None            # container class of lr_graph; None = the reference's BreakpointGraph when importable
 
     def _init_state(self):
         """Per-instance containers (the reference keeps them as class attributes, ibg:22-61; App. A.10)."""
@@ -272,13 +287,16 @@ class HostSteps(PathConstraintSteps):
                 if srce[3] == seg[0] and seg[1] < srce[4] < seg[2] and srce[5] in '+-':
                     add_split(ai, srce[4], srce[5], len(self.new_bp_list) + srci, 4)
 
+        # the container: `graph_cls` of the instance / class when set, else the reference's class when importable, else
+        # the local one with the same row layouts (coral_b200/breakpoint_graph.py)
+        graph_cls = getattr(self, "graph_cls", None) or reference_graph_class() or _LocalBreakpointGraph
         next_id = 1
         for seg in self.amplicon_intervals:
             if seg[3] not in self.ccid2id:
                 self.ccid2id[seg[3]] = next_id
                 next_id += 1
         for _ in range(len(self.ccid2id)):
-            self.lr_graph.append(BreakpointGraph())
+            self.lr_graph.append(graph_cls())
 
         for ai in splits.keys():
             cuts = splits[ai]

@@ -41,12 +41,12 @@ class bam_to_breakpoint_nanopore(HostSteps):
         while the full scan is still pulling CIGAR / SEQ bytes over the link; `read_cns`'s coverage sum is evaluated
         when `normal_cov` / `min_cluster_cutoff` are first read; 172 vs 200 ms per C2 pass),
         "mapped_lazy" (pre-scan only; the full scan runs when a method needs it), "auto" (mapped_async when the
-        buffer has the 64 bytes of slack the mapped modes need, else copy) or "device_ingest" (opt-in: `lr_bamfile` is
-        inflated and framed on the GPU; CPU-verified only so far, see csrc/ingest.cu)."""
+        buffer has the 64 bytes of slack the mapped modes need, else copy) or "device_ingest" (`lr_bamfile` is
+        inflated and framed on the GPU, the records never exist in host memory: csrc/ingest.cu)."""
         self._init_state()
         self._normal_pending = None              # read_cns's coverage call, deferred while the scan is still running
         if placement == "device_ingest":
-            # opt-in (SURVEY 8f rank 3, csrc/ingest.cu): the file's BGZF bytes go to the GPU as they are on disk and are
+            # SURVEY 8f rank 3 (csrc/ingest.cu): the file's BGZF bytes go to the GPU as they are on disk and are
             # inflated and framed there; no host copy of the records exists, read names come back through the ctx
             self._ctx = _abi.Context(device)
             gpu_ops.set_default_device(device)
@@ -544,7 +544,10 @@ def reconstruct_graph(args):
         b2bn.assign_cov()
         logging.info(_t() + "Fetched read coverage for all sequence and concordant edges.")
         for gi, g in enumerate(b2bn.lr_graph):
-            if hasattr(g, "compute_cn_lr"):
-                g.compute_cn_lr(b2bn.normal_cov)
+            if hasattr(g, "compute_cn_lr"):          # the reference's own class (host_steps.reference_graph_class)
+                g.compute_cn_lr(b2bn.normal_cov)     # reference :1388-1389, cvxopt
+            else:
+                logging.warning(_t() + "compute_cn_lr unavailable (the reference's breakpoint_graph / cvxopt is not "
+                                "importable here): amplicon %d graph is written with CN 0.0." % (gi + 1))
             output_breakpoint_graph_lr(g, args.output_prefix + "_amplicon" + str(gi + 1) + "_graph.txt")
     return b2bn

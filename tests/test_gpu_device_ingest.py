@@ -1,12 +1,7 @@
-"""GPU tests of the device-side BAM ingest (csrc/ingest.cu).
-
-OPT-IN: the kernels were written after the round's GPU budget was spent and have not run on a B200 yet (their decoder
-core and framing steps are verified on the CPU, tests/test_ingest_cpu.py).  Until a first supervised run these tests
-only run with CORAL_TEST_UNVERIFIED=1, so that an unproven kernel cannot take the box (and the rest of the GPU suite)
-down with it:
-
-    CORAL_TEST_UNVERIFIED=1 timeout 300 python -m pytest tests/test_unverified_device_ingest.py -q -m gpu
-"""
+"""GPU tests of the device-side BAM ingest (csrc/ingest.cu): BGZF inflate + record framing on
+the GPU against the host reader (zlib) — record table, name hashes, SA/NM columns, read names — and the whole pipeline
+from placement="device_ingest" against the reference-generated fixtures.  First run on a B200 in round 2 (4 passed,
+gpurun visit 1); the decoder core and the framing steps are also verified on the CPU (tests/test_ingest_cpu.py)."""
 import os
 
 import numpy as np
@@ -16,9 +11,7 @@ import test_golden_cpu as G
 import test_ingest_cpu as H
 from sim import bgzf
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("CORAL_TEST_UNVERIFIED") != "1",
-                                 reason="device-side ingest has not run on a B200 yet: set CORAL_TEST_UNVERIFIED=1")]
+pytestmark = pytest.mark.gpu
 
 
 def _ingest(path):

@@ -196,3 +196,34 @@ def test_empty_and_malformed_inputs(built_lib, edge):
     with pytest.raises(RuntimeError):
         c.region_coverage([0, 0], [100, 150], [200, 250])
     c.close()
+
+
+@pytest.mark.parametrize("placement", ["mapped", "mapped_async", "mapped_lazy"])
+def test_unpinned_buffer_ending_at_a_page_boundary(built_lib, edge, placement):
+    """A caller's plain (not page-locked) buffer whose last record ends 16 bytes before a page boundary: the 64 bytes of
+    slack the ABI promises the kernels lie mostly on the NEXT page, which must be registered with the rest
+    (csrc/abi.cu: cudaHostRegister(nbytes + 64)) — else the device over-read faults."""
+    import mmap
+    from coral_b200 import _abi
+    rec, off = edge["rec"], edge["off"]
+    nb = int(off[-1])
+    page = mmap.PAGESIZE
+    npages = (nb + 16 + page - 1) // page
+    mm = mmap.mmap(-1, (npages + 1) * page)                        # anonymous, page aligned, not pinned
+    buf = np.frombuffer(mm, np.uint8)
+    start = npages * page - 16 - nb
+    assert start >= 0 and start % 16 == 0 and (start + nb + 16) % page == 0
+    buf[start:start + nb] = rec[:nb]
+    c = _abi.Context(0)
+    c.set_references([r[0] for r in REFS])
+    c.load_records(buf[start:start + nb], off, placement=placement, slack=page)
+    c.wait_scan()
+    _table_matches(c.record_table(), edge["ora"])
+    f = c.fetch()
+    c2 = _ctx(rec, off)
+    f2 = c2.fetch()
+    for k in f2:
+        assert np.array_equal(f[k], f2[k]), k
+    c.close(); c2.close()
+    del buf
+    mm.close()

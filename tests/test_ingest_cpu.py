@@ -1,7 +1,7 @@
 """CPU tests of the device-side BAM ingest's host-verifiable pieces (csrc/inflate.cuh, csrc/ingest.cu — SURVEY.md §8f
 rank 3): the DEFLATE core and every per-element framing step are __host__ __device__; coral_ingest_host_check runs
 them on the CPU and must reproduce the host reader (zlib + serial framing, csrc/bam_reader.cpp) byte for byte.
-The kernels themselves are exercised by tests/test_unverified_device_ingest.py (opt-in until they have run on a B200)."""
+The kernels themselves are exercised by tests/test_gpu_device_ingest.py (-m gpu)."""
 import os
 import struct
 import zlib
