@@ -239,12 +239,29 @@ class AlignedSegment(object):
         return base, blocks
 
 
+_MEMORY_BAMS = {}
+
+
+def register_memory_bam(key, refs, data, rec_off):
+    """Make ``AlignmentFile("mem:<key>")`` open an already decoded record set instead of a file: `refs` [(name, length)],
+    `data` = bytes holding the alignment records, `rec_off` = uint64[n+1] record offsets into it (any framing — the shim
+    only ever addresses records through their offsets).  What bench.py's reference legs use at BASELINE.json's full
+    size, so that the CPU arm starts where the GPU arm's e2e starts: from decoded records in host memory."""
+    if not isinstance(data, bytes):
+        data = bytes(data)
+    _MEMORY_BAMS[key] = (list(refs), data, np.ascontiguousarray(rec_off, dtype=np.uint64))
+    return "mem:" + key
+
+
 class AlignmentFile(object):
     def __init__(self, path, mode="rb"):
         assert mode == "rb"
         self.filename = path
-        self._data = inflate_bgzf(path)
-        self.refs, self._off = parse_bam(self._data)
+        if isinstance(path, str) and path.startswith("mem:"):
+            self.refs, self._data, self._off = _MEMORY_BAMS[path[4:]]
+        else:
+            self._data = inflate_bgzf(path)
+            self.refs, self._off = parse_bam(self._data)
         self.references = tuple(r[0] for r in self.refs)
         self.lengths = tuple(r[1] for r in self.refs)
         self._tid_of = {r: i for i, r in enumerate(self.references)}

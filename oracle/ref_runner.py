@@ -18,7 +18,19 @@ import sys
 import time
 import types
 
-REF_SRC = os.environ.get("CORAL_REFERENCE_SRC", "/root/reference/src")
+def _ref_src():
+    """CORAL_REFERENCE_SRC, else /root/reference/src (build container), else the travelling copy oracle/_ref/src
+    (oracle/make_ref.py: byte-identical files, git-ignored) — what exists on the GPU box."""
+    if os.environ.get("CORAL_REFERENCE_SRC"):
+        return os.environ["CORAL_REFERENCE_SRC"]
+    here = os.path.dirname(os.path.abspath(__file__))
+    for d in ("/root/reference/src", os.path.join(here, "_ref", "src")):
+        if os.path.exists(os.path.join(d, "infer_breakpoint_graph.py")):
+            return d
+    return "/root/reference/src"
+
+
+REF_SRC = _ref_src()
 
 
 def install_shims():

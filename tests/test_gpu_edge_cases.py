@@ -224,6 +224,4 @@ def test_unpinned_buffer_ending_at_a_page_boundary(built_lib, edge, placement):
     f2 = c2.fetch()
     for k in f2:
         assert np.array_equal(f[k], f2[k]), k
-    c.close(); c2.close()
-    del buf
-    mm.close()
+    c.close(); c2.close()        # (the anonymous mapping is released with its last view)

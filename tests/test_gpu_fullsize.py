@@ -1,8 +1,24 @@
-"""Size-independent properties at BASELINE.json's full size (C2: 260 k records, 13 GB of decoded BAM, 7.2 aligned
-Gbases), where the CPU oracle would take hours: sums against the generator's own counts, additivity of coverage,
-idempotence of the scan, equality of the two record placements, structural invariants of the chimeric table."""
+"""Parity at BASELINE.json's NAMED sizes.
+
+(1) Against the UNMODIFIED reference: tests/golden/{full_c1,full_c2,full_c3,full_c1n,sub_c4,sub_c5}.json.gz hold compact
+digests (tests/golden/full_digest.py) of the state the reference itself produced on C1 / C2 / C3 at scale 1.0 and on
+stated sub-samples of C4 / C5 (tests/golden/make_full_digests.py: minutes per case in the build container — C2 x1.0 is
+75 s of BAM inflate + 74 s of reference Python).  The CUDA class must reproduce every digest: breakpoints, read-support
+sets, the chimeric table, normal_cov, per-edge counts, byte-identical graph.txt, path constraints.
+(2) Size-independent properties on C2 x1.0 (13 GB of decoded BAM): sums against the generator's own counts, additivity
+of coverage, idempotence of the scan, equality of the record placements, invariants of the chimeric table."""
+import gzip
+import json
+import os
+import subprocess
+import sys
+
 import numpy as np
 import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "golden"))
+import full_digest as FD  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 
@@ -28,6 +44,35 @@ def _load(cfg, data, placement):
     else:
         c.load_records(data.rec, data.rec_off)
     return c
+
+
+def _digest_case(case, tmp_path_factory, *extra):
+    gold_path = os.path.join(HERE, "golden", case + ".json.gz")
+    if not os.path.exists(gold_path):
+        pytest.skip("no committed digest for " + case)
+    with gzip.open(gold_path, "rt") as fp:
+        gold = json.load(fp)
+    out = str(tmp_path_factory.mktemp("fd_" + case) / "digest.json")
+    env = dict(os.environ, PYTHONHASHSEED="0")
+    subprocess.check_call([sys.executable, os.path.join(HERE, "run_full_digest.py"), case, out] + list(extra), env=env)
+    got = json.load(open(out))
+    assert got["n_records"] == gold["n_records"] and got["decoded_bytes"] == gold["decoded_bytes"]
+    assert FD.compare_digests(got["stages"], gold["stages"]) == []
+    for a, b in zip(got["stages"]["assign_cov"]["graphs"], gold["stages"]["assign_cov"]["graphs"]):
+        assert a["graph_txt"] == b["graph_txt"]                 # byte-identical graph.txt (CN column 0: no cvxopt)
+    return got
+
+
+@pytest.mark.parametrize("case", ["full_c1", "full_c2", "full_c3", "full_c1n", "sub_c4", "sub_c5"])
+def test_named_size_matches_the_unmodified_reference(built_lib, case, tmp_path_factory):
+    _digest_case(case, tmp_path_factory)
+
+
+@pytest.mark.parametrize("case,world", [("full_c2", 3), ("sub_c4", 4)])
+def test_named_size_sharded_matches_the_unmodified_reference(built_lib, case, world, tmp_path_factory):
+    """The same digests from `world` contiguous genomic-bin shards of the file (thread ranks on one GPU): every junction
+    of C4 has its two sides on different shards, so the chimeric exchange carries cross-shard reads."""
+    _digest_case(case, tmp_path_factory, "auto", "--world", str(world))
 
 
 def test_full_size_properties(built_lib, c2_full):
