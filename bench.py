@@ -344,8 +344,13 @@ def build_plan(eng, cn_seg):
     return plan
 
 
-def device_pass(ctx, plan, gpu_ops):
-    """One pass of the hot path on device-resident records; every result table is read back."""
+def device_pass(ctx, plan, gpu_ops, pipelined=True):
+    """One pass of the hot path on device-resident records; every result table is read back.
+    pipelined: as ONE stream of kernels (coral_pass_begin / coral_pass_end): the calls below only enqueue, the result
+    arrays are filled by one deferred copy each when the pass ends with its single synchronisation; launch sizes that
+    depend on device results are those of the previous pass over the same records, checked on the device."""
+    if pipelined:
+        ctx.pass_begin()
     ctx.rescan()
     out = {}
     out["normal"] = ctx.region_coverage(*plan["normal"])
@@ -355,10 +360,13 @@ def device_pass(ctx, plan, gpu_ops):
     if len(c["chr1"]):
         out["cl1"] = gpu_ops.cluster_arrays(ctx, c, plan["cutoff"], 2000, plan["cutoff"], 100)
     cand = ctx.candidates_l(*plan["intervals"])
+    out["cand"] = cand
     if cand["n"]:
-        out["cl2"] = gpu_ops.cluster_arrays(ctx, cand, plan["cutoff"], 2000, plan["cutoff"], 100)
+        out["cl2"] = ctx.cluster_call_candidates(cand["n"], plan["cutoff"], 2000, plan["cutoff"], 100)
     out["seq"] = ctx.region_coverage(*plan["seq_edges"])
     out["conc"] = ctx.concordant(*plan["conc"])
+    if pipelined:
+        out["replayed"] = ctx.pass_end()
     return out
 
 
@@ -503,6 +511,9 @@ def main():
                     help="C2 = BASELINE.json configs[1] (the headline, default); C3 / C1 / C1n: extra lines for profiles/ "
                          "(small-deletion stage, non-ACGT coverage path); N=1 only")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (development aid)")
+    ap.add_argument("--no-pipeline", action="store_true",
+                    help="device pass call by call (a synchronisation inside every entry point) instead of as one pipelined "
+                         "pass (development aid: what the pass mode buys)")
     ap.add_argument("--e2e-placement", default="mapped_async", choices=["mapped", "mapped_async", "copy"],
                     help="e2e arm: kernels read the pinned host records in place over PCIe (mapped; mapped_async = fetch and "
                          "the host steps after it run next to the scan, the default at N=1: 172 vs 200 ms per C2 pass) or after a full "
@@ -634,7 +645,7 @@ def main():
     def one_pass():
         if world > 1:
             return sharded_device_pass(eng0, plan, gpu_ops)
-        return device_pass(ctx, plan, gpu_ops)
+        return device_pass(ctx, plan, gpu_ops, pipelined=not a.no_pipeline)
 
     def n_launches():
         return ctx.launch_count + (eng0._cctx.launch_count if world > 1 else 0)
@@ -681,8 +692,9 @@ def main():
     barrier()
     t0 = time.perf_counter()
     scan_ms, stage_ms = [], np.zeros(8)
+    replayed = 0
     for _ in range(a.steps):
-        one_pass()
+        replayed += int(bool(one_pass().get("replayed")))
         scan_ms.append(ctx.stage_ms(0))
         stage_ms += np.array([max(ctx.stage_ms(s), 0.0) for s in range(8)])
     barrier()
@@ -747,6 +759,10 @@ def main():
                 "d2h_bytes_per_step": d2h, "placement": a.e2e_placement, "steps": e2e_steps,
                 "ms_per_pass": [round(x, 2) for x in e2e_ms], "stage_ms": e2e_stage},
         "gpu_launches": int(launches_all),
+        "device_pass": {"pipelined": (world == 1 and not a.no_pipeline), "steps_without_intermediate_sync": replayed,
+                        "note": "one stream of kernels per step (coral_pass_begin / coral_pass_end): one synchronisation and one "
+                                "deferred copy per result table; launch sizes that depend on device results are replayed from the "
+                                "previous pass over the same records and checked on the device"},
         "roofline": {"bound": "hbm", "kernel": "k_scan_records", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": k_ms,

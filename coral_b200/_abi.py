@@ -170,6 +170,31 @@ class Context(object):
         self._L = L
         self.references = ()
         self._keep = []
+        self._pass_keep = None      # inside a pipelined pass: objects the C side writes at pass_end + finalizers
+        self._pass_fin = []
+
+    # ---- pipelined pass (include/coral_b200.h: coral_pass_begin / coral_pass_end) --------------------------------
+    def pass_begin(self):
+        """Until pass_end() the entry points only enqueue their kernels: the arrays they return are FILLED at pass_end()
+        (do not read them before), counts are those of the last complete pass over the same inputs."""
+        self._check(self._L.coral_pass_begin(self._h))
+        self._pass_keep, self._pass_fin = [], []
+
+    def pass_end(self):
+        """-> True when the pass ran without intermediate synchronisation (sizes replayed from the previous pass)."""
+        rp = ctypes.c_int32()
+        try:
+            self._check(self._L.coral_pass_end(self._h, ctypes.byref(rp)))
+            for fn in self._pass_fin:
+                fn()
+        finally:
+            self._pass_keep, self._pass_fin = None, []
+        return bool(rp.value)
+
+    def _hold(self, *objs):
+        """Keep output buffers alive until pass_end (the C side holds their addresses)."""
+        if self._pass_keep is not None:
+            self._pass_keep.extend(objs)
 
     def _check(self, rc):
         if rc != 0:
@@ -332,6 +357,7 @@ class Context(object):
         bs = np.zeros(n, np.int64)
         rc = np.zeros(n, np.int64)
         self._check(self._L.coral_region_coverage(self._h, _p(tid), _p(start), _p(stop), n, _p(bs), _p(rc)))
+        self._hold(bs, rc)
         return bs, rc
 
     def fetch(self):
@@ -341,6 +367,9 @@ class Context(object):
         self._check(self._L.coral_fetch(self._h, ctypes.byref(nr), ctypes.byref(na), ctypes.byref(s1), ctypes.byref(s2),
                                         ctypes.byref(nn), ctypes.byref(zd)))
         nr, na = nr.value, na.value
+        if self._pass_keep is not None:          # the nm sums are written at pass_end
+            self._hold(s1, s2, nn, zd)
+            self._pass_fin.append(lambda: out.update(nm_sum=s1.value, nm_sumsq=s2.value, nm_n=nn.value, nm_zero_div=zd.value))
         out = {"n_reads": nr, "n_aln": na, "nm_sum": s1.value, "nm_sumsq": s2.value, "nm_n": nn.value,
                "nm_zero_div": zd.value,
                "read_first_rec": np.zeros(nr, np.uint32), "read_len": np.zeros(nr, np.int64),
@@ -353,6 +382,7 @@ class Context(object):
             self._h, _p(out["read_first_rec"]), _p(out["read_len"]), _p(out["read_status"]), _p(out["aln_ptr"]),
             _p(out["qs"]), _p(out["qe"]), _p(out["tid"]), _p(out["rstart"]), _p(out["rend"]), _p(out["strand"]),
             _p(out["mapq"]), _p(out["nm"])))
+        self._hold(out)
         return out
 
     @staticmethod
@@ -372,6 +402,7 @@ class Context(object):
             self._check(self._L.coral_get_smalldel(self._h, _p(out["rec"]), _p(out["ai"]), _p(out["next_start"]),
                                                    _p(out["prev_end"]), _p(out["first_start"]), _p(out["last_end"]),
                                                    _p(out["mapq"])))
+        self._hold(out)
         return out
 
     def candidates_l(self, tid, start, end_incl):
@@ -389,6 +420,7 @@ class Context(object):
                 self._h, _p(out["read"]), _p(out["i"]), _p(out["j"]), _p(out["chr1"]), _p(out["pos1"]), _p(out["o1"]),
                 _p(out["chr2"]), _p(out["pos2"]), _p(out["o2"]), _p(out["rgap"]), _p(out["flag"]), _p(out["mq1"]),
                 _p(out["mq2"])))
+        self._hold(out)
         return out
 
     def cluster_call(self, chr1, pos1, o1, chr2, pos2, o2, rgap, flag, mq1, mq2, min_cluster_size, bp_distance_cutoff,
@@ -403,7 +435,9 @@ class Context(object):
             self._h, ctypes.c_int64(n), _p(chr1), _p(pos1), _p(o1), _p(chr2), _p(pos2), _p(o2), _p(rgap), _p(flag),
             _p(mq1), _p(mq2), ctypes.c_double(min_cluster_size), ctypes.c_int32(bp_distance_cutoff),
             ctypes.c_double(peel_cutoff), ctypes.c_int32(match_cutoff), ctypes.c_int32(max_peels), ctypes.byref(nc)))
-        nc = nc.value
+        return self._clusters_out(n, nc.value)
+
+    def _clusters_out(self, n, nc):
         out = {"n_clusters": nc, "order": np.zeros(n, np.uint32), "cluster_ptr": np.zeros(nc + 1, np.uint32),
                "n_sub": np.zeros(nc, np.int32), "sub_of": np.zeros(n, np.int32), "row_pos1": np.zeros(n, np.int32),
                "row_pos2": np.zeros(n, np.int32), "row_nb": np.zeros(n, np.int32), "row_first": np.zeros(n, np.uint32),
@@ -412,7 +446,17 @@ class Context(object):
             self._check(self._L.coral_get_clusters(
                 self._h, _p(out["order"]), _p(out["cluster_ptr"]), _p(out["n_sub"]), _p(out["sub_of"]), _p(out["row_pos1"]),
                 _p(out["row_pos2"]), _p(out["row_nb"]), _p(out["row_first"]), _p(out["row_stats"])))
+        self._hold(out)
         return out
+
+    def cluster_call_candidates(self, n, min_cluster_size, bp_distance_cutoff, peel_cutoff, match_cutoff, max_peels=0):
+        """cluster_call on the candidate table the last candidates_l / candidates_pair left on the device (`n` = its size):
+        the candidates do not travel through the host."""
+        nc = ctypes.c_int64()
+        self._check(self._L.coral_cluster_call_candidates(
+            self._h, ctypes.c_double(min_cluster_size), ctypes.c_int32(bp_distance_cutoff), ctypes.c_double(peel_cutoff),
+            ctypes.c_int32(match_cutoff), ctypes.c_int32(max_peels), ctypes.byref(nc)))
+        return self._clusters_out(int(n), nc.value)
 
     def concordant_rows_only(self, tid, p):
         """The (edge, record, mask) rows of this ctx's records stay on the device (concordant_pack); no count."""
@@ -430,6 +474,7 @@ class Context(object):
         rows = {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
         if nr:
             self._check(self._L.coral_get_concordant_rows(self._h, _p(rows["edge"]), _p(rows["rec"]), _p(rows["mask"])))
+        self._hold(rows)
         return rows
 
     def concordant(self, tid, p, rb_edge, rb_rec, fetch_rows=True):
@@ -444,6 +489,7 @@ class Context(object):
         self._check(self._L.coral_concordant(self._h, _p(tid), _p(p), n, ctypes.c_int64(len(rb_edge)), _p(rb_edge), _p(rb_rec),
                                              _p(cnt), ctypes.byref(nr)))
         self._stab_n = nr = nr.value
+        self._hold(cnt)
         if fetch_rows:
             return cnt, self.concordant_rows()
         return cnt, {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
@@ -536,6 +582,7 @@ class Context(object):
                 self._h, _p(out["read"]), _p(out["i"]), _p(out["j"]), _p(out["chr1"]), _p(out["pos1"]), _p(out["o1"]),
                 _p(out["chr2"]), _p(out["pos2"]), _p(out["o2"]), _p(out["rgap"]), _p(out["flag"]), _p(out["mq1"]),
                 _p(out["mq2"])))
+        self._hold(out)
         return out
 
     def candidates_pair(self, reads, tid2, start2, end2):

@@ -4,6 +4,7 @@
 #include <new>
 
 #include "ctx.h"
+#include "relops.cuh"
 
 extern "C" {
 
@@ -53,6 +54,8 @@ void coral_destroy(coral_ctx* c) {
                      &c->chim.read_first_rec, &c->chim.read_len, &c->chim.read_status, &c->chim.aln_ptr, &c->chim.qs,
                      &c->chim.qe, &c->chim.tid, &c->chim.rs, &c->chim.re, &c->chim.strand, &c->chim.mapq, &c->chim.nm};
     for (DevBuf* b : all) b->release();
+    if (c->pass.d_flag) cudaFree(c->pass.d_flag);
+    for (auto& ch : c->pass.pinned) cudaFreeHost(ch.p);
     for (DevBuf& b : c->sw) b.release();
     for (DevBuf& b : c->cw) b.release();
     for (DevBuf& b : c->pw) b.release();
@@ -116,6 +119,8 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     c->loaded = false;
     c->rows_only = false;
     c->sa_side_valid = false;
+    c->pass.invalidate();                  // recorded sizes belong to the previous records
+    if (c->pass.active) { c->err = "coral_load_records inside a pass"; return CORAL_E_STATE; }
     for (int64_t i = 0; i < n; i++) {
         if (offsets[i] & 15) { c->err = "record offsets must be 16-byte aligned"; return CORAL_E_ARG; }
         if (offsets[i] + 36 > nbytes || offsets[i + 1] < offsets[i] + 36 || offsets[i + 1] > nbytes) {
@@ -177,10 +182,65 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     return CORAL_OK;
 }
 
+// ---- pipelined pass (PassState, ctx.h) -------------------------------------------------------------------------------
+int coral_pass_begin(coral_ctx* c) {
+    if (!c) return CORAL_E_ARG;
+    PassState& P = c->pass;
+    if (P.active) { c->err = "coral_pass_begin inside a pass"; return CORAL_E_STATE; }
+    if (!c->loaded) { c->err = "coral_pass_begin before coral_load_records"; return CORAL_E_STATE; }
+    cudaSetDevice(c->device);
+    CORAL_TRY(coral_wait_scan(c));
+    if (!P.d_flag) CORAL_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&P.d_flag), 64));
+    CORAL_CUDA(c, cudaMemsetAsync(P.d_flag, 0, 64, c->stream));
+    P.active = true;
+    P.replay = P.complete && !P.vals.empty();
+    if (!P.replay) { P.vals.clear(); P.keys.clear(); }
+    P.complete = false;
+    P.cur = P.kcur = 0;
+    P.copies.clear();
+    P.after.clear();
+    for (auto& ch : P.pinned) ch.used = 0;
+    return CORAL_OK;
+}
+
+int coral_pass_end(coral_ctx* c, int32_t* replayed) {
+    if (!c) return CORAL_E_ARG;
+    PassState& P = c->pass;
+    if (!P.active) { c->err = "coral_pass_end outside a pass"; return CORAL_E_STATE; }
+    cudaSetDevice(c->device);
+    P.active = false;
+    uint32_t bad = 0;
+    cudaError_t e = cudaMemcpyAsync(&bad, P.d_flag, 4, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) {
+        P.invalidate(); P.copies.clear(); P.after.clear();
+        c->err = std::string("coral_pass_end: ") + cudaGetErrorString(e);
+        return CORAL_E_CUDA;
+    }
+    const bool was_replay = P.replay;
+    if (replayed) *replayed = was_replay ? 1 : 0;
+    if (bad != 0) {          // the device disagreed with a replayed size: nothing of this pass can be trusted
+        P.invalidate(); P.copies.clear(); P.after.clear();
+        c->err = "pipelined pass diverged from the recorded one (" + std::to_string(bad) +
+                 " size(s) differ): the records behind a CORAL_RECORDS_DEVICE load changed? Run the pass again.";
+        return CORAL_E_STATE;
+    }
+    for (const auto& cp : P.copies) memcpy(cp.dst, cp.src, cp.bytes);
+    P.copies.clear();
+    int rc = CORAL_OK;
+    for (auto& fn : P.after) { const int r = fn(); if (r != CORAL_OK && rc == CORAL_OK) rc = r; }
+    P.after.clear();
+    if (was_replay) { P.vals.resize(P.cur); P.keys.resize(P.kcur); P.n_replayed++; }
+    P.complete = rc == CORAL_OK;
+    if (!P.complete) P.invalidate();
+    return rc;
+}
+
 int coral_rescan(coral_ctx* c) {
     if (!c) return CORAL_E_ARG;
     if (!c->loaded || c->rows_only) { c->err = "coral_rescan before coral_load_records"; return CORAL_E_STATE; }
     cudaSetDevice(c->device);
+    if (c->pass.active) coral::pass_call(c, coral::pass_hash(coral::PASS_H0, "rescan", 6));
     return coral_run_scan(c);
 }
 

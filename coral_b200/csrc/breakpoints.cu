@@ -8,6 +8,8 @@
 //    :11-15 `interval_overlap` and :37-44 `interval_overlap_l`, over the device-resident chimeric table.
 #include <vector>
 
+#include <cstring>
+
 #include "ctx.h"
 #include "dev_util.cuh"
 #include "relops.cuh"
@@ -220,6 +222,14 @@ __global__ void k_align2bp_pair(int64_t n_sel, const uint32_t* __restrict__ sel,
         }                                                                                \
     } while (0)
 
+static uint64_t interval_key(const char* name, const int32_t* tid, const int32_t* start, const int32_t* end, int32_t n) {
+    using namespace coral;
+    uint64_t k = pass_hash(PASS_H0, name, strlen(name));
+    k = pass_hash(k, &n, 4);
+    if (n > 0) { k = pass_hash(k, tid, (size_t)n * 4); k = pass_hash(k, start, (size_t)n * 4); k = pass_hash(k, end, (size_t)n * 4); }
+    return k;
+}
+
 static int upload_intervals(coral_ctx* c, DevBuf& buf, const int32_t* tid, const int32_t* start, const int32_t* end,
                             int32_t n, coral::Intervals* out) {
     using namespace coral;
@@ -244,6 +254,7 @@ extern "C" int coral_smalldel(coral_ctx* c, const int32_t* tid, const int32_t* s
     T.valid = false; T.n = 0;
     const int64_t n_ev = c->gaps.n;
     if (n_rows) *n_rows = 0;
+    if (c->pass.active) pass_call(c, interval_key("smalldel", tid, start, end_incl, n_intervals));
     if (n_ev == 0 || n_intervals == 0) { T.valid = true; return CORAL_OK; }
     Intervals I;
     CORAL_TRY(upload_intervals(c, c->s0, tid, start, end_incl, n_intervals, &I));
@@ -259,8 +270,7 @@ extern "C" int coral_smalldel(coral_ctx* c, const int32_t* tid, const int32_t* s
     CORAL_CUDA(c, cudaMemsetAsync(cnt + n_ev, 0, 4, c->stream));
     CORAL_TRY(exclusive_sum_u32(c, cnt, base, n_ev + 1));
     uint32_t n = 0;
-    CORAL_TRY(d2h(c, &n, base + n_ev, 1));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    CORAL_TRY(pass_resolve(c, &n, base + n_ev));
     if (n > 0) {
         CORAL_CUDA(c, c->s2.ensure((size_t)n * 24 + 64));
         uint64_t* key_a = c->s2.as<uint64_t>();
@@ -279,7 +289,7 @@ extern "C" int coral_smalldel(coral_ctx* c, const int32_t* tid, const int32_t* s
                   rt.fbs.as<int32_t>(), rt.lbe.as<int32_t>(), rt.flag_mapq.as<uint32_t>(), o);
     }
     c->stage_end(CORAL_STAGE_SMALLDEL);
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    CORAL_TRY(pass_sync(c));
     T.n = n;
     T.valid = true;
     if (n_rows) *n_rows = n;
@@ -294,15 +304,14 @@ extern "C" int coral_get_smalldel(coral_ctx* c, uint32_t* rec, int32_t* ai, int3
     cudaSetDevice(c->device);
     SmallDelTable& T = c->sdel;
     const size_t n = (size_t)T.n;
-    if (rec) CORAL_TRY(d2h(c, rec, T.rec.p, n));
-    if (ai) CORAL_TRY(d2h(c, ai, T.ai.p, n));
-    if (next_start) CORAL_TRY(d2h(c, next_start, T.next_start.p, n));
-    if (prev_end) CORAL_TRY(d2h(c, prev_end, T.prev_end.p, n));
-    if (first_start) CORAL_TRY(d2h(c, first_start, T.first_start.p, n));
-    if (last_end) CORAL_TRY(d2h(c, last_end, T.last_end.p, n));
-    if (mapq) CORAL_TRY(d2h(c, mapq, T.mapq.p, n));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
-    return CORAL_OK;
+    if (rec) CORAL_TRY(d2h_result(c, rec, T.rec.p, n));
+    if (ai) CORAL_TRY(d2h_result(c, ai, T.ai.p, n));
+    if (next_start) CORAL_TRY(d2h_result(c, next_start, T.next_start.p, n));
+    if (prev_end) CORAL_TRY(d2h_result(c, prev_end, T.prev_end.p, n));
+    if (first_start) CORAL_TRY(d2h_result(c, first_start, T.first_start.p, n));
+    if (last_end) CORAL_TRY(d2h_result(c, last_end, T.last_end.p, n));
+    if (mapq) CORAL_TRY(d2h_result(c, mapq, T.mapq.p, n));
+    return pass_sync(c);
 }
 
 extern "C" int coral_candidates_l(coral_ctx* c, const int32_t* tid, const int32_t* start, const int32_t* end_incl,
@@ -316,6 +325,7 @@ extern "C" int coral_candidates_l(coral_ctx* c, const int32_t* tid, const int32_
     if (n_cand) *n_cand = 0;
     ChimericTable& H = c->chim;
     const int64_t nr = H.n_reads;
+    if (c->pass.active) pass_call(c, interval_key("candidates_l", tid, start, end_incl, n_intervals));
     if (nr == 0) { T.valid = true; return CORAL_OK; }
     Intervals I;
     CORAL_TRY(upload_intervals(c, c->s0, tid, start, end_incl, n_intervals, &I));
@@ -333,8 +343,7 @@ extern "C" int coral_candidates_l(coral_ctx* c, const int32_t* tid, const int32_
     CORAL_CUDA(c, cudaMemsetAsync(cnt + nr, 0, 4, c->stream));
     CORAL_TRY(exclusive_sum_u32(c, cnt, ptr, nr + 1));
     uint32_t n = 0;
-    CORAL_TRY(d2h(c, &n, ptr + nr, 1));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    CORAL_TRY(pass_resolve(c, &n, ptr + nr));
     if (n > 0) {
         DevBuf* c4[] = {&T.read, &T.i, &T.j, &T.chr1, &T.pos1, &T.chr2, &T.pos2, &T.rgap, &T.mq1, &T.mq2};
         for (DevBuf* b : c4) CORAL_CUDA(c, b->ensure((size_t)n * 4));
@@ -348,8 +357,9 @@ extern "C" int coral_candidates_l(coral_ctx* c, const int32_t* tid, const int32_
     }
     c->stage_end(CORAL_STAGE_CANDIDATES);
     int32_t st[2] = {0, 0};
-    CORAL_TRY(d2h(c, st, c->status.p, 2));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    uint64_t st64 = 0;
+    CORAL_TRY(pass_resolve(c, &st64, c->status.p));          // two status words
+    memcpy(st, &st64, 8);
     if (st[1] != 0) { c->err = "KeyError: contig of a breakpoint is not in global_names.chr_idx"; return CORAL_E_FORMAT; }
     T.n = n;
     T.valid = true;
@@ -366,21 +376,20 @@ extern "C" int coral_get_candidates(coral_ctx* c, uint32_t* read, int32_t* i, in
     cudaSetDevice(c->device);
     CandTable& T = c->cand;
     const size_t n = (size_t)T.n;
-    if (read) CORAL_TRY(d2h(c, read, T.read.p, n));
-    if (i) CORAL_TRY(d2h(c, i, T.i.p, n));
-    if (j) CORAL_TRY(d2h(c, j, T.j.p, n));
-    if (chr1) CORAL_TRY(d2h(c, chr1, T.chr1.p, n));
-    if (pos1) CORAL_TRY(d2h(c, pos1, T.pos1.p, n));
-    if (o1) CORAL_TRY(d2h(c, o1, T.o1.p, n));
-    if (chr2) CORAL_TRY(d2h(c, chr2, T.chr2.p, n));
-    if (pos2) CORAL_TRY(d2h(c, pos2, T.pos2.p, n));
-    if (o2) CORAL_TRY(d2h(c, o2, T.o2.p, n));
-    if (rgap) CORAL_TRY(d2h(c, rgap, T.rgap.p, n));
-    if (flag) CORAL_TRY(d2h(c, flag, T.flag.p, n));
-    if (mq1) CORAL_TRY(d2h(c, mq1, T.mq1.p, n));
-    if (mq2) CORAL_TRY(d2h(c, mq2, T.mq2.p, n));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
-    return CORAL_OK;
+    if (read) CORAL_TRY(d2h_result(c, read, T.read.p, n));
+    if (i) CORAL_TRY(d2h_result(c, i, T.i.p, n));
+    if (j) CORAL_TRY(d2h_result(c, j, T.j.p, n));
+    if (chr1) CORAL_TRY(d2h_result(c, chr1, T.chr1.p, n));
+    if (pos1) CORAL_TRY(d2h_result(c, pos1, T.pos1.p, n));
+    if (o1) CORAL_TRY(d2h_result(c, o1, T.o1.p, n));
+    if (chr2) CORAL_TRY(d2h_result(c, chr2, T.chr2.p, n));
+    if (pos2) CORAL_TRY(d2h_result(c, pos2, T.pos2.p, n));
+    if (o2) CORAL_TRY(d2h_result(c, o2, T.o2.p, n));
+    if (rgap) CORAL_TRY(d2h_result(c, rgap, T.rgap.p, n));
+    if (flag) CORAL_TRY(d2h_result(c, flag, T.flag.p, n));
+    if (mq1) CORAL_TRY(d2h_result(c, mq1, T.mq1.p, n));
+    if (mq2) CORAL_TRY(d2h_result(c, mq2, T.mq2.p, n));
+    return pass_sync(c);
 }
 
 // Replace the device chimeric table with one supplied by the caller (operator forms of alignment2bp*).

@@ -449,18 +449,8 @@ enum { W_CHR1, W_POS1, W_CHR2, W_POS2, W_RGAP, W_MQ1, W_MQ2, W_O1, W_O2, W_FLAG,
        W_GID, W_GSTART, W_GFIRST, W_GBIG, W_SEG, W_CSTART, W_LABEL, W_SCR, W_ORDER, W_CPTR, W_ALIVE, W_SORT1, W_SORT2,
        W_ROWI, W_STATS, W_SUBOF, W_NSUB };
 
-extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, const int32_t* pos1, const uint8_t* o1,
-                                  const int32_t* chr2, const int32_t* pos2, const uint8_t* o2, const int32_t* rgap,
-                                  const uint8_t* flag, const int32_t* mq1, const int32_t* mq2, double min_cluster_size,
-                                  int32_t bp_distance_cutoff, double peel_cutoff, int32_t match_cutoff, int32_t max_peels,
-                                  int64_t* n_clusters) {
-    using namespace coral;
-    if (!c || n < 0) return CORAL_E_ARG;
-    cudaSetDevice(c->device);
-    c->cl_valid = false; c->cl_n = n; c->cl_n_clusters = 0;
-    if (n_clusters) *n_clusters = 0;
-    if (n == 0) { c->cl_valid = true; return CORAL_OK; }
-    if (n >= ((int64_t)1 << 31)) { c->err = "too many candidates"; return CORAL_E_ARG; }
+// Work buffers for n candidates.
+static int cluster_ensure(coral_ctx* c, int64_t n) {
     DevBuf* w = c->cw;
     const size_t n4 = (size_t)n * 4, n8 = (size_t)n * 8;
     const int i4[] = {W_CHR1, W_POS1, W_CHR2, W_POS2, W_RGAP, W_MQ1, W_MQ2, W_IDXA, W_IDXB, W_HEAD, W_GID, W_SEG, W_LABEL, W_SCR,
@@ -476,6 +466,38 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     CORAL_CUDA(c, w[W_SORT2].ensure(2 * n4 + 16));
     CORAL_CUDA(c, w[W_ROWI].ensure(4 * n4));   // pos1, pos2, nb, first_alive rows
     CORAL_CUDA(c, w[W_STATS].ensure(6 * n8));
+    return CORAL_OK;
+}
+
+static int cluster_core(coral_ctx* c, int64_t n, coral::CandIn C, double min_cluster_size, int32_t bp_distance_cutoff,
+                        double peel_cutoff, int32_t match_cutoff, int32_t max_peels, int64_t* n_clusters);
+
+extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, const int32_t* pos1, const uint8_t* o1,
+                                  const int32_t* chr2, const int32_t* pos2, const uint8_t* o2, const int32_t* rgap,
+                                  const uint8_t* flag, const int32_t* mq1, const int32_t* mq2, double min_cluster_size,
+                                  int32_t bp_distance_cutoff, double peel_cutoff, int32_t match_cutoff, int32_t max_peels,
+                                  int64_t* n_clusters) {
+    using namespace coral;
+    if (!c || n < 0) return CORAL_E_ARG;
+    cudaSetDevice(c->device);
+    c->cl_valid = false; c->cl_n = n; c->cl_n_clusters = 0;
+    if (n_clusters) *n_clusters = 0;
+    if (c->pass.active) {
+        uint64_t k = pass_hash(PASS_H0, "cluster_call", 12);
+        const int64_t a[2] = {n, (int64_t)max_peels}; const double d[2] = {min_cluster_size, peel_cutoff};
+        const int32_t b[2] = {bp_distance_cutoff, match_cutoff};
+        k = pass_hash(pass_hash(pass_hash(k, a, 16), d, 16), b, 8);
+        if (n > 0) {
+            k = pass_hash(k, chr1, n * 4); k = pass_hash(k, pos1, n * 4); k = pass_hash(k, chr2, n * 4); k = pass_hash(k, pos2, n * 4);
+            k = pass_hash(k, o1, n); k = pass_hash(k, o2, n); k = pass_hash(k, rgap, n * 4); k = pass_hash(k, flag, n);
+            k = pass_hash(k, mq1, n * 4); k = pass_hash(k, mq2, n * 4);
+        }
+        pass_call(c, k);
+    }
+    if (n == 0) { c->cl_valid = true; return CORAL_OK; }
+    if (n >= ((int64_t)1 << 31)) { c->err = "too many candidates"; return CORAL_E_ARG; }
+    CORAL_TRY(cluster_ensure(c, n));
+    DevBuf* w = c->cw;
     CORAL_TRY(h2d(c, w[W_CHR1].p, chr1, (size_t)n)); CORAL_TRY(h2d(c, w[W_POS1].p, pos1, (size_t)n));
     CORAL_TRY(h2d(c, w[W_CHR2].p, chr2, (size_t)n)); CORAL_TRY(h2d(c, w[W_POS2].p, pos2, (size_t)n));
     CORAL_TRY(h2d(c, w[W_RGAP].p, rgap, (size_t)n)); CORAL_TRY(h2d(c, w[W_MQ1].p, mq1, (size_t)n));
@@ -484,6 +506,39 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     CandIn C{w[W_CHR1].as<int32_t>(), w[W_POS1].as<int32_t>(), w[W_CHR2].as<int32_t>(), w[W_POS2].as<int32_t>(),
              w[W_RGAP].as<int32_t>(), w[W_MQ1].as<int32_t>(), w[W_MQ2].as<int32_t>(), w[W_O1].as<uint8_t>(),
              w[W_O2].as<uint8_t>(), w[W_FLAG].as<uint8_t>()};
+    return cluster_core(c, n, C, min_cluster_size, bp_distance_cutoff, peel_cutoff, match_cutoff, max_peels, n_clusters);
+}
+
+// The same call on the candidate table coral_candidates_l / coral_candidates_pair left on the device (no round trip of
+// the candidates through the host): what find_breakpoints does with its candidate list (ibg:687-716).
+extern "C" int coral_cluster_call_candidates(coral_ctx* c, double min_cluster_size, int32_t bp_distance_cutoff,
+                                             double peel_cutoff, int32_t match_cutoff, int32_t max_peels,
+                                             int64_t* n_clusters) {
+    using namespace coral;
+    if (!c) return CORAL_E_ARG;
+    if (!c->cand.valid) { c->err = "coral_cluster_call_candidates before coral_candidates_l"; return CORAL_E_STATE; }
+    cudaSetDevice(c->device);
+    const int64_t n = c->cand.n;
+    c->cl_valid = false; c->cl_n = n; c->cl_n_clusters = 0;
+    if (n_clusters) *n_clusters = 0;
+    if (c->pass.active) {
+        uint64_t k = pass_hash(PASS_H0, "cluster_call_candidates", 23);
+        const int64_t a[1] = {(int64_t)max_peels}; const double d[2] = {min_cluster_size, peel_cutoff};
+        const int32_t b[2] = {bp_distance_cutoff, match_cutoff};
+        pass_call(c, pass_hash(pass_hash(pass_hash(k, a, 8), d, 16), b, 8));
+    }
+    if (n == 0) { c->cl_valid = true; return CORAL_OK; }
+    CORAL_TRY(cluster_ensure(c, n));
+    CandTable& T = c->cand;
+    CandIn C{T.chr1.as<int32_t>(), T.pos1.as<int32_t>(), T.chr2.as<int32_t>(), T.pos2.as<int32_t>(), T.rgap.as<int32_t>(),
+             T.mq1.as<int32_t>(), T.mq2.as<int32_t>(), T.o1.as<uint8_t>(), T.o2.as<uint8_t>(), T.flag.as<uint8_t>()};
+    return cluster_core(c, n, C, min_cluster_size, bp_distance_cutoff, peel_cutoff, match_cutoff, max_peels, n_clusters);
+}
+
+static int cluster_core(coral_ctx* c, int64_t n, coral::CandIn C, double min_cluster_size, int32_t bp_distance_cutoff,
+                        double peel_cutoff, int32_t match_cutoff, int32_t max_peels, int64_t* n_clusters) {
+    using namespace coral;
+    DevBuf* w = c->cw;
     uint64_t* keyA = w[W_KEYA].as<uint64_t>(); uint64_t* keyB = w[W_KEYB].as<uint64_t>();
     uint32_t* idxA = w[W_IDXA].as<uint32_t>(); uint32_t* idxB = w[W_IDXB].as<uint32_t>();
     uint32_t* head = w[W_HEAD].as<uint32_t>(); uint32_t* gid = w[W_GID].as<uint32_t>();
@@ -501,9 +556,8 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     LAUNCH_1D(k_key_heads, n, n, keyB, head);
     CORAL_TRY(inclusive_sum_u32(c, head, head, n));
     uint32_t n_groups = 0;
-    CORAL_TRY(d2h(c, &n_groups, head + n - 1, 1));
     LAUNCH_1D(k_group_assign, n, n, idxB, head, gid, gstart, gfirst);
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    CORAL_TRY(pass_resolve(c, &n_groups, head + n - 1));
     LAUNCH_1D(k_group_big, (int64_t)n_groups, (int64_t)n_groups, gstart, n, min_cluster_size, gbig);
     // runs along pos1 within a group (idxB is grouped by gid already; sort by (gid, pos1))
     LAUNCH_1D(k_seg_pos_key, n, n, idxB, gid, C.pos1, keyA);
@@ -517,12 +571,11 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     LAUNCH_1D(k_gap_heads, n, n, keyB, idxB, gid, gbig, bp_distance_cutoff, head);
     CORAL_TRY(inclusive_sum_u32(c, head, head, n));
     uint32_t n_comp = 0;
-    CORAL_TRY(d2h(c, &n_comp, head + n - 1, 1));
     LAUNCH_1D(k_scatter_seg, n, n, idxB, head, seg);
+    CORAL_TRY(pass_resolve(c, &n_comp, head + n - 1));      // (head is not written again before the next scan)
     // members of each component in input order
     LAUNCH_1D(k_seg_idx_key, n, n, seg, keyA, idxA);
     CORAL_TRY(sort_pairs_u64(c, keyA, keyB, idxA, idxB, n, 0, 32 + bits_n));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
     LAUNCH_1D(k_seg_starts, n, n, keyB, cstart, n_comp);
     k_component_cluster<<<n_comp, CL_THREADS, 0, c->stream>>>(cstart, idxB, C, gid, gbig, bp_distance_cutoff, label,
                                                              w[W_SCR].as<uint32_t>());
@@ -536,8 +589,7 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     LAUNCH_1D(k_key_heads, n, n, keyB, head);
     CORAL_TRY(inclusive_sum_u32(c, head, head, n));
     uint32_t n_cl = 0;
-    CORAL_TRY(d2h(c, &n_cl, head + n - 1, 1));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    CORAL_TRY(pass_resolve(c, &n_cl, head + n - 1));
     LAUNCH_1D(k_cluster_ptr, n, n, head, cptr, n_cl);
     c->stage_end(CORAL_STAGE_CLUSTER);
 
@@ -551,7 +603,7 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     c->n_launches++;
     CORAL_CUDA(c, cudaGetLastError());
     c->stage_end(CORAL_STAGE_BPC2BP);
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    CORAL_TRY(pass_sync(c));
     c->cl_n_clusters = n_cl;
     c->cl_valid = true;
     if (n_clusters) *n_clusters = n_cl;
@@ -569,15 +621,14 @@ extern "C" int coral_get_clusters(coral_ctx* c, uint32_t* order, uint32_t* clust
     if (n == 0) { if (cluster_ptr) cluster_ptr[0] = 0; return CORAL_OK; }
     DevBuf* w = c->cw;
     int32_t* rowi = w[W_ROWI].as<int32_t>();
-    if (order) CORAL_TRY(d2h(c, order, w[W_ORDER].p, n));
-    if (cluster_ptr) CORAL_TRY(d2h(c, cluster_ptr, w[W_CPTR].p, nc + 1));
-    if (n_sub) CORAL_TRY(d2h(c, n_sub, w[W_NSUB].p, nc));
-    if (sub_of) CORAL_TRY(d2h(c, sub_of, w[W_SUBOF].p, n));
-    if (row_pos1) CORAL_TRY(d2h(c, row_pos1, rowi, n));
-    if (row_pos2) CORAL_TRY(d2h(c, row_pos2, rowi + n, n));
-    if (row_nb) CORAL_TRY(d2h(c, row_nb, rowi + 2 * n, n));
-    if (row_first) CORAL_TRY(d2h(c, row_first, rowi + 3 * n, n));
-    if (row_stats) CORAL_TRY(d2h(c, row_stats, w[W_STATS].p, 6 * n));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
-    return CORAL_OK;
+    if (order) CORAL_TRY(d2h_result(c, order, w[W_ORDER].p, n));
+    if (cluster_ptr) CORAL_TRY(d2h_result(c, cluster_ptr, w[W_CPTR].p, nc + 1));
+    if (n_sub) CORAL_TRY(d2h_result(c, n_sub, w[W_NSUB].p, nc));
+    if (sub_of) CORAL_TRY(d2h_result(c, sub_of, w[W_SUBOF].p, n));
+    if (row_pos1) CORAL_TRY(d2h_result(c, row_pos1, rowi, n));
+    if (row_pos2) CORAL_TRY(d2h_result(c, row_pos2, rowi + n, n));
+    if (row_nb) CORAL_TRY(d2h_result(c, row_nb, rowi + 2 * n, n));
+    if (row_first) CORAL_TRY(d2h_result(c, row_first, rowi + 3 * n, n));
+    if (row_stats) CORAL_TRY(d2h_result(c, row_stats, w[W_STATS].p, 6 * n));
+    return pass_sync(c);
 }

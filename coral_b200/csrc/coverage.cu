@@ -10,6 +10,7 @@
 // non-ACGT query bases, re-walk their own CIGAR (and SEQ) in a second, warp-per-pair kernel.
 #include "ctx.h"
 #include "dev_util.cuh"
+#include "relops.cuh"
 
 namespace coral {
 
@@ -151,6 +152,12 @@ int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t*
     if (!ctx->loaded) { ctx->err = "coral_region_coverage before coral_load_records"; return CORAL_E_STATE; }
     CORAL_TRY(coral_wait_scan(ctx));
     if (n < 0) { ctx->err = "negative region count"; return CORAL_E_ARG; }
+    if (ctx->pass.active) {
+        uint64_t k = pass_hash(PASS_H0, "region_coverage", 15);
+        k = pass_hash(k, &n, 4);
+        if (n > 0) { k = pass_hash(k, tid, (size_t)n * 4); k = pass_hash(k, start, (size_t)n * 4); k = pass_hash(k, stop, (size_t)n * 4); }
+        pass_call(ctx, k);
+    }
     if (n == 0) return CORAL_OK;
     for (int32_t i = 0; i < n; i++) {
         if (stop[i] < start[i] || tid[i] < 0) { ctx->err = "bad region"; return CORAL_E_ARG; }
@@ -189,8 +196,7 @@ int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t*
         ctx->n_launches++;
         CORAL_CUDA(ctx, cudaGetLastError());
         unsigned long long n_slow = 0;
-        CORAL_CUDA(ctx, cudaMemcpyAsync(&n_slow, d_slow_n, 8, cudaMemcpyDeviceToHost, st));
-        CORAL_CUDA(ctx, cudaStreamSynchronize(st));
+        CORAL_TRY(pass_resolve(ctx, &n_slow, d_slow_n));
         if ((int64_t)n_slow > slow_cap) { slow_cap = (int64_t)n_slow + 1024; continue; }
         if (n_slow) {
             const int64_t warps_per_block = 8;
@@ -205,12 +211,8 @@ int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t*
         break;
     }
     ctx->stage_end(CORAL_STAGE_COVERAGE);
-    std::vector<unsigned long long> h((size_t)n * 2);
-    CORAL_CUDA(ctx, cudaMemcpyAsync(h.data(), d_sum, (size_t)n * 16, cudaMemcpyDeviceToHost, st));
-    CORAL_CUDA(ctx, cudaStreamSynchronize(st));
-    for (int32_t i = 0; i < n; i++) {
-        if (base_sum) base_sum[i] = (int64_t)h[i];
-        if (rec_count) rec_count[i] = (int64_t)h[(size_t)n + i];
-    }
-    return CORAL_OK;
+    // (the sums are below 2^63: the same 64 bits as the caller's int64)
+    if (base_sum) CORAL_TRY(d2h_result(ctx, reinterpret_cast<unsigned long long*>(base_sum), d_sum, (size_t)n));
+    if (rec_count) CORAL_TRY(d2h_result(ctx, reinterpret_cast<unsigned long long*>(rec_count), d_cnt, (size_t)n));
+    return pass_sync(ctx);
 }

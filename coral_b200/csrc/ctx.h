@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -113,6 +114,34 @@ struct PathTable {
     bool valid = false;
 };
 
+// Pipelined pass (coral_pass_begin / coral_pass_end, include/coral_b200.h): between the two calls the entry points only
+// ENQUEUE their work.  Two things make that possible:
+//   * result copies are deferred: device -> page-locked staging in stream order, staging -> the caller's arrays at
+//     coral_pass_end, after the one synchronisation of the pass;
+//   * the device scalars that size later launches (number of SA records, entries, reads, clusters ...) are taken from
+//     the last complete pass over the SAME inputs instead of being read back: the first pass over new inputs runs
+//     with a read-back at each such point and records the values ("recording"); later passes replay them and a
+//     one-thread kernel per value checks the device's own value against the replayed one.  Results are deterministic
+//     functions of (records, call sequence, host inputs), which is what the plan is keyed on, so a divergence can only
+//     come from a caller overwriting a CORAL_RECORDS_DEVICE buffer in place; it is reported, never silent.
+struct PassState {
+    bool active = false;      // between coral_pass_begin and coral_pass_end
+    bool replay = false;      // sizes come from `vals`
+    bool complete = false;    // `vals` / `keys` describe a whole pass
+    std::vector<uint64_t> vals;
+    size_t cur = 0;
+    std::vector<uint64_t> keys;   // one per entry-point call: hash of (entry point, host inputs)
+    size_t kcur = 0;
+    struct Chunk { uint8_t* p; size_t cap, used; };
+    std::vector<Chunk> pinned;
+    struct Copy { void* dst; const uint8_t* src; size_t bytes; };
+    std::vector<Copy> copies;
+    std::vector<std::function<int()>> after;   // host post-processing of deferred results, in call order
+    uint32_t* d_flag = nullptr;                // device: number of replayed values the device disagreed with
+    uint64_t n_replayed = 0;                   // statistics: passes that ran without intermediate synchronisation
+    void invalidate() { vals.clear(); keys.clear(); complete = false; }
+};
+
 struct coral_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -171,6 +200,8 @@ struct coral_ctx {
     // scratch
     DevBuf s0, s1, s2, s3, s4, s5, s6, s7;
     DevBuf cub_tmp;
+
+    PassState pass;
 
     // launch accounting (bench reports gpu_launches)
     uint64_t n_launches = 0;

@@ -9,6 +9,7 @@
 //   5. read_length = l_seq of the first record with flag < 256 carrying the same name (binary-search join)
 //   6. per read: (qs, qe, al) by signature, rint by strand, stable insertion sort by (qs, qe)
 //   7. reads ordered by their first SA-bearing record (dict insertion order of the reference)
+#include <memory>
 #include <vector>
 
 #include "ctx.h"
@@ -398,6 +399,7 @@ int coral_run_fetch(coral_ctx* c) {
     T.valid = false; T.n_reads = 0; T.n_aln = 0;
     const int64_t n = c->nrec;
     RecordTable& rt = c->rt;
+    if (c->pass.active) pass_call(c, pass_hash(PASS_H0, "fetch", 5));
     // where the SA strings are read from: the records, or — after a pre-scan (asynchronous / lazy placements) — its
     // side copy in HBM, addressed through per-record offsets chosen so that base + offset + sa_off is the copy
     const uint8_t* recs = c->sa_side_valid ? c->sa_side.as<uint8_t>() : c->d_recs;
@@ -423,15 +425,20 @@ int coral_run_fetch(coral_ctx* c) {
     LAUNCH_1D(k_flag_sa, n, n, rt.sa_off.as<uint32_t>(), d_flag);
     CORAL_TRY(select_flagged_iota(c, d_flag, d_sa_rec, d_cnt, n));
     uint32_t n_sa = 0;
-    CORAL_TRY(d2h(c, &n_sa, d_cnt, 1));
-    std::vector<double> part((size_t)std::max<int64_t>(nblk, 1) * 4, 0.0);
-    CORAL_TRY(d2h(c, part.data(), c->s7.p, (size_t)nblk * 4));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
-    T.nm_sum = T.nm_sq = 0; T.nm_n = 0; T.nm_zero_div = 0;
-    for (int64_t b = 0; b < nblk; b++) {
-        T.nm_sum += part[4 * b]; T.nm_sq += part[4 * b + 1];
-        T.nm_n += (int64_t)part[4 * b + 2]; T.nm_zero_div += (int64_t)part[4 * b + 3];
-    }
+    // the per-block partial sums are a RESULT (inside a pipelined pass they arrive at coral_pass_end) ...
+    auto part = std::make_shared<std::vector<double>>((size_t)std::max<int64_t>(nblk, 1) * 4, 0.0);
+    CORAL_TRY(d2h_result(c, part->data(), c->s7.p, (size_t)nblk * 4));
+    // ... the number of SA-bearing records sizes the launches below
+    CORAL_TRY(pass_resolve(c, &n_sa, d_cnt));
+    CORAL_TRY(pass_after(c, [c, part, nblk]() {
+        ChimericTable& T = c->chim;
+        T.nm_sum = T.nm_sq = 0; T.nm_n = 0; T.nm_zero_div = 0;
+        for (int64_t b = 0; b < nblk; b++) {
+            T.nm_sum += (*part)[4 * b]; T.nm_sq += (*part)[4 * b + 1];
+            T.nm_n += (int64_t)(*part)[4 * b + 2]; T.nm_zero_div += (int64_t)(*part)[4 * b + 3];
+        }
+        return CORAL_OK;
+    }));
     if (n_sa == 0) { T.valid = true; c->stage_end(CORAL_STAGE_FETCH); return CORAL_OK; }
 
     // entries per SA record -> bases
@@ -442,8 +449,7 @@ int coral_run_fetch(coral_ctx* c) {
     CORAL_CUDA(c, cudaMemsetAsync(d_nent + n_sa, 0, 4, c->stream));
     CORAL_TRY(exclusive_sum_u32(c, d_nent, d_base, (int64_t)n_sa + 1));
     uint32_t n_ent = 0;
-    CORAL_TRY(d2h(c, &n_ent, d_base + n_sa, 1));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    CORAL_TRY(pass_resolve(c, &n_ent, d_base + n_sa));
 
     // 2-3. entry ranges + parse
     CORAL_CUDA(c, c->s3.ensure((size_t)n_ent * 12));
@@ -491,9 +497,8 @@ int coral_run_fetch(coral_ctx* c) {
                   full ? ~0ull : name_key_mask, head, d_mixed);
         CORAL_TRY(inclusive_sum_u32(c, head, head, n_ent));
         uint32_t mixed = 0;
-        CORAL_TRY(d2h(c, &n_seg, head + n_ent - 1, 1));
-        CORAL_TRY(d2h(c, &mixed, d_mixed, 1));
-        CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+        CORAL_TRY(pass_resolve(c, &n_seg, head + n_ent - 1));
+        CORAL_TRY(pass_resolve(c, &mixed, d_mixed));
         if (!mixed) break;
     }
     LAUNCH_1D(k_segments, (int64_t)n_ent, (int64_t)n_ent, ent, perm, head, seg_start, seg_of);
@@ -528,9 +533,8 @@ int coral_run_fetch(coral_ctx* c) {
     LAUNCH_1D(k_gather_u32, (int64_t)n_seg, (int64_t)n_seg, order, seg_cnt, cnt_ranked);
     CORAL_TRY(exclusive_sum_u32(c, cnt_ranked, T.aln_ptr.as<uint32_t>(), n_seg));
     uint32_t last_ptr = 0, last_cnt = 0;
-    CORAL_TRY(d2h(c, &last_ptr, T.aln_ptr.as<uint32_t>() + n_seg - 1, 1));
-    CORAL_TRY(d2h(c, &last_cnt, cnt_ranked + n_seg - 1, 1));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    CORAL_TRY(pass_resolve(c, &last_ptr, T.aln_ptr.as<uint32_t>() + n_seg - 1));
+    CORAL_TRY(pass_resolve(c, &last_cnt, cnt_ranked + n_seg - 1));
     const uint32_t n_aln = last_ptr + last_cnt;
     const size_t na = std::max<uint32_t>(n_aln, 1);
     DevBuf* a4[] = {&T.qs, &T.qe, &T.tid, &T.rs, &T.re, &T.mapq};
@@ -543,7 +547,7 @@ int coral_run_fetch(coral_ctx* c) {
     LAUNCH_1D(k_read_fill, (int64_t)n_seg, (int64_t)n_seg, (int64_t)n_ent, ent, perm, seg_start, keep, first_primary, seg_status, order,
               rt.lseq.as<uint32_t>(), n_aln, o);
     c->stage_end(CORAL_STAGE_FETCH);
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    CORAL_TRY(pass_sync(c));
     T.n_reads = n_seg;
     T.n_aln = n_aln;
     T.valid = true;
@@ -591,11 +595,13 @@ extern "C" int coral_fetch(coral_ctx* c, int64_t* n_reads, int64_t* n_alignments
     CORAL_TRY(coral_run_fetch(c));
     if (n_reads) *n_reads = c->chim.n_reads;
     if (n_alignments) *n_alignments = c->chim.n_aln;
-    if (nm_sum) *nm_sum = c->chim.nm_sum;
-    if (nm_sumsq) *nm_sumsq = c->chim.nm_sq;
-    if (nm_n) *nm_n = c->chim.nm_n;
-    if (nm_zero_div) *nm_zero_div = c->chim.nm_zero_div;
-    return CORAL_OK;
+    return coral::pass_after(c, [=]() {       // inside a pipelined pass the nm sums arrive at coral_pass_end
+        if (nm_sum) *nm_sum = c->chim.nm_sum;
+        if (nm_sumsq) *nm_sumsq = c->chim.nm_sq;
+        if (nm_n) *nm_n = c->chim.nm_n;
+        if (nm_zero_div) *nm_zero_div = c->chim.nm_zero_div;
+        return CORAL_OK;
+    });
 }
 
 extern "C" int coral_get_chimeric(coral_ctx* c, uint32_t* read_first_rec, int64_t* read_len, int32_t* read_status,
@@ -608,20 +614,19 @@ extern "C" int coral_get_chimeric(coral_ctx* c, uint32_t* read_first_rec, int64_
     ChimericTable& T = c->chim;
     const size_t nr = (size_t)T.n_reads, na = (size_t)T.n_aln;
     if (nr == 0) { if (aln_ptr) aln_ptr[0] = 0; return CORAL_OK; }
-    if (read_first_rec) CORAL_TRY(d2h(c, read_first_rec, T.read_first_rec.p, nr));
-    if (read_len) CORAL_TRY(d2h(c, read_len, T.read_len.p, nr));
-    if (read_status) CORAL_TRY(d2h(c, read_status, T.read_status.p, nr));
-    if (aln_ptr) CORAL_TRY(d2h(c, aln_ptr, T.aln_ptr.p, nr + 1));
-    if (qs) CORAL_TRY(d2h(c, qs, T.qs.p, na));
-    if (qe) CORAL_TRY(d2h(c, qe, T.qe.p, na));
-    if (tid) CORAL_TRY(d2h(c, tid, T.tid.p, na));
-    if (rstart) CORAL_TRY(d2h(c, rstart, T.rs.p, na));
-    if (rend) CORAL_TRY(d2h(c, rend, T.re.p, na));
-    if (strand) CORAL_TRY(d2h(c, strand, T.strand.p, na));
-    if (mapq) CORAL_TRY(d2h(c, mapq, T.mapq.p, na));
-    if (nm) CORAL_TRY(d2h(c, nm, T.nm.p, na));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
-    return CORAL_OK;
+    if (read_first_rec) CORAL_TRY(d2h_result(c, read_first_rec, T.read_first_rec.p, nr));
+    if (read_len) CORAL_TRY(d2h_result(c, read_len, T.read_len.p, nr));
+    if (read_status) CORAL_TRY(d2h_result(c, read_status, T.read_status.p, nr));
+    if (aln_ptr) CORAL_TRY(d2h_result(c, aln_ptr, T.aln_ptr.p, nr + 1));
+    if (qs) CORAL_TRY(d2h_result(c, qs, T.qs.p, na));
+    if (qe) CORAL_TRY(d2h_result(c, qe, T.qe.p, na));
+    if (tid) CORAL_TRY(d2h_result(c, tid, T.tid.p, na));
+    if (rstart) CORAL_TRY(d2h_result(c, rstart, T.rs.p, na));
+    if (rend) CORAL_TRY(d2h_result(c, rend, T.re.p, na));
+    if (strand) CORAL_TRY(d2h_result(c, strand, T.strand.p, na));
+    if (mapq) CORAL_TRY(d2h_result(c, mapq, T.mapq.p, na));
+    if (nm) CORAL_TRY(d2h_result(c, nm, T.nm.p, na));
+    return pass_sync(c);
 }
 
 // ---- operator form: alignment_from_satags on caller-supplied SA text ---------------------------------

@@ -4,6 +4,8 @@
 #pragma once
 #include <cub/cub.cuh>
 
+#include <cstring>
+
 #include "ctx.h"
 
 namespace coral {
@@ -55,6 +57,105 @@ inline int select_flagged_iota(coral_ctx* c, const uint8_t* flags, uint32_t* out
     return CORAL_OK;
 }
 
+// ---- pipelined pass helpers (PassState, ctx.h) ---------------------------------------------------------------------
+static __global__ void k_pass_check(const void* d, unsigned long long expect, int nbytes, uint32_t* flag) {
+    const unsigned long long v = nbytes == 8 ? *static_cast<const unsigned long long*>(d)
+                                             : (unsigned long long)*static_cast<const uint32_t*>(d);
+    if (v != expect) atomicAdd(flag, 1u);
+}
+
+inline uint64_t pass_hash(uint64_t h, const void* p, size_t bytes) {      // FNV-1a over host input arrays
+    const uint8_t* b = static_cast<const uint8_t*>(p);
+    for (size_t i = 0; i < bytes; i++) { h ^= b[i]; h *= 0x100000001B3ull; }
+    return h;
+}
+constexpr uint64_t PASS_H0 = 0xCBF29CE484222325ull;
+
+// Every entry point that can run inside a pass announces itself with a key over its host inputs.  A replayed pass
+// whose call sequence departs from the recorded one continues as a recording pass from that call on.
+inline void pass_call(coral_ctx* c, uint64_t key) {
+    PassState& P = c->pass;
+    if (!P.active) return;
+    if (P.replay) {
+        if (P.kcur < P.keys.size() && P.keys[P.kcur] == key) { P.kcur++; return; }
+        P.replay = false;
+        P.vals.resize(P.cur);
+        P.keys.resize(P.kcur);
+    }
+    P.keys.push_back(key);
+    P.kcur = P.keys.size();
+}
+
+// A device scalar (4 or 8 bytes) that sizes later launches.  Outside a pass and while recording: read back now.
+// While replaying: the recorded value, checked on the device.
+template <class T>
+inline int pass_resolve(coral_ctx* c, T* out, const void* d_src) {
+    static_assert(sizeof(T) == 4 || sizeof(T) == 8, "4- or 8-byte scalars");
+    PassState& P = c->pass;
+    if (P.active && P.replay && P.cur < P.vals.size()) {
+        const uint64_t v = P.vals[P.cur++];
+        T t;
+        memcpy(&t, &v, sizeof(T));
+        *out = t;
+        k_pass_check<<<1, 1, 0, c->stream>>>(d_src, (unsigned long long)v, (int)sizeof(T), P.d_flag);
+        c->n_launches++;
+        return CORAL_OK;
+    }
+    if (P.active && P.replay) {       // the recorded sequence is shorter than this pass: record from here on
+        P.replay = false;
+        P.keys.resize(P.kcur);
+    }
+    CORAL_CUDA(c, cudaMemcpyAsync(out, d_src, sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (P.active) {
+        uint64_t v = 0;
+        memcpy(&v, out, sizeof(T));
+        P.vals.push_back(v);
+        P.cur = P.vals.size();
+    }
+    return CORAL_OK;
+}
+
+inline uint8_t* pass_stage(coral_ctx* c, size_t bytes) {          // page-locked staging for one deferred copy
+    PassState& P = c->pass;
+    bytes = (bytes + 63) & ~(size_t)63;
+    for (auto& ch : P.pinned)
+        if (ch.cap - ch.used >= bytes) { uint8_t* r = ch.p + ch.used; ch.used += bytes; return r; }
+    const size_t cap = std::max<size_t>(bytes, (size_t)8 << 20);
+    uint8_t* p = nullptr;
+    if (cudaHostAlloc(reinterpret_cast<void**>(&p), cap, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+    P.pinned.push_back(PassState::Chunk{p, cap, bytes});
+    return p;
+}
+
+// Copy of a RESULT to the caller's array: now (the caller synchronises) or, inside a pass, at coral_pass_end.
+template <class T>
+inline int d2h_result(coral_ctx* c, T* dst, const void* src, size_t n) {
+    if (n == 0) return CORAL_OK;
+    PassState& P = c->pass;
+    if (P.active) {
+        uint8_t* st = pass_stage(c, n * sizeof(T));
+        if (!st) { c->err = "cudaHostAlloc failed for the pass staging buffer"; return CORAL_E_NOMEM; }
+        CORAL_CUDA(c, cudaMemcpyAsync(st, src, n * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+        P.copies.push_back(PassState::Copy{dst, st, n * sizeof(T)});
+        return CORAL_OK;
+    }
+    CORAL_CUDA(c, cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+    return CORAL_OK;
+}
+// The synchronisation that ends an entry point: skipped inside a pass (coral_pass_end synchronises once).
+inline int pass_sync(coral_ctx* c) {
+    if (c->pass.active) return CORAL_OK;
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    return CORAL_OK;
+}
+// Host post-processing of results that were just copied: now, or after the pass's synchronisation.
+inline int pass_after(coral_ctx* c, std::function<int()> fn) {
+    if (c->pass.active) { c->pass.after.push_back(std::move(fn)); return CORAL_OK; }
+    return fn();
+}
+
+// Immediate copy (the caller synchronises right after): entry points that do not take part in pipelined passes.
 template <class T>
 inline int d2h(coral_ctx* c, T* dst, const void* src, size_t n) {
     if (n == 0) return CORAL_OK;

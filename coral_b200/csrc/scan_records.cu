@@ -20,6 +20,7 @@
 //     exact per-nibble count only runs for 16-byte chunks that contain a non-ACGT code.
 #include "ctx.h"
 #include "dev_util.cuh"
+#include "relops.cuh"
 
 namespace coral {
 
@@ -810,9 +811,16 @@ int scan_verdict(coral_ctx* ctx, cudaStream_t st) {
     GapEvents& g = ctx->gaps;
     unsigned long long total = 0;
     int32_t sw[2] = {0, 0};
-    CORAL_CUDA(ctx, cudaMemcpyAsync(&total, g.counter.p, 8, cudaMemcpyDeviceToHost, st));
-    CORAL_CUDA(ctx, cudaMemcpyAsync(sw, ctx->scan_status.p, 8, cudaMemcpyDeviceToHost, st));
-    CORAL_CUDA(ctx, cudaStreamSynchronize(st));
+    if (st == ctx->stream) {          // a rescan inside a pipelined pass replays the event count and checks the status
+        unsigned long long sw64 = 0;
+        CORAL_TRY(pass_resolve(ctx, &total, g.counter.p));
+        CORAL_TRY(pass_resolve(ctx, &sw64, ctx->scan_status.p));
+        memcpy(sw, &sw64, 8);
+    } else {
+        CORAL_CUDA(ctx, cudaMemcpyAsync(&total, g.counter.p, 8, cudaMemcpyDeviceToHost, st));
+        CORAL_CUDA(ctx, cudaMemcpyAsync(sw, ctx->scan_status.p, 8, cudaMemcpyDeviceToHost, st));
+        CORAL_CUDA(ctx, cudaStreamSynchronize(st));
+    }
     if (sw[1] != 0) {
         ctx->err = "record framing inconsistent with the record core in " + std::to_string(sw[1]) + " record(s)";
         return CORAL_E_FORMAT;

@@ -151,11 +151,8 @@ int count_names(coral_ctx* c, const NameSet& set, int32_t n_edges, int64_t* lr_c
     LAUNCH_1D(k_name_keys, n, set, rows, keyA, pa);
     CORAL_TRY(sort_pairs_u64(c, keyA, keyB, pa, pb, n, 0, 24));
     LAUNCH_1D(k_name_count, n, n, keyB, pb, rows, d_count, (int64_t)n_edges);
-    std::vector<unsigned long long> h((size_t)n_edges);
-    CORAL_TRY(d2h(c, h.data(), d_count, (size_t)n_edges));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
-    for (int32_t i = 0; i < n_edges; i++) lr_count[i] = (int64_t)h[i];
-    return CORAL_OK;
+    CORAL_TRY(d2h_result(c, reinterpret_cast<unsigned long long*>(lr_count), d_count, (size_t)n_edges));   // same 64 bits
+    return pass_sync(c);
 }
 
 }  // namespace
@@ -170,6 +167,14 @@ extern "C" int coral_concordant(coral_ctx* c, const int32_t* tid, const int32_t*
     cudaSetDevice(c->device);
     c->stab_n = 0; c->stab_valid = false;
     if (n_union_rows) *n_union_rows = 0;
+    if (c->pass.active) {
+        uint64_t k = pass_hash(PASS_H0, lr_count ? "concordant" : "concordant_rows", lr_count ? 10 : 15);
+        const int64_t a[2] = {n_edges, n_rbps};
+        k = pass_hash(k, a, 16);
+        if (n_edges > 0) { k = pass_hash(k, tid, (size_t)n_edges * 4); k = pass_hash(k, p, (size_t)n_edges * 4); }
+        if (n_rbps > 0) { k = pass_hash(k, rb_edge, (size_t)n_rbps * 4); k = pass_hash(k, rb_rec, (size_t)n_rbps * 4); }
+        pass_call(c, k);
+    }
     if (n_edges == 0) { c->stab_valid = true; return CORAL_OK; }
     for (int32_t i = 0; i < n_edges; i++) {
         if (i > 0 && (tid[i] < tid[i - 1] || (tid[i] == tid[i - 1] && p[i] <= p[i - 1]))) {
@@ -202,8 +207,7 @@ extern "C" int coral_concordant(coral_ctx* c, const int32_t* tid, const int32_t*
         CORAL_CUDA(c, cudaMemsetAsync(d_nrows, 0, 8, c->stream));
         LAUNCH_1D(k_stab_rows, c->nrec, c->nrec, rt.tid.as<int32_t>(), rt.pos.as<int32_t>(), rt.endpos.as<int32_t>(), E,
                   w[3].as<uint32_t>(), w[4].as<uint32_t>(), w[5].as<uint32_t>(), d_nrows, cap);
-        CORAL_TRY(d2h(c, &n_rows, d_nrows, 1));
-        CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+        CORAL_TRY(pass_resolve(c, &n_rows, d_nrows));
         if ((int64_t)n_rows <= cap) break;
         cap = (int64_t)n_rows + 1024;
     }
@@ -236,11 +240,10 @@ extern "C" int coral_get_concordant_rows(coral_ctx* c, uint32_t* edge, uint32_t*
     cudaSetDevice(c->device);
     const size_t n = (size_t)c->stab_n;
     if (n == 0) return CORAL_OK;
-    if (edge) CORAL_TRY(d2h(c, edge, c->sw[3].p, n));
-    if (rec) CORAL_TRY(d2h(c, rec, c->sw[4].p, n));
-    if (mask) CORAL_TRY(d2h(c, mask, c->sw[5].p, n));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
-    return CORAL_OK;
+    if (edge) CORAL_TRY(d2h_result(c, edge, c->sw[3].p, n));
+    if (rec) CORAL_TRY(d2h_result(c, rec, c->sw[4].p, n));
+    if (mask) CORAL_TRY(d2h_result(c, mask, c->sw[5].p, n));
+    return pass_sync(c);
 }
 
 // ---- multi-GPU form ----------------------------------------------------------------------------

@@ -116,6 +116,26 @@ uint64_t coral_launch_count(const coral_ctx* ctx);
  * device-resident benchmark starts with). */
 int coral_rescan(coral_ctx* ctx);
 
+/* ---- pipelined pass ---------------------------------------------------------------------------------------------- *
+ * Between coral_pass_begin and coral_pass_end the entry points listed below only ENQUEUE their kernels and return: no
+ * call synchronises with the device, every output array they were given is filled when coral_pass_end returns (the
+ * arrays must stay valid until then), and the whole pass costs one synchronisation.  The scalars that size the
+ * launches of a later kernel (number of SA-bearing records, SA entries, chimeric reads, alignments, candidates,
+ * clusters, gap events ...) — and the counts these calls return (*n_reads, *n_rows, *n_clusters ...) — are those of
+ * the last complete pass over the SAME records with the SAME sequence of calls and host inputs; a one-thread kernel per
+ * value checks the device's own value against it.  The first pass over new inputs (and any pass whose calls depart from
+ * the recorded sequence, from that call on) reads those scalars back as usual and records them.  coral_pass_end
+ * returns CORAL_E_STATE if the device disagreed with a replayed value (only possible when the caller overwrote a
+ * CORAL_RECORDS_DEVICE buffer in place): nothing of that pass is delivered and the next pass records again.
+ * *replayed (nullable) = 1 when the pass ran without intermediate synchronisation.
+ * Entry points that take part: coral_rescan, coral_region_coverage, coral_fetch + coral_get_chimeric, coral_smalldel +
+ * coral_get_smalldel, coral_candidates_l + coral_get_candidates, coral_cluster_call(_candidates) + coral_get_clusters,
+ * coral_concordant + coral_get_concordant_rows.  Any other entry point may be called inside a pass; it synchronises.
+ * This is how one step of the device-resident benchmark runs the path (reference call order
+ * infer_breakpoint_graph.py:1354-1386) as one stream of kernels. */
+int coral_pass_begin(coral_ctx* ctx);
+int coral_pass_end(coral_ctx* ctx, int32_t* replayed);
+
 /* Device time of the kernels of one stage during its most recent run, from CUDA events recorded on the
  * ctx's own stream around the launches (milliseconds; < 0 if the stage has not run). */
 #define CORAL_STAGE_SCAN 0
@@ -264,6 +284,10 @@ int coral_cluster_call(coral_ctx* ctx, int64_t n, const int32_t* chr1, const int
                        const uint8_t* flag, const int32_t* mq1, const int32_t* mq2, double min_cluster_size,
                        int32_t bp_distance_cutoff, double peel_cutoff, int32_t match_cutoff, int32_t max_peels,
                        int64_t* n_clusters);
+/* The same call on the candidate table coral_candidates_l / coral_candidates_pair left on the device (what
+ * find_breakpoints does with its candidate list, ibg:687-716): the candidates do not travel through the host. */
+int coral_cluster_call_candidates(coral_ctx* ctx, double min_cluster_size, int32_t bp_distance_cutoff, double peel_cutoff,
+                                  int32_t match_cutoff, int32_t max_peels, int64_t* n_clusters);
 int coral_get_clusters(coral_ctx* ctx, uint32_t* order, uint32_t* cluster_ptr, int32_t* n_sub, int32_t* sub_of,
                        int32_t* row_pos1, int32_t* row_pos2, int32_t* row_nb, uint32_t* row_first, double* row_stats);
 

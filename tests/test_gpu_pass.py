@@ -1,0 +1,107 @@
+"""Pipelined pass (coral_pass_begin / coral_pass_end): the hot path enqueued as one stream of kernels must deliver exactly
+what the same calls deliver one by one — on the recording pass, on replayed passes (no intermediate synchronisation), and
+when the call sequence or a host input changes between passes."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _same(a, b, path=""):
+    if isinstance(a, dict):
+        assert set(a) == set(b), path
+        for k in a:
+            _same(a[k], b[k], path + "/" + str(k))
+    elif isinstance(a, (tuple, list)):
+        assert len(a) == len(b), path
+        for i, (x, y) in enumerate(zip(a, b)):
+            _same(x, y, "%s[%d]" % (path, i))
+    elif isinstance(a, np.ndarray):
+        assert np.array_equal(a, b), path
+    else:
+        assert a == b, path
+
+
+def _calls(ctx, plan, cutoff):
+    from coral_b200 import gpu_ops
+    out = {}
+    ctx.rescan()
+    out["normal"] = ctx.region_coverage(*plan["normal"])
+    out["fetch"] = ctx.fetch()
+    out["smalldel"] = ctx.smalldel(*plan["intervals"])
+    if len(plan["sd_cand"]["chr1"]):
+        out["cl1"] = gpu_ops.cluster_arrays(ctx, plan["sd_cand"], cutoff, 2000, cutoff, 100)
+    cand = ctx.candidates_l(*plan["intervals"])
+    out["cand"] = cand
+    if cand["n"]:
+        out["cl2"] = ctx.cluster_call_candidates(cand["n"], cutoff, 2000, cutoff, 100)
+    out["seq"] = ctx.region_coverage(*plan["seq"])
+    out["conc"] = ctx.concordant(*plan["conc"])
+    return out
+
+
+@pytest.mark.parametrize("cfg_name,scale", [("C2", 0.03), ("C3", 0.01), ("C4", 0.006)])
+def test_pipelined_pass_equals_call_by_call(built_lib, dataset, cfg_name, scale):
+    from coral_b200 import _abi, gpu_ops
+    ds = dataset(cfg_name, scale=scale)
+    cfg, data = ds["cfg"], ds["data"]
+    names = [r[0] for r in cfg.refs]
+    ctx = _abi.Context(0)
+    ctx.set_references(names)
+    ctx.load_records(data.rec, data.rec_off)
+    t = ctx.record_table()
+    tid_of = {n: i for i, n in enumerate(names)}
+    seeds = sorted((tid_of[c], s, e) for (c, s, e) in cfg.seeds)
+    iv = tuple(np.array(x, np.int32) for x in zip(*seeds))
+    # regions / edges: the seed intervals cut in three, stab points at the cuts
+    reg, pts = [], []
+    for (tt, s, e) in seeds:
+        a, b = s + (e - s) // 3, s + 2 * (e - s) // 3
+        reg += [(tt, s, a), (tt, a + 1, b), (tt, b + 1, e + 1)]
+        pts += [(tt, a), (tt, b)]
+    normal = [(tid_of[c], lo, lo + 2_000_000) for (c, lo, hi) in cfg.background]
+    sd = ctx.smalldel(*iv)
+    n_sd = sd["n"]
+    sd_cand = {"chr1": sd["ai"].astype(np.int32), "pos1": sd["next_start"], "chr2": sd["ai"].astype(np.int32), "pos2": sd["prev_end"],
+               "o1": np.ones(n_sd, np.uint8), "o2": np.zeros(n_sd, np.uint8), "rgap": np.zeros(n_sd, np.int32),
+               "flag": np.zeros(n_sd, np.uint8), "mq1": np.full(n_sd, -1, np.int32), "mq2": np.full(n_sd, -1, np.int32)}
+    rng = np.random.default_rng(3)
+    rb_rec = rng.choice(len(t["tid"]), 40, replace=False).astype(np.uint32)
+    rb_edge = rng.integers(0, len(pts), 40).astype(np.uint32)
+    plan = {"normal": tuple(np.array(x, np.int32) for x in zip(*sorted(normal))), "intervals": iv, "sd_cand": sd_cand,
+            "seq": tuple(np.array(x, np.int32) for x in zip(*reg)),
+            "conc": (np.array([p[0] for p in pts], np.int32), np.array([p[1] for p in pts], np.int32), rb_edge, rb_rec)}
+    want = _calls(ctx, plan, 3.0)
+    if cfg_name == "C3":
+        assert want["smalldel"]["n"] > 0 and "cl1" in want
+    assert want["fetch"]["n_reads"] > 0 and want["cand"]["n"] > 0
+    for k in range(3):                      # recording pass, then two replayed ones
+        ctx.pass_begin()
+        got = _calls(ctx, plan, 3.0)
+        replayed = ctx.pass_end()
+        assert replayed == (k > 0)
+        _same(got, want)
+    # a host input changes (other cutoff -> other cluster calls): the pass re-records from that call on, results stay right
+    want2 = _calls(ctx, plan, 5.0)
+    ctx.pass_begin()
+    got2 = _calls(ctx, plan, 5.0)
+    ctx.pass_end()
+    _same(got2, want2)
+    ctx.pass_begin()
+    got2 = _calls(ctx, plan, 5.0)
+    assert ctx.pass_end() is True
+    _same(got2, want2)
+    # an entry point outside the pass protocol inside a pass: it synchronises, everything still arrives
+    ctx.pass_begin()
+    got3 = _calls(ctx, plan, 5.0)
+    tab = ctx.record_table()
+    ctx.pass_end()
+    _same(got3, want2)
+    assert np.array_equal(tab["endpos"], t["endpos"])
+    # new records invalidate the recorded sizes
+    ctx.load_records(data.rec, data.rec_off)
+    ctx.pass_begin()
+    got4 = _calls(ctx, plan, 5.0)
+    assert ctx.pass_end() is False
+    _same(got4, want2)
+    ctx.close()
