@@ -34,9 +34,10 @@ def lib():
     """Load libcoral_b200.so (fails loudly when it has not been built)."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
+        path = os.environ.get("CORAL_B200_LIB", LIB_PATH)      # development aid: a kernel variant built beside the library
+        if not os.path.exists(path):
             raise ImportError("libcoral_b200.so is missing: run `python -m coral_b200.build` (no CPU fallback exists)")
-        L = ctypes.CDLL(LIB_PATH)
+        L = ctypes.CDLL(path)
         L.coral_last_error.restype = ctypes.c_char_p
         L.coral_n_records.restype = ctypes.c_int64
         L.coral_launch_count.restype = ctypes.c_uint64

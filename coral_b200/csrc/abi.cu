@@ -182,6 +182,8 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     return CORAL_OK;
 }
 
+void coral_release_cached_memory(void) { coral_mem::trim(); }
+
 // ---- pipelined pass (PassState, ctx.h) -------------------------------------------------------------------------------
 int coral_pass_begin(coral_ctx* c) {
     if (!c) return CORAL_E_ARG;

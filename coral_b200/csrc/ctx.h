@@ -27,22 +27,72 @@
         if (r__ != CORAL_OK) return r__; \
     } while (0)
 
-// cudaFree waits for every kernel in flight on the device — including an asynchronous record scan, which is exactly
-// what the entry points running next to it must not wait for.  While such a scan is pending, freed blocks are parked
-// and released when it is joined.  (A ctx is single-threaded; the counters are only touched by asynchronous loads.)
+// Device memory of all ctxs of the process comes from one small caching allocator: cudaMalloc / cudaFree synchronise
+// the whole device (cudaFree waits for every kernel in flight, including an asynchronous record scan — exactly what the
+// entry points running next to it must not wait for) and cost 0.1-1 ms each, which is most of what opening and
+// closing a ctx per BAM costs.  Released blocks are kept (up to `limit` bytes per process) and handed to the next
+// request of a similar size.  While an asynchronous scan is pending, blocks released by buffers that grow are parked
+// until the scan is joined (its kernel may still be writing them).  (A ctx is single-threaded, the allocator is
+// shared by the ctxs of all threads.)
+#include <mutex>
 namespace coral_mem {
+struct Block { void* p; size_t cap; int dev; };
+inline std::mutex mu;
 inline int defer = 0;
-inline std::vector<void*> parked;
-inline void release(void* p) {
-    if (!p) return;
-    if (defer > 0) parked.push_back(p); else cudaFree(p);
+inline std::vector<Block> parked, cache;
+inline size_t cached_bytes = 0;
+inline size_t limit = (size_t)64 << 30;
+inline cudaError_t acquire(void** out, size_t want, size_t* got) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    {
+        std::lock_guard<std::mutex> g(mu);
+        size_t best = (size_t)-1;
+        for (size_t i = 0; i < cache.size(); i++)
+            if (cache[i].dev == dev && cache[i].cap >= want && cache[i].cap <= 2 * want + ((size_t)1 << 20) &&
+                (best == (size_t)-1 || cache[i].cap < cache[best].cap))
+                best = i;
+        if (best != (size_t)-1) {
+            *out = cache[best].p; *got = cache[best].cap;
+            cached_bytes -= cache[best].cap;
+            cache[best] = cache.back(); cache.pop_back();
+            return cudaSuccess;
+        }
+    }
+    cudaError_t e = cudaMalloc(out, want);
+    if (e != cudaSuccess) {                       // out of memory: give the cached blocks back and try once more
+        cudaGetLastError();
+        std::vector<Block> drop;
+        { std::lock_guard<std::mutex> g(mu); drop.swap(cache); cached_bytes = 0; }
+        for (const Block& b : drop) cudaFree(b.p);
+        e = cudaMalloc(out, want);
+    }
+    *got = want;
+    return e;
 }
-inline void scan_started() { defer++; }
+inline void to_cache(const Block& b) {            // caller holds mu
+    if (cached_bytes + b.cap <= limit) { cache.push_back(b); cached_bytes += b.cap; }
+    else cudaFree(b.p);
+}
+inline void release(void* p, size_t cap) {
+    if (!p) return;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> g(mu);
+    if (defer > 0) parked.push_back(Block{p, cap, dev}); else to_cache(Block{p, cap, dev});
+}
+inline void scan_started() { std::lock_guard<std::mutex> g(mu); defer++; }
 inline void scan_joined() {
+    std::lock_guard<std::mutex> g(mu);
     if (defer > 0 && --defer == 0) {
-        for (void* p : parked) cudaFree(p);
+        for (const Block& b : parked) to_cache(b);
         parked.clear();
     }
+}
+inline void trim() {                              // give every cached block back to the driver
+    std::vector<Block> drop;
+    { std::lock_guard<std::mutex> g(mu); drop.swap(cache); cached_bytes = 0; }
+    for (const Block& b : drop) cudaFree(b.p);
 }
 }  // namespace coral_mem
 
@@ -54,15 +104,16 @@ struct DevBuf {
     size_t cap = 0;
     cudaError_t ensure(size_t bytes) {
         if (bytes <= cap) return cudaSuccess;
-        coral_mem::release(p);
+        coral_mem::release(p, cap);
         p = nullptr;
-        size_t want = bytes + bytes / 8 + 256;
-        cudaError_t e = cudaMalloc(&p, want);
-        cap = (e == cudaSuccess) ? want : 0;
+        size_t want = bytes + bytes / 8 + 256, got = 0;
+        cudaError_t e = coral_mem::acquire(&p, want, &got);
+        cap = (e == cudaSuccess) ? got : 0;
+        if (e != cudaSuccess) p = nullptr;
         return e;
     }
     void release() {
-        coral_mem::release(p);
+        coral_mem::release(p, cap);
         p = nullptr;
         cap = 0;
     }

@@ -53,6 +53,10 @@ void coral_default_params(coral_params* p);
 int coral_create(int device, coral_ctx** out);
 void coral_destroy(coral_ctx* ctx);
 const char* coral_last_error(const coral_ctx* ctx);
+/* Device buffers of destroyed (or regrown) ctxs are kept by a per-process caching allocator and handed to the next ctx
+ * (opening a ctx per BAM then costs no cudaMalloc / cudaFree, which synchronise the device); this gives them all back
+ * to the driver. */
+void coral_release_cached_memory(void);
 int coral_set_params(coral_ctx* ctx, const coral_params* p);
 /* Named switches that do not change any result.  "full_name_sort" = 1: coral_fetch groups SA entries by a full
  * 128-bit name sort instead of the 40-bit sort it normally tries first (the path it falls back to when two read

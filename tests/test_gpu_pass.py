@@ -40,7 +40,15 @@ def _calls(ctx, plan, cutoff):
     return out
 
 
-@pytest.mark.parametrize("cfg_name,scale", [("C2", 0.03), ("C3", 0.01), ("C4", 0.006)])
+def _canon(out):
+    """The stab rows come out in the order their atomics landed: compare them sorted."""
+    cnt, rows = out["conc"]
+    o = np.lexsort((rows["mask"], rows["rec"], rows["edge"]))
+    out["conc"] = (cnt, {k: v[o] for k, v in rows.items()})
+    return out
+
+
+@pytest.mark.parametrize("cfg_name,scale", [("C2", 0.03), ("C3", 0.01), ("C1", 0.05)])
 def test_pipelined_pass_equals_call_by_call(built_lib, dataset, cfg_name, scale):
     from coral_b200 import _abi, gpu_ops
     ds = dataset(cfg_name, scale=scale)
@@ -71,37 +79,39 @@ def test_pipelined_pass_equals_call_by_call(built_lib, dataset, cfg_name, scale)
     plan = {"normal": tuple(np.array(x, np.int32) for x in zip(*sorted(normal))), "intervals": iv, "sd_cand": sd_cand,
             "seq": tuple(np.array(x, np.int32) for x in zip(*reg)),
             "conc": (np.array([p[0] for p in pts], np.int32), np.array([p[1] for p in pts], np.int32), rb_edge, rb_rec)}
-    want = _calls(ctx, plan, 3.0)
+    want = _canon(_calls(ctx, plan, 3.0))
     if cfg_name == "C3":
         assert want["smalldel"]["n"] > 0 and "cl1" in want
-    assert want["fetch"]["n_reads"] > 0 and want["cand"]["n"] > 0
+    assert want["fetch"]["n_reads"] > 0
+    if cfg_name == "C1":                    # junctions inside one amplicon interval: alignment2bp_l emits candidates
+        assert want["cand"]["n"] > 0 and "cl2" in want
     for k in range(3):                      # recording pass, then two replayed ones
         ctx.pass_begin()
         got = _calls(ctx, plan, 3.0)
         replayed = ctx.pass_end()
         assert replayed == (k > 0)
-        _same(got, want)
+        _same(_canon(got), want)
     # a host input changes (other cutoff -> other cluster calls): the pass re-records from that call on, results stay right
-    want2 = _calls(ctx, plan, 5.0)
+    want2 = _canon(_calls(ctx, plan, 5.0))
     ctx.pass_begin()
     got2 = _calls(ctx, plan, 5.0)
     ctx.pass_end()
-    _same(got2, want2)
+    _same(_canon(got2), want2)
     ctx.pass_begin()
     got2 = _calls(ctx, plan, 5.0)
     assert ctx.pass_end() is True
-    _same(got2, want2)
+    _same(_canon(got2), want2)
     # an entry point outside the pass protocol inside a pass: it synchronises, everything still arrives
     ctx.pass_begin()
     got3 = _calls(ctx, plan, 5.0)
     tab = ctx.record_table()
     ctx.pass_end()
-    _same(got3, want2)
+    _same(_canon(got3), want2)
     assert np.array_equal(tab["endpos"], t["endpos"])
     # new records invalidate the recorded sizes
     ctx.load_records(data.rec, data.rec_off)
     ctx.pass_begin()
     got4 = _calls(ctx, plan, 5.0)
     assert ctx.pass_end() is False
-    _same(got4, want2)
+    _same(_canon(got4), want2)
     ctx.close()
