@@ -353,16 +353,18 @@ def device_pass(ctx, plan, gpu_ops, pipelined=True):
         ctx.pass_begin()
     ctx.rescan()
     out = {}
-    out["normal"] = ctx.region_coverage(*plan["normal"])
+    # first what only needs the columns of the pre-scan (core fields, name hash, SA / NM): in a pipelined pass these
+    # kernels run next to the full scan, which is joined by the first call below that reads its CIGAR / SEQ columns
     out["fetch"] = ctx.fetch()
-    out["smalldel"] = ctx.smalldel(*plan["intervals"])
-    c = plan["smalldel_cand"]
-    if len(c["chr1"]):
-        out["cl1"] = gpu_ops.cluster_arrays(ctx, c, plan["cutoff"], 2000, plan["cutoff"], 100)
     cand = ctx.candidates_l(*plan["intervals"])
     out["cand"] = cand
     if cand["n"]:
         out["cl2"] = ctx.cluster_call_candidates(cand["n"], plan["cutoff"], 2000, plan["cutoff"], 100)
+    out["normal"] = ctx.region_coverage(*plan["normal"])
+    out["smalldel"] = ctx.smalldel(*plan["intervals"])
+    c = plan["smalldel_cand"]
+    if len(c["chr1"]):
+        out["cl1"] = gpu_ops.cluster_arrays(ctx, c, plan["cutoff"], 2000, plan["cutoff"], 100)
     out["seq"] = ctx.region_coverage(*plan["seq_edges"])
     out["conc"] = ctx.concordant(*plan["conc"])
     if pipelined:

@@ -41,6 +41,7 @@ void coral_destroy(coral_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->scan_stream) { cudaStreamSynchronize(c->scan_stream); cudaStreamDestroy(c->scan_stream); }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->scan_pending) coral_mem::scan_joined();
     c->scan_pending = false;
     if (c->stream) cudaStreamSynchronize(c->stream);
@@ -86,6 +87,7 @@ int coral_set_params(coral_ctx* c, const coral_params* p) {
 int coral_set_option(coral_ctx* c, const char* name, int64_t value) {
     if (!c || !name) return CORAL_E_ARG;
     if (std::string(name) == "full_name_sort") { c->force_full_name_sort = value != 0; return CORAL_OK; }
+    if (std::string(name) == "pass_overlap_scan") { c->pass.overlap_scan = value != 0; c->pass.invalidate(); return CORAL_OK; }
     c->err = std::string("unknown option: ") + name;
     return CORAL_E_ARG;
 }
@@ -210,6 +212,8 @@ int coral_pass_end(coral_ctx* c, int32_t* replayed) {
     PassState& P = c->pass;
     if (!P.active) { c->err = "coral_pass_end outside a pass"; return CORAL_E_STATE; }
     cudaSetDevice(c->device);
+    int join_rc = CORAL_OK;
+    if (c->scan_pending) join_rc = coral_wait_scan(c);     // a rescan nothing joined: its verdict belongs to this pass
     P.active = false;
     uint32_t bad = 0;
     cudaError_t e = cudaMemcpyAsync(&bad, P.d_flag, 4, cudaMemcpyDeviceToHost, c->stream);
@@ -221,6 +225,7 @@ int coral_pass_end(coral_ctx* c, int32_t* replayed) {
     }
     const bool was_replay = P.replay;
     if (replayed) *replayed = was_replay ? 1 : 0;
+    if (join_rc != CORAL_OK) { P.invalidate(); P.copies.clear(); P.after.clear(); return join_rc; }
     if (bad != 0) {          // the device disagreed with a replayed size: nothing of this pass can be trusted
         P.invalidate(); P.copies.clear(); P.after.clear();
         c->err = "pipelined pass diverged from the recorded one (" + std::to_string(bad) +
@@ -242,7 +247,10 @@ int coral_rescan(coral_ctx* c) {
     if (!c) return CORAL_E_ARG;
     if (!c->loaded || c->rows_only) { c->err = "coral_rescan before coral_load_records"; return CORAL_E_STATE; }
     cudaSetDevice(c->device);
-    if (c->pass.active) coral::pass_call(c, coral::pass_hash(coral::PASS_H0, "rescan", 6));
+    if (c->pass.active) {
+        coral::pass_call(c, coral::pass_hash(coral::PASS_H0, c->pass.overlap_scan ? "rescan+" : "rescan", 7));
+        if (c->pass.overlap_scan) return coral_start_scan_overlapped(c);
+    }
     return coral_run_scan(c);
 }
 

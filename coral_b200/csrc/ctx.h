@@ -179,6 +179,7 @@ struct PassState {
     bool active = false;      // between coral_pass_begin and coral_pass_end
     bool replay = false;      // sizes come from `vals`
     bool complete = false;    // `vals` / `keys` describe a whole pass
+    bool overlap_scan = true; // coral_rescan inside a pass: pre-scan + full scan on its own stream (option "pass_overlap_scan")
     std::vector<uint64_t> vals;
     size_t cur = 0;
     std::vector<uint64_t> keys;   // one per entry-point call: hash of (entry point, host inputs)
@@ -244,6 +245,7 @@ struct coral_ctx {
     DevBuf scan_status;   // the record scan's own status words (it may run next to other entry points)
     cudaStream_t scan_stream = nullptr;   // CORAL_RECORDS_HOST_MAPPED_ASYNC: the full scan runs here ...
     bool scan_pending = false;            // ... until coral_wait_scan() joins it
+    cudaEvent_t ev_fork = nullptr;        // orders the scan stream behind the ctx's stream (coral_start_scan_overlapped)
     DevBuf sa_side, sa_side_off;          // SA strings copied to HBM by the pre-scan, and where each record's sits
     bool sa_side_valid = false;
     bool scan_lazy = false;               // CORAL_RECORDS_HOST_MAPPED_LAZY: pre-scan done, full scan not started yet
@@ -274,6 +276,7 @@ int coral_upload_ref_hashes(coral_ctx* ctx);
 void coral_release_tables(coral_ctx* ctx);
 int coral_run_scan(coral_ctx* ctx);
 int coral_start_scan_async(coral_ctx* ctx, bool launch_full_scan);
+int coral_start_scan_overlapped(coral_ctx* ctx);
 int coral_run_fetch(coral_ctx* ctx);
 int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
                               int32_t n, int64_t* base_sum, int64_t* rec_count);

@@ -111,8 +111,13 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
     return r;
 }
 //                                   op:   3 N 2 D 1 I 0 M           7 = 6 P 5 H 4 S
+#define CIG_TM_LO 0x00000001u          //   0   0   0   1
+#define CIG_TM_HI 0x01000000u          //                              1   0   0   0
 #define CIG_TN_LO 0x01010100u          //   1   1   1   0        non-M-type (everything but M, =, X)
 #define CIG_TN_HI 0x00010101u          //                              0   1   1   1
+#ifndef SC_NM_TABLE
+#define SC_NM_TABLE 0
+#endif
 #define CIG_TD_LO 0x01010000u          //   1   1   0   0
 #define CIG_TD_HI 0x00000000u
 #define CIG_TQ_LO 0x00000100u          //   0   0   1   0
@@ -272,25 +277,6 @@ __device__ __noinline__ AuxOut aux_walk_global(const uint8_t* p, const uint8_t* 
     return r;
 }
 
-// The 8 CIGAR ops of one lane (word slots mw .. mw + 7 of the stage; the op array is not word aligned inside a record:
-// one funnel shift per op), slots outside [w_first, w_end) of an edge window neutralised.  The hot loop consumes the
-// ops at once; the rare paths load them again instead of keeping eight registers alive across the loop body.
-__device__ __forceinline__ void cig_load8(uint32_t (&v)[8], uint32_t wa, uint32_t sh, bool edge, int32_t mw, int32_t w_first,
-                                          int32_t w_end) {
-    const uint4 qa = lds128(wa), qb = lds128(wa + 16);
-    const uint32_t nx = lds32(wa + 32);
-    v[0] = __funnelshift_r(qa.x, qa.y, sh); v[1] = __funnelshift_r(qa.y, qa.z, sh);
-    v[2] = __funnelshift_r(qa.z, qa.w, sh); v[3] = __funnelshift_r(qa.w, qb.x, sh);
-    v[4] = __funnelshift_r(qb.x, qb.y, sh); v[5] = __funnelshift_r(qb.y, qb.z, sh);
-    v[6] = __funnelshift_r(qb.z, qb.w, sh); v[7] = __funnelshift_r(qb.w, nx, sh);
-    if (edge) {
-        const uint4 ma = cigar_mask_edge(make_uint4(v[0], v[1], v[2], v[3]), mw, w_first, w_end);
-        const uint4 mb = cigar_mask_edge(make_uint4(v[4], v[5], v[6], v[7]), mw + 4, w_first, w_end);
-        v[0] = ma.x; v[1] = ma.y; v[2] = ma.z; v[3] = ma.w;
-        v[4] = mb.x; v[5] = mb.y; v[6] = mb.z; v[7] = mb.w;
-    }
-}
-
 // Per-warp control block in shared memory (addressed by shared-window offsets).  Lane 0 is the warp's producer:
 // it owns the generator state, pulls record indices from the global queue, issues the bulk copies and publishes
 // one descriptor per stage; all lanes consume.  Keeping this state out of registers is what lets 32 warps live
@@ -301,11 +287,7 @@ constexpr uint32_t WC_GEN = WC_BAR + ((8 * SC_NST + 15) & ~15);   // {base lo, b
 constexpr uint32_t WC_REC = WC_GEN + 32;                 // {pos, l_seq, n_cig, c0} {s1, rec_size, unmapped, -}
 constexpr uint32_t WC_BYTES = WC_REC + 32;
 constexpr size_t SC_RING_BYTES = (size_t)SC_WARPS * SC_NST * SC_SB;
-// A 256-op CIGAR window starts at a 16-byte boundary at or below its first op and always spans 1 KB + one word, so it
-// may begin 12 bytes in front of a stage and end ~1 KB behind it: that much shared memory exists on both sides of the
-// ring (the bytes read there are neutralised by the edge mask).
-constexpr uint32_t SC_PAD_HEAD = 16, SC_PAD_TAIL = 1104;
-constexpr size_t SC_SMEM_TOTAL = SC_PAD_HEAD + SC_RING_BYTES + (size_t)SC_WARPS * WC_BYTES + SC_PAD_TAIL;
+constexpr size_t SC_SMEM_TOTAL = SC_RING_BYTES + (size_t)SC_WARPS * WC_BYTES;
 
 enum { G_NEW = 0, G_R1 = 1, G_AUX = 2, G_DONE = 3 };
 
@@ -390,7 +372,7 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
     const uint32_t lane = lane_id();
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    const uint32_t smem0 = smem_u32(smem) + SC_PAD_HEAD;
+    const uint32_t smem0 = smem_u32(smem);
     const uint32_t ctl = smem0 + (uint32_t)SC_RING_BYTES + warp * WC_BYTES;
     uint32_t ahead = 0;          // lane 0: next record index, fetched one grab early
     if (lane == 0) {
@@ -481,8 +463,6 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
         const uint32_t n_cig = rc0.z, c0 = rc0.w;
 
         // ---- CIGAR ops fully inside this segment ---------------------------------------------------------
-        // 8 consecutive ops per lane and trip (two LDS.128 + the word behind them), 256 ops per warp and trip: the
-        // per-window work (ballot, reductions, the gap-event trigger, loop control) is paid once per 256 ops.
         if (cig_next < n_cig && seg_end >= c0 + 4) {
             const uint32_t i_hi = min(n_cig, (seg_end - c0) >> 2);
             if (i_hi > cig_next) {
@@ -491,34 +471,60 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
                 const int32_t w_first = wc + (int32_t)cig_next;
                 const int32_t w_end = wc + (int32_t)i_hi;                          // first word slot past the last op
 #pragma unroll 1
-                for (int32_t w0 = w_first & ~3; w0 < w_end; w0 += 256) {
-                    const int32_t mw = w0 + 8 * (int32_t)lane;
-                    // a window may reach up to 1 KB past the segment (and 12 bytes in front of it): the ring has that
-                    // much slack on both sides (SC_PAD), whatever is read there is neutralised by the edge mask
-                    const uint32_t wa = buf + 4 * mw;
-                    const bool edge = w0 < w_first || w0 + 256 > w_end;
-                    uint32_t v[8];
-                    cig_load8(v, wa, sh, edge, mw, w_first, w_end);
-                    // classes by byte tables indexed with op & 7 (X = 8 lands on M): non-M-type {I,D,N,S,H,P}, D/N, {I,S,H}.
-                    // Every table has 0 for op 0, so the selector's upper (zero) nibbles give clean 0/1 multipliers.
-                    // (nothing of v[] stays live behind this loop: the rare paths below load the window again)
-                    uint32_t nm_it = 0, dn_it = 0, dn_after = 0, tot_a = 0, tot_b = 0, all_nm = 1;
-#pragma unroll
-                    for (int j = 0; j < 8; j++) {
-                        const uint32_t sel = v[j] & 7u;
-                        const uint32_t nmj = prmt(CIG_TN_LO, CIG_TN_HI, sel);
-                        const uint32_t bdj = prmt(CIG_TD_LO, CIG_TD_HI, sel);
-                        const uint32_t bq = prmt(CIG_TQ_LO, CIG_TQ_HI, sel);
-                        const uint32_t ln = v[j] >> 4;
-                        if (j & 1) tot_b += ln; else tot_a += ln;
-                        all_nm &= nmj;
-                        nm_it = nmj * ln + nm_it;
-                        dn_it = bdj * ln + dn_it;
-                        ishsum = bq * ln + ishsum;
-                        dn_after = bdj * ln + dn_after * nmj;      // D/N bases behind the lane's last M-type op
+                for (int32_t w0 = w_first & ~3; w0 < w_end; w0 += 128) {
+                    const int32_t mw = w0 + 4 * (int32_t)lane;
+                    uint4 q = make_uint4(0, 0, 0, 0);
+                    if (mw * 4 + 16 <= SC_SB) q = lds128(buf + 4 * mw);
+                    uint32_t nx = __shfl_down_sync(FULL_MASK, q.x, 1);
+                    if (lane == 31) nx = (mw * 4 + 20 <= SC_SB) ? lds32(buf + 4 * mw + 16) : 0u;
+                    uint32_t v[4];
+                    v[0] = __funnelshift_r(q.x, q.y, sh);
+                    v[1] = __funnelshift_r(q.y, q.z, sh);
+                    v[2] = __funnelshift_r(q.z, q.w, sh);
+                    v[3] = __funnelshift_r(q.w, nx, sh);
+                    if (w0 < w_first || w0 + 128 > w_end) {    // edge window: neutralise slots outside [cig_next, i_hi)
+                        const uint4 mv = cigar_mask_edge(make_uint4(v[0], v[1], v[2], v[3]), mw, w_first, w_end);
+                        v[0] = mv.x; v[1] = mv.y; v[2] = mv.z; v[3] = mv.w;
                     }
-                    const uint32_t m_it = tot_a + tot_b - nm_it;
-                    const bool lane_m = all_nm == 0;
+                    uint32_t bm[4], bd[4], len[4], m_it = 0, dn_it = 0, dn_after = 0;
+#if SC_NM_TABLE
+                    // variant: the table of the NON-M-type ops {I,D,N,S,H,P} instead of the M-type one.  Like the D/N and
+                    // {I,S,H} tables it has 0 for op 0, so the selector is op & 7 alone (its zero upper nibbles pick
+                    // entry 0 = clean upper bytes); M-type bases = all bases - non-M bases; the open-gap recurrence
+                    // multiplies by the non-M flag directly.
+                    uint32_t nmv[4], tot = 0, nm_it = 0;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const uint32_t sel = v[j] & 7u;
+                        nmv[j] = prmt(CIG_TN_LO, CIG_TN_HI, sel);
+                        bd[j] = prmt(CIG_TD_LO, CIG_TD_HI, sel);
+                        const uint32_t bq = prmt(CIG_TQ_LO, CIG_TQ_HI, sel);
+                        len[j] = v[j] >> 4;
+                        tot += len[j];
+                        nm_it = nmv[j] * len[j] + nm_it;
+                        dn_it = bd[j] * len[j] + dn_it;
+                        ishsum = bq * len[j] + ishsum;
+                        dn_after = bd[j] * len[j] + dn_after * nmv[j];
+                    }
+                    m_it = tot - nm_it;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) bm[j] = nmv[j] ^ 1u;          // only the rare paths below read bm[]
+                    const bool lane_m = (nmv[0] & nmv[1] & nmv[2] & nmv[3]) == 0;
+#else
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const uint32_t sel = (v[j] & 7u) | sel_or;
+                        bm[j] = prmt(CIG_TM_LO, CIG_TM_HI, sel);
+                        bd[j] = prmt(CIG_TD_LO, CIG_TD_HI, sel);
+                        const uint32_t bq = prmt(CIG_TQ_LO, CIG_TQ_HI, sel);
+                        len[j] = v[j] >> 4;
+                        m_it = bm[j] * len[j] + m_it;
+                        dn_it = bd[j] * len[j] + dn_it;
+                        ishsum = bq * len[j] + ishsum;
+                        dn_after = bd[j] * len[j] + dn_after * (bm[j] ^ 1u);
+                    }
+                    const bool lane_m = (bm[0] | bm[1] | bm[2] | bm[3]) != 0;
+#endif
                     const uint32_t dn_tot = __reduce_add_sync(FULL_MASK, dn_it);
                     const uint32_t mball = __ballot_sync(FULL_MASK, lane_m);
                     // exact gap events: only when the D/N bases of this window (+ the open gap) could exceed the cut
@@ -528,16 +534,12 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
                         const int32_t lane_tot = (int32_t)(m_it + dn_it);
                         const int32_t incl = warp_incl_sum_i32(lane_tot);
                         int32_t cur = base_ref + incl - lane_tot;
-                        int32_t st[8], last_m_end = -1;
-                        uint32_t mmask = 0;                       // bit j: op j of this lane is M-type
-                        cig_load8(v, wa, sh, edge, mw, w_first, w_end);
+                        int32_t st[4], last_m_end = -1;
 #pragma unroll
-                        for (int j = 0; j < 8; j++) {
-                            const uint32_t sel = v[j] & 7u;
-                            const uint32_t nmj = prmt(CIG_TN_LO, CIG_TN_HI, sel), bdj = prmt(CIG_TD_LO, CIG_TD_HI, sel);
+                        for (int j = 0; j < 4; j++) {
                             st[j] = cur;
-                            cur += (int32_t)(((nmj ^ 1u) | bdj) * (v[j] >> 4));
-                            if (!nmj) { last_m_end = cur; mmask |= 1u << j; }
+                            cur += (int32_t)((bm[j] | bd[j]) * len[j]);
+                            if (bm[j]) last_m_end = cur;
                         }
                         const uint32_t before = mball & lt_mask;
                         const int src = before ? 31 - __clz(before) : 0;
@@ -545,24 +547,20 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
                         bool have_prev = before != 0;
                         if (!have_prev) { prev = base_ref - (int32_t)carried; have_prev = seen_m; }
                         uint32_t evmask = 0, nbefore = 0, ntot = 0;
-                        int32_t evprev[8];
+                        int32_t evprev[4];
 #pragma unroll
-                        for (int j = 0; j < 8; j++) {
+                        for (int j = 0; j < 4; j++) {
                             evprev[j] = prev;
                             bool e = false;
-                            if (mmask & (1u << j)) {
+                            if (bm[j]) {
                                 e = have_prev && (st[j] - prev) > min_del_len;
-                                prev = st[j] + (int32_t)(v[j] >> 4);
+                                prev = st[j] + (int32_t)len[j];
                                 have_prev = true;
                             }
                             if (e) evmask |= 1u << j;
-                        }
-                        // slots in op order: lane-major, so a lane's events follow those of all lower lanes
-                        {
-                            const uint32_t mine = __popc(evmask);
-                            const uint32_t incl_e = (uint32_t)warp_incl_sum_i32((int32_t)mine);
-                            nbefore = incl_e - mine;
-                            ntot = __shfl_sync(FULL_MASK, incl_e, 31);
+                            const uint32_t b = __ballot_sync(FULL_MASK, e);
+                            nbefore += __popc(b & lt_mask);
+                            ntot += __popc(b);
                         }
                         if (ntot) {
                             unsigned long long slot0 = 0;
@@ -570,7 +568,7 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
                             slot0 = __shfl_sync(FULL_MASK, slot0, 0);
                             uint32_t r = nbefore;
 #pragma unroll
-                            for (int j = 0; j < 8; j++) {
+                            for (int j = 0; j < 4; j++) {
                                 if (evmask & (1u << j)) {
                                     const unsigned long long sl = slot0 + r;
                                     if ((int64_t)sl < ev.capacity) {
@@ -592,12 +590,10 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
                             if ((int)lane < fl_) lead = dn_it;
                             else if ((int)lane == fl_) {
                                 uint32_t open = 1;
-                                cig_load8(v, wa, sh, edge, mw, w_first, w_end);
 #pragma unroll
-                                for (int j = 0; j < 8; j++) {
-                                    const uint32_t sel = v[j] & 7u;
-                                    open &= prmt(CIG_TN_LO, CIG_TN_HI, sel);
-                                    lead += open * prmt(CIG_TD_LO, CIG_TD_HI, sel) * (v[j] >> 4);
+                                for (int j = 0; j < 4; j++) {
+                                    open &= bm[j] ^ 1u;
+                                    lead += open * bd[j] * len[j];
                                 }
                             }
                             lead = __reduce_add_sync(FULL_MASK, lead);
@@ -938,6 +934,61 @@ int coral_start_scan_async(coral_ctx* ctx, bool launch_full_scan) {
     return CORAL_OK;
 }
 
+// Rescan inside a pipelined pass (device-resident records): a pre-scan (record core, read name, aux block: ~150 B per
+// record) fills the columns coral_fetch / coral_candidates_* / coral_cluster_call read, then the full scan runs on its own
+// stream — all SMs but a few block slots, which is where the small kernels of those entry points run MEANWHILE on the
+// ctx's stream.  Entry points that need the scan's CIGAR / SEQ columns join it with a stream dependency
+// (coral_wait_scan).  Same kernels, same columns, same values as coral_run_scan.
+int coral_start_scan_overlapped(coral_ctx* ctx) {
+    using namespace coral;
+    const int64_t n = ctx->nrec;
+    if (n == 0) return coral_run_scan(ctx);
+    ctx->scan_lazy = false;
+    ctx->sa_side_valid = false;
+    if (ctx->scan_pending) {
+        ctx->scan_pending = false;
+        cudaStreamSynchronize(ctx->scan_stream);
+        coral_mem::scan_joined();
+    }
+    CORAL_TRY(scan_ensure_tables(ctx));
+    if (!ctx->scan_stream) CORAL_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->scan_stream, cudaStreamNonBlocking));
+    if (!ctx->ev_fork) CORAL_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    GapEvents& g = ctx->gaps;
+    CORAL_CUDA(ctx, cudaMemsetAsync(g.counter.p, 0, 16, ctx->stream));
+    CORAL_CUDA(ctx, cudaMemsetAsync(ctx->scan_status.p, 0, 64, ctx->stream));
+    CORAL_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
+    CORAL_CUDA(ctx, cudaStreamWaitEvent(ctx->scan_stream, ctx->ev_fork, 0));
+    ScanCols o = scan_cols(ctx);
+    ScanEvents e{g.rec.as<uint32_t>(), g.k.as<uint32_t>(), g.next_start.as<int32_t>(), g.prev_end.as<int32_t>(),
+                 g.counter.as<unsigned long long>(), g.capacity};
+    int per_sm = 0;
+    CORAL_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_scan_records, SC_WARPS * 32, SC_SMEM_TOTAL));
+    if (per_sm < 1) per_sm = 1;
+    const int64_t want = (n + SC_WARPS - 1) / SC_WARPS;
+    const int64_t full = (int64_t)ctx->sm_count * per_sm;
+    const int64_t reserve = per_sm > 1 ? std::max<int64_t>(8, ctx->sm_count / 8) : 0;     // block slots left to the small kernels
+    const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>(want, full - reserve));
+    if (!ctx->ev_beg[CORAL_STAGE_SCAN]) { cudaEventCreate(&ctx->ev_beg[CORAL_STAGE_SCAN]); cudaEventCreate(&ctx->ev_end[CORAL_STAGE_SCAN]); }
+    cudaEventRecord(ctx->ev_beg[CORAL_STAGE_SCAN], ctx->scan_stream);
+    k_scan_records<<<blocks, SC_WARPS * 32, SC_SMEM_TOTAL, ctx->scan_stream>>>(
+        ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, ctx->prm.min_del_len, o, e, ctx->scan_status.as<int32_t>(),
+        reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1), 0u);
+    cudaEventRecord(ctx->ev_end[CORAL_STAGE_SCAN], ctx->scan_stream);
+    ctx->ev_valid[CORAL_STAGE_SCAN] = true;
+    ctx->n_launches++;
+    CORAL_CUDA(ctx, cudaGetLastError());
+    // the pre-scan, on the ctx's stream: what runs next on this stream (fetch ...) reads its columns
+    SideText side{nullptr, nullptr, 0, nullptr};
+    const int pre_blocks = (int)std::min<int64_t>((n + 7) / 8, (int64_t)ctx->sm_count * 8);
+    k_prescan_records<<<pre_blocks, 256, 0, ctx->stream>>>(ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, o, side,
+                                                          ctx->scan_status.as<int32_t>());
+    ctx->n_launches++;
+    CORAL_CUDA(ctx, cudaGetLastError());
+    ctx->scan_pending = true;
+    coral_mem::scan_started();
+    return CORAL_OK;
+}
+
 extern "C" int coral_wait_scan(coral_ctx* ctx) {
     if (!ctx) return CORAL_E_ARG;
     if (ctx->scan_lazy) {
@@ -947,7 +998,15 @@ extern "C" int coral_wait_scan(coral_ctx* ctx) {
     if (!ctx->scan_pending) return CORAL_OK;
     cudaSetDevice(ctx->device);
     ctx->scan_pending = false;
-    const int v = scan_verdict(ctx, ctx->scan_stream);
+    int v;
+    if (ctx->pass.active) {
+        // inside a pipelined pass the join is a dependency between streams, not a host synchronisation: what follows on
+        // the ctx's stream waits for the scan kernel; its verdict is resolved like every other size of the pass
+        CORAL_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_end[CORAL_STAGE_SCAN], 0));
+        v = scan_verdict(ctx, ctx->stream);
+    } else {
+        v = scan_verdict(ctx, ctx->scan_stream);
+    }
     coral_mem::scan_joined();
     if (v == 1) return coral_run_scan(ctx);      // more gap events than the buffer held: synchronous rescan with room
     return v;

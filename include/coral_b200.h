@@ -60,7 +60,9 @@ void coral_release_cached_memory(void);
 int coral_set_params(coral_ctx* ctx, const coral_params* p);
 /* Named switches that do not change any result.  "full_name_sort" = 1: coral_fetch groups SA entries by a full
  * 128-bit name sort instead of the 40-bit sort it normally tries first (the path it falls back to when two read
- * names share those bits; exposed so that tests can cover it).  Unknown names return CORAL_E_ARG. */
+ * names share those bits; exposed so that tests can cover it).  "pass_overlap_scan" = 0: coral_rescan inside a
+ * pipelined pass runs the one-kernel scan on the ctx's stream instead of pre-scan + full scan on a second stream
+ * (default 1, see coral_pass_begin).  Unknown names return CORAL_E_ARG. */
 int coral_set_option(coral_ctx* ctx, const char* name, int64_t value);
 
 /* Reference sequence table (BAM header order).  `names` = n NUL-terminated strings back to back.
@@ -135,6 +137,9 @@ int coral_rescan(coral_ctx* ctx);
  * Entry points that take part: coral_rescan, coral_region_coverage, coral_fetch + coral_get_chimeric, coral_smalldel +
  * coral_get_smalldel, coral_candidates_l + coral_get_candidates, coral_cluster_call(_candidates) + coral_get_clusters,
  * coral_concordant + coral_get_concordant_rows.  Any other entry point may be called inside a pass; it synchronises.
+ * coral_rescan inside a pass splits the scan as the asynchronous load does: a pre-scan fills the columns coral_fetch /
+ * coral_candidates_* / coral_cluster_call read, the full scan then runs on a second stream next to those entry points'
+ * kernels, and the first entry point that needs its CIGAR / SEQ columns joins it by a stream dependency.
  * This is how one step of the device-resident benchmark runs the path (reference call order
  * infer_breakpoint_graph.py:1354-1386) as one stream of kernels. */
 int coral_pass_begin(coral_ctx* ctx);

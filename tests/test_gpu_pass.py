@@ -22,19 +22,27 @@ def _same(a, b, path=""):
         assert a == b, path
 
 
-def _calls(ctx, plan, cutoff):
+def _calls(ctx, plan, cutoff, fetch_first=False):
+    """fetch_first: the order bench.py uses — what only needs the pre-scan's columns comes first and runs, inside a
+    pass, next to the full scan (coral_rescan in a pass = pre-scan + full scan on a second stream)."""
     from coral_b200 import gpu_ops
     out = {}
     ctx.rescan()
+
+    def chimeric():
+        out["fetch"] = ctx.fetch()
+        cand = ctx.candidates_l(*plan["intervals"])
+        out["cand"] = cand
+        if cand["n"]:
+            out["cl2"] = ctx.cluster_call_candidates(cand["n"], cutoff, 2000, cutoff, 100)
+    if fetch_first:
+        chimeric()
     out["normal"] = ctx.region_coverage(*plan["normal"])
-    out["fetch"] = ctx.fetch()
     out["smalldel"] = ctx.smalldel(*plan["intervals"])
     if len(plan["sd_cand"]["chr1"]):
         out["cl1"] = gpu_ops.cluster_arrays(ctx, plan["sd_cand"], cutoff, 2000, cutoff, 100)
-    cand = ctx.candidates_l(*plan["intervals"])
-    out["cand"] = cand
-    if cand["n"]:
-        out["cl2"] = ctx.cluster_call_candidates(cand["n"], cutoff, 2000, cutoff, 100)
+    if not fetch_first:
+        chimeric()
     out["seq"] = ctx.region_coverage(*plan["seq"])
     out["conc"] = ctx.concordant(*plan["conc"])
     return out
@@ -91,6 +99,19 @@ def test_pipelined_pass_equals_call_by_call(built_lib, dataset, cfg_name, scale)
         replayed = ctx.pass_end()
         assert replayed == (k > 0)
         _same(_canon(got), want)
+    for k in range(3):                      # the overlapped order: another call sequence, so it records first
+        ctx.pass_begin()
+        got = _calls(ctx, plan, 3.0, fetch_first=True)
+        replayed = ctx.pass_end()
+        assert replayed == (k > 0)
+        _same(_canon(got), want)
+    ctx.set_option("pass_overlap_scan", 0)  # the one-kernel scan on the ctx's stream
+    for k in range(2):
+        ctx.pass_begin()
+        got = _calls(ctx, plan, 3.0, fetch_first=True)
+        ctx.pass_end()
+        _same(_canon(got), want)
+    ctx.set_option("pass_overlap_scan", 1)
     # a host input changes (other cutoff -> other cluster calls): the pass re-records from that call on, results stay right
     want2 = _canon(_calls(ctx, plan, 5.0))
     ctx.pass_begin()
