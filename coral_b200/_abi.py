@@ -459,6 +459,19 @@ class Context(object):
             ctypes.c_int32(match_cutoff), ctypes.c_int32(max_peels), ctypes.byref(nc)))
         return self._clusters_out(int(n), nc.value)
 
+    def bp_match(self, a1, a4, minus1, minus2, rgap, b1, b4, cutoff1, cutoff2):
+        """coral_bp_match over n pairs -> uint8[n]."""
+        i64 = lambda a: np.ascontiguousarray(a, dtype=np.int64)
+        u8 = lambda a: np.ascontiguousarray(a, dtype=np.uint8)
+        a1, a4, b1, b4 = map(i64, (a1, a4, b1, b4))
+        minus1, minus2 = u8(minus1), u8(minus2)
+        rgap = np.ascontiguousarray(rgap, dtype=np.float64)
+        n = len(a1)
+        out = np.zeros(n, np.uint8)
+        self._check(self._L.coral_bp_match(self._h, ctypes.c_int64(n), _p(a1), _p(a4), _p(minus1), _p(minus2), _p(rgap), _p(b1),
+                                           _p(b4), ctypes.c_int64(int(cutoff1)), ctypes.c_int64(int(cutoff2)), _p(out)))
+        return out
+
     def concordant_rows_only(self, tid, p):
         """The (edge, record, mask) rows of this ctx's records stay on the device (concordant_pack); no count."""
         tid = np.ascontiguousarray(tid, dtype=np.int32)

@@ -68,15 +68,15 @@ def interval2bp(R1, R2, r=(), rgap=0):
 
 
 def bp_match(bp1, bp2, rgap, bp_distance_cutoff):
-    """reference :391-416 for one pair, through the same device routine the peel loop uses."""
+    """reference :391-416 for one pair (any rgap, one cutoff per coordinate), evaluated by the device routine the peel
+    loop uses (coral_bp_match); the chromosome / orientation comparison of :396 happens here, on the strings."""
     if not (bp1[0] == bp2[0] and bp1[3] == bp2[3] and bp1[2] == bp2[2] and bp1[5] == bp2[5]):
         return False
-    if bp_distance_cutoff[0] != bp_distance_cutoff[1] or rgap != bp1[7] * 1.2:
-        raise NotImplementedError("bp_match drop-in supports the reference's call shape: rgap = bp1[7] * 1.2, equal cutoffs")
-    probe = list(bp1[:11]) + [-1] * max(0, 11 - len(bp1))
-    target = list(probe)
-    target[1], target[4] = bp2[1], bp2[4]
-    return gpu_ops.match_one(probe, int(bp2[1]), int(bp2[4]), int(bp_distance_cutoff[0]))
+    ctx = gpu_ops.default_context()
+    r = ctx.bp_match([int(bp1[1])], [int(bp1[4])], [0 if bp1[2] == '+' else 1 if bp1[2] == '-' else 2],
+                     [0 if bp1[5] == '+' else 1 if bp1[5] == '-' else 2], [float(rgap)], [int(bp2[1])], [int(bp2[4])],
+                     int(bp_distance_cutoff[0]), int(bp_distance_cutoff[1]))
+    return bool(r[0])
 
 
 def _chimeric_to_device(ctx, reads):

@@ -198,19 +198,33 @@ __device__ __forceinline__ double u128_to_double(u128 v) {
 }
 
 // bp_match(bp_, bp, rgap = bp_[7] * 1.2, [c, c]) for members of one cluster (chr/orientation equal), bu:391-416
-__device__ __forceinline__ bool bp_match_dev(int32_t p1, int32_t p4, bool minus1, bool minus2, int32_t rgap_i,
-                                             int32_t b1, int32_t b4, int32_t c) {
-    const int64_t d1 = (int64_t)p1 - b1, d2 = (int64_t)p4 - b4;
-    const bool near1 = (d1 < 0 ? -d1 : d1) < c, near2 = (d2 < 0 ? -d2 : d2) < c;
-    const double rgap = __dmul_rn((double)rgap_i, 1.2);
+// general form: any rgap (double), one cutoff per coordinate
+__device__ __forceinline__ bool bp_match_gen(int64_t p1, int64_t p4, bool plus1, bool minus1, bool plus2, bool minus2,
+                                             double rgap, int64_t b1, int64_t b4, int64_t c1, int64_t c2) {
+    const int64_t d1 = p1 - b1, d2 = p4 - b4;
+    const bool near1 = (d1 < 0 ? -d1 : d1) < c1, near2 = (d2 < 0 ? -d2 : d2) < c2;
     if (rgap <= 0) return near1 && near2;
     double slack = rgap;
     bool used1 = false, used2 = false;
-    if (!minus1 && d1 <= -(int64_t)c) { slack = __dsub_rn(slack, (double)(-d1 - c + 1)); used1 = true; }
-    if (minus1 && d1 >= (int64_t)c) { slack = __dsub_rn(slack, (double)(d1 - c + 1)); used1 = true; }
-    if (!minus2 && d2 <= -(int64_t)c) { slack = __dsub_rn(slack, (double)(-d2 - c + 1)); used2 = true; }
-    if (minus2 && d2 >= (int64_t)c) { slack = __dsub_rn(slack, (double)(d2 - c + 1)); used2 = true; }
+    if (plus1 && d1 <= -c1) { slack = __dsub_rn(slack, (double)(-d1 - c1 + 1)); used1 = true; }
+    if (minus1 && d1 >= c1) { slack = __dsub_rn(slack, (double)(d1 - c1 + 1)); used1 = true; }
+    if (plus2 && d2 <= -c2) { slack = __dsub_rn(slack, (double)(-d2 - c2 + 1)); used2 = true; }
+    if (minus2 && d2 >= c2) { slack = __dsub_rn(slack, (double)(d2 - c2 + 1)); used2 = true; }
     return ((used1 && slack >= 0) || near1) && ((used2 && slack >= 0) || near2);
+}
+__device__ __forceinline__ bool bp_match_dev(int32_t p1, int32_t p4, bool minus1, bool minus2, int32_t rgap_i,
+                                             int32_t b1, int32_t b4, int32_t c) {
+    return bp_match_gen(p1, p4, !minus1, minus1, !minus2, minus2, __dmul_rn((double)rgap_i, 1.2), b1, b4, c, c);
+}
+
+// operator form of bp_match (bu:391-416) over n pairs
+__global__ void k_bp_match(int64_t n, const int64_t* __restrict__ a1, const int64_t* __restrict__ a4,
+                           const uint8_t* __restrict__ m1, const uint8_t* __restrict__ m2, const double* __restrict__ rgap,
+                           const int64_t* __restrict__ b1, const int64_t* __restrict__ b4, int64_t c1, int64_t c2,
+                           uint8_t* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n)       // orientation codes: 0 '+', 1 '-', anything else = neither (the reference compares strings)
+        out[i] = bp_match_gen(a1[i], a4[i], m1[i] == 0, m1[i] == 1, m2[i] == 0, m2[i] == 1, rgap[i], b1[i], b4[i], c1, c2) ? 1 : 0;
 }
 
 // signed variant (positions may be negative in synthetic operator tests; Python sums are exact either way)
@@ -607,6 +621,33 @@ static int cluster_core(coral_ctx* c, int64_t n, coral::CandIn C, double min_clu
     c->cl_n_clusters = n_cl;
     c->cl_valid = true;
     if (n_clusters) *n_clusters = n_cl;
+    return CORAL_OK;
+}
+
+// Operator form of breakpoint_utilities.bp_match (bu:391-416) for n pairs whose chromosomes and orientations already
+// agree (the caller compares those: they are strings on its side): pos1 / pos2 of bp1 and bp2, the orientation of each
+// end of bp1 (0 '+', 1 '-'), rgap as the reference passes it (any double), one cutoff per coordinate.
+extern "C" int coral_bp_match(coral_ctx* c, int64_t n, const int64_t* bp1_pos1, const int64_t* bp1_pos2, const uint8_t* minus1,
+                              const uint8_t* minus2, const double* rgap, const int64_t* bp2_pos1, const int64_t* bp2_pos2,
+                              int64_t cutoff1, int64_t cutoff2, uint8_t* out) {
+    using namespace coral;
+    if (!c || n < 0) return CORAL_E_ARG;
+    if (n == 0) return CORAL_OK;
+    cudaSetDevice(c->device);
+    DevBuf& w = c->cw[W_STATS];
+    const size_t n8 = (size_t)n * 8;
+    CORAL_CUDA(c, w.ensure(5 * n8 + 3 * (size_t)n + 64));
+    int64_t* d = w.as<int64_t>();
+    uint8_t* u = reinterpret_cast<uint8_t*>(d + 5 * n);
+    CORAL_TRY(h2d(c, d, bp1_pos1, (size_t)n)); CORAL_TRY(h2d(c, d + n, bp1_pos2, (size_t)n));
+    CORAL_TRY(h2d(c, d + 2 * n, bp2_pos1, (size_t)n)); CORAL_TRY(h2d(c, d + 3 * n, bp2_pos2, (size_t)n));
+    CORAL_TRY(h2d(c, d + 4 * n, rgap, (size_t)n));
+    CORAL_TRY(h2d(c, u, minus1, (size_t)n)); CORAL_TRY(h2d(c, u + n, minus2, (size_t)n));
+    LAUNCH_1D(k_bp_match, n, n, d, d + n, u, u + n, reinterpret_cast<const double*>(d + 4 * n), d + 2 * n, d + 3 * n, cutoff1,
+              cutoff2, u + 2 * n);
+    CORAL_TRY(d2h(c, out, u + 2 * n, (size_t)n));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->cl_valid = false;          // the row-statistics buffer of the last cluster call was reused
     return CORAL_OK;
 }
 

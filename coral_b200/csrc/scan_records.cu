@@ -116,7 +116,7 @@ __device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
 #define CIG_TN_LO 0x01010100u          //   1   1   1   0        non-M-type (everything but M, =, X)
 #define CIG_TN_HI 0x00010101u          //                              0   1   1   1
 #ifndef SC_NM_TABLE
-#define SC_NM_TABLE 0
+#define SC_NM_TABLE 1
 #endif
 #define CIG_TD_LO 0x01010000u          //   1   1   0   0
 #define CIG_TD_HI 0x00000000u

@@ -89,21 +89,3 @@ def bpc2bp(bp_cluster, bp_distance_cutoff, ctx=None):
     bpr = [bp_cluster[i][6] for i in range(len(bp_cluster)) if sub[i] == 0]
     rest = [bp_cluster[i] for i in range(len(bp_cluster)) if sub[i] != 0]
     return bp, bpr, stats_row(r["row_stats"][0]), rest
-
-
-def match_one(bp_, pos1, pos2, cutoff, ctx=None):
-    """bp_match(bp_, [.., pos1, .., pos2, ..], bp_[7] * 1.2, [cutoff, cutoff]) evaluated by the device peel routine:
-    a two-member cluster {probe at (pos1, pos2) with rgap 0, bp_} whose call position is forced to the probe."""
-    ctx = ctx or default_context()
-    # A single-member cluster calls its own position; match the candidate against it in a second one-member call.
-    probe = list(bp_)
-    probe[1], probe[4], probe[7] = pos1, pos2, 0
-    a = flatten_bp_list([probe])
-    r = cluster_arrays(ctx, a, float("inf"), 2000, 0.0, cutoff, max_peels=1)
-    assert int(r["row_pos1"][0]) == pos1 and int(r["row_pos2"][0]) == pos2
-    # Now a cluster of [probe x3, candidate]: the mode is the probe position; candidate matches iff bp_match holds.
-    a = flatten_bp_list([probe, probe, probe, list(bp_)])
-    r = cluster_arrays(ctx, a, float("inf"), 2000, 0.0, cutoff, max_peels=1)
-    if int(r["row_pos1"][0]) != pos1 or int(r["row_pos2"][0]) != pos2:
-        raise NotImplementedError("bp_match drop-in: probe position was filtered by the 3-sigma rule")
-    return bool(r["sub_of"][3] == 0)

@@ -300,6 +300,14 @@ int coral_cluster_call_candidates(coral_ctx* ctx, double min_cluster_size, int32
 int coral_get_clusters(coral_ctx* ctx, uint32_t* order, uint32_t* cluster_ptr, int32_t* n_sub, int32_t* sub_of,
                        int32_t* row_pos1, int32_t* row_pos2, int32_t* row_nb, uint32_t* row_first, double* row_stats);
 
+/* Operator form of breakpoint_utilities.bp_match(bp1, bp2, rgap, [cutoff1, cutoff2]) (bu:391-416) over n pairs whose
+ * chromosomes and orientations already agree (strings on the caller's side): positions of both breakpoints, the
+ * orientation of each end of bp1 (0 '+', 1 '-'), rgap as the reference passes it (any double).  out[i] = 1 / 0.
+ * Invalidates the result of the last coral_cluster_call (shares its buffers). */
+int coral_bp_match(coral_ctx* ctx, int64_t n, const int64_t* bp1_pos1, const int64_t* bp1_pos2, const uint8_t* minus1,
+                   const uint8_t* minus2, const double* rgap, const int64_t* bp2_pos1, const int64_t* bp2_pos2,
+                   int64_t cutoff1, int64_t cutoff2, uint8_t* out);
+
 /* ---- concordant edges ------------------------------------------------------------------------------ *
  * replaces the concordant-edge loop of assign_cov (ibg:1039-1055) for n edges (tid, p) -> (tid, p+1),
  * sorted by (tid, p).  rbps: rows (edge index, record index) naming, through any record of the read, the

@@ -241,6 +241,13 @@ def bpc2bp_vectors(rng):
         b1 = make_bp(0, "chr7", int(rng.integers(900, 1300)), o1, "chr7", int(rng.integers(8800, 9200)), o2, rgap=int(rng.integers(-50, 400)))
         b2 = make_bp(1, "chr7" if rng.random() < 0.9 else "chr1", 1100, o1 if rng.random() < 0.9 else '+', "chr7", 9000, o2)
         out.append({"fn": "bp_match", "args": [b1, b2, b1[7] * 1.2, [100, 100]]})
+    # call shapes the reference itself never uses: any rgap (float), one cutoff per coordinate, zero / negative rgap
+    for t in range(120):
+        o1, o2 = "+-"[int(rng.integers(2))], "+-"[int(rng.integers(2))]
+        b1 = make_bp(0, "chr7", int(rng.integers(700, 1500)), o1, "chr7", int(rng.integers(8600, 9400)), o2, rgap=int(rng.integers(-50, 400)))
+        b2 = make_bp(1, "chr7" if rng.random() < 0.95 else "chr1", 1100, o1 if rng.random() < 0.95 else '+', "chr7", 9000, o2)
+        rgap = float(rng.choice([0.0, -3.5, 17.25, 80.0, 250.5, 1e3])) if t % 3 else float(rng.integers(-10, 600)) * 0.7
+        out.append({"fn": "bp_match", "args": [b1, b2, rgap, [int(rng.choice([1, 50, 100, 333])), int(rng.choice([1, 80, 100, 500]))]]})
     return out
 
 
