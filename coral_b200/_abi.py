@@ -42,6 +42,7 @@ def lib():
         L.coral_n_records.restype = ctypes.c_int64
         L.coral_launch_count.restype = ctypes.c_uint64
         L.coral_stage_ms.restype = ctypes.c_float
+        L.coral_stage_offset_ms.restype = ctypes.c_float
         L.coral_bam_n_records.restype = ctypes.c_int64
         L.coral_bam_ref_len.restype = ctypes.c_int64
         L.coral_bam_ref_name.restype = ctypes.c_char_p
@@ -331,6 +332,12 @@ class Context(object):
 
     def stage_ms(self, stage):
         return float(self._L.coral_stage_ms(self._h, int(stage)))
+
+    def reset_stage_times(self):
+        self._L.coral_reset_stage_times(self._h)
+
+    def stage_offset_ms(self, stage_a, which_a, stage_b, which_b):
+        return float(self._L.coral_stage_offset_ms(self._h, int(stage_a), int(which_a), int(stage_b), int(which_b)))
 
     @property
     def n_records(self):

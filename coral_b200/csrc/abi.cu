@@ -56,6 +56,13 @@ void coral_destroy(coral_ctx* c) {
                      &c->chim.qe, &c->chim.tid, &c->chim.rs, &c->chim.re, &c->chim.strand, &c->chim.mapq, &c->chim.nm};
     for (DevBuf* b : all) b->release();
     if (c->pass.d_flag) cudaFree(c->pass.d_flag);
+    for (cudaEvent_t e : c->pass.events) cudaEventDestroy(e);
+    for (auto& in : c->pass.inputs) if (in.p) coral_mem::release(in.p, in.cap);
+    if (c->pass.lane_stream) { cudaStreamSynchronize(c->pass.lane_stream); cudaStreamDestroy(c->pass.lane_stream); }
+    if (c->pass.ev_lane_begin) cudaEventDestroy(c->pass.ev_lane_begin);
+    if (c->pass.ev_lane_done) cudaEventDestroy(c->pass.ev_lane_done);
+    for (DevBuf& b : c->lane_s) b.release();
+    c->lane_cub_tmp.release(); c->lane_status.release();
     for (auto& ch : c->pass.pinned) cudaFreeHost(ch.p);
     for (DevBuf& b : c->sw) b.release();
     for (DevBuf& b : c->cw) b.release();
@@ -72,7 +79,7 @@ void coral_destroy(coral_ctx* c) {
         if (c->ev_beg[i]) cudaEventDestroy(c->ev_beg[i]);
         if (c->ev_end[i]) cudaEventDestroy(c->ev_end[i]);
     }
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->owns_stream && c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }
 
@@ -87,6 +94,8 @@ int coral_set_params(coral_ctx* c, const coral_params* p) {
 int coral_set_option(coral_ctx* c, const char* name, int64_t value) {
     if (!c || !name) return CORAL_E_ARG;
     if (std::string(name) == "full_name_sort") { c->force_full_name_sort = value != 0; return CORAL_OK; }
+    if (std::string(name) == "pass_fork") { c->pass.fork = value != 0; return CORAL_OK; }
+    if (std::string(name) == "pass_scan_reserve") { c->pass.scan_reserve = value; return CORAL_OK; }
     if (std::string(name) == "pass_overlap_scan") { c->pass.overlap_scan = value != 0; c->pass.invalidate(); return CORAL_OK; }
     c->err = std::string("unknown option: ") + name;
     return CORAL_E_ARG;
@@ -186,6 +195,51 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
 
 void coral_release_cached_memory(void) { coral_mem::trim(); }
 
+// ---- streams of a ctx (for callers that enqueue their own work — NCCL collectives — between entry points of a pass) --
+uint64_t coral_stream_handle(coral_ctx* c, int which) {
+    if (!c) return 0;
+    cudaSetDevice(c->device);
+    if (which == 0) return (uint64_t)reinterpret_cast<uintptr_t>(c->pass.in_lane ? c->pass.lane_stream : c->stream);
+    PassState& P = c->pass;
+    if (!P.lane_stream) {
+        if (cudaStreamCreateWithFlags(&P.lane_stream, cudaStreamNonBlocking) != cudaSuccess) return 0;
+        cudaEventCreateWithFlags(&P.ev_lane_begin, cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&P.ev_lane_done, cudaEventDisableTiming);
+    }
+    return (uint64_t)reinterpret_cast<uintptr_t>(P.in_lane ? c->stream : P.lane_stream);
+}
+
+int coral_adopt_stream(coral_ctx* c, uint64_t handle) {
+    if (!c || !handle) return CORAL_E_ARG;
+    if (c->pass.active) { c->err = "coral_adopt_stream inside a pass"; return CORAL_E_STATE; }
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->owns_stream && c->stream) cudaStreamDestroy(c->stream);
+    c->stream = reinterpret_cast<cudaStream_t>((uintptr_t)handle);
+    c->owns_stream = false;
+    return CORAL_OK;
+}
+
+// A host value of the CALLER that must be the same in a replayed pass (e.g. the message sizes of the other ranks of an
+// exchange): recorded while the pass records, handed back while it replays.
+int coral_pass_note(coral_ctx* c, uint64_t value, uint64_t* out, int32_t* replayed) {
+    if (!c || !out) return CORAL_E_ARG;
+    PassState& P = c->pass;
+    if (!P.active) { *out = value; if (replayed) *replayed = 0; return CORAL_OK; }
+    if (P.replay && P.cur < P.vals.size()) {
+        *out = P.vals[P.cur++];
+        if (replayed) *replayed = 1;
+        return CORAL_OK;
+    }
+    if (P.replay) { P.replay = false; P.vals.resize(P.cur); P.keys.resize(P.kcur); }
+    P.vals.push_back(value);
+    P.cur = P.vals.size();
+    *out = value;
+    if (replayed) *replayed = 0;
+    return CORAL_OK;
+}
+int coral_pass_replaying(const coral_ctx* c) { return (c && c->pass.active && c->pass.replay) ? 1 : 0; }
+
 // ---- pipelined pass (PassState, ctx.h) -------------------------------------------------------------------------------
 int coral_pass_begin(coral_ctx* c) {
     if (!c) return CORAL_E_ARG;
@@ -203,6 +257,9 @@ int coral_pass_begin(coral_ctx* c) {
     P.cur = P.kcur = 0;
     P.copies.clear();
     P.after.clear();
+    P.n_events = 0;
+    P.in_cur = 0;
+    P.lane_started = false;
     for (auto& ch : P.pinned) ch.used = 0;
     return CORAL_OK;
 }
@@ -214,10 +271,29 @@ int coral_pass_end(coral_ctx* c, int32_t* replayed) {
     cudaSetDevice(c->device);
     int join_rc = CORAL_OK;
     if (c->scan_pending) join_rc = coral_wait_scan(c);     // a rescan nothing joined: its verdict belongs to this pass
+    if (P.lane_started) {                                  // the second lane joins the ctx's stream
+        cudaEventRecord(P.ev_lane_done, P.lane_stream);
+        cudaStreamWaitEvent(c->stream, P.ev_lane_done, 0);
+        P.lane_started = false;
+    }
     P.active = false;
     uint32_t bad = 0;
-    cudaError_t e = cudaMemcpyAsync(&bad, P.d_flag, 4, cudaMemcpyDeviceToHost, c->stream);
+    uint32_t* bad_pinned = reinterpret_cast<uint32_t*>(coral::pass_stage(c, 64));
+    cudaError_t e = bad_pinned ? cudaMemcpyAsync(bad_pinned, P.d_flag, 4, cudaMemcpyDeviceToHost, c->stream) : cudaErrorMemoryAllocation;
+    // groups of result copies whose event has fired go to the caller's arrays now, while the device still works on
+    // the later stages (valid only if the pass does not diverge: a divergent pass is reported below and its arrays are
+    // garbage either way)
+    size_t done = 0;
+    if (e == cudaSuccess) {
+        for (; done < P.copies.size(); done++) {
+            const auto& cp = P.copies[done];
+            if (cp.group < 0) break;
+            if (cudaEventSynchronize(P.events[cp.group]) != cudaSuccess) break;
+            memcpy(cp.dst, cp.src, cp.bytes);
+        }
+    }
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) bad = *bad_pinned;
     if (e != cudaSuccess) {
         P.invalidate(); P.copies.clear(); P.after.clear();
         c->err = std::string("coral_pass_end: ") + cudaGetErrorString(e);
@@ -232,7 +308,7 @@ int coral_pass_end(coral_ctx* c, int32_t* replayed) {
                  " size(s) differ): the records behind a CORAL_RECORDS_DEVICE load changed? Run the pass again.";
         return CORAL_E_STATE;
     }
-    for (const auto& cp : P.copies) memcpy(cp.dst, cp.src, cp.bytes);
+    for (size_t k = done; k < P.copies.size(); k++) memcpy(P.copies[k].dst, P.copies[k].src, P.copies[k].bytes);
     P.copies.clear();
     int rc = CORAL_OK;
     for (auto& fn : P.after) { const int r = fn(); if (r != CORAL_OK && rc == CORAL_OK) rc = r; }
@@ -261,6 +337,22 @@ float coral_stage_ms(coral_ctx* c, int stage) {
     if (cudaEventSynchronize(c->ev_end[stage]) != cudaSuccess) return -1.f;
     if (cudaEventElapsedTime(&ms, c->ev_beg[stage], c->ev_end[stage]) != cudaSuccess) return -1.f;
     return ms;
+}
+
+// Time from one stage event to another (begin: which = 0, end: which = 1), across the ctx's streams: where the stages
+// of a pipelined pass sit relative to the scan running next to them.  < 0 when an event is missing.
+float coral_stage_offset_ms(coral_ctx* c, int stage_a, int which_a, int stage_b, int which_b) {
+    if (!c || stage_a < 0 || stage_a >= CORAL_N_STAGES || stage_b < 0 || stage_b >= CORAL_N_STAGES) return -1.f;
+    if (!c->ev_valid[stage_a] || !c->ev_valid[stage_b]) return -1.f;
+    cudaSetDevice(c->device);
+    cudaEvent_t a = which_a ? c->ev_end[stage_a] : c->ev_beg[stage_a], b = which_b ? c->ev_end[stage_b] : c->ev_beg[stage_b];
+    float ms = -1.f;
+    if (cudaEventSynchronize(a) != cudaSuccess || cudaEventSynchronize(b) != cudaSuccess) return -1.f;
+    if (cudaEventElapsedTime(&ms, a, b) != cudaSuccess) { cudaGetLastError(); return -1.f; }
+    return ms;
+}
+void coral_reset_stage_times(coral_ctx* c) {
+    if (c) for (int s = 0; s < CORAL_N_STAGES; s++) c->ev_valid[s] = false;
 }
 
 int64_t coral_n_records(const coral_ctx* c) { return c ? c->nrec : -1; }

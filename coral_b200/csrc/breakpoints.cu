@@ -235,9 +235,9 @@ static int upload_intervals(coral_ctx* c, DevBuf& buf, const int32_t* tid, const
     using namespace coral;
     CORAL_CUDA(c, buf.ensure((size_t)std::max(n, 1) * 12));
     int32_t* d = buf.as<int32_t>();
-    CORAL_TRY(h2d(c, d, tid, (size_t)n));
-    CORAL_TRY(h2d(c, d + n, start, (size_t)n));
-    CORAL_TRY(h2d(c, d + 2 * (size_t)n, end, (size_t)n));
+    CORAL_TRY(h2d_keyed(c, d, tid, (size_t)n));
+    CORAL_TRY(h2d_keyed(c, d + n, start, (size_t)n));
+    CORAL_TRY(h2d_keyed(c, d + 2 * (size_t)n, end, (size_t)n));
     *out = Intervals{d, d + n, d + 2 * (size_t)n, n};
     return CORAL_OK;
 }
@@ -316,6 +316,7 @@ extern "C" int coral_get_smalldel(coral_ctx* c, uint32_t* rec, int32_t* ai, int3
 
 extern "C" int coral_candidates_l(coral_ctx* c, const int32_t* tid, const int32_t* start, const int32_t* end_incl,
                                   int32_t n_intervals, int64_t* n_cand) {
+    coral::PassLane lane__(c);
     using namespace coral;
     if (!c || n_intervals < 0) return CORAL_E_ARG;
     if (!c->chim.valid) { c->err = "coral_candidates_l before coral_fetch"; return CORAL_E_STATE; }
@@ -370,6 +371,7 @@ extern "C" int coral_candidates_l(coral_ctx* c, const int32_t* tid, const int32_
 extern "C" int coral_get_candidates(coral_ctx* c, uint32_t* read, int32_t* i, int32_t* j, int32_t* chr1, int32_t* pos1,
                                     uint8_t* o1, int32_t* chr2, int32_t* pos2, uint8_t* o2, int32_t* rgap, uint8_t* flag,
                                     int32_t* mq1, int32_t* mq2) {
+    coral::PassLane lane__(c);
     using namespace coral;
     if (!c) return CORAL_E_ARG;
     if (!c->cand.valid) { c->err = "coral_get_candidates before coral_candidates_l"; return CORAL_E_STATE; }
@@ -423,6 +425,7 @@ extern "C" int coral_set_chimeric(coral_ctx* c, int64_t n_reads, const uint32_t*
 
 extern "C" int coral_candidates_pair(coral_ctx* c, const uint32_t* reads, int64_t n_sel, const int32_t* tid2,
                                      const int32_t* start2, const int32_t* end2, int64_t* n_cand) {
+    coral::PassLane lane__(c);
     using namespace coral;
     if (!c || n_sel < 0) return CORAL_E_ARG;
     if (!c->chim.valid) { c->err = "coral_candidates_pair before coral_fetch"; return CORAL_E_STATE; }
@@ -431,6 +434,12 @@ extern "C" int coral_candidates_pair(coral_ctx* c, const uint32_t* reads, int64_
     T.valid = false; T.n = 0;
     if (n_cand) *n_cand = 0;
     ChimericTable& H = c->chim;
+    if (c->pass.active) {
+        uint64_t k = interval_key("candidates_pair", tid2, start2, end2, 2);
+        k = pass_hash(k, &n_sel, 8);
+        if (n_sel > 0) k = pass_hash(k, reads, (size_t)n_sel * 4);
+        pass_call(c, k);
+    }
     if (n_sel == 0) { T.valid = true; return CORAL_OK; }
     for (int64_t k = 0; k < n_sel; k++) if ((int64_t)reads[k] >= H.n_reads) { c->err = "read index out of range"; return CORAL_E_ARG; }
     Intervals I;
@@ -442,7 +451,7 @@ extern "C" int coral_candidates_pair(coral_ctx* c, const uint32_t* reads, int64_
     uint32_t* cnt = c->s1.as<uint32_t>();
     uint32_t* ptr = cnt + n_sel + 1;
     uint32_t* d_sel = ptr + n_sel + 1;
-    CORAL_TRY(h2d(c, d_sel, reads, (size_t)n_sel));
+    CORAL_TRY(h2d_keyed(c, d_sel, reads, (size_t)n_sel));
     CORAL_CUDA(c, c->status.ensure(64));
     CORAL_CUDA(c, cudaMemsetAsync(c->status.p, 0, 64, c->stream));
     CandCols none{};

@@ -491,6 +491,7 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
                                   const uint8_t* flag, const int32_t* mq1, const int32_t* mq2, double min_cluster_size,
                                   int32_t bp_distance_cutoff, double peel_cutoff, int32_t match_cutoff, int32_t max_peels,
                                   int64_t* n_clusters) {
+    coral::PassLane lane__(c);
     using namespace coral;
     if (!c || n < 0) return CORAL_E_ARG;
     cudaSetDevice(c->device);
@@ -512,11 +513,11 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
     if (n >= ((int64_t)1 << 31)) { c->err = "too many candidates"; return CORAL_E_ARG; }
     CORAL_TRY(cluster_ensure(c, n));
     DevBuf* w = c->cw;
-    CORAL_TRY(h2d(c, w[W_CHR1].p, chr1, (size_t)n)); CORAL_TRY(h2d(c, w[W_POS1].p, pos1, (size_t)n));
-    CORAL_TRY(h2d(c, w[W_CHR2].p, chr2, (size_t)n)); CORAL_TRY(h2d(c, w[W_POS2].p, pos2, (size_t)n));
-    CORAL_TRY(h2d(c, w[W_RGAP].p, rgap, (size_t)n)); CORAL_TRY(h2d(c, w[W_MQ1].p, mq1, (size_t)n));
-    CORAL_TRY(h2d(c, w[W_MQ2].p, mq2, (size_t)n)); CORAL_TRY(h2d(c, w[W_O1].p, o1, (size_t)n));
-    CORAL_TRY(h2d(c, w[W_O2].p, o2, (size_t)n)); CORAL_TRY(h2d(c, w[W_FLAG].p, flag, (size_t)n));
+    CORAL_TRY(h2d_keyed(c, w[W_CHR1].p, chr1, (size_t)n)); CORAL_TRY(h2d_keyed(c, w[W_POS1].p, pos1, (size_t)n));
+    CORAL_TRY(h2d_keyed(c, w[W_CHR2].p, chr2, (size_t)n)); CORAL_TRY(h2d_keyed(c, w[W_POS2].p, pos2, (size_t)n));
+    CORAL_TRY(h2d_keyed(c, w[W_RGAP].p, rgap, (size_t)n)); CORAL_TRY(h2d_keyed(c, w[W_MQ1].p, mq1, (size_t)n));
+    CORAL_TRY(h2d_keyed(c, w[W_MQ2].p, mq2, (size_t)n)); CORAL_TRY(h2d_keyed(c, w[W_O1].p, o1, (size_t)n));
+    CORAL_TRY(h2d_keyed(c, w[W_O2].p, o2, (size_t)n)); CORAL_TRY(h2d_keyed(c, w[W_FLAG].p, flag, (size_t)n));
     CandIn C{w[W_CHR1].as<int32_t>(), w[W_POS1].as<int32_t>(), w[W_CHR2].as<int32_t>(), w[W_POS2].as<int32_t>(),
              w[W_RGAP].as<int32_t>(), w[W_MQ1].as<int32_t>(), w[W_MQ2].as<int32_t>(), w[W_O1].as<uint8_t>(),
              w[W_O2].as<uint8_t>(), w[W_FLAG].as<uint8_t>()};
@@ -528,6 +529,7 @@ extern "C" int coral_cluster_call(coral_ctx* c, int64_t n, const int32_t* chr1, 
 extern "C" int coral_cluster_call_candidates(coral_ctx* c, double min_cluster_size, int32_t bp_distance_cutoff,
                                              double peel_cutoff, int32_t match_cutoff, int32_t max_peels,
                                              int64_t* n_clusters) {
+    coral::PassLane lane__(c);
     using namespace coral;
     if (!c) return CORAL_E_ARG;
     if (!c->cand.valid) { c->err = "coral_cluster_call_candidates before coral_candidates_l"; return CORAL_E_STATE; }
@@ -654,6 +656,7 @@ extern "C" int coral_bp_match(coral_ctx* c, int64_t n, const int64_t* bp1_pos1, 
 extern "C" int coral_get_clusters(coral_ctx* c, uint32_t* order, uint32_t* cluster_ptr, int32_t* n_sub, int32_t* sub_of,
                                   int32_t* row_pos1, int32_t* row_pos2, int32_t* row_nb, uint32_t* row_first,
                                   double* row_stats) {
+    coral::PassLane lane__(c);
     using namespace coral;
     if (!c) return CORAL_E_ARG;
     if (!c->cl_valid) { c->err = "coral_get_clusters before coral_cluster_call"; return CORAL_E_STATE; }

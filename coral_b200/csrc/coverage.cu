@@ -171,9 +171,9 @@ int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t*
     CORAL_CUDA(ctx, ctx->s0.ensure(rb * 3));
     CORAL_CUDA(ctx, ctx->s1.ensure((size_t)n * 16 + 8));
     int32_t* d_reg = ctx->s0.as<int32_t>();
-    CORAL_CUDA(ctx, cudaMemcpyAsync(d_reg, tid, rb, cudaMemcpyHostToDevice, st));
-    CORAL_CUDA(ctx, cudaMemcpyAsync(d_reg + n, start, rb, cudaMemcpyHostToDevice, st));
-    CORAL_CUDA(ctx, cudaMemcpyAsync(d_reg + 2 * (size_t)n, stop, rb, cudaMemcpyHostToDevice, st));
+    CORAL_TRY(h2d_keyed(ctx, d_reg, tid, (size_t)n));
+    CORAL_TRY(h2d_keyed(ctx, d_reg + n, start, (size_t)n));
+    CORAL_TRY(h2d_keyed(ctx, d_reg + 2 * (size_t)n, stop, (size_t)n));
     unsigned long long* d_sum = ctx->s1.as<unsigned long long>();
     unsigned long long* d_cnt = d_sum + n;
     unsigned long long* d_slow_n = d_cnt + n;

@@ -179,24 +179,41 @@ struct PassState {
     bool active = false;      // between coral_pass_begin and coral_pass_end
     bool replay = false;      // sizes come from `vals`
     bool complete = false;    // `vals` / `keys` describe a whole pass
-    bool overlap_scan = true; // coral_rescan inside a pass: pre-scan + full scan on its own stream (option "pass_overlap_scan")
+    // second lane: inside a pass the chimeric chain (fetch -> candidates -> cluster + peel) runs on its own stream with
+    // its own scratch buffers, next to the coverage / small-deletion / concordant stages on the ctx's stream
+    bool fork = true;                          // option "pass_fork"
+    bool lane_started = false;                 // the lane's stream already waits for the main stream's work of this pass
+    bool in_lane = false;
+    cudaStream_t lane_stream = nullptr;
+    cudaEvent_t ev_lane_begin = nullptr, ev_lane_done = nullptr;
+    int64_t scan_reserve = -1; // block slots the overlapped scan leaves free (-1: one per SM; option "pass_scan_reserve")
+    bool overlap_scan = false; // coral_rescan inside a pass as pre-scan + full scan on its own stream (option
+                               // "pass_overlap_scan"; off by default: measured, the second lane after a full-speed scan wins)
     std::vector<uint64_t> vals;
     size_t cur = 0;
     std::vector<uint64_t> keys;   // one per entry-point call: hash of (entry point, host inputs)
     size_t kcur = 0;
     struct Chunk { uint8_t* p; size_t cap, used; };
     std::vector<Chunk> pinned;
-    struct Copy { void* dst; const uint8_t* src; size_t bytes; };
+    struct Copy { void* dst; const uint8_t* src; size_t bytes; int group; };
     std::vector<Copy> copies;
+    std::vector<cudaEvent_t> events;           // one per group of result copies (pass_sync)
+    size_t n_events = 0;
     std::vector<std::function<int()>> after;   // host post-processing of deferred results, in call order
+    // input arrays of the entry points, kept on the device between passes: a replayed pass has the SAME inputs (that
+    // is what the call keys compare), so instead of crossing PCIe again they are copied device-to-device
+    struct Input { void* p = nullptr; size_t cap = 0, bytes = 0; };
+    std::vector<Input> inputs;
+    size_t in_cur = 0;
     uint32_t* d_flag = nullptr;                // device: number of replayed values the device disagreed with
     uint64_t n_replayed = 0;                   // statistics: passes that ran without intermediate synchronisation
-    void invalidate() { vals.clear(); keys.clear(); complete = false; }
+    void invalidate() { vals.clear(); keys.clear(); complete = false; for (auto& i : inputs) i.bytes = 0; }
 };
 
 struct coral_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    bool owns_stream = true;      // false after coral_adopt_stream
     std::string err;
     coral_params prm;
 
@@ -253,6 +270,7 @@ struct coral_ctx {
     // scratch
     DevBuf s0, s1, s2, s3, s4, s5, s6, s7;
     DevBuf cub_tmp;
+    DevBuf lane_s[8], lane_cub_tmp, lane_status;   // the second lane's own set (swapped in by PassLane)
 
     PassState pass;
 

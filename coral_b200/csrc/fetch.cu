@@ -590,6 +590,7 @@ extern "C" int coral_nm_partials(coral_ctx* c, double* nm_sum, double* nm_sumsq,
 
 extern "C" int coral_fetch(coral_ctx* c, int64_t* n_reads, int64_t* n_alignments, double* nm_sum, double* nm_sumsq,
                            int64_t* nm_n, int64_t* nm_zero_div) {
+    coral::PassLane lane__(c);
     if (!c) return CORAL_E_ARG;
     cudaSetDevice(c->device);
     CORAL_TRY(coral_run_fetch(c));
@@ -607,6 +608,7 @@ extern "C" int coral_fetch(coral_ctx* c, int64_t* n_reads, int64_t* n_alignments
 extern "C" int coral_get_chimeric(coral_ctx* c, uint32_t* read_first_rec, int64_t* read_len, int32_t* read_status,
                                   uint32_t* aln_ptr, int32_t* qs, int32_t* qe, int32_t* tid, int32_t* rstart, int32_t* rend,
                                   uint8_t* strand, int32_t* mapq, int64_t* nm) {
+    coral::PassLane lane__(c);
     using namespace coral;
     if (!c) return CORAL_E_ARG;
     if (!c->chim.valid) { c->err = "coral_get_chimeric before coral_fetch"; return CORAL_E_STATE; }

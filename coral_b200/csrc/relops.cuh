@@ -5,6 +5,7 @@
 #include <cub/cub.cuh>
 
 #include <cstring>
+#include <utility>
 
 #include "ctx.h"
 
@@ -64,6 +65,14 @@ static __global__ void k_pass_check(const void* d, unsigned long long expect, in
     if (v != expect) atomicAdd(flag, 1u);
 }
 
+static __global__ void k_copy_words(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, size_t bytes) {
+    const size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i + 4 <= bytes && ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 3) == 0)
+        *reinterpret_cast<uint32_t*>(dst + i) = *reinterpret_cast<const uint32_t*>(src + i);
+    else
+        for (size_t k = i; k < bytes && k < i + 4; k++) dst[k] = src[k];
+}
+
 inline uint64_t pass_hash(uint64_t h, const void* p, size_t bytes) {      // FNV-1a over host input arrays
     const uint8_t* b = static_cast<const uint8_t*>(p);
     for (size_t i = 0; i < bytes; i++) { h ^= b[i]; h *= 0x100000001B3ull; }
@@ -103,6 +112,7 @@ inline int pass_resolve(coral_ctx* c, T* out, const void* d_src) {
     }
     if (P.active && P.replay) {       // the recorded sequence is shorter than this pass: record from here on
         P.replay = false;
+        P.vals.resize(P.cur);
         P.keys.resize(P.kcur);
     }
     CORAL_CUDA(c, cudaMemcpyAsync(out, d_src, sizeof(T), cudaMemcpyDeviceToHost, c->stream));
@@ -111,6 +121,34 @@ inline int pass_resolve(coral_ctx* c, T* out, const void* d_src) {
         uint64_t v = 0;
         memcpy(&v, out, sizeof(T));
         P.vals.push_back(v);
+        P.cur = P.vals.size();
+    }
+    return CORAL_OK;
+}
+
+// Array form: n (<= 128) 8-byte words, one check kernel for all of them.
+struct PassWords { unsigned long long w[128]; };
+static __global__ void k_pass_check_n(const unsigned long long* d, PassWords expect, int n, uint32_t* flag) {
+    const int i = threadIdx.x;
+    if (i < n && d[i] != expect.w[i]) atomicAdd(flag, 1u);
+}
+inline int pass_resolve_n(coral_ctx* c, uint64_t* out, const void* d_src, int n) {
+    if (n <= 0) return CORAL_OK;
+    if (n > 128) { c->err = "pass_resolve_n: more than 128 words"; return CORAL_E_ARG; }
+    PassState& P = c->pass;
+    if (P.active && P.replay && P.cur + (size_t)n <= P.vals.size()) {
+        PassWords ex;
+        for (int i = 0; i < n; i++) { out[i] = P.vals[P.cur + i]; ex.w[i] = out[i]; }
+        P.cur += (size_t)n;
+        k_pass_check_n<<<1, 128, 0, c->stream>>>(static_cast<const unsigned long long*>(d_src), ex, n, P.d_flag);
+        c->n_launches++;
+        return CORAL_OK;
+    }
+    if (P.active && P.replay) { P.replay = false; P.vals.resize(P.cur); P.keys.resize(P.kcur); }
+    CORAL_CUDA(c, cudaMemcpyAsync(out, d_src, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (P.active) {
+        for (int i = 0; i < n; i++) P.vals.push_back(out[i]);
         P.cur = P.vals.size();
     }
     return CORAL_OK;
@@ -137,7 +175,7 @@ inline int d2h_result(coral_ctx* c, T* dst, const void* src, size_t n) {
         uint8_t* st = pass_stage(c, n * sizeof(T));
         if (!st) { c->err = "cudaHostAlloc failed for the pass staging buffer"; return CORAL_E_NOMEM; }
         CORAL_CUDA(c, cudaMemcpyAsync(st, src, n * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
-        P.copies.push_back(PassState::Copy{dst, st, n * sizeof(T)});
+        P.copies.push_back(PassState::Copy{dst, st, n * sizeof(T), -1});
         return CORAL_OK;
     }
     CORAL_CUDA(c, cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
@@ -145,7 +183,24 @@ inline int d2h_result(coral_ctx* c, T* dst, const void* src, size_t n) {
 }
 // The synchronisation that ends an entry point: skipped inside a pass (coral_pass_end synchronises once).
 inline int pass_sync(coral_ctx* c) {
-    if (c->pass.active) return CORAL_OK;
+    PassState& P = c->pass;
+    if (P.active) {
+        // the result copies enqueued since the last mark form a group behind one event: coral_pass_end hands a group to
+        // the caller's arrays as soon as ITS event has fired, while later stages are still running on the device
+        size_t first = P.copies.size();
+        while (first > 0 && P.copies[first - 1].group < 0) first--;
+        if (first < P.copies.size()) {
+            if (P.n_events == P.events.size()) {
+                cudaEvent_t e;
+                CORAL_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                P.events.push_back(e);
+            }
+            const int g = (int)P.n_events++;
+            CORAL_CUDA(c, cudaEventRecord(P.events[g], c->stream));
+            for (size_t k = first; k < P.copies.size(); k++) P.copies[k].group = g;
+        }
+        return CORAL_OK;
+    }
     CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
     return CORAL_OK;
 }
@@ -155,6 +210,45 @@ inline int pass_after(coral_ctx* c, std::function<int()> fn) {
     return fn();
 }
 
+// RAII guard of the entry points of the chimeric chain (coral_fetch, coral_candidates_*, coral_cluster_call*, their
+// getters): inside a pass with the second lane enabled they run on the lane's stream with the lane's scratch buffers.
+// The lane's stream waits once per pass for everything the main stream was given before the first such call (the
+// scan, or its pre-scan); coral_pass_end joins the lane.
+struct PassLane {
+    coral_ctx* c;
+    bool on = false;
+    static void swap_sets(coral_ctx* c) {
+        DevBuf* m[8] = {&c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->s6, &c->s7};
+        for (int k = 0; k < 8; k++) std::swap(*m[k], c->lane_s[k]);
+        std::swap(c->cub_tmp, c->lane_cub_tmp);
+        std::swap(c->status, c->lane_status);
+        std::swap(c->stream, c->pass.lane_stream);
+    }
+    explicit PassLane(coral_ctx* ctx) : c(ctx) {
+        if (!c) return;
+        PassState& P = c->pass;
+        if (!P.active || !P.fork || P.in_lane) return;
+        if (!P.lane_stream) {
+            if (cudaStreamCreateWithFlags(&P.lane_stream, cudaStreamNonBlocking) != cudaSuccess) return;
+            cudaEventCreateWithFlags(&P.ev_lane_begin, cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&P.ev_lane_done, cudaEventDisableTiming);
+        }
+        if (!P.lane_started) {
+            cudaEventRecord(P.ev_lane_begin, c->stream);
+            cudaStreamWaitEvent(P.lane_stream, P.ev_lane_begin, 0);
+            P.lane_started = true;
+        }
+        swap_sets(c);
+        P.in_lane = true;
+        on = true;
+    }
+    ~PassLane() {
+        if (!on) return;
+        swap_sets(c);
+        c->pass.in_lane = false;
+    }
+};
+
 // Immediate copy (the caller synchronises right after): entry points that do not take part in pipelined passes.
 template <class T>
 inline int d2h(coral_ctx* c, T* dst, const void* src, size_t n) {
@@ -162,10 +256,59 @@ inline int d2h(coral_ctx* c, T* dst, const void* src, size_t n) {
     CORAL_CUDA(c, cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
     return CORAL_OK;
 }
+// Copy of an INPUT array to the device.  Outside a pass: a plain asynchronous copy.  Inside a pass every input array has
+// a slot (its position in the pass) in a device-side cache: a recording pass fills the slot through page-locked staging
+// (a copy from pageable memory takes the driver's slow path: tens of microseconds of stream time each), a replayed pass
+// — whose inputs are the recorded ones, the call keys say so — copies slot -> destination on the device, so no input
+// crosses PCIe again (measured: 0.17 ms of stream time per coral_region_coverage call before, for three small arrays).
+// ONLY for inputs that the entry point's call key (pass_call) covers: h2d() below is the form for everything else.
+template <class T>
+inline int h2d_keyed(coral_ctx* c, void* dst, const T* src, size_t n) {
+    if (n == 0) return CORAL_OK;
+    PassState& P = c->pass;
+    const size_t bytes = n * sizeof(T);
+    if (!P.active) {
+        CORAL_CUDA(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream));
+        return CORAL_OK;
+    }
+    const size_t slot = P.in_cur++;
+    if (P.inputs.size() <= slot) P.inputs.resize(slot + 1);
+    PassState::Input& in = P.inputs[slot];
+    if (!(P.replay && in.p && in.bytes == bytes)) {
+        if (in.cap < bytes) {
+            if (in.p) coral_mem::release(in.p, in.cap);
+            in.p = nullptr; in.cap = 0;
+            size_t got = 0;
+            CORAL_CUDA(c, coral_mem::acquire(&in.p, bytes + 256, &got));
+            in.cap = got;
+        }
+        uint8_t* st = pass_stage(c, bytes);
+        if (!st) { c->err = "cudaHostAlloc failed for the pass staging buffer"; return CORAL_E_NOMEM; }
+        memcpy(st, src, bytes);
+        CORAL_CUDA(c, cudaMemcpyAsync(in.p, st, bytes, cudaMemcpyHostToDevice, c->stream));
+        in.bytes = bytes;
+    }
+    // slot -> destination with a kernel, not the copy engine: a copy-engine operation between two kernels of a stream
+    // costs a hand-over between the engines on both sides (tens of microseconds of stream time, measured)
+    const size_t words = (bytes + 3) / 4;
+    k_copy_words<<<(unsigned)((words + 255) / 256), 256, 0, c->stream>>>(static_cast<const uint8_t*>(in.p),
+                                                                          static_cast<uint8_t*>(dst), bytes);
+    c->n_launches++;
+    return CORAL_OK;
+}
+
+// Input copy of an entry point without a call key: asynchronous copy, through page-locked staging inside a pass.
 template <class T>
 inline int h2d(coral_ctx* c, void* dst, const T* src, size_t n) {
     if (n == 0) return CORAL_OK;
-    CORAL_CUDA(c, cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+    const void* from = src;
+    if (c->pass.active) {
+        uint8_t* st = pass_stage(c, n * sizeof(T));
+        if (!st) { c->err = "cudaHostAlloc failed for the pass staging buffer"; return CORAL_E_NOMEM; }
+        memcpy(st, src, n * sizeof(T));
+        from = st;
+    }
+    CORAL_CUDA(c, cudaMemcpyAsync(dst, from, n * sizeof(T), cudaMemcpyHostToDevice, c->stream));
     return CORAL_OK;
 }
 

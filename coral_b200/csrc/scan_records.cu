@@ -956,9 +956,19 @@ int coral_start_scan_overlapped(coral_ctx* ctx) {
     GapEvents& g = ctx->gaps;
     CORAL_CUDA(ctx, cudaMemsetAsync(g.counter.p, 0, 16, ctx->stream));
     CORAL_CUDA(ctx, cudaMemsetAsync(ctx->scan_status.p, 0, 64, ctx->stream));
+    ScanCols o = scan_cols(ctx);
+    // the pre-scan first, alone on the device (it is latency-bound: two dependent loads per record, and needs every
+    // warp slot to finish in tens of microseconds); what runs next on the ctx's stream (fetch ...) reads its columns
+    SideText side{nullptr, nullptr, 0, nullptr};
+    const int pre_blocks = (int)std::min<int64_t>((n + 7) / 8, (int64_t)ctx->sm_count * 8);
+    ctx->stage_begin(CORAL_STAGE_PRESCAN);
+    k_prescan_records<<<pre_blocks, 256, 0, ctx->stream>>>(ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, o, side,
+                                                          ctx->scan_status.as<int32_t>());
+    ctx->stage_end(CORAL_STAGE_PRESCAN);
+    ctx->n_launches++;
+    CORAL_CUDA(ctx, cudaGetLastError());
     CORAL_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
     CORAL_CUDA(ctx, cudaStreamWaitEvent(ctx->scan_stream, ctx->ev_fork, 0));
-    ScanCols o = scan_cols(ctx);
     ScanEvents e{g.rec.as<uint32_t>(), g.k.as<uint32_t>(), g.next_start.as<int32_t>(), g.prev_end.as<int32_t>(),
                  g.counter.as<unsigned long long>(), g.capacity};
     int per_sm = 0;
@@ -966,7 +976,9 @@ int coral_start_scan_overlapped(coral_ctx* ctx) {
     if (per_sm < 1) per_sm = 1;
     const int64_t want = (n + SC_WARPS - 1) / SC_WARPS;
     const int64_t full = (int64_t)ctx->sm_count * per_sm;
-    const int64_t reserve = per_sm > 1 ? std::max<int64_t>(8, ctx->sm_count / 8) : 0;     // block slots left to the small kernels
+    // block slots left to the small kernels that run next to the scan: by default one of the per_sm slots of every SM
+    const int64_t reserve = per_sm > 1 ? (ctx->pass.scan_reserve >= 0 ? std::min<int64_t>(ctx->pass.scan_reserve, full - ctx->sm_count)
+                                                                      : (int64_t)ctx->sm_count) : 0;
     const int blocks = (int)std::max<int64_t>(1, std::min<int64_t>(want, full - reserve));
     if (!ctx->ev_beg[CORAL_STAGE_SCAN]) { cudaEventCreate(&ctx->ev_beg[CORAL_STAGE_SCAN]); cudaEventCreate(&ctx->ev_end[CORAL_STAGE_SCAN]); }
     cudaEventRecord(ctx->ev_beg[CORAL_STAGE_SCAN], ctx->scan_stream);
@@ -975,13 +987,6 @@ int coral_start_scan_overlapped(coral_ctx* ctx) {
         reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1), 0u);
     cudaEventRecord(ctx->ev_end[CORAL_STAGE_SCAN], ctx->scan_stream);
     ctx->ev_valid[CORAL_STAGE_SCAN] = true;
-    ctx->n_launches++;
-    CORAL_CUDA(ctx, cudaGetLastError());
-    // the pre-scan, on the ctx's stream: what runs next on this stream (fetch ...) reads its columns
-    SideText side{nullptr, nullptr, 0, nullptr};
-    const int pre_blocks = (int)std::min<int64_t>((n + 7) / 8, (int64_t)ctx->sm_count * 8);
-    k_prescan_records<<<pre_blocks, 256, 0, ctx->stream>>>(ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, o, side,
-                                                          ctx->scan_status.as<int32_t>());
     ctx->n_launches++;
     CORAL_CUDA(ctx, cudaGetLastError());
     ctx->scan_pending = true;

@@ -189,15 +189,15 @@ extern "C" int coral_concordant(coral_ctx* c, const int32_t* tid, const int32_t*
     DevBuf* w = c->sw;
     CORAL_CUDA(c, w[0].ensure((size_t)n_edges * 8 + 16));
     int32_t* d_e = w[0].as<int32_t>();
-    CORAL_TRY(h2d(c, d_e, tid, (size_t)n_edges));
-    CORAL_TRY(h2d(c, d_e + n_edges, p, (size_t)n_edges));
+    CORAL_TRY(h2d_keyed(c, d_e, tid, (size_t)n_edges));
+    CORAL_TRY(h2d_keyed(c, d_e + n_edges, p, (size_t)n_edges));
     Edges E{d_e, d_e + n_edges, n_edges, c->prm.min_bp_match_cutoff};
     CORAL_CUDA(c, w[1].ensure(16));
     unsigned long long* d_nrows = w[1].as<unsigned long long>();
     CORAL_CUDA(c, w[2].ensure((size_t)std::max<int64_t>(n_rbps, 1) * 8));
     uint32_t* d_rb = w[2].as<uint32_t>();
-    CORAL_TRY(h2d(c, d_rb, rb_edge, (size_t)n_rbps));
-    CORAL_TRY(h2d(c, d_rb + n_rbps, rb_rec, (size_t)n_rbps));
+    CORAL_TRY(h2d_keyed(c, d_rb, rb_edge, (size_t)n_rbps));
+    CORAL_TRY(h2d_keyed(c, d_rb + n_rbps, rb_rec, (size_t)n_rbps));
     c->stage_begin(CORAL_STAGE_STAB);
     int64_t cap = std::max<int64_t>((int64_t)1 << 16, (int64_t)(w[3].cap / 4) - n_rbps);
     unsigned long long n_rows = 0;

@@ -137,13 +137,25 @@ int coral_rescan(coral_ctx* ctx);
  * Entry points that take part: coral_rescan, coral_region_coverage, coral_fetch + coral_get_chimeric, coral_smalldel +
  * coral_get_smalldel, coral_candidates_l + coral_get_candidates, coral_cluster_call(_candidates) + coral_get_clusters,
  * coral_concordant + coral_get_concordant_rows.  Any other entry point may be called inside a pass; it synchronises.
- * coral_rescan inside a pass splits the scan as the asynchronous load does: a pre-scan fills the columns coral_fetch /
- * coral_candidates_* / coral_cluster_call read, the full scan then runs on a second stream next to those entry points'
- * kernels, and the first entry point that needs its CIGAR / SEQ columns joins it by a stream dependency.
+ * Two lanes: inside a pass the chimeric chain (coral_fetch, coral_candidates_*, coral_cluster_call* and their getters)
+ * runs on a second stream with its own scratch buffers, next to the coverage / small-deletion / concordant entry points
+ * on the ctx's stream (option "pass_fork", default 1); coral_pass_end joins the two.  Option "pass_overlap_scan" = 1
+ * additionally splits coral_rescan as the asynchronous load does (pre-scan, then the full scan on a third stream with
+ * "pass_scan_reserve" block slots left free; default 0 — measured slower on one GPU).
+ * Streams of a process should not share a hardware queue: set CUDA_DEVICE_MAX_CONNECTIONS=32 before CUDA starts.
  * This is how one step of the device-resident benchmark runs the path (reference call order
  * infer_breakpoint_graph.py:1354-1386) as one stream of kernels. */
 int coral_pass_begin(coral_ctx* ctx);
 int coral_pass_end(coral_ctx* ctx, int32_t* replayed);
+/* For callers that enqueue work of their own between the entry points of a pass (the multi-GPU engine: NCCL
+ * collectives): the ctx's streams as CUstream / cudaStream_t values (which = 0: the stream the entry points outside the
+ * chimeric chain use; 1: the second lane), a way to make a ctx run on a stream it does not own (the rows-only ctx of the
+ * multi-GPU engine runs on the second lane of the records ctx), and values of the caller that a replayed pass must
+ * see again (the message sizes of the other ranks): recorded while the pass records, handed back while it replays. */
+uint64_t coral_stream_handle(coral_ctx* ctx, int which);
+int coral_adopt_stream(coral_ctx* ctx, uint64_t stream);
+int coral_pass_note(coral_ctx* ctx, uint64_t value, uint64_t* out, int32_t* replayed);
+int coral_pass_replaying(const coral_ctx* ctx);
 
 /* Device time of the kernels of one stage during its most recent run, from CUDA events recorded on the
  * ctx's own stream around the launches (milliseconds; < 0 if the stage has not run). */
@@ -156,8 +168,14 @@ int coral_pass_end(coral_ctx* ctx, int32_t* replayed);
 #define CORAL_STAGE_BPC2BP 6
 #define CORAL_STAGE_STAB 7
 #define CORAL_STAGE_PATHS 8
-#define CORAL_N_STAGES 9
+#define CORAL_STAGE_PRESCAN 9   /* the pre-scan of an asynchronous load / of coral_rescan inside a pipelined pass */
+#define CORAL_N_STAGES 10
 float coral_stage_ms(coral_ctx* ctx, int stage);
+/* Forget the stage times recorded so far (coral_stage_ms then reports only stages that ran since), and the time from
+ * one stage event to another — begin (which = 0) or end (which = 1) — across the ctx's streams: where the stages of a
+ * pipelined pass sit relative to the scan that runs next to them. */
+void coral_reset_stage_times(coral_ctx* ctx);
+float coral_stage_offset_ms(coral_ctx* ctx, int stage_a, int which_a, int stage_b, int which_b);
 
 /* Per-record scan table copied to host arrays (any pointer may be NULL to skip that column). */
 int coral_get_record_table(coral_ctx* ctx, int32_t* tid, int32_t* pos, int32_t* endpos, int32_t* flag,

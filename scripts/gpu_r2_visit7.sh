@@ -1,6 +1,10 @@
 #!/bin/bash
 set -u
 mkdir -p gpurun_out
-( timeout 300 python scripts/pass_timing.py --overlap 1 ) > gpurun_out/v7_pt1.json 2> gpurun_out/v7_pt1.err
-( timeout 300 python scripts/pass_timing.py --overlap 0 ) > gpurun_out/v7_pt0.json 2> gpurun_out/v7_pt0.err
-cat gpurun_out/v7_pt1.json gpurun_out/v7_pt0.json; tail -3 gpurun_out/v7_pt1.err
+python - <<'PY' > gpurun_out/v7_all.json 2> gpurun_out/v7_all.err
+import subprocess, sys
+for r in (-1, 18, 74, 296):
+    p = subprocess.run([sys.executable, "scripts/pass_timing.py", "--overlap", "1", "--reserve", str(r)], capture_output=True, text=True)
+    print(p.stdout.strip().splitlines()[-1] if p.stdout.strip() else p.stderr[-500:])
+PY
+cat gpurun_out/v7_all.json

@@ -3,6 +3,8 @@
     python scripts/pass_timing.py [--scale 1.0] [--overlap 1]
 """
 import argparse
+import os as _os
+_os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")   # streams of a ctx (scan, lane) must not share a hardware queue
 import json
 import os
 import sys
@@ -21,6 +23,8 @@ def main():
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--overlap", type=int, default=1)
     ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--reserve", type=int, default=-1)
+    ap.add_argument("--fork", type=int, default=1)
     a = ap.parse_args()
     import bench
     from sim.generate import simulate
@@ -35,6 +39,8 @@ def main():
     plan = bench.build_plan(eng, cns)
     ctx = eng._ctx
     ctx.set_option("pass_overlap_scan", a.overlap)
+    ctx.set_option("pass_scan_reserve", a.reserve)
+    ctx.set_option("pass_fork", a.fork)
     laps = {}
 
     def one():
@@ -61,11 +67,17 @@ def main():
     for _ in range(5):
         one()
     laps.clear()
+    ctx.reset_stage_times()
     for _ in range(a.reps):
         one()
     out = {k: round(float(np.mean(v)), 4) for k, v in laps.items()}
     out["stage_ms"] = {n: round(ctx.stage_ms(i), 4) for i, n in enumerate(["scan", "coverage", "fetch", "smalldel", "candidates", "cluster", "bpc2bp", "concordant"])}
     out["overlap"] = a.overlap
+    out["reserve"] = a.reserve
+    out["fork"] = a.fork
+    names = ["scan", "coverage", "fetch", "smalldel", "candidates", "cluster", "bpc2bp", "concordant"]
+    out["timeline_ms_from_scan_begin"] = {n: [round(ctx.stage_offset_ms(0, 0, i, 0), 4), round(ctx.stage_offset_ms(0, 0, i, 1), 4)]
+                                          for i, n in enumerate(names) if ctx.stage_ms(i) >= 0}
     print(json.dumps(out))
 
 
