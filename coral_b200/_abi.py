@@ -368,6 +368,18 @@ class Context(object):
         self._hold(bs, rc)
         return bs, rc
 
+    def region_coverage_static(self, tid, start, stop):
+        """coral_region_coverage_static: the same result through the entry point that allocates nothing (fixed-size static
+        device scratch; at most CORAL_STATIC_MAX_REGIONS regions, see include/coral_b200.h)."""
+        tid = np.ascontiguousarray(tid, dtype=np.int32)
+        start = np.ascontiguousarray(start, dtype=np.int32)
+        stop = np.ascontiguousarray(stop, dtype=np.int32)
+        n = len(tid)
+        bs = np.zeros(n, np.int64)
+        rc = np.zeros(n, np.int64)
+        self._check(self._L.coral_region_coverage_static(self._h, _p(tid), _p(start), _p(stop), n, _p(bs), _p(rc)))
+        return bs, rc
+
     def fetch(self):
         """coral_fetch + coral_get_chimeric -> dict of numpy arrays (see include/coral_b200.h)."""
         nr = ctypes.c_int64(); na = ctypes.c_int64(); s1 = ctypes.c_double(); s2 = ctypes.c_double()

@@ -216,3 +216,126 @@ int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t*
     if (rec_count) CORAL_TRY(d2h_result(ctx, reinterpret_cast<unsigned long long*>(rec_count), d_cnt, (size_t)n));
     return pass_sync(ctx);
 }
+
+// ---- allocation-free variant (coral_region_coverage_static) -------------------------------------------------------
+// For callers that may not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it).  Everything coral_run_region_coverage keeps in grow-only ctx buffers — the region arrays, the two accumulators,
+// the slow-pair counter and the (record, region) list of the exact re-walk — lives in ONE file-scope device array of a
+// fixed size instead: every GPU that loads the library holds it (CORAL_STATIC_SCRATCH_BYTES) until the process exits.
+// All calls on a device share the array and it keeps the last call's contents: the accumulators and the counter are
+// cleared by every call, and two calls whose kernels overlap on the GPU (different ctxs / streams of one device) race.
+namespace coral {
+
+constexpr int32_t kStaticMaxRegions = CORAL_STATIC_MAX_REGIONS;
+constexpr int64_t kStaticMaxSlow = CORAL_STATIC_MAX_SLOW_PAIRS;
+// layout (bytes): [0, 12 R) tid | start | stop (int32 each) ; [12 R, 28 R) base_sum | rec_count (u64 each) ;
+//                 [28 R, 28 R + 8) slow counter ; then 248 bytes of padding ; slow_rec u32[S] ; slow_reg i32[S]
+constexpr size_t kStaticOffAcc = (size_t)kStaticMaxRegions * 12;
+constexpr size_t kStaticOffSlowN = kStaticOffAcc + (size_t)kStaticMaxRegions * 16;
+constexpr size_t kStaticOffSlowRec = kStaticOffSlowN + 256;
+constexpr size_t kStaticOffSlowReg = kStaticOffSlowRec + (size_t)kStaticMaxSlow * 4;
+constexpr size_t kStaticBytes = kStaticOffSlowReg + (size_t)kStaticMaxSlow * 4;
+static_assert(kStaticBytes == CORAL_STATIC_SCRATCH_BYTES, "include/coral_b200.h states the size of the static scratch");
+static_assert(kStaticOffAcc % 256 == 0 && kStaticOffSlowRec % 256 == 0, "sub-arrays keep the array's alignment");
+
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+// In host code `g_static_scratch` is only the host-side stand-in of the symbol, not a device address: the address a
+// kernel can use comes from cudaGetSymbolAddress, asked once per device with that device current.
+static std::mutex g_static_mu;
+static unsigned char* g_static_ptr[64] = {};
+
+static int static_scratch(coral_ctx* ctx, unsigned char** out) {
+    if (ctx->device < 0 || ctx->device >= 64) { ctx->err = "device index beyond the static scratch table"; return CORAL_E_ARG; }
+    std::lock_guard<std::mutex> g(g_static_mu);
+    if (!g_static_ptr[ctx->device]) {
+        CORAL_CUDA(ctx, cudaSetDevice(ctx->device));
+        void* p = nullptr;
+        CORAL_CUDA(ctx, cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) { ctx->err = "cudaGetSymbolAddress returned a null address"; return CORAL_E_CUDA; }
+        g_static_ptr[ctx->device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_static_ptr[ctx->device];
+    return CORAL_OK;
+}
+
+}  // namespace coral
+
+extern "C" int coral_region_coverage_static(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
+                                            int32_t n, int64_t* base_sum, int64_t* rec_count) {
+    using namespace coral;
+    if (!ctx) return CORAL_E_ARG;
+    if (!ctx->loaded || ctx->rows_only) { ctx->err = "coral_region_coverage_static needs loaded records"; return CORAL_E_STATE; }
+    if (ctx->scan_pending || ctx->scan_lazy) {
+        ctx->err = "coral_region_coverage_static: the record scan is still pending (call coral_wait_scan first)";
+        return CORAL_E_STATE;
+    }
+    if (ctx->pass.active) { ctx->err = "coral_region_coverage_static inside a pipelined pass"; return CORAL_E_STATE; }
+    if (n < 0 || (n > 0 && (!tid || !start || !stop))) { ctx->err = "bad region arrays"; return CORAL_E_ARG; }
+    if (n > kStaticMaxRegions) {
+        char b[160];
+        snprintf(b, sizeof b, "coral_region_coverage_static: %d regions exceed the static scratch (at most %d per call)", n,
+                 kStaticMaxRegions);
+        ctx->err = b;
+        return CORAL_E_ARG;
+    }
+    if (n == 0) return CORAL_OK;
+    for (int32_t i = 0; i < n; i++) {
+        if (stop[i] < start[i] || tid[i] < 0) { ctx->err = "bad region"; return CORAL_E_ARG; }
+        if (i > 0 && (tid[i] < tid[i - 1] || (tid[i] == tid[i - 1] && start[i] < stop[i - 1]))) {
+            ctx->err = "regions must be sorted by (tid, start) and disjoint";
+            return CORAL_E_ARG;
+        }
+    }
+    CORAL_CUDA(ctx, cudaSetDevice(ctx->device));
+    unsigned char* base = nullptr;
+    CORAL_TRY(static_scratch(ctx, &base));
+    cudaStream_t st = ctx->stream;
+    int32_t* d_tid = reinterpret_cast<int32_t*>(base);
+    int32_t* d_start = d_tid + kStaticMaxRegions;
+    int32_t* d_stop = d_start + kStaticMaxRegions;
+    unsigned long long* d_sum = reinterpret_cast<unsigned long long*>(base + kStaticOffAcc);
+    unsigned long long* d_cnt = d_sum + kStaticMaxRegions;
+    unsigned long long* d_slow_n = reinterpret_cast<unsigned long long*>(base + kStaticOffSlowN);
+    uint32_t* d_slow_rec = reinterpret_cast<uint32_t*>(base + kStaticOffSlowRec);
+    int32_t* d_slow_reg = reinterpret_cast<int32_t*>(base + kStaticOffSlowReg);
+    CORAL_CUDA(ctx, cudaMemcpyAsync(d_tid, tid, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    CORAL_CUDA(ctx, cudaMemcpyAsync(d_start, start, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    CORAL_CUDA(ctx, cudaMemcpyAsync(d_stop, stop, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    // the array keeps the previous call's sums and counter: what must start at zero is cleared here
+    CORAL_CUDA(ctx, cudaMemsetAsync(d_sum, 0, kStaticOffSlowN + 8 - kStaticOffAcc, st));
+    Regions R{d_tid, d_start, d_stop, n};
+    const int64_t nrec = ctx->nrec;
+    RecordTable& t = ctx->rt;
+    if (nrec > 0) {
+        const int threads = 256;
+        const int blocks = (int)((nrec + threads - 1) / threads);
+        k_region_cov_fast<<<blocks, threads, 0, st>>>(
+            nrec, t.tid.as<int32_t>(), t.pos.as<int32_t>(), t.endpos.as<int32_t>(), t.flag_mapq.as<uint32_t>(),
+            t.lseq.as<uint32_t>(), t.infer.as<uint32_t>(), t.mbases.as<uint32_t>(), t.nonacgt.as<uint32_t>(), R, d_sum,
+            d_cnt, d_slow_rec, d_slow_reg, d_slow_n, kStaticMaxSlow);
+        ctx->n_launches++;
+        CORAL_CUDA(ctx, cudaGetLastError());
+        unsigned long long n_slow = 0;
+        CORAL_CUDA(ctx, cudaMemcpyAsync(&n_slow, d_slow_n, 8, cudaMemcpyDeviceToHost, st));
+        CORAL_CUDA(ctx, cudaStreamSynchronize(st));
+        if ((int64_t)n_slow > kStaticMaxSlow) {
+            char b[200];
+            snprintf(b, sizeof b, "coral_region_coverage_static: %llu (record, region) pairs need the exact walk, the static "
+                     "scratch holds %lld; use coral_region_coverage", n_slow, (long long)kStaticMaxSlow);
+            ctx->err = b;
+            return CORAL_E_ARG;
+        }
+        if (n_slow) {
+            int sblocks = (int)std::min<int64_t>(((int64_t)n_slow + 7) / 8, (int64_t)ctx->sm_count * 8);
+            k_region_cov_slow<<<sblocks, 256, 0, st>>>(ctx->d_recs, ctx->d_off.as<uint64_t>(), d_slow_rec, d_slow_reg,
+                                                       (int64_t)n_slow, t.nonacgt.as<uint32_t>(), R, d_sum);
+            ctx->n_launches++;
+            CORAL_CUDA(ctx, cudaGetLastError());
+        }
+    }
+    if (base_sum) CORAL_CUDA(ctx, cudaMemcpyAsync(base_sum, d_sum, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    if (rec_count) CORAL_CUDA(ctx, cudaMemcpyAsync(rec_count, d_cnt, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+    CORAL_CUDA(ctx, cudaStreamSynchronize(st));
+    return CORAL_OK;
+}

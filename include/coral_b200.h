@@ -191,6 +191,24 @@ int coral_get_record_table(coral_ctx* ctx, int32_t* tid, int32_t* pos, int32_t* 
 int coral_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
                           int32_t n_regions, int64_t* base_sum, int64_t* rec_count);
 
+/* Allocation-free variant of coral_region_coverage.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, same results, but the call allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine): the region arrays, the accumulators and the (record, region) list of the exact re-walk live in a
+ * file-scope `static __device__` array of CORAL_STATIC_SCRATCH_BYTES (csrc/coverage.cu) that every GPU which loads
+ * the library holds until the process exits.  Limits: n_regions <= CORAL_STATIC_MAX_REGIONS and at most
+ * CORAL_STATIC_MAX_SLOW_PAIRS (record, region) pairs that need the exact walk (records straddling a region boundary
+ * or carrying non-ACGT bases); beyond either the call fails with CORAL_E_ARG and a text that says which (use
+ * coral_region_coverage then).  The record scan must have been joined (CORAL_E_STATE while an asynchronous scan is
+ * pending) and the call is refused inside a pipelined pass.  All calls on one device share the array, which keeps the
+ * previous call's contents (each call clears what must start at zero): calls that overlap on the GPU — two ctxs or
+ * threads on one device — race and must be serialised by the caller. */
+#define CORAL_STATIC_MAX_REGIONS 4096
+#define CORAL_STATIC_MAX_SLOW_PAIRS 65536
+#define CORAL_STATIC_SCRATCH_BYTES 639232
+int coral_region_coverage_static(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
+                                 int32_t n_regions, int64_t* base_sum, int64_t* rec_count);
+
 /* ---- fetch ------------------------------------------------------------------------------------- *
  * replaces bam_to_breakpoint_nanopore.fetch (ibg:139-174) + cigar_parsing.alignment_from_satags
  * (cigar_parsing.py:232-269, cigar2pos* :17-215) over ALL loaded records.
