@@ -81,7 +81,7 @@ class ClockSampler(threading.Thread):
                 self.rows.append([str(sm), str(sm_max)] + ["Active" if why & b else "Not Active" for b in bits])
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(float(os.environ.get("CORAL_BENCH_SAMPLER_S", "0.02")))
 
     def _nvml_index(self):
         vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
@@ -154,12 +154,24 @@ WORKLOADS = {
     "C3": ("C3", {}, "C3 small-deletion-heavy amplicon: 60x HiFi 15 kb, 300 in-CIGAR deletions, dense D ops"),
     "C1": ("C1", {}, "C1 single ecDNA: 2 Mb amplicon, 4 SVs, 30x ONT 20 kb"),
     "C1n": ("C1", {"p_n": 0.001}, "C1 single ecDNA with 0.1 % N bases (non-ACGT slow path of coverage)"),
+    # BASELINE.json configs[3] / [4] on the sub-samples the unmodified reference could be run on in the build container
+    # (tests/golden/full_digest.py: sub_c4, sub_c5 — committed reference digests).  With --gpus N > 1 ONE file is cut into N
+    # contiguous genomic-bin shards (strong scaling): chimeric reads cross the shard cuts at every junction
+    "C4": ("sub_c4", {}, "C4 complex amplicon, 200 breakpoints / 4 chromosomes, ONT 50 kb, sub-sample at 25x of the named 100x"),
+    "C5": ("sub_c5", {}, "C5 whole-genome shape on chr19-22, 6 seed intervals, 30x ONT 20 kb, 0.5 % chimeric noise reads (sub-sample)"),
 }
+STRONG = ("C4", "C5")          # workloads that are one file cut into N shards when N > 1
 
 
 def workload_config(scale, seed_shift=0, workload="C2"):
     from sim import configs
     name, over, _ = WORKLOADS[workload]
+    if name.startswith("sub_"):
+        sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+        import full_digest as FD
+        if scale != 1.0:
+            raise SystemExit("--workload %s is a fixed sub-sample (its reference digest is committed): use --scale 1.0" % workload)
+        return FD.make_cfg(name)
     if name == "C2":
         cfg = configs.c2_multi_segment(scale=scale, seed=20240215 + 2 + 1000 * seed_shift)
     else:
@@ -175,6 +187,9 @@ def config_dict(a, world, n_rec, nbytes, aligned, n_bp, alg_bytes):
             "records_per_gpu": int(n_rec), "record_bytes_per_gpu": int(nbytes), "aligned_gbases_per_gpu": aligned / 1e9,
             "breakpoints_found": int(n_bp),
             "sharding": ("single GPU" if world == 1 else
+                         "ONE coordinate-sorted file cut into N contiguous genomic-bin shards balanced by decoded bytes (strong "
+                         "scaling): chimeric reads cross the cuts; exchange of chimeric fetch rows / parsed chimeric tables / "
+                         "small-del rows / concordant rows and integer sums of coverage inside every step" if a.workload in STRONG else
                          "rank r = r-th contiguous genomic-bin shard (its own 3 chromosomes, C2-shaped) of one "
                          "24-contig file; NCCL exchange of chimeric fetch rows / small-del rows / concordant "
                          "rows and all-reduce of coverage sums inside every step"),
@@ -352,7 +367,7 @@ def device_pass(ctx, plan, gpu_ops, pipelined=True):
     arrays are filled by one deferred copy each when the pass ends with its single synchronisation; launch sizes that
     depend on device results are those of the previous pass over the same records, checked on the device."""
     if pipelined:
-        ctx.pass_begin()
+        ctx.pass_begin(pinned_results=True)     # result arrays in page-locked memory: direct DMA, valid until the next pass
     ctx.rescan()
     out = {}
     # first what only needs the columns of the pre-scan (core fields, name hash, SA / NM): in a pipelined pass these
@@ -377,29 +392,41 @@ def device_pass(ctx, plan, gpu_ops, pipelined=True):
 SHARD_MS = {}
 
 
-def sharded_device_pass(eng, plan, gpu_ops):
-    """The same pass on one shard of the file, with the exchanges of SURVEY.md §8e inside (all ranks in lockstep)."""
-    ctx = eng._ctx
+def sharded_device_pass(eng, plan, gpu_ops, pipelined=False):
+    """The same pass on one shard of the file, with the exchanges of SURVEY.md §8e inside (all ranks in lockstep).
+    pipelined (needs the peer-memory transport): the whole pass — packing kernels, exchanges over NVLink, the rank's
+    share of fetch, merges, coverage, concordant counts — is enqueued as one stream of kernels per lane on both
+    contexts (records ctx + rows-only ctx) and synchronised once."""
+    ctx, cctx = eng._ctx, eng._cctx
     out = {}
     t = [time.perf_counter()]
 
     def lap(name):
         t.append(time.perf_counter())
         SHARD_MS[name] = SHARD_MS.get(name, 0.0) + (t[-1] - t[-2]) * 1e3
+    if pipelined:
+        ctx.pass_begin(pinned_results=True); cctx.pass_begin(pinned_results=True)
     ctx.rescan(); lap("scan")
-    out["normal"] = eng._region_counts(*plan["normal"]); lap("normal_cov+allreduce")
+    # the chimeric chain first: inside a pipelined pass it runs on the second lane next to the stages below
     out["fetch"], _ = eng._run_fetch(); lap("fetch_exchange")
-    out["smalldel"] = eng._smalldel_rows(*plan["intervals"]); lap("smalldel+gather")
+    cand = cctx.candidates_l(*plan["intervals"])
+    out["cand"] = cand
+    if cand["n"]:
+        out["cl2"] = cctx.cluster_call_candidates(cand["n"], plan["cutoff"], 2000, plan["cutoff"], 100)
+    lap("candidates+cluster")
+    out["normal"] = eng._region_counts(*plan["normal"]); lap("normal_cov+sum")
+    out["smalldel"] = eng._smalldel_gather(*plan["intervals"]); lap("smalldel+gather")
     c = plan["smalldel_cand"]
     if len(c["chr1"]):
         out["cl1"] = gpu_ops.cluster_arrays(ctx, c, plan["cutoff"], 2000, plan["cutoff"], 100)
-    cand = eng._chim_ctx.candidates_l(*plan["intervals"])
-    if cand["n"]:
-        out["cl2"] = gpu_ops.cluster_arrays(ctx, cand, plan["cutoff"], 2000, plan["cutoff"], 100)
-    lap("candidates+cluster")
-    out["seq"] = eng._region_counts(*plan["seq_edges"]); lap("seq_cov+allreduce")
-    cnt = eng._concordant_counts(plan["uniq"], plan["rbps"])[0]        # local stab rows, combined by name hash (NCCL)
+    out["seq"] = eng._region_counts(*plan["seq_edges"]); lap("seq_cov+sum")
+    cnt = eng._concordant_counts(plan["uniq"], plan["rbps"])[0]        # local stab rows, combined by name hash
     out["conc"] = cnt; lap("concordant+gather")
+    if pipelined:
+        r1 = cctx.pass_end()
+        r2 = ctx.pass_end()
+        out["replayed"] = bool(r1 and r2)
+        lap("pass_end")
     return out
 
 
@@ -415,7 +442,56 @@ def result_bytes(out):
     return n
 
 
-DIGEST_OF = {"C2": "full_c2", "C3": "full_c3", "C1": "full_c1", "C1n": "full_c1n"}
+FILE_SAMPLE_SCALE = 0.1
+
+
+def e2e_from_file(a, device, scale):
+    """`.bam` file bytes -> graph + coverage through the public class, both ingest forms, on a sample of the workload
+    written as a real BGZF BAM: (1) device_ingest — the compressed bytes cross PCIe, BGZF inflate and record framing run
+    on the GPU (csrc/ingest.cu), the records never exist in host memory; (2) host reader — zlib on all host threads,
+    records framed into a page-locked buffer, kernels read them in place (what `e2e` above starts from).  The timed
+    region of each pass starts with the path of the file and ends after closebam().  The inflate share of the reference
+    arm (pysam / htslib, one thread) is `cpu_baseline.stage_s.open` resp. the reference line's `stage_s`."""
+    import tempfile
+    import numpy as np
+    from sim.generate import simulate, write_dataset
+    from coral_b200.infer_breakpoint_graph import bam_to_breakpoint_nanopore
+    from coral_b200.host_steps import gc_paused
+    cfg = workload_config(scale, workload=a.workload)
+    data = simulate(cfg)
+    paths = write_dataset(data, tempfile.mkdtemp(prefix="coral_file_"))
+    bam_bytes = os.path.getsize(paths["bam"])
+    res = {"sample": "%s at scale %g (%d records, %.2f GB decoded) as a BGZF BAM of %.2f GB" %
+                     (a.workload, scale, data.n_records, int(data.rec_off[-1]) / 1e9, bam_bytes / 1e9),
+           "records": int(data.n_records), "bam_bytes": int(bam_bytes), "decoded_bytes": int(data.rec_off[-1])}
+    digests = {}
+    for kind, kw in (("device_ingest", dict(placement="device_ingest")), ("host_reader", dict(placement="auto"))):
+        ms, stage = [], {}
+        for it in range(4):
+            with gc_paused():
+                t0 = time.perf_counter()
+                eng = bam_to_breakpoint_nanopore(paths["bam"], paths["seed"], device=device, **kw)
+                t1 = time.perf_counter()
+                eng.read_cns(paths["cn_seg"]); eng.fetch(); eng.hash_alignment_to_seg(); eng.find_amplicon_intervals()
+                eng.find_smalldel_breakpoints(); eng.find_breakpoints(); eng.build_graph(); eng.assign_cov()
+                txt = [g.graph_text() if hasattr(g, "graph_text") else None for g in eng.lr_graph]
+                n_bp = len(eng.new_bp_list)
+                cov = eng.normal_cov
+                eng.closebam()
+                del eng
+                t2 = time.perf_counter()
+            if it:                     # the first pass warms the allocator / page-locks
+                ms.append((t2 - t0) * 1e3)
+                stage = {"open+ingest+scan": (t1 - t0) * 1e3, "pipeline": (t2 - t1) * 1e3}
+        digests[kind] = (n_bp, cov, txt)
+        res[kind] = {"ms_per_pass": [round(x, 2) for x in ms], "records_per_s": data.n_records / (float(np.mean(ms)) * 1e-3),
+                     "bam_GB_per_s": bam_bytes / (float(np.mean(ms)) * 1e6), "last_pass_ms": stage}
+    res["identical_results"] = digests["device_ingest"] == digests["host_reader"]
+    res["h2d_bytes_per_pass"] = {"device_ingest": int(bam_bytes), "host_reader": "the record fields the scan pulls over PCIe (QUAL never crosses)"}
+    return res
+
+
+DIGEST_OF = {"C2": "full_c2", "C3": "full_c3", "C1": "full_c1", "C1n": "full_c1n", "C4": "sub_c4", "C5": "sub_c5"}
 
 
 def parity_check(a, rank, world, local, make_engine, cns, comm):
@@ -453,6 +529,31 @@ def parity_check(a, rank, world, local, make_engine, cns, comm):
                                               for g in st["assign_cov"]["graphs"]]}}
     import torch
     import torch.distributed as dist
+    if a.workload in STRONG:
+        # the file of this workload is the one the committed digest of the UNMODIFIED reference was made on: the sharded
+        # run over the real process group must reproduce it (rank 0 compares; every rank must agree with rank 0)
+        case = DIGEST_OF[a.workload]
+        with gzip.open(os.path.join(ROOT, "tests", "golden", "%s.json.gz" % case), "rt") as fp:
+            gold = json.load(fp)
+        with gc_paused():
+            eng = make_engine("copy")
+            st = util.run_pipeline(eng, cns)
+            eng.closebam()
+        dig = FD.digest_state(st)
+        bad = FD.compare_digests(dig, gold["stages"])
+        dig_cmp = json.loads(json.dumps(dig))
+        dig_cmp.get("fetch", {}).pop("nm_stats", None)         # f64 sums in rank order: within 1e-9, compared above on rank 0
+        h = hashlib.sha1(json.dumps(dig_cmp, sort_keys=True).encode()).digest()[:8]
+        t = torch.tensor([int.from_bytes(h, "little") >> 1, len(bad)], dtype=torch.int64, device="cuda")
+        lo, hi = t.clone(), t.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        same = bool(lo[0] == hi[0])
+        return {"parity_ok": int(hi[1]) == 0 and same,
+                "parity": {"against": "tests/golden/%s.json.gz (digest of the unmodified reference's state on this file), sharded run "
+                                      "over the real process group" % case, "stages_compared": sorted(gold["stages"]),
+                           "mismatches": [list(b) for b in bad], "identical_on_all_ranks": same,
+                           "graph_txt_sha1": [hashlib.sha1(g["graph_txt"].encode()).hexdigest() for g in st["assign_cov"]["graphs"]]}}
     import make_golden
     import test_golden_cpu as G
     from sim.generate import simulate
@@ -465,7 +566,7 @@ def parity_check(a, rank, world, local, make_engine, cns, comm):
         data = simulate(cfg)
         recs = RecordSet([c for c, _ in cfg.refs], data.rec, data.rec_off)
         c_cns, c_seed = write_inputs(cfg, tempfile.mkdtemp(prefix="coral_parity_%d_" % rank))
-        eng = sharded.make_sharded_engine(recs, c_seed, comm, device=local)
+        eng = sharded.make_sharded_engine(recs, c_seed, comm, device=local, xchg=make_engine.xchg)
         st = util.jsonify(util.run_pipeline(eng, c_cns, stop_after="assign_cov"))
         eng.closebam()
         want = {k: v for k, v in G.load_golden(case)["stages"].items() if k != "compute_path_constraints"}
@@ -518,10 +619,15 @@ def main():
     ap.add_argument("--no-pipeline", action="store_true",
                     help="device pass call by call (a synchronisation inside every entry point) instead of as one pipelined "
                          "pass (development aid: what the pass mode buys)")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: the exchanges of the sharded pass as kernels over peer memory (NVLink, csrc/xchg.cu; the pass "
+                         "is then one stream of kernels per rank) or as torch.distributed / NCCL collectives issued by the "
+                         "host between kernels (the baseline this is measured against)")
     ap.add_argument("--e2e-placement", default="mapped_async", choices=["mapped", "mapped_async", "copy"],
                     help="e2e arm: kernels read the pinned host records in place over PCIe (mapped; mapped_async = fetch and "
                          "the host steps after it run next to the scan, the default at N=1: 172 vs 200 ms per C2 pass) or after a full "
                          "H2D copy")
+    ap.add_argument("--no-file", action="store_true", help="skip the e2e_from_file leg (development aid)")
     ap.add_argument("--only", default="", help="'scan': time the record-scan kernel alone; 'e2e': per-pass stage times of "
                                                "the e2e arm alone (development aids)")
     ap.add_argument("--cprofile", action="store_true", help="cProfile of 20 device passes on rank 0 (development aid)")
@@ -551,16 +657,22 @@ def main():
     from coral_b200.host_steps import gc_paused
     import tempfile
 
-    comm = None
+    comm = xchg = None
     if world > 1:
         # weak scaling: rank r holds a C2-shaped sample on its own three chromosomes of one 24-contig file, i.e. the
         # r-th contiguous genomic-bin shard of ONE coordinate-sorted BAM (sim/configs.py::c2_shard)
         import types
         from sim import configs
         from coral_b200 import sharded
-        cfg, all_cn, all_seeds = configs.c2_shard(rank, world, scale=a.scale)
-        cfg_files = types.SimpleNamespace(cn_rows=all_cn, seeds=all_seeds)
+        if a.workload in STRONG:
+            cfg = cfg_files = workload_config(a.scale, workload=a.workload)     # every rank simulates the file, keeps its shard
+        elif a.workload == "C2":
+            cfg, all_cn, all_seeds = configs.c2_shard(rank, world, scale=a.scale)
+            cfg_files = types.SimpleNamespace(cn_rows=all_cn, seeds=all_seeds)
+        else:
+            raise SystemExit("--workload %s runs on one GPU only" % a.workload)
         comm = sharded.TorchComm(device=torch.device("cuda", local))
+        xchg = sharded.make_xchg(comm, local) if a.exchange == "peer" else None
     else:
         cfg = workload_config(a.scale, workload=a.workload)
         cfg_files = cfg
@@ -570,7 +682,20 @@ def main():
         pinned["t"] = torch.empty(nbytes + 64, dtype=torch.uint8).pin_memory()   # 64 B of slack: mapped placement
         return pinned["t"].numpy()[:nbytes]
 
-    data = simulate(cfg, alloc=alloc)
+    strong = world > 1 and a.workload in STRONG
+    if strong:
+        # one file, N contiguous shards balanced by decoded bytes (sharded.shard_ranges): this rank's records go into its
+        # own page-locked buffer, re-based offsets; the whole file only exists while it is being cut
+        whole = simulate(cfg)
+        off = np.asarray(whole.rec_off, dtype=np.uint64)
+        r0, r1 = sharded.shard_ranges(off, world)[rank]
+        b0, b1 = int(off[r0]), int(off[r1])
+        buf = alloc(b1 - b0)
+        buf[:] = whole.rec[b0:b1]
+        data = types.SimpleNamespace(rec=buf, rec_off=(off[r0:r1 + 1] - np.uint64(b0)).astype(np.uint64), n_records=r1 - r0)
+        del whole
+    else:
+        data = simulate(cfg, alloc=alloc)
     n_rec = data.n_records
     nbytes = int(data.rec_off[-1])
     recs = RecordSet([c for c, _ in cfg.refs], data.rec, data.rec_off, rec_slack=64)
@@ -578,9 +703,10 @@ def main():
 
     def make_engine(placement):
         if world > 1:
-            return sharded.make_sharded_engine(recs, seed, comm, device=local, placement=placement, presharded=True)
+            return sharded.make_sharded_engine(recs, seed, comm, device=local, placement=placement, presharded=True, xchg=xchg)
         return bam_to_breakpoint_nanopore(None, seed, device=local, records=recs, placement=placement)
     make_engine.records = recs
+    make_engine.xchg = xchg
     alg_bytes = record_field_bytes(data.rec, data.rec_off)
 
     if a.only == "scan":
@@ -643,12 +769,14 @@ def main():
     eng0 = make_engine("copy")
     plan = build_plan(eng0, cns)
     ctx = eng0._ctx
+    if world > 1:
+        eng0.materialise = rank == 0       # the replicated result tables are delivered to rank 0's host only
     tab = ctx.record_table()
     aligned = int(tab["aligned_bases"].sum())
     n_bp = len(eng0.new_bp_list)
     def one_pass():
         if world > 1:
-            return sharded_device_pass(eng0, plan, gpu_ops)
+            return sharded_device_pass(eng0, plan, gpu_ops, pipelined=(xchg is not None and not a.no_pipeline))
         return device_pass(ctx, plan, gpu_ops, pipelined=not a.no_pipeline)
 
     def n_launches():
@@ -702,9 +830,10 @@ def main():
         replayed += int(bool(one_pass().get("replayed")))
         # the roofline kernel: in a pipelined pass the aux walk of the scan runs as a separate pre-scan kernel, so the
         # time that goes with the scan's algorithmic bytes is pre-scan + scan
-        scan_ms.append(ctx.stage_ms(0) + max(ctx.stage_ms(9), 0.0))
-        prescan_ms.append(max(ctx.stage_ms(9), 0.0))
-        stage_ms += np.array([max(ctx.stage_ms(s), 0.0) for s in range(8)])
+        sm = np.maximum(ctx.stage_ms_all().astype(np.float64), 0.0)      # one call: CUDA-event times of this step's stages
+        scan_ms.append(sm[0] + sm[9])
+        prescan_ms.append(sm[9])
+        stage_ms += sm[:8]
     barrier()
     dt = time.perf_counter() - t0
     launches = n_launches() - l0
@@ -743,6 +872,12 @@ def main():
                    "note": "not part of value / e2e; the CPU port's time for the same step is cpu_baseline.stage_s.path_constraints"}
         eng.closebam()
 
+    # SURVEY 8f-3 (the step before the path): .bam bytes -> graph, on a bounded sample of the workload written as a real
+    # BGZF file (the full-size file takes minutes to deflate on the host; the sample is stated in the line)
+    file_info = None
+    if world == 1 and not a.no_file and a.scale >= 0.5:
+        file_info = e2e_from_file(a, local, FILE_SAMPLE_SCALE * a.scale)
+
     tt = torch.tensor([dt, dt_e2e], dtype=torch.float64, device="cuda")
     tot = torch.tensor([n_rec, aligned, launches], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -758,7 +893,7 @@ def main():
     out = {
         "metric": METRIC, "value": n_rec_all * a.steps / dt, "unit": "records/s",
         "n_gpus": world, "steps": a.steps, "warmup": warm, "ms_per_step": dt / a.steps * 1e3,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "higher_is_better": True, "scaling": ("strong" if strong else "weak"), "vs_baseline": None,
         "dtype": "u8/int32/int64 (f64 stats)", "data": "synthetic",
         "config": config_dict(a, world, n_rec, nbytes, aligned, n_bp, alg_bytes),
         "aligned_gbases_per_s": aligned_all * a.steps / dt / 1e9,
@@ -767,7 +902,8 @@ def main():
                 "d2h_bytes_per_step": d2h, "placement": a.e2e_placement, "steps": e2e_steps,
                 "ms_per_pass": [round(x, 2) for x in e2e_ms], "stage_ms": e2e_stage},
         "gpu_launches": int(launches_all),
-        "device_pass": {"pipelined": (world == 1 and not a.no_pipeline), "steps_without_intermediate_sync": replayed,
+        "device_pass": {"pipelined": ((world == 1 or xchg is not None) and not a.no_pipeline), "steps_without_intermediate_sync": replayed,
+                        "exchange": (None if world == 1 else a.exchange),
                         "note": "one stream of kernels per step (coral_pass_begin / coral_pass_end): one synchronisation and one "
                                 "deferred copy per result table; launch sizes that depend on device results are replayed from the "
                                 "previous pass over the same records and checked on the device"},
@@ -785,6 +921,8 @@ def main():
     out.update(parity)
     if pc_info is not None:
         out["path_constraints_step"] = pc_info
+    if file_info is not None:
+        out["e2e_from_file"] = file_info
     if world > 1:
         out["sharded_stage_ms_per_step"] = {k: v / a.steps for k, v in SHARD_MS.items()}
         out["fetch_exchange_ms_per_step"] = {k: v / a.steps for k, v in eng0.fetch_laps.items()}
@@ -802,6 +940,8 @@ def main():
                 out["cpu_baseline"] = {"error": repr(ex)}
         print(json.dumps(out), flush=True)
     if world > 1:
+        if xchg is not None:
+            sharded.close_xchg(comm, xchg)
         dist.destroy_process_group()
     if out.get("parity_ok") is False:
         sys.exit(3)

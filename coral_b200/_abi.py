@@ -159,6 +159,61 @@ class BamFile(object):
             pass
 
 
+XCHG_CHANNELS = 8
+XCHG_HANDLE_BYTES = 64
+# channels of the multi-GPU engine (sharded.py) and their default slot sizes (largest message per rank)
+CH_SA, CH_EXTRA, CH_CHIM, CH_SDEL, CH_CONC, CH_COV, CH_MISC = 0, 1, 2, 3, 4, 5, 6
+XCHG_DEFAULT_SLOTS = (32 << 20, 8 << 20, 32 << 20, 1 << 20, 32 << 20, 1 << 20, 1 << 20, 0)
+
+
+class Xchg(object):
+    """One rank's exchange window (csrc/xchg.cu): create on every rank, all-gather the handles over any transport,
+    connect, barrier, exchange ...; barrier again before close()."""
+
+    def __init__(self, device, rank, world, slot_bytes=XCHG_DEFAULT_SLOTS):
+        L = lib()
+        L.coral_xchg_last_error.restype = ctypes.c_char_p
+        slots = np.zeros(XCHG_CHANNELS, np.uint64)
+        slots[:len(slot_bytes)] = slot_bytes
+        h = ctypes.c_void_p()
+        rc = L.coral_xchg_create(int(device), int(rank), int(world), _p(slots), ctypes.byref(h))
+        if rc != 0:
+            raise CoralError(rc, "coral_xchg_create failed")
+        self._h, self._L = h, L
+        self.rank, self.world, self.device = int(rank), int(world), int(device)
+
+    def _check(self, rc):
+        if rc != 0:
+            raise CoralError(rc, self._L.coral_xchg_last_error(self._h).decode())
+
+    def handle(self):
+        """-> (64-byte IPC handle as bytes, device address of the local window)."""
+        hb = np.zeros(XCHG_HANDLE_BYTES, np.uint8)
+        ptr = ctypes.c_uint64()
+        self._check(self._L.coral_xchg_handle(self._h, _p(hb), ctypes.byref(ptr)))
+        return hb.tobytes(), int(ptr.value)
+
+    def connect(self, handles, same_process_ptrs=None):
+        """handles: list of `world` 64-byte handles in rank order; same_process_ptrs: window addresses of the ranks that
+        are threads of this process (0 elsewhere)."""
+        hb = np.frombuffer(b"".join(handles), np.uint8).copy()
+        sp = None if same_process_ptrs is None else np.ascontiguousarray(same_process_ptrs, dtype=np.uint64)
+        self._check(self._L.coral_xchg_connect(self._h, _p(hb), _p(sp)))
+
+    def set_timeout(self, seconds):
+        self._check(self._L.coral_xchg_set_timeout(self._h, ctypes.c_double(seconds)))
+
+    def timeouts(self):
+        n = ctypes.c_int32()
+        self._check(self._L.coral_xchg_timeouts(self._h, ctypes.byref(n)))
+        return int(n.value)
+
+    def close(self):
+        if self._h is not None:
+            self._L.coral_xchg_destroy(self._h)
+            self._h = None
+
+
 class Context(object):
     """One coral_ctx bound to one GPU."""
 
@@ -174,13 +229,42 @@ class Context(object):
         self._keep = []
         self._pass_keep = None      # inside a pipelined pass: objects the C side writes at pass_end + finalizers
         self._pass_fin = []
+        self._arena = []            # page-locked chunks [address, capacity, used] of pass_begin(pinned_results=True)
+        self._pinned_results = False
 
     # ---- pipelined pass (include/coral_b200.h: coral_pass_begin / coral_pass_end) --------------------------------
-    def pass_begin(self):
+    def pass_begin(self, pinned_results=False):
         """Until pass_end() the entry points only enqueue their kernels: the arrays they return are FILLED at pass_end()
-        (do not read them before), counts are those of the last complete pass over the same inputs."""
+        (do not read them before), counts are those of the last complete pass over the same inputs.
+        pinned_results: the arrays returned inside this pass are views of a page-locked arena owned by the ctx (their
+        copies are direct DMAs, nothing is staged or memcpy'd when the pass ends) and stay valid until the next
+        pass_begin(pinned_results=True) on this ctx — for callers that consume a pass's results before the next pass."""
         self._check(self._L.coral_pass_begin(self._h))
         self._pass_keep, self._pass_fin = [], []
+        self._pinned_results = bool(pinned_results)
+        if pinned_results:
+            for ch in self._arena:
+                ch[2] = 0
+
+    def _z(self, shape, dtype=np.float64):
+        """Output array: numpy zeros, or — inside a pass with pinned_results — an (uninitialised) view of the arena."""
+        if self._pass_keep is None or not getattr(self, "_pinned_results", False):
+            return np.zeros(shape, dtype)
+        dt = np.dtype(dtype)
+        count = int(np.prod(shape)) if not isinstance(shape, (int, np.integer)) else int(shape)
+        nbytes = (count * dt.itemsize + 63) & ~63
+        for ch in self._arena:
+            if ch[1] - ch[2] >= nbytes:
+                break
+        else:
+            cap = max(nbytes, 8 << 20)
+            ptr = ctypes.c_void_p()
+            self._check(self._L.coral_host_alloc(ctypes.c_uint64(cap), ctypes.byref(ptr)))
+            ch = [ptr.value, cap, 0]
+            self._arena.append(ch)
+        buf = (ctypes.c_uint8 * max(nbytes, 1)).from_address(ch[0] + ch[2])
+        ch[2] += nbytes
+        return np.frombuffer(buf, dtype=dt, count=count).reshape(shape)
 
     def pass_end(self):
         """-> True when the pass ran without intermediate synchronisation (sizes replayed from the previous pass)."""
@@ -206,6 +290,9 @@ class Context(object):
         if self._h is not None:
             self._L.coral_destroy(self._h)
             self._h = None
+            for ch in self._arena:
+                self._L.coral_host_free(ctypes.c_void_p(ch[0]))
+            self._arena = []
 
     def __del__(self):
         try:
@@ -259,8 +346,8 @@ class Context(object):
     # ---- multi-GPU exchange of fetch (include/coral_b200.h) ---------------------------------------------------
     def record_keys(self):
         n = self.n_records
-        out = {"name_lo": np.zeros(n, np.uint64), "name_hi": np.zeros(n, np.uint64), "sa_off": np.zeros(n, np.uint32),
-               "sa_len": np.zeros(n, np.uint32), "nm": np.zeros(n, np.int32)}
+        out = {"name_lo": self._z(n, np.uint64), "name_hi": self._z(n, np.uint64), "sa_off": self._z(n, np.uint32),
+               "sa_len": self._z(n, np.uint32), "nm": self._z(n, np.int32)}
         self._check(self._L.coral_get_record_keys(self._h, _p(out["name_lo"]), _p(out["name_hi"]), _p(out["sa_off"]),
                                                   _p(out["sa_len"]), _p(out["nm"])))
         return out
@@ -299,7 +386,7 @@ class Context(object):
         """Both gathered message sets -> this (rows-only) ctx.  -> (n_rows, nm partial sums per rank: 4 arrays)."""
         s1 = np.ascontiguousarray(starts1, dtype=np.uint64); s2 = np.ascontiguousarray(starts2, dtype=np.uint64)
         w = len(s1)
-        a = np.zeros(w, np.float64); b = np.zeros(w, np.float64); cn = np.zeros(w, np.int64); zd = np.zeros(w, np.int64)
+        a = self._z(w, np.float64); b = self._z(w, np.float64); cn = self._z(w, np.int64); zd = self._z(w, np.int64)
         n = ctypes.c_int64()
         self._check(self._L.coral_unpack_rows(self._h, w, ctypes.c_void_p(buf1_ptr), _p(s1), ctypes.c_void_p(buf2_ptr), _p(s2),
                                               _p(a), _p(b), _p(cn), _p(zd), ctypes.byref(n)))
@@ -313,10 +400,71 @@ class Context(object):
 
     def count_name_msgs(self, n_edges, buf_ptr, starts, sizes, rb_ptr, n_rb):
         st = np.ascontiguousarray(starts, dtype=np.uint64); sz = np.ascontiguousarray(sizes, dtype=np.uint64)
-        cnt = np.zeros(max(n_edges, 1), np.int64)
+        cnt = self._z(max(n_edges, 1), np.int64)
         self._check(self._L.coral_count_name_msgs(self._h, int(n_edges), len(st), ctypes.c_void_p(buf_ptr), _p(st), _p(sz),
                                                   ctypes.c_void_p(rb_ptr), ctypes.c_int64(n_rb), _p(cnt)))
+        self._hold(cnt)
         return cnt[:n_edges]
+
+    # ---- exchanges over peer memory (csrc/xchg.cu) and the distributed fetch (csrc/chimeric_merge.cu) -------------
+    def xchg_allgather(self, xchg, channel, ptr, nbytes, lane=False):
+        """All-gather of one device message per rank -> (gathered device buffer address, starts, sizes)."""
+        w = xchg.world
+        buf = ctypes.c_uint64(); st = self._z(w, np.uint64); sz = self._z(w, np.uint64)
+        self._check(self._L.coral_xchg_allgather(self._h, xchg._h, int(channel), ctypes.c_uint64(ptr), ctypes.c_uint64(nbytes),
+                                                 int(bool(lane)), ctypes.byref(buf), _p(st), _p(sz)))
+        return int(buf.value), st, sz
+
+    def xchg_allreduce(self, xchg, channel, values):
+        v = np.ascontiguousarray(values, dtype=np.int64).copy()
+        self._check(self._L.coral_xchg_allreduce_i64(self._h, xchg._h, int(channel), _p(v), len(v)))
+        return v
+
+    def region_coverage_sharded(self, xchg, channel, tid, start, stop):
+        """region_coverage summed over all shards of the file (every rank calls it with the same regions)."""
+        tid = np.ascontiguousarray(tid, dtype=np.int32)
+        start = np.ascontiguousarray(start, dtype=np.int32)
+        stop = np.ascontiguousarray(stop, dtype=np.int32)
+        n = len(tid)
+        bs = self._z(n, np.int64)
+        rc = self._z(n, np.int64)
+        self._check(self._L.coral_region_coverage_sharded(self._h, xchg._h, int(channel), _p(tid), _p(start), _p(stop), n,
+                                                          _p(bs), _p(rc)))
+        self._hold(bs, rc)
+        return bs, rc
+
+    def pack_chimeric(self):
+        ptr = ctypes.c_uint64(); nb = ctypes.c_uint64()
+        self._check(self._L.coral_pack_chimeric(self._h, ctypes.byref(ptr), ctypes.byref(nb)))
+        return int(ptr.value), int(nb.value)
+
+    def merge_chimeric(self, buf_ptr, starts):
+        """Gathered partial chimeric tables -> this ctx's table in the 1-GPU order.  -> (n_reads, n_alignments)."""
+        st = np.ascontiguousarray(starts, dtype=np.uint64)
+        nr = ctypes.c_int64(); na = ctypes.c_int64()
+        self._check(self._L.coral_merge_chimeric(self._h, len(st), ctypes.c_void_p(buf_ptr), _p(st), ctypes.byref(nr),
+                                                 ctypes.byref(na)))
+        return int(nr.value), int(na.value)
+
+    def smalldel_pack(self):
+        ptr = ctypes.c_uint64(); nb = ctypes.c_uint64()
+        self._check(self._L.coral_smalldel_pack(self._h, ctypes.byref(ptr), ctypes.byref(nb)))
+        return int(ptr.value), int(nb.value)
+
+    def read_device(self, ptr, nbytes, lane=False):
+        """Device bytes -> numpy uint8 array (filled at pass_end inside a pipelined pass)."""
+        out = self._z(int(nbytes), np.uint8)
+        if nbytes:
+            self._check(self._L.coral_read_device(self._h, ctypes.c_uint64(ptr), ctypes.c_uint64(nbytes), _p(out), int(bool(lane))))
+        self._hold(out)
+        return out
+
+    def stream_handle(self, which=0):
+        self._L.coral_stream_handle.restype = ctypes.c_uint64
+        return int(self._L.coral_stream_handle(self._h, int(which)))
+
+    def adopt_stream(self, handle):
+        self._check(self._L.coral_adopt_stream(self._h, ctypes.c_uint64(handle)))
 
     def device_view(self):
         """Device addresses (recs, offsets, name_lo, name_hi, flag_mapq, l_seq, nm, sa_off, sa_len)."""
@@ -332,6 +480,12 @@ class Context(object):
 
     def stage_ms(self, stage):
         return float(self._L.coral_stage_ms(self._h, int(stage)))
+
+    def stage_ms_all(self):
+        """Device time of every stage's most recent run (float32[10], < 0 where a stage has not run), one call."""
+        out = np.zeros(10, np.float32)
+        self._check(self._L.coral_stage_ms_all(self._h, _p(out)))
+        return out
 
     def reset_stage_times(self):
         self._L.coral_reset_stage_times(self._h)
@@ -349,8 +503,8 @@ class Context(object):
 
     def record_table(self):
         n = self.n_records
-        cols = {k: np.zeros(n, np.int32) for k in ("tid", "pos", "endpos", "flag", "mapq", "n_cigar")}
-        cols.update({k: np.zeros(n, np.int64) for k in ("l_seq", "infer_len", "aligned_bases", "non_acgt")})
+        cols = {k: self._z(n, np.int32) for k in ("tid", "pos", "endpos", "flag", "mapq", "n_cigar")}
+        cols.update({k: self._z(n, np.int64) for k in ("l_seq", "infer_len", "aligned_bases", "non_acgt")})
         self._check(self._L.coral_get_record_table(
             self._h, _p(cols["tid"]), _p(cols["pos"]), _p(cols["endpos"]), _p(cols["flag"]), _p(cols["mapq"]),
             _p(cols["l_seq"]), _p(cols["n_cigar"]), _p(cols["infer_len"]), _p(cols["aligned_bases"]), _p(cols["non_acgt"])))
@@ -362,8 +516,8 @@ class Context(object):
         start = np.ascontiguousarray(start, dtype=np.int32)
         stop = np.ascontiguousarray(stop, dtype=np.int32)
         n = len(tid)
-        bs = np.zeros(n, np.int64)
-        rc = np.zeros(n, np.int64)
+        bs = self._z(n, np.int64)
+        rc = self._z(n, np.int64)
         self._check(self._L.coral_region_coverage(self._h, _p(tid), _p(start), _p(stop), n, _p(bs), _p(rc)))
         self._hold(bs, rc)
         return bs, rc
@@ -375,13 +529,14 @@ class Context(object):
         start = np.ascontiguousarray(start, dtype=np.int32)
         stop = np.ascontiguousarray(stop, dtype=np.int32)
         n = len(tid)
-        bs = np.zeros(n, np.int64)
-        rc = np.zeros(n, np.int64)
+        bs = self._z(n, np.int64)
+        rc = self._z(n, np.int64)
         self._check(self._L.coral_region_coverage_static(self._h, _p(tid), _p(start), _p(stop), n, _p(bs), _p(rc)))
         return bs, rc
 
-    def fetch(self):
-        """coral_fetch + coral_get_chimeric -> dict of numpy arrays (see include/coral_b200.h)."""
+    def fetch(self, read_back=True):
+        """coral_fetch + coral_get_chimeric -> dict of numpy arrays (see include/coral_b200.h).
+        read_back=False: the table stays on the device (counts and nm sums only)."""
         nr = ctypes.c_int64(); na = ctypes.c_int64(); s1 = ctypes.c_double(); s2 = ctypes.c_double()
         nn = ctypes.c_int64(); zd = ctypes.c_int64()
         self._check(self._L.coral_fetch(self._h, ctypes.byref(nr), ctypes.byref(na), ctypes.byref(s1), ctypes.byref(s2),
@@ -391,13 +546,21 @@ class Context(object):
             self._hold(s1, s2, nn, zd)
             self._pass_fin.append(lambda: out.update(nm_sum=s1.value, nm_sumsq=s2.value, nm_n=nn.value, nm_zero_div=zd.value))
         out = {"n_reads": nr, "n_aln": na, "nm_sum": s1.value, "nm_sumsq": s2.value, "nm_n": nn.value,
-               "nm_zero_div": zd.value,
-               "read_first_rec": np.zeros(nr, np.uint32), "read_len": np.zeros(nr, np.int64),
-               "read_status": np.zeros(nr, np.int32), "aln_ptr": np.zeros(nr + 1, np.uint32)}
+               "nm_zero_div": zd.value}
+        if not read_back:
+            return out
+        return self.get_chimeric(nr, na, out)
+
+    def get_chimeric(self, nr, na, out=None):
+        """coral_get_chimeric of the table on the device (after fetch / merge_chimeric) -> dict of numpy arrays."""
+        out = {} if out is None else out
+        out.update({"n_reads": nr, "n_aln": na,
+               "read_first_rec": self._z(nr, np.uint32), "read_len": self._z(nr, np.int64),
+               "read_status": self._z(nr, np.int32), "aln_ptr": self._z(nr + 1, np.uint32)})
         for k in ("qs", "qe", "tid", "rstart", "rend", "mapq"):
-            out[k] = np.zeros(na, np.int32)
-        out["strand"] = np.zeros(na, np.uint8)
-        out["nm"] = np.zeros(na, np.int64)
+            out[k] = self._z(na, np.int32)
+        out["strand"] = self._z(na, np.uint8)
+        out["nm"] = self._z(na, np.int64)
         self._check(self._L.coral_get_chimeric(
             self._h, _p(out["read_first_rec"]), _p(out["read_len"]), _p(out["read_status"]), _p(out["aln_ptr"]),
             _p(out["qs"]), _p(out["qe"]), _p(out["tid"]), _p(out["rstart"]), _p(out["rend"]), _p(out["strand"]),
@@ -415,9 +578,9 @@ class Context(object):
         n = ctypes.c_int64()
         self._check(self._L.coral_smalldel(self._h, _p(t), _p(s), _p(e), len(t), ctypes.byref(n)))
         n = n.value
-        out = {"n": n, "rec": np.zeros(n, np.uint32)}
+        out = {"n": n, "rec": self._z(n, np.uint32)}
         for k in ("ai", "next_start", "prev_end", "first_start", "last_end", "mapq"):
-            out[k] = np.zeros(n, np.int32)
+            out[k] = self._z(n, np.int32)
         if n:
             self._check(self._L.coral_get_smalldel(self._h, _p(out["rec"]), _p(out["ai"]), _p(out["next_start"]),
                                                    _p(out["prev_end"]), _p(out["first_start"]), _p(out["last_end"]),
@@ -430,11 +593,11 @@ class Context(object):
         n = ctypes.c_int64()
         self._check(self._L.coral_candidates_l(self._h, _p(t), _p(s), _p(e), len(t), ctypes.byref(n)))
         n = n.value
-        out = {"n": n, "read": np.zeros(n, np.uint32)}
+        out = {"n": n, "read": self._z(n, np.uint32)}
         for k in ("i", "j", "chr1", "pos1", "chr2", "pos2", "rgap", "mq1", "mq2"):
-            out[k] = np.zeros(n, np.int32)
+            out[k] = self._z(n, np.int32)
         for k in ("o1", "o2", "flag"):
-            out[k] = np.zeros(n, np.uint8)
+            out[k] = self._z(n, np.uint8)
         if n:
             self._check(self._L.coral_get_candidates(
                 self._h, _p(out["read"]), _p(out["i"]), _p(out["j"]), _p(out["chr1"]), _p(out["pos1"]), _p(out["o1"]),
@@ -458,10 +621,10 @@ class Context(object):
         return self._clusters_out(n, nc.value)
 
     def _clusters_out(self, n, nc):
-        out = {"n_clusters": nc, "order": np.zeros(n, np.uint32), "cluster_ptr": np.zeros(nc + 1, np.uint32),
-               "n_sub": np.zeros(nc, np.int32), "sub_of": np.zeros(n, np.int32), "row_pos1": np.zeros(n, np.int32),
-               "row_pos2": np.zeros(n, np.int32), "row_nb": np.zeros(n, np.int32), "row_first": np.zeros(n, np.uint32),
-               "row_stats": np.zeros((n, 6), np.float64)}
+        out = {"n_clusters": nc, "order": self._z(n, np.uint32), "cluster_ptr": self._z(nc + 1, np.uint32),
+               "n_sub": self._z(nc, np.int32), "sub_of": self._z(n, np.int32), "row_pos1": self._z(n, np.int32),
+               "row_pos2": self._z(n, np.int32), "row_nb": self._z(n, np.int32), "row_first": self._z(n, np.uint32),
+               "row_stats": self._z((n, 6), np.float64)}
         if n:
             self._check(self._L.coral_get_clusters(
                 self._h, _p(out["order"]), _p(out["cluster_ptr"]), _p(out["n_sub"]), _p(out["sub_of"]), _p(out["row_pos1"]),
@@ -486,7 +649,7 @@ class Context(object):
         minus1, minus2 = u8(minus1), u8(minus2)
         rgap = np.ascontiguousarray(rgap, dtype=np.float64)
         n = len(a1)
-        out = np.zeros(n, np.uint8)
+        out = self._z(n, np.uint8)
         self._check(self._L.coral_bp_match(self._h, ctypes.c_int64(n), _p(a1), _p(a4), _p(minus1), _p(minus2), _p(rgap), _p(b1),
                                            _p(b4), ctypes.c_int64(int(cutoff1)), ctypes.c_int64(int(cutoff2)), _p(out)))
         return out
@@ -504,7 +667,7 @@ class Context(object):
     def concordant_rows(self):
         """(edge, record, mask) rows of the last concordant / concordant_rows_only call, read back to the host."""
         nr = self._stab_n
-        rows = {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
+        rows = {"edge": self._z(nr, np.uint32), "rec": self._z(nr, np.uint32), "mask": self._z(nr, np.uint32)}
         if nr:
             self._check(self._L.coral_get_concordant_rows(self._h, _p(rows["edge"]), _p(rows["rec"]), _p(rows["mask"])))
         self._hold(rows)
@@ -517,7 +680,7 @@ class Context(object):
         rb_edge = np.ascontiguousarray(rb_edge, dtype=np.uint32)
         rb_rec = np.ascontiguousarray(rb_rec, dtype=np.uint32)
         n = len(tid)
-        cnt = np.zeros(n, np.int64)
+        cnt = self._z(n, np.int64)
         nr = ctypes.c_int64()
         self._check(self._L.coral_concordant(self._h, _p(tid), _p(p), n, ctypes.c_int64(len(rb_edge)), _p(rb_edge), _p(rb_rec),
                                              _p(cnt), ctypes.byref(nr)))
@@ -525,13 +688,13 @@ class Context(object):
         self._hold(cnt)
         if fetch_rows:
             return cnt, self.concordant_rows()
-        return cnt, {"edge": np.zeros(nr, np.uint32), "rec": np.zeros(nr, np.uint32), "mask": np.zeros(nr, np.uint32)}
+        return cnt, {"edge": self._z(nr, np.uint32), "rec": self._z(nr, np.uint32), "mask": self._z(nr, np.uint32)}
 
     def cn_segment_index(self, seg_tid, seg_begin, seg_end, seg_idx, n_aln):
         """hash_alignment_to_seg lookups (ibg:181-210) for every alignment of the chimeric table -> (lo, hi) int32."""
         i32 = lambda a: np.ascontiguousarray(a, dtype=np.int32)
         seg_tid, seg_begin, seg_end, seg_idx = map(i32, (seg_tid, seg_begin, seg_end, seg_idx))
-        lo, hi = np.zeros(n_aln, np.int32), np.zeros(n_aln, np.int32)
+        lo, hi = self._z(n_aln, np.int32), self._z(n_aln, np.int32)
         self._check(self._L.coral_cn_segment_index(self._h, _p(seg_tid), _p(seg_begin), _p(seg_end), _p(seg_idx),
                                                    ctypes.c_int32(len(seg_tid)), _p(lo), _p(hi)))
         return lo, hi
@@ -562,7 +725,7 @@ class Context(object):
         idx = np.ascontiguousarray(idx, dtype=np.uint32)
         if len(idx) == 0:
             return []
-        out = np.zeros(len(idx) * 256, np.uint8)
+        out = self._z(len(idx) * 256, np.uint8)
         self._check(self._L.coral_get_read_names(self._h, _p(idx), ctypes.c_int64(len(idx)), _p(out)))
         rows = out.reshape(len(idx), 256)
         ln = (rows != 0).argmin(axis=1)          # first NUL (names are at most 254 characters + NUL)
@@ -585,8 +748,8 @@ class Context(object):
             ctypes.c_int32(len(se_tid)), _p(name_rec), ctypes.c_int64(len(name_rec)), _p(name_lo), _p(name_hi),
             ctypes.c_int64(len(name_lo)), ctypes.c_int32(min_overlap), ctypes.c_int32(min_mapq), ctypes.byref(n)))
         n = int(n.value)
-        out = {"n": n, "rec": np.zeros(n, np.uint32), "iv": np.zeros(n, np.int32), "first": np.zeros(n, np.int32),
-               "last": np.zeros(n, np.int32)}
+        out = {"n": n, "rec": self._z(n, np.uint32), "iv": self._z(n, np.int32), "first": self._z(n, np.int32),
+               "last": self._z(n, np.int32)}
         if n:
             self._check(self._L.coral_get_alignment_paths(self._h, _p(out["rec"]), _p(out["iv"]), _p(out["first"]), _p(out["last"])))
         return out
@@ -594,10 +757,10 @@ class Context(object):
     def sa_text(self, text, ent_ptr, ent_beg, ent_end, read_len):
         n_reads = len(read_len)
         ne = int(ent_ptr[-1])
-        out = {"status": np.zeros(n_reads, np.int32)}
+        out = {"status": self._z(n_reads, np.int32)}
         for k in ("qs", "qe", "al", "rstart", "rend", "nm"):
-            out[k] = np.zeros(ne, np.int64)
-        out["strand"] = np.zeros(ne, np.uint8); out["mapq"] = np.zeros(ne, np.int32); out["src"] = np.zeros(ne, np.uint32)
+            out[k] = self._z(ne, np.int64)
+        out["strand"] = self._z(ne, np.uint8); out["mapq"] = self._z(ne, np.int32); out["src"] = self._z(ne, np.uint32)
         self._check(self._L.coral_sa_text(
             self._h, text, ctypes.c_uint64(len(text)), ctypes.c_int64(n_reads), _p(ent_ptr), _p(ent_beg), _p(ent_end),
             _p(read_len), _p(out["status"]), _p(out["qs"]), _p(out["qe"]), _p(out["al"]), _p(out["rstart"]), _p(out["rend"]),
@@ -605,11 +768,11 @@ class Context(object):
         return out
 
     def _get_candidates(self, n):
-        out = {"n": n, "read": np.zeros(n, np.uint32)}
+        out = {"n": n, "read": self._z(n, np.uint32)}
         for k in ("i", "j", "chr1", "pos1", "chr2", "pos2", "rgap", "mq1", "mq2"):
-            out[k] = np.zeros(n, np.int32)
+            out[k] = self._z(n, np.int32)
         for k in ("o1", "o2", "flag"):
-            out[k] = np.zeros(n, np.uint8)
+            out[k] = self._z(n, np.uint8)
         if n:
             self._check(self._L.coral_get_candidates(
                 self._h, _p(out["read"]), _p(out["i"]), _p(out["j"]), _p(out["chr1"]), _p(out["pos1"]), _p(out["o1"]),

@@ -44,9 +44,11 @@ void coral_destroy(coral_ctx* c) {
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->scan_pending) coral_mem::scan_joined();
     c->scan_pending = false;
-    if (c->stream) cudaStreamSynchronize(c->stream);
+    // (an adopted stream belongs to another ctx that may already be gone: it is not touched here; the caller of
+    // coral_adopt_stream destroys this ctx before, or synchronises, the owner — sharded.py keeps the owner alive)
+    if (c->stream && c->owns_stream) cudaStreamSynchronize(c->stream);
     if (c->host_registered) cudaHostUnregister(c->host_registered);
-    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status, &c->scan_status, &c->sa_side, &c->sa_side_off, &c->xmsg[0], &c->xmsg[1], &c->xmsg[2],
+    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status, &c->scan_status, &c->sa_side, &c->sa_side_off, &c->xmsg[0], &c->xmsg[1], &c->xmsg[2], &c->xmsg[3],
                      &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->s6, &c->s7, &c->cub_tmp,
                      &c->rt.tid, &c->rt.pos, &c->rt.endpos, &c->rt.flag_mapq, &c->rt.lseq, &c->rt.ncig, &c->rt.infer,
                      &c->rt.mbases, &c->rt.nonacgt, &c->rt.fbs, &c->rt.lbe, &c->rt.name_lo, &c->rt.name_hi,
@@ -61,6 +63,8 @@ void coral_destroy(coral_ctx* c) {
     if (c->pass.lane_stream) { cudaStreamSynchronize(c->pass.lane_stream); cudaStreamDestroy(c->pass.lane_stream); }
     if (c->pass.ev_lane_begin) cudaEventDestroy(c->pass.ev_lane_begin);
     if (c->pass.ev_lane_done) cudaEventDestroy(c->pass.ev_lane_done);
+    if (c->pass.side_stream) { cudaStreamSynchronize(c->pass.side_stream); cudaStreamDestroy(c->pass.side_stream); }
+    for (cudaEvent_t e : c->pass.side_events) cudaEventDestroy(e);
     for (DevBuf& b : c->lane_s) b.release();
     c->lane_cub_tmp.release(); c->lane_status.release();
     for (auto& ch : c->pass.pinned) cudaFreeHost(ch.p);
@@ -94,6 +98,8 @@ int coral_set_params(coral_ctx* c, const coral_params* p) {
 int coral_set_option(coral_ctx* c, const char* name, int64_t value) {
     if (!c || !name) return CORAL_E_ARG;
     if (std::string(name) == "full_name_sort") { c->force_full_name_sort = value != 0; return CORAL_OK; }
+    if (std::string(name) == "fetch_part_world") { if (value < 1 || value > 16) return CORAL_E_ARG; c->fetch_part_world = (int32_t)value; c->pass.invalidate(); return CORAL_OK; }
+    if (std::string(name) == "fetch_part_rank") { if (value < 0 || value > 15) return CORAL_E_ARG; c->fetch_part_rank = (int32_t)value; c->pass.invalidate(); return CORAL_OK; }
     if (std::string(name) == "pass_fork") { c->pass.fork = value != 0; return CORAL_OK; }
     if (std::string(name) == "pass_scan_reserve") { c->pass.scan_reserve = value; return CORAL_OK; }
     if (std::string(name) == "pass_overlap_scan") { c->pass.overlap_scan = value != 0; c->pass.invalidate(); return CORAL_OK; }
@@ -195,6 +201,15 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
 
 void coral_release_cached_memory(void) { coral_mem::trim(); }
 
+// Page-locked host memory for result arrays: inside a pipelined pass a result copy into such an array is a direct DMA
+// (no staging buffer, no host memcpy when the pass ends).
+int coral_host_alloc(uint64_t nbytes, void** out) {
+    if (!out) return CORAL_E_ARG;
+    *out = nullptr;
+    return cudaHostAlloc(out, (size_t)std::max<uint64_t>(nbytes, 1), cudaHostAllocPortable) == cudaSuccess ? CORAL_OK : CORAL_E_NOMEM;
+}
+void coral_host_free(void* p) { if (p) cudaFreeHost(p); }
+
 // ---- streams of a ctx (for callers that enqueue their own work — NCCL collectives — between entry points of a pass) --
 uint64_t coral_stream_handle(coral_ctx* c, int which) {
     if (!c) return 0;
@@ -245,9 +260,10 @@ int coral_pass_begin(coral_ctx* c) {
     if (!c) return CORAL_E_ARG;
     PassState& P = c->pass;
     if (P.active) { c->err = "coral_pass_begin inside a pass"; return CORAL_E_STATE; }
-    if (!c->loaded) { c->err = "coral_pass_begin before coral_load_records"; return CORAL_E_STATE; }
+    // (a ctx without records may open a pass: the rows-only ctx of the multi-GPU engine is filled inside it by
+    // coral_unpack_rows; the entry points check what they need themselves)
     cudaSetDevice(c->device);
-    CORAL_TRY(coral_wait_scan(c));
+    if (c->loaded) CORAL_TRY(coral_wait_scan(c));
     if (!P.d_flag) CORAL_CUDA(c, cudaMalloc(reinterpret_cast<void**>(&P.d_flag), 64));
     CORAL_CUDA(c, cudaMemsetAsync(P.d_flag, 0, 64, c->stream));
     P.active = true;
@@ -260,6 +276,10 @@ int coral_pass_begin(coral_ctx* c) {
     P.n_events = 0;
     P.in_cur = 0;
     P.lane_started = false;
+    P.pending.clear();
+    P.n_side_events = 0;
+    P.side_on = P.side_used = false;
+    P.side_mask = 0;
     for (auto& ch : P.pinned) ch.used = 0;
     return CORAL_OK;
 }
@@ -276,6 +296,7 @@ int coral_pass_end(coral_ctx* c, int32_t* replayed) {
         cudaStreamWaitEvent(c->stream, P.ev_lane_done, 0);
         P.lane_started = false;
     }
+    coral::pass_flush_checks(c);
     P.active = false;
     uint32_t bad = 0;
     uint32_t* bad_pinned = reinterpret_cast<uint32_t*>(coral::pass_stage(c, 64));
@@ -293,6 +314,7 @@ int coral_pass_end(coral_ctx* c, int32_t* replayed) {
         }
     }
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess && P.side_used) e = cudaStreamSynchronize(P.side_stream);
     if (e == cudaSuccess) bad = *bad_pinned;
     if (e != cudaSuccess) {
         P.invalidate(); P.copies.clear(); P.after.clear();
@@ -339,6 +361,20 @@ float coral_stage_ms(coral_ctx* c, int stage) {
     return ms;
 }
 
+// All stage times of the most recent runs in one call (out[CORAL_N_STAGES], < 0 where a stage has not run).
+int coral_stage_ms_all(coral_ctx* c, float* out) {
+    if (!c || !out) return CORAL_E_ARG;
+    cudaSetDevice(c->device);
+    for (int s = 0; s < CORAL_N_STAGES; s++) {
+        out[s] = -1.f;
+        if (!c->ev_valid[s]) continue;
+        if (cudaEventSynchronize(c->ev_end[s]) != cudaSuccess) continue;
+        float ms = -1.f;
+        if (cudaEventElapsedTime(&ms, c->ev_beg[s], c->ev_end[s]) == cudaSuccess) out[s] = ms; else cudaGetLastError();
+    }
+    return CORAL_OK;
+}
+
 // Time from one stage event to another (begin: which = 0, end: which = 1), across the ctx's streams: where the stages
 // of a pipelined pass sit relative to the scan running next to them.  < 0 when an event is missing.
 float coral_stage_offset_ms(coral_ctx* c, int stage_a, int which_a, int stage_b, int which_b) {
@@ -364,6 +400,16 @@ int coral_region_coverage(coral_ctx* c, const int32_t* tid, const int32_t* start
     if (c->rows_only) { c->err = "coral_region_coverage on a rows-only ctx"; return CORAL_E_STATE; }
     cudaSetDevice(c->device);
     return coral_run_region_coverage(c, tid, start, stop, n, base_sum, rec_count);
+}
+
+// Sharded form: the sums over ALL shards of the file (in-place integer all-reduce of the accumulators over peer
+// memory between the kernels and the result copy); every rank calls it with the same regions.
+int coral_region_coverage_sharded(coral_ctx* c, coral_xchg* x, int32_t channel, const int32_t* tid, const int32_t* start,
+                                  const int32_t* stop, int32_t n, int64_t* base_sum, int64_t* rec_count) {
+    if (!c || !x) return CORAL_E_ARG;
+    if (c->rows_only) { c->err = "coral_region_coverage_sharded on a rows-only ctx"; return CORAL_E_STATE; }
+    cudaSetDevice(c->device);
+    return coral_run_region_coverage(c, tid, start, stop, n, base_sum, rec_count, x, channel);
 }
 
 }  // extern "C"

@@ -252,6 +252,7 @@ extern "C" int coral_smalldel(coral_ctx* c, const int32_t* tid, const int32_t* s
     cudaSetDevice(c->device);
     SmallDelTable& T = c->sdel;
     T.valid = false; T.n = 0;
+    CORAL_TRY(pass_side_join(c, SIDE_SDEL));
     const int64_t n_ev = c->gaps.n;
     if (n_rows) *n_rows = 0;
     if (c->pass.active) pass_call(c, interval_key("smalldel", tid, start, end_incl, n_intervals));
@@ -304,6 +305,7 @@ extern "C" int coral_get_smalldel(coral_ctx* c, uint32_t* rec, int32_t* ai, int3
     cudaSetDevice(c->device);
     SmallDelTable& T = c->sdel;
     const size_t n = (size_t)T.n;
+    if (n) CORAL_TRY(pass_side_begin(c, SIDE_SDEL));   // the table stays as it is until the next coral_smalldel
     if (rec) CORAL_TRY(d2h_result(c, rec, T.rec.p, n));
     if (ai) CORAL_TRY(d2h_result(c, ai, T.ai.p, n));
     if (next_start) CORAL_TRY(d2h_result(c, next_start, T.next_start.p, n));
@@ -323,6 +325,7 @@ extern "C" int coral_candidates_l(coral_ctx* c, const int32_t* tid, const int32_
     cudaSetDevice(c->device);
     CandTable& T = c->cand;
     T.valid = false; T.n = 0;
+    CORAL_TRY(pass_side_join(c, SIDE_CAND));
     if (n_cand) *n_cand = 0;
     ChimericTable& H = c->chim;
     const int64_t nr = H.n_reads;
@@ -378,6 +381,7 @@ extern "C" int coral_get_candidates(coral_ctx* c, uint32_t* read, int32_t* i, in
     cudaSetDevice(c->device);
     CandTable& T = c->cand;
     const size_t n = (size_t)T.n;
+    if (n) CORAL_TRY(pass_side_begin(c, SIDE_CAND));   // the table stays as it is until the next coral_candidates_*
     if (read) CORAL_TRY(d2h_result(c, read, T.read.p, n));
     if (i) CORAL_TRY(d2h_result(c, i, T.i.p, n));
     if (j) CORAL_TRY(d2h_result(c, j, T.j.p, n));
@@ -403,6 +407,7 @@ extern "C" int coral_set_chimeric(coral_ctx* c, int64_t n_reads, const uint32_t*
     cudaSetDevice(c->device);
     ChimericTable& T = c->chim;
     T.valid = false;
+    CORAL_TRY(pass_side_join(c, SIDE_CHIM));
     const size_t nr = (size_t)n_reads, na = aln_ptr[n_reads];
     const size_t na1 = std::max<size_t>(na, 1), nr1 = std::max<size_t>(nr, 1);
     CORAL_CUDA(c, T.aln_ptr.ensure((nr + 1) * 4)); CORAL_CUDA(c, T.read_status.ensure(nr1 * 4));
@@ -432,6 +437,7 @@ extern "C" int coral_candidates_pair(coral_ctx* c, const uint32_t* reads, int64_
     cudaSetDevice(c->device);
     CandTable& T = c->cand;
     T.valid = false; T.n = 0;
+    CORAL_TRY(pass_side_join(c, SIDE_CAND));
     if (n_cand) *n_cand = 0;
     ChimericTable& H = c->chim;
     if (c->pass.active) {

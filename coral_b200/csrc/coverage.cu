@@ -79,14 +79,43 @@ __global__ void k_region_cov_fast(int64_t n, const int32_t* __restrict__ tid, co
 }
 
 // Exact walk for (record, region) pairs: clipped M/=/X overlap minus non-ACGT aligned query bases.
-__global__ void k_region_cov_slow(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off,
-                                  const uint32_t* __restrict__ slow_rec, const int32_t* __restrict__ slow_reg,
-                                  int64_t n_pairs, const uint32_t* __restrict__ nonacgt, Regions R,
-                                  unsigned long long* base_sum) {
+// One block (8 warps) per pair.  A 30 kb ONT read carries thousands of CIGAR ops and the position of an op depends on
+// all ops before it, so a single warp walking the whole CIGAR is a long dependent chain (the first version: 110-145 us
+// for a few thousand pairs, latency-bound).  Here the CIGAR is cut into 8 slices: phase 1 sums the reference / query
+// advance of each slice (plain per-lane sums, one warp reduction per slice), a prefix over the 8 sums gives every
+// slice its start, and phase 2 runs the exact clipped walk only on the slices that overlap the region.
+// number of query bases in [q0, q0 + n) whose 4-bit code is not A/C/G/T (1, 2, 4, 8); eight bases per 32-bit word once
+// q is on a byte boundary (the order of the nibbles inside a word does not matter for a count)
+__device__ __forceinline__ uint32_t non_acgt_in_range(const uint8_t* __restrict__ seq, int64_t q0, int32_t n) {
+    uint32_t bad = 0;
+    int64_t q = q0;
+    const int64_t end = q0 + n;
+    if ((q & 1) && q < end) {
+        const uint32_t nib = seq[q >> 1] & 15u;
+        bad += !(nib == 1 || nib == 2 || nib == 4 || nib == 8);
+        q++;
+    }
+    for (; q + 8 <= end; q += 8)
+        bad += non_acgt_nibbles((uint64_t)ld_u32_any(seq + (q >> 1)) | 0x1111111100000000ull);
+    for (; q < end; q++) {
+        const uint32_t by = seq[q >> 1];
+        const uint32_t nib = (q & 1) ? (by & 15u) : (by >> 4);
+        bad += !(nib == 1 || nib == 2 || nib == 4 || nib == 8);
+    }
+    return bad;
+}
+
+constexpr int COV_WARPS = 8;
+__global__ void __launch_bounds__(COV_WARPS * 32)
+k_region_cov_slow(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off,
+                  const uint32_t* __restrict__ slow_rec, const int32_t* __restrict__ slow_reg,
+                  int64_t n_pairs, const uint32_t* __restrict__ nonacgt, Regions R,
+                  unsigned long long* base_sum) {
+    __shared__ int32_t s_ref[COV_WARPS];
+    __shared__ long long s_q[COV_WARPS];
     const uint32_t lane = lane_id();
-    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (; w < n_pairs; w += nw) {
+    const uint32_t warp = threadIdx.x >> 5;
+    for (int64_t w = blockIdx.x; w < n_pairs; w += gridDim.x) {
         const uint32_t rec = slow_rec[w];
         const int32_t ri = slow_reg[w];
         const int32_t rs = R.start[ri], re = R.stop[ri];
@@ -97,63 +126,73 @@ __global__ void k_region_cov_slow(const uint8_t* __restrict__ recs, const uint64
         const uint8_t* cig = r + 36 + l_name;
         const uint8_t* seq = cig + 4ull * n_cig;
         const bool check_seq = nonacgt[rec] != 0;
+        const uint32_t per = ((n_cig + COV_WARPS * 32 - 1) / (COV_WARPS * 32)) * 32;    // ops per slice, a multiple of 32
+        const uint32_t b0 = min(warp * per, n_cig), b1 = min(b0 + per, n_cig);
+        // phase 1: advance of this slice
+        int32_t rsum = 0;
+        long long qsum = 0;
+        for (uint32_t k = b0 + lane; k < b1; k += 32) {
+            const uint32_t v = ld_u32_any(cig + 4ull * k);
+            const uint32_t op = v & 15u;
+            const int32_t len = (int32_t)(v >> 4);
+            const bool is_m = (op == 0 || op == 7 || op == 8);
+            rsum += (is_m || op == 2 || op == 3) ? len : 0;
+            qsum += (is_m || op == 1 || op == 4) ? len : 0;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            rsum += __shfl_xor_sync(FULL_MASK, rsum, d);
+            qsum += __shfl_xor_sync(FULL_MASK, qsum, d);
+        }
+        if (lane == 0) { s_ref[warp] = rsum; s_q[warp] = qsum; }
+        __syncthreads();
         int32_t refpos = pos;
         int64_t qpos = 0;
+        for (uint32_t k = 0; k < warp; k++) { refpos += s_ref[k]; qpos += s_q[k]; }
         unsigned long long total = 0;
-        // 4 chunks of 32 ops per trip: the four loads are issued together (the walk is latency-bound), and the walk
-        // stops once the region's end is behind the reference position
-        for (uint32_t base = 0; base < n_cig && refpos < re; base += 128) {
-            uint32_t vv[4];
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const uint32_t k = base + 32u * u + lane;
-                vv[u] = (k < n_cig) ? ld_u32_any(cig + 4ull * k) : 0xFu;
-            }
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const uint32_t v = vv[u];
+        // phase 2: only slices that overlap [rs, re)
+        if (b0 < b1 && refpos < re && refpos + rsum > rs) {
+            for (uint32_t base = b0; base < b1 && refpos < re; base += 32) {
+                const uint32_t k = base + lane;
+                const uint32_t v = (k < b1) ? ld_u32_any(cig + 4ull * k) : 0xFu;
                 const uint32_t op = v & 15u;
                 const int32_t len = (int32_t)(v >> 4);
                 const bool is_m = (op == 0 || op == 7 || op == 8);
                 const int32_t rlen = (is_m || op == 2 || op == 3) ? len : 0;
                 const int32_t qlen = (is_m || op == 1 || op == 4) ? len : 0;
                 const int32_t ri_incl = warp_incl_sum_i32(rlen);
-                const int32_t qi_incl = warp_incl_sum_i32(qlen);
+                int32_t qi_incl = 0;
+                if (check_seq) qi_incl = warp_incl_sum_i32(qlen);      // query offsets only matter for the non-ACGT test
                 if (is_m) {
                     const int32_t s = refpos + ri_incl - rlen;
                     const int32_t a = max(s, rs), b = min(s + len, re);
                     if (b > a) {
                         total += (unsigned long long)(b - a);
                         if (check_seq) {
-                            int64_t q0 = qpos + (qi_incl - qlen) + (a - s);
-                            for (int32_t x = 0; x < b - a; x++) {
-                                int64_t q = q0 + x;
-                                uint32_t by = seq[q >> 1];
-                                uint32_t nib = (q & 1) ? (by & 15u) : (by >> 4);
-                                if (!(nib == 1 || nib == 2 || nib == 4 || nib == 8)) total -= 1;
-                            }
+                            total -= non_acgt_in_range(seq, qpos + (qi_incl - qlen) + (a - s), b - a);
                         }
                     }
                 }
                 refpos += __shfl_sync(FULL_MASK, ri_incl, 31);
-                qpos += __shfl_sync(FULL_MASK, qi_incl, 31);
+                if (check_seq) qpos += __shfl_sync(FULL_MASK, qi_incl, 31);
             }
         }
         total = warp_sum_u64(total);
         if (lane == 0 && total) atomicAdd(base_sum + ri, total);
+        __syncthreads();          // s_ref / s_q are reused by the next pair
     }
 }
 
 }  // namespace coral
 
 int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
-                              int32_t n, int64_t* base_sum, int64_t* rec_count) {
+                              int32_t n, int64_t* base_sum, int64_t* rec_count, coral_xchg* xchg, int xchg_channel) {
     using namespace coral;
     if (!ctx->loaded) { ctx->err = "coral_region_coverage before coral_load_records"; return CORAL_E_STATE; }
     CORAL_TRY(coral_wait_scan(ctx));
     if (n < 0) { ctx->err = "negative region count"; return CORAL_E_ARG; }
     if (ctx->pass.active) {
-        uint64_t k = pass_hash(PASS_H0, "region_coverage", 15);
+        uint64_t k = pass_hash(PASS_H0, xchg ? "region_coverage_x" : "region_coverage", xchg ? 17 : 15);
         k = pass_hash(k, &n, 4);
         if (n > 0) { k = pass_hash(k, tid, (size_t)n * 4); k = pass_hash(k, start, (size_t)n * 4); k = pass_hash(k, stop, (size_t)n * 4); }
         pass_call(ctx, k);
@@ -199,9 +238,7 @@ int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t*
         CORAL_TRY(pass_resolve(ctx, &n_slow, d_slow_n));
         if ((int64_t)n_slow > slow_cap) { slow_cap = (int64_t)n_slow + 1024; continue; }
         if (n_slow) {
-            const int64_t warps_per_block = 8;
-            int sblocks = (int)std::min<int64_t>(((int64_t)n_slow + warps_per_block - 1) / warps_per_block,
-                                                 (int64_t)ctx->sm_count * 8);
+            int sblocks = (int)std::min<int64_t>((int64_t)n_slow, (int64_t)ctx->sm_count * 8);
             k_region_cov_slow<<<sblocks, 256, 0, st>>>(ctx->d_recs, ctx->d_off.as<uint64_t>(), ctx->s2.as<uint32_t>(),
                                                        ctx->s3.as<int32_t>(), (int64_t)n_slow, t.nonacgt.as<uint32_t>(),
                                                        R, d_sum);
@@ -211,6 +248,9 @@ int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t*
         break;
     }
     ctx->stage_end(CORAL_STAGE_COVERAGE);
+    // sharded form: a record is owned by exactly one shard, so the sums over the file are the integer sums of the
+    // shards' accumulators (both arrays are contiguous), added up in place over peer memory (xchg.cu)
+    if (xchg) CORAL_TRY(coral_xchg_sum_device(ctx, xchg, xchg_channel, d_sum, 2 * (int64_t)n));
     // (the sums are below 2^63: the same 64 bits as the caller's int64)
     if (base_sum) CORAL_TRY(d2h_result(ctx, reinterpret_cast<unsigned long long*>(base_sum), d_sum, (size_t)n));
     if (rec_count) CORAL_TRY(d2h_result(ctx, reinterpret_cast<unsigned long long*>(rec_count), d_cnt, (size_t)n));
@@ -327,7 +367,7 @@ extern "C" int coral_region_coverage_static(coral_ctx* ctx, const int32_t* tid, 
             return CORAL_E_ARG;
         }
         if (n_slow) {
-            int sblocks = (int)std::min<int64_t>(((int64_t)n_slow + 7) / 8, (int64_t)ctx->sm_count * 8);
+            int sblocks = (int)std::min<int64_t>((int64_t)n_slow, (int64_t)ctx->sm_count * 8);
             k_region_cov_slow<<<sblocks, 256, 0, st>>>(ctx->d_recs, ctx->d_off.as<uint64_t>(), d_slow_rec, d_slow_reg,
                                                        (int64_t)n_slow, t.nonacgt.as<uint32_t>(), R, d_sum);
             ctx->n_launches++;

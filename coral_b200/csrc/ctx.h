@@ -205,6 +205,15 @@ struct PassState {
     struct Input { void* p = nullptr; size_t cap = 0, bytes = 0; };
     std::vector<Input> inputs;
     size_t in_cur = 0;
+    // checks of replayed values that may wait until the end of the entry point that resolved them (one kernel for all)
+    struct Pending { const void* d; unsigned long long expect; int nbytes; };
+    std::vector<Pending> pending;
+    // result copies of tables nothing overwrites before the pass ends run on a side stream, off the critical path
+    cudaStream_t side_stream = nullptr;
+    std::vector<cudaEvent_t> side_events;
+    size_t n_side_events = 0;
+    bool side_on = false, side_used = false;
+    int side_mask = 0;                         // tables with result copies on the side stream (relops.cuh SIDE_*)
     uint32_t* d_flag = nullptr;                // device: number of replayed values the device disagreed with
     uint64_t n_replayed = 0;                   // statistics: passes that ran without intermediate synchronisation
     void invalidate() { vals.clear(); keys.clear(); complete = false; for (auto& i : inputs) i.bytes = 0; }
@@ -233,6 +242,7 @@ struct coral_ctx {
     bool has_ordinal = false;
     bool force_full_name_sort = false;   // test hook: take the 128-bit name sort of coral_fetch (its fallback path)
     bool rows_only = false;   // ctx was filled by coral_load_rows: only fetch / candidates / cluster are valid
+    int32_t fetch_part_rank = 0, fetch_part_world = 1;   // options "fetch_part_rank" / "fetch_part_world" (see coral_set_option)
 
     RecordTable rt;
     GapEvents gaps;
@@ -257,7 +267,7 @@ struct coral_ctx {
     bool ing_ready = false;
     int ing_serial_chase = 0;      // 1 when the last ingest had to fall back to the serial chase
     DevBuf ing_comp, ing_stream, ing_recs, ing_w[8];
-    DevBuf xmsg[3];  // packed exchange messages (SA rows, extra primaries, concordant rows): live until the next pack
+    DevBuf xmsg[4];  // packed exchange messages (SA rows / chimeric table, extra primaries, concordant rows, small-deletion rows): live until the next pack
     DevBuf status;  // int32[8] device status words (format errors etc.)
     DevBuf scan_status;   // the record scan's own status words (it may run next to other entry points)
     cudaStream_t scan_stream = nullptr;   // CORAL_RECORDS_HOST_MAPPED_ASYNC: the full scan runs here ...
@@ -297,4 +307,7 @@ int coral_start_scan_async(coral_ctx* ctx, bool launch_full_scan);
 int coral_start_scan_overlapped(coral_ctx* ctx);
 int coral_run_fetch(coral_ctx* ctx);
 int coral_run_region_coverage(coral_ctx* ctx, const int32_t* tid, const int32_t* start, const int32_t* stop,
-                              int32_t n, int64_t* base_sum, int64_t* rec_count);
+                              int32_t n, int64_t* base_sum, int64_t* rec_count, coral_xchg* xchg = nullptr,
+                              int xchg_channel = 0);
+int coral_nm_partials_device(coral_ctx* ctx, double** d_out4);
+int coral_xchg_sum_device(coral_ctx* ctx, coral_xchg* x, int channel, unsigned long long* d_words, int64_t n);

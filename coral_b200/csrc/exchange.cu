@@ -72,7 +72,11 @@ __global__ void k_pack_rows(int64_t n, const uint32_t* __restrict__ f, const uin
     for (uint32_t k = lane; k < sl; k += 32) text[t0 + name_len + k] = rec[so + k];
 }
 
-__global__ void k_write_hdr(MsgHdr* h, MsgHdr v) { *h = v; }
+// d_nm (nullable): the four nm_stats sums, reduced on the device (k_nm_reduce)
+__global__ void k_write_hdr(MsgHdr* h, MsgHdr v, const double* d_nm) {
+    if (d_nm) { v.nm_sum = d_nm[0]; v.nm_sq = d_nm[1]; v.nm_n = (int64_t)d_nm[2]; v.nm_zd = (int64_t)d_nm[3]; }
+    *h = v;
+}
 
 // ---- extra primaries: membership of local non-SA primaries in the gathered SA-name set ----------------------
 struct MsgSet {               // up to 16 ranks per call chunk is plenty for one node; more ranks loop on the host
@@ -219,7 +223,7 @@ int inclusive_sum_u32_to_u64(coral_ctx* c, const uint32_t* in, uint64_t* out, in
 }
 
 // message of the records flagged in c->s0 (uint32 per record): rows in file order + their text
-int pack_flagged(coral_ctx* c, int kind, MsgHdr hdr, DevBuf& msg, uint64_t* d_msg, uint64_t* nbytes) {
+int pack_flagged(coral_ctx* c, int kind, MsgHdr hdr, DevBuf& msg, uint64_t* d_msg, uint64_t* nbytes, const double* d_nm = nullptr) {
     const int64_t n = c->nrec;
     RecordTable& t = c->rt;
     uint32_t n_rows = 0;
@@ -233,15 +237,15 @@ int pack_flagged(coral_ctx* c, int kind, MsgHdr hdr, DevBuf& msg, uint64_t* d_ms
                   c->s1.as<uint32_t>());
         CORAL_TRY(inclusive_sum_u32(c, f, c->s2.as<uint32_t>(), n));
         CORAL_TRY(inclusive_sum_u32_to_u64(c, c->s1.as<uint32_t>(), c->s3.as<uint64_t>(), n));
-        CORAL_TRY(d2h(c, &n_rows, c->s2.as<uint32_t>() + (n - 1), 1));
-        CORAL_TRY(d2h(c, &text_bytes, c->s3.as<uint64_t>() + (n - 1), 1));
-        CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+        // the two sizes shape the message: read back (outside a pass / while recording) or replayed and checked
+        CORAL_TRY(pass_resolve(c, &n_rows, c->s2.as<uint32_t>() + (n - 1)));
+        CORAL_TRY(pass_resolve(c, &text_bytes, c->s3.as<uint64_t>() + (n - 1)));
     }
     const uint64_t body = sizeof(MsgHdr) + (uint64_t)n_rows * sizeof(RowMsg);
     const uint64_t total = body + ((text_bytes + 15) & ~(uint64_t)15);
     CORAL_CUDA(c, msg.ensure(total));
     hdr.n_rows = n_rows; hdr.text_bytes = text_bytes; hdr.kind = (uint64_t)kind; hdr.pad = 0;
-    k_write_hdr<<<1, 1, 0, c->stream>>>(msg.as<MsgHdr>(), hdr);
+    k_write_hdr<<<1, 1, 0, c->stream>>>(msg.as<MsgHdr>(), hdr, d_nm);
     c->n_launches++;
     if (total > body) CORAL_CUDA(c, cudaMemsetAsync(msg.as<uint8_t>() + total - 16, 0, 16, c->stream));
     if (n_rows) {
@@ -251,7 +255,7 @@ int pack_flagged(coral_ctx* c, int kind, MsgHdr hdr, DevBuf& msg, uint64_t* d_ms
         LAUNCH_1D(k_pack_rows, threads, n, f, c->s2.as<uint32_t>(), c->s3.as<uint64_t>(), c->s1.as<uint32_t>(), in,
                   reinterpret_cast<RowMsg*>(msg.as<uint8_t>() + sizeof(MsgHdr)), msg.as<uint8_t>() + body);
     }
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (!c->pass.active) CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
     if (d_msg) *d_msg = (uint64_t)reinterpret_cast<uintptr_t>(msg.p);
     if (nbytes) *nbytes = total;
     return CORAL_OK;
@@ -274,8 +278,8 @@ int read_msgs(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf, const uint64_
     c->n_launches++;
     CORAL_CUDA(c, cudaGetLastError());
     hdrs->resize((size_t)n_ranks);
-    CORAL_CUDA(c, cudaMemcpyAsync(hdrs->data(), c->s7.p, (size_t)words * 8, cudaMemcpyDeviceToHost, c->stream));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    static_assert(sizeof(MsgHdr) == 64, "8 words per header");
+    CORAL_TRY(pass_resolve_n(c, reinterpret_cast<uint64_t*>(hdrs->data()), c->s7.p, words));
     set->row0[0] = 0;
     for (int r = 0; r < n_ranks; r++) {
         if ((*hdrs)[r].kind != (uint64_t)kind) { c->err = "unexpected message kind in the gathered buffer"; return CORAL_E_FORMAT; }
@@ -294,6 +298,8 @@ int coral_pack_sa_rows(coral_ctx* c, uint64_t* d_msg, uint64_t* nbytes) {
     if (!c->loaded || c->rows_only) { c->err = "coral_pack_sa_rows needs a ctx with records"; return CORAL_E_STATE; }
     CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
+    coral::PassLane lane__(c);          // part of the chimeric chain: second lane inside a pipelined pass
+    if (c->pass.active) pass_call(c, pass_hash(PASS_H0, "pack_sa_rows", 12));
     const int64_t n = c->nrec;
     CORAL_CUDA(c, c->s0.ensure((size_t)std::max<int64_t>(n, 1) * 4));
     LAUNCH_1D(k_flag_has_sa, n, n, c->rt.sa_off.as<uint32_t>(), c->s0.as<uint32_t>());
@@ -310,6 +316,12 @@ int coral_pack_extra_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf, c
     if (!c->loaded || c->rows_only) { c->err = "coral_pack_extra_rows needs a ctx with records"; return CORAL_E_STATE; }
     CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
+    coral::PassLane lane__(c);
+    if (c->pass.active) {
+        uint64_t k = pass_hash(PASS_H0, "pack_extra_rows", 15);
+        k = pass_hash(k, &n_ranks, 4);
+        pass_call(c, pass_hash(k, starts, (size_t)std::max(n_ranks, 0) * 8));
+    }
     MsgSet set;
     std::vector<MsgHdr> hdrs;
     CORAL_TRY(read_msgs(c, n_ranks, d_buf, starts, MSG_SA, &set, &hdrs));
@@ -333,8 +345,10 @@ int coral_pack_extra_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf, c
         CORAL_CUDA(c, cudaMemsetAsync(c->s0.p, 0, (size_t)n * 4, c->stream));
     }
     MsgHdr h{};
-    CORAL_TRY(coral_nm_partials(c, &h.nm_sum, &h.nm_sq, &h.nm_n, &h.nm_zd));
-    return pack_flagged(c, MSG_EXTRA, h, c->xmsg[1], d_msg, nbytes);
+    // this shard's nm_stats partial sums (ibg:153-157) ride in the header: reduced on the device, written by k_write_hdr
+    double* d_nm = nullptr;
+    CORAL_TRY(coral_nm_partials_device(c, &d_nm));
+    return pack_flagged(c, MSG_EXTRA, h, c->xmsg[1], d_msg, nbytes, d_nm);
 }
 
 // Both gathered message sets -> the columns of a rows-only ctx (rows in global file order: rank order, then record
@@ -344,6 +358,12 @@ int coral_unpack_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf1, cons
                       int64_t* n_rows_out) {
     if (!c || !d_buf1 || !starts1 || !d_buf2 || !starts2) return CORAL_E_ARG;
     cudaSetDevice(c->device);
+    if (c->pass.active) {
+        uint64_t k = pass_hash(PASS_H0, "unpack_rows", 11);
+        k = pass_hash(k, &n_ranks, 4);
+        k = pass_hash(k, starts1, (size_t)std::max(n_ranks, 0) * 8);
+        pass_call(c, pass_hash(k, starts2, (size_t)std::max(n_ranks, 0) * 8));
+    }
     UnpackPlan p;
     std::vector<MsgHdr> h1, h2;
     CORAL_TRY(read_msgs(c, n_ranks, d_buf1, starts1, MSG_SA, &p.sa, &h1));
@@ -383,7 +403,7 @@ int coral_unpack_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf1, cons
     for (DevBuf* b : b8) CORAL_CUDA(c, b->ensure(n8));
     DevBuf* b4[] = {&t.flag_mapq, &t.lseq, &t.nm, &t.sa_off, &t.sa_len};
     for (DevBuf* b : b4) CORAL_CUDA(c, b->ensure(n4));
-    CORAL_CUDA(c, cudaMemcpyAsync(c->d_off.as<uint64_t>() + n, &text, 8, cudaMemcpyHostToDevice, c->stream));
+    CORAL_TRY(h2d(c, c->d_off.as<uint64_t>() + n, &text, 1));
     RowCols o{c->d_off.as<uint64_t>(), t.name_lo.as<uint64_t>(), t.name_hi.as<uint64_t>(), t.flag_mapq.as<uint32_t>(),
               t.lseq.as<uint32_t>(), t.sa_off.as<uint32_t>(), t.sa_len.as<uint32_t>(), t.nm.as<int32_t>()};
     LAUNCH_1D(k_unpack_rows, n, p, o);
@@ -398,7 +418,7 @@ int coral_unpack_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf1, cons
     CORAL_CUDA(c, c->status.ensure(64));
     CORAL_CUDA(c, cudaMemsetAsync(c->status.p, 0, 64, c->stream));
     CORAL_CUDA(c, c->gaps.counter.ensure(16));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (!c->pass.active) CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
     c->loaded = true;
     if (n_rows_out) *n_rows_out = n;
     return CORAL_OK;

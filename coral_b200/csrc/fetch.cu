@@ -20,9 +20,13 @@
 namespace coral {
 
 // ---- 1. ------------------------------------------------------------------------------------------
-__global__ void k_flag_sa(int64_t n, const uint32_t* __restrict__ sa_off, uint8_t* __restrict__ flag) {
+// part_world > 1 (rows-only ctx of the multi-GPU engine): this rank only parses the reads whose name hash falls into
+// its residue class — every rank holds all gathered rows, the reads are split N ways, the parsed tables are merged
+// (chimeric_merge.cu)
+__global__ void k_flag_sa(int64_t n, const uint32_t* __restrict__ sa_off, const uint64_t* __restrict__ name_lo,
+                          uint32_t part_rank, uint32_t part_world, uint8_t* __restrict__ flag) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) flag[i] = sa_off[i] != 0;
+    if (i < n) flag[i] = sa_off[i] != 0 && (part_world <= 1 || (uint32_t)((name_lo[i] >> 20) % part_world) == part_rank);
 }
 
 // warp per SA record: number of entries of s[:-1].split(';')
@@ -163,10 +167,13 @@ __global__ void k_parse_entries(const uint8_t* __restrict__ recs, const uint64_t
 }
 
 // ---- 4. ------------------------------------------------------------------------------------------
+// iota (nullable): also writes the identity permutation (saves a launch before the first sort)
 __global__ void k_gather_name(int64_t n, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
-                              const uint64_t* __restrict__ name, uint64_t* __restrict__ key) {
+                              const uint64_t* __restrict__ name, uint64_t* __restrict__ key, uint32_t* __restrict__ iota) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) key[i] = name[ent[perm ? perm[i] : i].rec];
+    if (i >= n) return;
+    key[i] = name[ent[perm ? perm[i] : i].rec];
+    if (iota) iota[i] = (uint32_t)i;
 }
 __global__ void k_iota(int64_t n, uint32_t* p) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -371,6 +378,24 @@ __global__ void k_nm_stats(int64_t n, const uint32_t* __restrict__ sa_off, const
     }
 }
 
+// per-block partial sums of k_nm_stats (4 doubles per block) -> 4 totals, in a fixed order (thread t takes blocks t,
+// t + 256, ... in increasing order, then a tree): deterministic, and within rounding of the host's serial sum
+__global__ void k_nm_reduce(const double* __restrict__ part, int64_t nblk, double* __restrict__ out) {
+    __shared__ double s[4][256];
+    double a[4] = {0, 0, 0, 0};
+    for (int64_t b = threadIdx.x; b < nblk; b += 256)
+        for (int k = 0; k < 4; k++) a[k] += part[4 * b + k];
+    for (int k = 0; k < 4; k++) s[k][threadIdx.x] = a[k];
+    __syncthreads();
+    for (int d = 128; d > 0; d >>= 1) {
+        if ((int)threadIdx.x < d)
+            for (int k = 0; k < 4; k++) s[k][threadIdx.x] += s[k][threadIdx.x + d];
+        __syncthreads();
+    }
+    if (threadIdx.x < 4) out[threadIdx.x] = s[threadIdx.x][0];
+}
+
+
 }  // namespace coral
 
 // ---- host orchestration ----------------------------------------------------------------------------
@@ -397,9 +422,13 @@ int coral_run_fetch(coral_ctx* c) {
     if (c->ref_names.empty()) { c->err = "coral_fetch before coral_set_references"; return CORAL_E_STATE; }
     ChimericTable& T = c->chim;
     T.valid = false; T.n_reads = 0; T.n_aln = 0;
+    CORAL_TRY(pass_side_join(c, SIDE_CHIM));
     const int64_t n = c->nrec;
     RecordTable& rt = c->rt;
-    if (c->pass.active) pass_call(c, pass_hash(PASS_H0, "fetch", 5));
+    if (c->pass.active) {
+        const int32_t part[2] = {c->fetch_part_rank, c->fetch_part_world};
+        pass_call(c, pass_hash(pass_hash(PASS_H0, "fetch", 5), part, 8));
+    }
     // where the SA strings are read from: the records, or — after a pre-scan (asynchronous / lazy placements) — its
     // side copy in HBM, addressed through per-record offsets chosen so that base + offset + sa_off is the copy
     const uint8_t* recs = c->sa_side_valid ? c->sa_side.as<uint8_t>() : c->d_recs;
@@ -422,14 +451,15 @@ int coral_run_fetch(coral_ctx* c) {
     uint8_t* d_flag = c->s0.as<uint8_t>();
     uint32_t* d_sa_rec = c->s1.as<uint32_t>();
     uint32_t* d_cnt = d_sa_rec + std::max<int64_t>(n, 1);
-    LAUNCH_1D(k_flag_sa, n, n, rt.sa_off.as<uint32_t>(), d_flag);
+    LAUNCH_1D(k_flag_sa, n, n, rt.sa_off.as<uint32_t>(), rt.name_lo.as<uint64_t>(), (uint32_t)c->fetch_part_rank,
+              (uint32_t)c->fetch_part_world, d_flag);
     CORAL_TRY(select_flagged_iota(c, d_flag, d_sa_rec, d_cnt, n));
     uint32_t n_sa = 0;
     // the per-block partial sums are a RESULT (inside a pipelined pass they arrive at coral_pass_end) ...
     auto part = std::make_shared<std::vector<double>>((size_t)std::max<int64_t>(nblk, 1) * 4, 0.0);
     CORAL_TRY(d2h_result(c, part->data(), c->s7.p, (size_t)nblk * 4));
     // ... the number of SA-bearing records sizes the launches below
-    CORAL_TRY(pass_resolve(c, &n_sa, d_cnt));
+    CORAL_TRY(pass_resolve_lazy(c, &n_sa, d_cnt));
     CORAL_TRY(pass_after(c, [c, part, nblk]() {
         ChimericTable& T = c->chim;
         T.nm_sum = T.nm_sq = 0; T.nm_n = 0; T.nm_zero_div = 0;
@@ -439,7 +469,7 @@ int coral_run_fetch(coral_ctx* c) {
         }
         return CORAL_OK;
     }));
-    if (n_sa == 0) { T.valid = true; c->stage_end(CORAL_STAGE_FETCH); return CORAL_OK; }
+    if (n_sa == 0) { CORAL_TRY(pass_flush_checks(c)); T.valid = true; c->stage_end(CORAL_STAGE_FETCH); return CORAL_OK; }
 
     // entries per SA record -> bases
     CORAL_CUDA(c, c->s2.ensure((size_t)(n_sa + 1) * 8 + 16));
@@ -449,7 +479,7 @@ int coral_run_fetch(coral_ctx* c) {
     CORAL_CUDA(c, cudaMemsetAsync(d_nent + n_sa, 0, 4, c->stream));
     CORAL_TRY(exclusive_sum_u32(c, d_nent, d_base, (int64_t)n_sa + 1));
     uint32_t n_ent = 0;
-    CORAL_TRY(pass_resolve(c, &n_ent, d_base + n_sa));
+    CORAL_TRY(pass_resolve_lazy(c, &n_ent, d_base + n_sa));
 
     // 2-3. entry ranges + parse
     CORAL_CUDA(c, c->s3.ensure((size_t)n_ent * 12));
@@ -481,14 +511,13 @@ int coral_run_fetch(coral_ctx* c) {
     uint64_t name_key_mask = 0;
     for (int full = c->force_full_name_sort ? 1 : 0; full < 2; full++) {
         name_key_mask = full ? 0 : ((1ull << 40) - 1);
-        LAUNCH_1D(k_iota, (int64_t)n_ent, (int64_t)n_ent, perm_a);
-        LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, (const uint32_t*)nullptr, rt.name_lo.as<uint64_t>(), key_a);
+        LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, (const uint32_t*)nullptr, rt.name_lo.as<uint64_t>(), key_a, perm_a);
         if (!full) {
             CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_a, perm_b, n_ent, 0, 40));
             perm = perm_b;
         } else {
             CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_a, perm_b, n_ent));
-            LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, perm_b, rt.name_hi.as<uint64_t>(), key_a);
+            LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, perm_b, rt.name_hi.as<uint64_t>(), key_a, (uint32_t*)nullptr);
             CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_b, perm_a, n_ent));
             perm = perm_a;
         }
@@ -497,9 +526,10 @@ int coral_run_fetch(coral_ctx* c) {
                   full ? ~0ull : name_key_mask, head, d_mixed);
         CORAL_TRY(inclusive_sum_u32(c, head, head, n_ent));
         uint32_t mixed = 0;
-        CORAL_TRY(pass_resolve(c, &n_seg, head + n_ent - 1));
-        CORAL_TRY(pass_resolve(c, &mixed, d_mixed));
+        CORAL_TRY(pass_resolve_lazy(c, &n_seg, head + n_ent - 1));
+        CORAL_TRY(pass_resolve_lazy(c, &mixed, d_mixed));
         if (!mixed) break;
+        CORAL_TRY(pass_flush_checks(c));       // the second round overwrites what the noted checks read
     }
     LAUNCH_1D(k_segments, (int64_t)n_ent, (int64_t)n_ent, ent, perm, head, seg_start, seg_of);
     LAUNCH_1D(k_mark_dups, (int64_t)n_ent, (int64_t)n_ent, ent, perm, seg_of, seg_start, keep);
@@ -529,12 +559,14 @@ int coral_run_fetch(coral_ctx* c) {
     uint32_t* cnt_ranked = seg_cnt + n_seg;
     LAUNCH_1D(k_read_counts, (int64_t)n_seg, (int64_t)n_seg, (int64_t)n_ent, ent, perm, seg_start, keep, first_primary, seg_status, seg_cnt);
     LAUNCH_1D(k_iota, (int64_t)n_seg, (int64_t)n_seg, seg_idx);
-    CORAL_TRY(sort_pairs_u64(c, seg_emit, seg_emit_sorted, seg_idx, order, n_seg, 0, 32));   // keys are entry indices
+    int emit_bits = 1;                                            // keys are entry indices < n_ent
+    while (emit_bits < 32 && ((uint64_t)1 << emit_bits) < (uint64_t)n_ent) emit_bits++;
+    CORAL_TRY(sort_pairs_u64(c, seg_emit, seg_emit_sorted, seg_idx, order, n_seg, 0, emit_bits));
     LAUNCH_1D(k_gather_u32, (int64_t)n_seg, (int64_t)n_seg, order, seg_cnt, cnt_ranked);
     CORAL_TRY(exclusive_sum_u32(c, cnt_ranked, T.aln_ptr.as<uint32_t>(), n_seg));
     uint32_t last_ptr = 0, last_cnt = 0;
-    CORAL_TRY(pass_resolve(c, &last_ptr, T.aln_ptr.as<uint32_t>() + n_seg - 1));
-    CORAL_TRY(pass_resolve(c, &last_cnt, cnt_ranked + n_seg - 1));
+    CORAL_TRY(pass_resolve_lazy(c, &last_ptr, T.aln_ptr.as<uint32_t>() + n_seg - 1));
+    CORAL_TRY(pass_resolve_lazy(c, &last_cnt, cnt_ranked + n_seg - 1));
     const uint32_t n_aln = last_ptr + last_cnt;
     const size_t na = std::max<uint32_t>(n_aln, 1);
     DevBuf* a4[] = {&T.qs, &T.qe, &T.tid, &T.rs, &T.re, &T.mapq};
@@ -546,11 +578,35 @@ int coral_run_fetch(coral_ctx* c) {
                T.re.as<int32_t>(), T.mapq.as<int32_t>(), T.strand.as<uint8_t>()};
     LAUNCH_1D(k_read_fill, (int64_t)n_seg, (int64_t)n_seg, (int64_t)n_ent, ent, perm, seg_start, keep, first_primary, seg_status, order,
               rt.lseq.as<uint32_t>(), n_aln, o);
+    CORAL_TRY(pass_flush_checks(c));           // one kernel for every size this call replayed
     c->stage_end(CORAL_STAGE_FETCH);
     CORAL_TRY(pass_sync(c));
     T.n_reads = n_seg;
     T.n_aln = n_aln;
     T.valid = true;
+    return CORAL_OK;
+}
+
+// Device form (the packed exchange): the four sums of this ctx's records, reduced on the device; *d_out = 4 doubles
+// (sum e, sum e^2, count, zero-division count) in ctx scratch, valid until the next use of s7 on this stream.
+int coral_nm_partials_device(coral_ctx* c, double** d_out) {
+    using namespace coral;
+    const int64_t n = c->nrec;
+    const int64_t nblk = (n + NM_BLOCK - 1) / NM_BLOCK;
+    RecordTable& rt = c->rt;
+    CORAL_CUDA(c, c->s7.ensure((size_t)std::max<int64_t>(nblk, 1) * 32 + 64));
+    double* part = c->s7.as<double>();
+    double* out = part + (size_t)std::max<int64_t>(nblk, 1) * 4;
+    if (n > 0) {
+        k_nm_stats<<<(unsigned)nblk, NM_BLOCK, 0, c->stream>>>(n, rt.sa_off.as<uint32_t>(), rt.flag_mapq.as<uint32_t>(),
+                                                              rt.tid.as<int32_t>(), rt.nm.as<int32_t>(), rt.lseq.as<uint32_t>(), part);
+        c->n_launches++;
+        CORAL_CUDA(c, cudaGetLastError());
+    }
+    k_nm_reduce<<<1, 256, 0, c->stream>>>(part, n > 0 ? nblk : 0, out);
+    c->n_launches++;
+    CORAL_CUDA(c, cudaGetLastError());
+    *d_out = out;
     return CORAL_OK;
 }
 
@@ -616,6 +672,7 @@ extern "C" int coral_get_chimeric(coral_ctx* c, uint32_t* read_first_rec, int64_
     ChimericTable& T = c->chim;
     const size_t nr = (size_t)T.n_reads, na = (size_t)T.n_aln;
     if (nr == 0) { if (aln_ptr) aln_ptr[0] = 0; return CORAL_OK; }
+    CORAL_TRY(pass_side_begin(c, SIDE_CHIM));  // the table stays as it is until the next coral_fetch / merge
     if (read_first_rec) CORAL_TRY(d2h_result(c, read_first_rec, T.read_first_rec.p, nr));
     if (read_len) CORAL_TRY(d2h_result(c, read_len, T.read_len.p, nr));
     if (read_status) CORAL_TRY(d2h_result(c, read_status, T.read_status.p, nr));

@@ -126,6 +126,44 @@ inline int pass_resolve(coral_ctx* c, T* out, const void* d_src) {
     return CORAL_OK;
 }
 
+// Lazy form for entry points whose resolved scalars stay untouched until the entry point returns: while replaying the
+// check is only noted, pass_flush_checks() launches ONE kernel for all noted values (every kernel on the critical path
+// of a pass costs microseconds whatever it does).  Must be flushed before the memory behind d_src is reused.
+struct PassChecks { const void* d[8]; unsigned long long expect[8]; int nbytes[8]; int n; };
+static __global__ void k_pass_check_multi(PassChecks a, uint32_t* flag) {
+    const int i = threadIdx.x;
+    if (i >= a.n) return;
+    const unsigned long long v = a.nbytes[i] == 8 ? *static_cast<const unsigned long long*>(a.d[i])
+                                                  : (unsigned long long)*static_cast<const uint32_t*>(a.d[i]);
+    if (v != a.expect[i]) atomicAdd(flag, 1u);
+}
+inline int pass_flush_checks(coral_ctx* c) {
+    PassState& P = c->pass;
+    for (size_t k = 0; k < P.pending.size(); k += 8) {
+        PassChecks a;
+        a.n = (int)std::min<size_t>(8, P.pending.size() - k);
+        for (int i = 0; i < a.n; i++) { a.d[i] = P.pending[k + i].d; a.expect[i] = P.pending[k + i].expect; a.nbytes[i] = P.pending[k + i].nbytes; }
+        k_pass_check_multi<<<1, 8, 0, c->stream>>>(a, P.d_flag);
+        c->n_launches++;
+    }
+    P.pending.clear();
+    return CORAL_OK;
+}
+template <class T>
+inline int pass_resolve_lazy(coral_ctx* c, T* out, const void* d_src) {
+    PassState& P = c->pass;
+    if (P.active && P.replay && P.cur < P.vals.size()) {
+        const uint64_t v = P.vals[P.cur++];
+        T t;
+        memcpy(&t, &v, sizeof(T));
+        *out = t;
+        P.pending.push_back(PassState::Pending{d_src, (unsigned long long)v, (int)sizeof(T)});
+        return CORAL_OK;
+    }
+    CORAL_TRY(pass_flush_checks(c));
+    return pass_resolve(c, out, d_src);
+}
+
 // Array form: n (<= 128) 8-byte words, one check kernel for all of them.
 struct PassWords { unsigned long long w[128]; };
 static __global__ void k_pass_check_n(const unsigned long long* d, PassWords expect, int n, uint32_t* flag) {
@@ -167,14 +205,61 @@ inline uint8_t* pass_stage(coral_ctx* c, size_t bytes) {          // page-locked
 }
 
 // Copy of a RESULT to the caller's array: now (the caller synchronises) or, inside a pass, at coral_pass_end.
+// From here to the next pass_sync() the result copies of a pass run on the pass's side stream, behind what the ctx's
+// stream holds now: for tables that nothing overwrites before the pass ends (the chimeric table, the candidate table,
+// the small-deletion and concordant rows), so that a dozen copy-engine operations do not sit between two kernels of the
+// critical path (measured: 80 us between the end of fetch and the first candidate kernel).
+enum { SIDE_CHIM = 1, SIDE_CAND = 2, SIDE_SDEL = 4, SIDE_STAB = 8 };
+inline int pass_side_event(coral_ctx* c, cudaEvent_t* out) {
+    PassState& P = c->pass;
+    if (P.n_side_events == P.side_events.size()) {
+        cudaEvent_t e;
+        CORAL_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        P.side_events.push_back(e);
+    }
+    *out = P.side_events[P.n_side_events++];
+    return CORAL_OK;
+}
+// An entry point that rewrites `table` while copies of it may still run on the side stream waits for them first.
+inline int pass_side_join(coral_ctx* c, int table) {
+    PassState& P = c->pass;
+    if (!P.active || !(P.side_mask & table)) return CORAL_OK;
+    cudaEvent_t e;
+    CORAL_TRY(pass_side_event(c, &e));
+    CORAL_CUDA(c, cudaEventRecord(e, P.side_stream));
+    CORAL_CUDA(c, cudaStreamWaitEvent(c->stream, e, 0));
+    P.side_mask = 0;
+    return CORAL_OK;
+}
+inline int pass_side_begin(coral_ctx* c, int table) {
+    PassState& P = c->pass;
+    if (!P.active) return CORAL_OK;
+    P.side_mask |= table;
+    if (!P.side_stream) CORAL_CUDA(c, cudaStreamCreateWithFlags(&P.side_stream, cudaStreamNonBlocking));
+    cudaEvent_t e;
+    CORAL_TRY(pass_side_event(c, &e));
+    CORAL_CUDA(c, cudaEventRecord(e, c->stream));
+    CORAL_CUDA(c, cudaStreamWaitEvent(P.side_stream, e, 0));
+    P.side_on = P.side_used = true;
+    return CORAL_OK;
+}
+
 template <class T>
 inline int d2h_result(coral_ctx* c, T* dst, const void* src, size_t n) {
     if (n == 0) return CORAL_OK;
     PassState& P = c->pass;
     if (P.active) {
+        // a page-locked destination (coral_host_alloc: what the Python binding hands out inside a pass when asked to)
+        // takes the copy directly: no staging buffer, no host memcpy at coral_pass_end
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, dst) == cudaSuccess && at.type == cudaMemoryTypeHost) {
+            CORAL_CUDA(c, cudaMemcpyAsync(dst, src, n * sizeof(T), cudaMemcpyDeviceToHost, P.side_on ? P.side_stream : c->stream));
+            return CORAL_OK;
+        }
+        cudaGetLastError();
         uint8_t* st = pass_stage(c, n * sizeof(T));
         if (!st) { c->err = "cudaHostAlloc failed for the pass staging buffer"; return CORAL_E_NOMEM; }
-        CORAL_CUDA(c, cudaMemcpyAsync(st, src, n * sizeof(T), cudaMemcpyDeviceToHost, c->stream));
+        CORAL_CUDA(c, cudaMemcpyAsync(st, src, n * sizeof(T), cudaMemcpyDeviceToHost, P.side_on ? P.side_stream : c->stream));
         P.copies.push_back(PassState::Copy{dst, st, n * sizeof(T), -1});
         return CORAL_OK;
     }
@@ -196,9 +281,10 @@ inline int pass_sync(coral_ctx* c) {
                 P.events.push_back(e);
             }
             const int g = (int)P.n_events++;
-            CORAL_CUDA(c, cudaEventRecord(P.events[g], c->stream));
+            CORAL_CUDA(c, cudaEventRecord(P.events[g], P.side_on ? P.side_stream : c->stream));
             for (size_t k = first; k < P.copies.size(); k++) P.copies[k].group = g;
         }
+        P.side_on = false;
         return CORAL_OK;
     }
     CORAL_CUDA(c, cudaStreamSynchronize(c->stream));

@@ -120,6 +120,7 @@ __global__ void k_name_count(int64_t n, const uint64_t* __restrict__ skey, const
     if ((m & 15u) == 15u && !(m & 16u) && (int64_t)me.edge < n_edges) atomicAdd(count + me.edge, 1ull);
 }
 
+__global__ void k_put_hdr(MsgHdr* h, MsgHdr v) { *h = v; }
 
 }  // namespace coral
 
@@ -166,6 +167,7 @@ extern "C" int coral_concordant(coral_ctx* c, const int32_t* tid, const int32_t*
     CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
     c->stab_n = 0; c->stab_valid = false;
+    CORAL_TRY(pass_side_join(c, SIDE_STAB));
     if (n_union_rows) *n_union_rows = 0;
     if (c->pass.active) {
         uint64_t k = pass_hash(PASS_H0, lr_count ? "concordant" : "concordant_rows", lr_count ? 10 : 15);
@@ -240,6 +242,7 @@ extern "C" int coral_get_concordant_rows(coral_ctx* c, uint32_t* edge, uint32_t*
     cudaSetDevice(c->device);
     const size_t n = (size_t)c->stab_n;
     if (n == 0) return CORAL_OK;
+    CORAL_TRY(pass_side_begin(c, SIDE_STAB));  // the rows stay as they are until the next coral_concordant
     if (edge) CORAL_TRY(d2h_result(c, edge, c->sw[3].p, n));
     if (rec) CORAL_TRY(d2h_result(c, rec, c->sw[4].p, n));
     if (mask) CORAL_TRY(d2h_result(c, mask, c->sw[5].p, n));
@@ -257,13 +260,15 @@ extern "C" int coral_concordant_pack(coral_ctx* c, uint64_t* d_msg, uint64_t* nb
     const uint64_t total = sizeof(MsgHdr) + (uint64_t)n * sizeof(NameRow);
     DevBuf& msg = c->xmsg[2];
     CORAL_CUDA(c, msg.ensure(total));
+    if (c->pass.active) pass_call(c, pass_hash(PASS_H0, "concordant_pack", 15));
     MsgHdr h{};
     h.n_rows = (uint64_t)n; h.kind = MSG_NAMES;
-    CORAL_CUDA(c, cudaMemcpyAsync(msg.p, &h, sizeof h, cudaMemcpyHostToDevice, c->stream));
+    k_put_hdr<<<1, 1, 0, c->stream>>>(msg.as<MsgHdr>(), h);
+    c->n_launches++;
     RecordTable& rt = c->rt;
     LAUNCH_1D(k_name_rows, n, n, c->sw[3].as<uint32_t>(), c->sw[4].as<uint32_t>(), c->sw[5].as<uint32_t>(),
               rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(), reinterpret_cast<NameRow*>(msg.as<uint8_t>() + sizeof(MsgHdr)));
-    CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (!c->pass.active) CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
     *d_msg = (uint64_t)reinterpret_cast<uintptr_t>(msg.p);
     *nbytes = total;
     return CORAL_OK;

@@ -263,10 +263,89 @@ class _ShardView(object):
         pass
 
 
-def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", presharded=False):
+def make_xchg(comm, device, slot_bytes=None, timeout_s=None):
+    """This rank's exchange window over peer memory (csrc/xchg.cu), connected to the windows of all ranks of `comm`:
+    the IPC handles travel once over the comm (ranks that are threads of one process hand over plain addresses)."""
+    import os
+    from . import _abi
+    x = _abi.Xchg(device, comm.rank, comm.world, _abi.XCHG_DEFAULT_SLOTS if slot_bytes is None else slot_bytes)
+    if timeout_s is not None:
+        x.set_timeout(timeout_s)
+    h, ptr = x.handle()
+    allh = comm.all_gather((h, ptr, os.getpid()))
+    same = [a[1] if (a[2] == os.getpid() and r != comm.rank) else 0 for r, a in enumerate(allh)]
+    x.connect([a[0] for a in allh], same)
+    comm.all_gather(0)                 # nobody exchanges before everybody has connected
+    return x
+
+
+def close_xchg(comm, x):
+    comm.all_gather(0)                 # a peer may still be writing into this window
+    x.close()
+
+
+class _PeerTransport(object):
+    """All-gather of device messages as two kernels over peer memory (NVLink); nothing visits the host."""
+    name = "peer"
+
+    def __init__(self, xchg):
+        self.x = xchg
+
+    def gather(self, ctx, channel, ptr, nbytes, lane=False):
+        return ctx.xchg_allgather(self.x, channel, ptr, nbytes, lane)
+
+    def read(self, ctx, gathered, lane=False):
+        b, st, sz = gathered
+        return [ctx.read_device(b + int(o), int(n), lane) for o, n in zip(st, sz)]
+
+    def region_counts(self, eng, tid, start, stop):
+        from . import _abi
+        return eng._ctx.region_coverage_sharded(self.x, _abi.CH_COV, tid, start, stop)
+
+
+class _NcclTransport(object):
+    """The same exchanges through torch.distributed (NCCL on the box, gloo / thread ranks in tests): one collective per
+    exchange issued by the host, sizes read back.  The baseline the peer-memory transport is measured against."""
+    name = "nccl"
+
+    def __init__(self, comm, device):
+        from . import exchange
+        self._ex = exchange
+        self._comm = comm
+        self._tc = exchange.TensorComm(comm)
+        self._device = device
+        self._keep = []
+
+    def gather(self, ctx, channel, ptr, nbytes, lane=False):
+        import torch
+        buf, st, sz = self._tc.gather_msgs(self._ex.view(ptr, nbytes, "|u1", torch.device("cuda", self._device)))
+        self._keep = (self._keep + [buf])[-8:]          # the gathered buffers must outlive their consumers
+        return buf.data_ptr(), np.asarray(st, np.uint64), np.asarray(sz, np.uint64)
+
+    def read(self, ctx, gathered, lane=False):
+        b, st, sz = gathered
+        for buf in self._keep:
+            if buf.data_ptr() == b:
+                raw = buf.cpu().numpy()
+                return [raw[int(o):int(o) + int(n)] for o, n in zip(st, sz)]
+        raise RuntimeError("gathered buffer no longer held")
+
+    def region_counts(self, eng, tid, start, stop):
+        bs, rc = eng._ctx.region_coverage(tid, start, stop)
+        tot = self._comm.all_reduce_sum(np.concatenate([bs, rc]).astype(np.int64))
+        return tot[:len(bs)], tot[len(bs):]
+
+
+_SDEL_ROW = np.dtype([("rec", "<u4"), ("ai", "<i4"), ("next_start", "<i4"), ("prev_end", "<i4"), ("first_start", "<i4"),
+                      ("last_end", "<i4"), ("mapq", "<i4"), ("pad", "<u4"), ("lo", "<i8"), ("hi", "<i8")])
+
+
+def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", presharded=False, xchg=None):
     """Factory (keeps the CUDA-bound import out of the CPU tests of the exchange logic).
     `records`: the whole file (every rank then takes its range of shard_ranges) or, with presharded=True, this rank's
-    own shard — ranks must hold increasing, contiguous ranges of one coordinate-sorted file."""
+    own shard — ranks must hold increasing, contiguous ranges of one coordinate-sorted file.
+    `xchg`: a connected exchange window (make_xchg): the exchanges then run as kernels over peer memory; without it they
+    go through torch.distributed collectives."""
     from . import _abi
     from .infer_breakpoint_graph import bam_to_breakpoint_nanopore
 
@@ -286,34 +365,29 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             bam_to_breakpoint_nanopore.__init__(self, None, seedfile, device=device, records=view, placement=placement)
             self._cctx = _abi.Context(device)          # rows-only ctx: the gathered fetch rows live here
             self._cctx.set_references(view.references)
+            # distributed fetch: every rank parses the reads of its residue class of the name hash, the partial tables are
+            # gathered and merged; the rows-only ctx runs on the second lane of the records ctx so that, inside a
+            # pipelined pass, its kernels are ordered with the packing kernels that feed them
+            self._cctx.set_option("fetch_part_world", comm.world)
+            self._cctx.set_option("fetch_part_rank", comm.rank)
+            self._cctx.set_option("pass_fork", 0)
+            self._cctx.adopt_stream(self._ctx.stream_handle(1))
+            self._cctx._stream_owner = self._ctx       # the adopted stream must outlive the ctx that runs on it
+            self._tp = _PeerTransport(xchg) if xchg is not None else _NcclTransport(comm, device)
+            self.materialise = True  # False: the replicated result tables stay on the device (ranks that only compute)
             self._row_names = None
             self._rbt = None
             self._edge_arrays = None
             self._name_hash = {}     # read name -> 128-bit hash as two int64 (for the rbps rows of the concordant combine)
-            self._tc = None
             self.fetch_laps = {}
 
         @property
         def _chim_ctx(self):
             return self._cctx
 
-        def _tcomm(self):
-            if self._tc is None:
-                from . import exchange
-                self._tc = exchange.TensorComm(self._comm)
-            return self._tc
-
-        def _gather(self, ptr, nbytes):
-            """All-gather of a device message the CUDA side packed -> (buffer, starts, sizes)."""
-            import torch
-            from . import exchange
-            return self._tcomm().gather_msgs(exchange.view(ptr, nbytes, "|u1", torch.device("cuda", device)))
-
-        # a12 / a10: additive over records -> integer all-reduce of the shard sums
+        # a12 / a10: additive over records -> integer sum of the shard accumulators
         def _region_counts(self, tid, start, stop):
-            bs, rc = self._ctx.region_coverage(tid, start, stop)
-            tot = self._comm.all_reduce_sum(np.concatenate([bs, rc]).astype(np.int64))
-            return tot[:len(bs)], tot[len(bs):]
+            return self._tp.region_counts(self, tid, start, stop)
 
         def _views(self):
             """Tensor views of this shard's name-hash columns (device memory owned by the ctx)."""
@@ -324,26 +398,37 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             dev = torch.device("cuda", device)
             return {"name_lo": exchange.view(p[2], n, "<i8", dev), "name_hi": exchange.view(p[3], n, "<i8", dev)}
 
-        # a1: the exchange, on the GPU.  Two packed messages per rank (csrc/exchange.cu), two all-gathers, and the
-        # gathered rows are unpacked straight into the rows-only ctx: nothing visits the host.
+        # a1: the exchange, on the GPU.  Two packed messages per rank (csrc/exchange.cu) are gathered and unpacked into
+        # the rows-only ctx, every rank parses its share of the reads, the partial tables are gathered and merged
+        # (csrc/chimeric_merge.cu): nothing visits the host.
         def _run_fetch(self):
             import time
-            ctx, cctx = self._ctx, self._cctx
+            ctx, cctx, tp = self._ctx, self._cctx, self._tp
             t = [time.perf_counter()]
 
             def lap(name):      # host wall time of the steps of the exchange (bench.py reports them)
                 t.append(time.perf_counter())
                 self.fetch_laps[name] = self.fetch_laps.get(name, 0.0) + (t[-1] - t[-2]) * 1e3
             m1 = ctx.pack_sa_rows(); lap("pack_sa_rows")
-            buf1, st1, _ = self._gather(*m1); lap("gather_1")
-            m2 = ctx.pack_extra_rows(buf1.data_ptr(), st1); lap("pack_extra_rows")
-            buf2, st2, _ = self._gather(*m2); lap("gather_2")
-            _, (s1, s2, nn, zd) = cctx.unpack_rows(buf1.data_ptr(), st1, buf2.data_ptr(), st2); lap("unpack_rows")
-            f = cctx.fetch(); lap("fetch_on_gathered_rows")
+            b1, st1, _ = tp.gather(ctx, _abi.CH_SA, *m1, lane=True); lap("gather_1")
+            m2 = ctx.pack_extra_rows(b1, st1); lap("pack_extra_rows")
+            b2, st2, _ = tp.gather(ctx, _abi.CH_EXTRA, *m2, lane=True); lap("gather_2")
+            _, (s1, s2, nn, zd) = cctx.unpack_rows(b1, st1, b2, st2); lap("unpack_rows")
+            f = cctx.fetch(read_back=False); lap("fetch_own_reads")
+            m3 = cctx.pack_chimeric(); lap("pack_chimeric")
+            b3, st3, _ = tp.gather(cctx, _abi.CH_CHIM, *m3); lap("gather_3")
+            nr, na = cctx.merge_chimeric(b3, st3); lap("merge_chimeric")
+            f["n_reads"], f["n_aln"] = nr, na
+            if self.materialise:
+                cctx.get_chimeric(nr, na, f); lap("read_back")
             # nm_stats (ibg:153-157) run over ALL records: the shard partials are summed in rank order (the f64 sum
             # order differs from the 1-GPU order: within 1e-9 relative, unused downstream)
-            f["nm_sum"] = float(s1.sum()); f["nm_sumsq"] = float(s2.sum())
-            f["nm_n"] = int(nn.sum()); f["nm_zero_div"] = int(zd.sum())
+            def nm_totals():
+                f["nm_sum"] = float(s1.sum()); f["nm_sumsq"] = float(s2.sum())
+                f["nm_n"] = int(nn.sum()); f["nm_zero_div"] = int(zd.sum())
+            nm_totals()
+            if cctx._pass_keep is not None:     # inside a pipelined pass fetch() fills its own (rows-only: empty) sums at
+                cctx._pass_fin.append(nm_totals)    # pass_end: the totals of the shards go in after that
             self._row_names = None
 
             def names_of(recs):
@@ -366,33 +451,45 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
             self._cctx.set_params(min_del_len=self.min_del_len, min_bp_match_cutoff=self.min_bp_match_cutoff_)
             bam_to_breakpoint_nanopore.find_breakpoints(self)
 
-        # a3: local gap rows (+ the name hash of each) as one host-built message per rank, merged in emission order
-        def _smalldel_rows(self, t, s, e):
-            import torch
-            from . import exchange
+        # a3: local gap rows (+ the name hash of each), packed on the device, gathered, merged in emission order
+        def _smalldel_gather(self, t, s, e):
+            """-> (local rows dict, list of per-rank raw messages; filled at pass_end inside a pipelined pass)."""
             rows = self._ctx.smalldel(t, s, e)
-            local = []
-            if rows["n"]:
-                recs = rows["rec"].astype(np.int64)
-                tv = self._views()
-                idx = torch.as_tensor(recs, device=tv["name_lo"].device)
-                lo, hi = tv["name_lo"][idx].cpu().tolist(), tv["name_hi"][idx].cpu().tolist()
-                urec, inv = np.unique(recs, return_inverse=True)
-                unames = self._names_of(urec)
-                names = [unames[k] for k in inv.tolist()]
-                local = list(zip(names, *(rows[k].tolist() for k in ("ai", "next_start", "prev_end", "first_start", "last_end",
-                                                                      "mapq")), lo, hi))
-            dev = torch.device("cuda", device)
-            buf, st, sz = self._tcomm().gather_msgs(exchange.host_msg(pack_smalldel(local), dev))
-            raw = buf.cpu().numpy()
-            merged = [r for a, n in zip(st, sz) for r in unpack_smalldel(raw[a:a + n])]
-            merged.sort(key=lambda r: r[1])           # stable: interval order, then rank (= file) order, then block order
-            for r in merged:
-                self._name_hash[r[0]] = (r[7], r[8])
-            return [r[:7] for r in merged]
+            g = self._tp.gather(self._ctx, _abi.CH_SDEL, *self._ctx.smalldel_pack())
+            return rows, self._tp.read(self._ctx, g)
+
+        @staticmethod
+        def _smalldel_merge(raws):
+            """Gathered messages -> rows (rank, rec, ai, next_start, prev_end, first_start, last_end, mapq, lo, hi) in the
+            reference's emission order: interval, then rank (= file) order, then block order."""
+            out = []
+            for r, raw in enumerate(raws):
+                n = int(np.frombuffer(raw[:8].tobytes(), np.uint64)[0])
+                body = np.frombuffer(raw[64:64 + 48 * n].tobytes(), _SDEL_ROW)
+                out.extend((r, int(x["rec"]), int(x["ai"]), int(x["next_start"]), int(x["prev_end"]), int(x["first_start"]),
+                            int(x["last_end"]), int(x["mapq"]), int(x["lo"]), int(x["hi"])) for x in body)
+            out.sort(key=lambda x: x[2])          # stable
+            return out
+
+        def _smalldel_rows(self, t, s, e):
+            rows, raws = self._smalldel_gather(t, s, e)
+            merged = self._smalldel_merge(raws)
+            # names: every rank knows the names of its own records; tens of rows
+            mine = sorted(set(x[1] for x in merged if x[0] == self._comm.rank))
+            local = dict(zip(mine, self._names_of(np.array(mine, np.int64)))) if mine else {}
+            table = {}
+            for r, part in enumerate(self._comm.all_gather(local)):
+                for rec, nm in part.items():
+                    table[(r, rec)] = nm
+            out = []
+            for x in merged:
+                nm = table[(x[0], x[1])]
+                self._name_hash[nm] = (x[8], x[9])
+                out.append((nm, ) + x[2:8])
+            return out
 
         # a11: name-level set algebra across shards, on name hashes: the local stab rows are packed on the device as
-        # (edge, name hash, mask), all-gathered, and counted by the same kernels on every rank
+        # (edge, name hash, mask), gathered, and counted by the same kernels on every rank
         def _concordant_counts(self, uniq, rbps):
             import torch
             ctx = self._ctx
@@ -403,18 +500,18 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
                 rb = [(k, ) + self._name_hash[nm] + (16, ) for k, names in enumerate(rbps) for nm in names if nm in self._name_hash]
                 self._rbt = (rbps, torch.as_tensor(np.array(rb, np.int64).reshape(-1, 4), device=torch.device("cuda", device)))
                 torch.cuda.current_stream().synchronize()
-            gathered = self._gather(*ctx.concordant_pack())
+            gathered = self._tp.gather(ctx, _abi.CH_CONC, *ctx.concordant_pack())
             rbt = self._rbt[1]
-            cnt = ctx.count_name_msgs(len(uniq), gathered[0].data_ptr(), gathered[1], gathered[2], rbt.data_ptr(), int(rbt.shape[0]))
+            cnt = ctx.count_name_msgs(len(uniq), gathered[0], gathered[1], gathered[2], rbt.data_ptr(), int(rbt.shape[0]))
             return cnt, gathered
 
         def _concordant_support(self, uniq, rbps):
-            cnt, (buf, st, sz) = self._concordant_counts(uniq, rbps)
+            cnt, gathered = self._concordant_counts(uniq, rbps)
             # ce[9] wants the read NAMES covering p or p+1: every rank contributes the names of its own records
             # (its message rows are in the order of its stab rows)
-            raw = buf.cpu().numpy()
+            raws = self._tp.read(self._ctx, gathered)
             rows = self._ctx.concordant_rows()
-            mine = raw[st[self._comm.rank] + 64:st[self._comm.rank] + sz[self._comm.rank]].view(np.int64).reshape(-1, 4)
+            mine = np.frombuffer(raws[self._comm.rank][64:].tobytes(), np.int64).reshape(-1, 4)
             sel = np.nonzero((rows["mask"] & 3) != 0)[0]
             urec, first = np.unique(rows["rec"][sel], return_index=True)
             keys = mine[sel[first]]
@@ -423,8 +520,8 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
                 table.update(zip(zip(part[0], part[1]), part[2]))
             self._ce_hash = table          # (hash lo, hi) -> name over every ce[9]: compute_path_constraints' name set
             out = [set() for _ in uniq]
-            for a, n in zip(st, sz):
-                g = raw[a + 64:a + n].view(np.int64).reshape(-1, 4)
+            for raw in raws:
+                g = np.frombuffer(raw[64:].tobytes(), np.int64).reshape(-1, 4)
                 g = g[(g[:, 3] & 3) != 0]
                 for e, lo, hi in g[:, :3].tolist():
                     out[e].add(table[(lo, hi)])

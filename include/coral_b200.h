@@ -145,6 +145,10 @@ int coral_rescan(coral_ctx* ctx);
  * Streams of a process should not share a hardware queue: set CUDA_DEVICE_MAX_CONNECTIONS=32 before CUDA starts.
  * This is how one step of the device-resident benchmark runs the path (reference call order
  * infer_breakpoint_graph.py:1354-1386) as one stream of kernels. */
+/* Result arrays in page-locked memory (coral_host_alloc) receive their copies by direct DMA inside a pass: no staging
+ * buffer and no host memcpy at coral_pass_end (1.3 MB of result tables per C2 pass: 0.1 ms of the step otherwise). */
+int coral_host_alloc(uint64_t nbytes, void** out);
+void coral_host_free(void* p);
 int coral_pass_begin(coral_ctx* ctx);
 int coral_pass_end(coral_ctx* ctx, int32_t* replayed);
 /* For callers that enqueue work of their own between the entry points of a pass (the multi-GPU engine: NCCL
@@ -171,6 +175,7 @@ int coral_pass_replaying(const coral_ctx* ctx);
 #define CORAL_STAGE_PRESCAN 9   /* the pre-scan of an asynchronous load / of coral_rescan inside a pipelined pass */
 #define CORAL_N_STAGES 10
 float coral_stage_ms(coral_ctx* ctx, int stage);
+int coral_stage_ms_all(coral_ctx* ctx, float* out /* [CORAL_N_STAGES] */);
 /* Forget the stage times recorded so far (coral_stage_ms then reports only stages that ran since), and the time from
  * one stage event to another — begin (which = 0) or end (which = 1) — across the ctx's streams: where the stages of a
  * pipelined pass sit relative to the scan that runs next to them. */
@@ -267,6 +272,62 @@ int coral_pack_extra_rows(coral_ctx* ctx, int32_t n_ranks, const uint8_t* d_buf,
 int coral_unpack_rows(coral_ctx* ctx, int32_t n_ranks, const uint8_t* d_buf1, const uint64_t* starts1, const uint8_t* d_buf2,
                       const uint64_t* starts2, double* nm_sum, double* nm_sumsq, int64_t* nm_n, int64_t* nm_zero_div,
                       int64_t* n_rows);
+
+/* ---- exchanges over peer memory (NVLink / NVSwitch), csrc/xchg.cu ------------------------------------------------ *
+ * The transport of the multi-GPU form of the path (the one real exchange is the SA union / first-primary
+ * rule of fetch, ibg:141-151; coverage sums and concordant name sets are combined the same way).  One process per GPU;
+ * every rank owns a WINDOW in its own HBM that the peers map once (CUDA IPC).  An all-gather of one variable-length
+ * message per rank is two kernels on the ctx's stream — a push that stores the message into this rank's slot of every
+ * peer's window and releases a sequence number, a one-warp wait on the local flags — and no host round trip: inside a
+ * pipelined pass the message sizes are replayed and checked on the device like every other launch size.
+ *   coral_xchg_create  : slot_bytes[CORAL_XCHG_CHANNELS] = largest message per channel (0: channel unused); the window
+ *                        holds 2 x world slots per channel.  A message beyond the slot size fails with CORAL_E_NOMEM.
+ *   coral_xchg_handle  : the 64-byte IPC handle the peers open (+ the window's device address, for ranks that are
+ *                        threads of the SAME process, where a handle cannot be opened);
+ *   coral_xchg_connect : handles of all ranks in rank order (the caller all-gathers them once, any transport); a host
+ *                        barrier of the caller must separate create / connect / first exchange / destroy on all ranks;
+ *   coral_xchg_allgather : message r of the group = d_buf[starts[r] : starts[r] + sizes[r]) in THIS rank's HBM, valid
+ *                        until this stream's next exchange but one on the channel; all ranks call the exchanges of a
+ *                        channel in the same order.  lane = 1: inside a pipelined pass, run on the ctx's second lane.
+ *   coral_xchg_allreduce_i64 : in-place integer sum over ranks of a small host array (synchronises).
+ * A wait gives up after the timeout (default 20 s): the call (or the pass) fails with CORAL_E_STATE instead of
+ * hanging the GPU; coral_xchg_timeouts reads and clears the count.  At most CORAL_XCHG_MAX_RANKS ranks. */
+typedef struct coral_xchg coral_xchg;
+#define CORAL_XCHG_MAX_RANKS 16
+#define CORAL_XCHG_CHANNELS 8
+#define CORAL_XCHG_HANDLE_BYTES 64
+int coral_xchg_create(int device, int32_t rank, int32_t world, const uint64_t* slot_bytes, coral_xchg** out);
+void coral_xchg_destroy(coral_xchg* x);
+const char* coral_xchg_last_error(const coral_xchg* x);
+int coral_xchg_handle(coral_xchg* x, uint8_t* handle, uint64_t* local_ptr);
+int coral_xchg_connect(coral_xchg* x, const uint8_t* handles, const uint64_t* same_process_ptrs);
+int coral_xchg_set_timeout(coral_xchg* x, double seconds);
+int coral_xchg_timeouts(coral_xchg* x, int32_t* n);
+int coral_xchg_allgather(coral_ctx* ctx, coral_xchg* x, int32_t channel, uint64_t d_msg, uint64_t nbytes, int32_t lane,
+                         uint64_t* d_buf, uint64_t* starts, uint64_t* sizes);
+int coral_xchg_allreduce_i64(coral_ctx* ctx, coral_xchg* x, int32_t channel, int64_t* values, int32_t n);
+/* coral_region_coverage over ALL shards of the file: every rank calls it with the same regions on its own shard; the
+ * accumulators are summed in place over peer memory between the kernels and the result copy (a record is owned by
+ * exactly one shard, so the sums of ibg:131 and ibg:1031-1034 are additive). */
+int coral_region_coverage_sharded(coral_ctx* ctx, coral_xchg* x, int32_t channel, const int32_t* tid, const int32_t* start,
+                                  const int32_t* stop, int32_t n_regions, int64_t* base_sum, int64_t* rec_count);
+
+/* Distributed fetch of the multi-GPU engine (csrc/chimeric_merge.cu): with options "fetch_part_world" = N and
+ * "fetch_part_rank" = r, coral_fetch on the rows-only ctx parses only the reads whose name hash falls into residue class
+ * r (all ranks hold all gathered rows; the SA entries are split N ways instead of parsed N times).
+ *   coral_pack_chimeric  : this ctx's chimeric table as one message (valid until the next pack on the ctx);
+ *   coral_merge_chimeric : the gathered messages of all ranks -> the table the 1-GPU coral_fetch over the whole file
+ *                          leaves (reads in the order of their first SA-bearing record, ibg:145-151; alignments in their
+ *                          stable (qs, qe) order, cp:263); coral_get_chimeric / coral_candidates_* / coral_cluster_call*
+ *                          then run unchanged;
+ *   coral_smalldel_pack  : the rows of the last coral_smalldel (+ 128-bit name hash) as one message (ibg:750-762, sharded);
+ *   coral_read_device    : device bytes handed out by this library -> host array, deferred to coral_pass_end inside a
+ *                          pipelined pass. */
+int coral_pack_chimeric(coral_ctx* ctx, uint64_t* d_msg, uint64_t* nbytes);
+int coral_merge_chimeric(coral_ctx* ctx, int32_t n_ranks, const uint8_t* d_buf, const uint64_t* starts, int64_t* n_reads,
+                         int64_t* n_alignments);
+int coral_smalldel_pack(coral_ctx* ctx, uint64_t* d_msg, uint64_t* nbytes);
+int coral_read_device(coral_ctx* ctx, uint64_t d_src, uint64_t nbytes, uint8_t* out, int32_t lane);
 
 /* Operator form of cigar_parsing.alignment_from_satags / cigar2pos* (cigar_parsing.py:17-269) on SA text the
  * caller supplies: `text` holds the entries, read r owns entries [ent_ptr[r], ent_ptr[r+1]) whose bytes are

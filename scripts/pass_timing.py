@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--reserve", type=int, default=-1)
     ap.add_argument("--fork", type=int, default=1)
+    ap.add_argument("--pinned", type=int, default=1)
     a = ap.parse_args()
     import bench
     from sim.generate import simulate
@@ -49,7 +50,7 @@ def main():
         def lap(k):
             t.append(time.perf_counter())
             laps.setdefault(k, []).append((t[-1] - t[-2]) * 1e3)
-        ctx.pass_begin(); lap("pass_begin")
+        ctx.pass_begin(pinned_results=bool(a.pinned)); lap("pass_begin")
         ctx.rescan(); lap("rescan")
         ctx.fetch(); lap("fetch")
         cand = ctx.candidates_l(*plan["intervals"]); lap("candidates_l")

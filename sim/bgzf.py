@@ -34,34 +34,48 @@ def bam_header_bytes(refs, text: str = None) -> bytes:
     return b"".join(out)
 
 
-def write_bam(path, refs, record_bytes, rec_off=None, level: int = 1):
+def write_bam(path, refs, record_bytes, rec_off=None, level: int = 1, threads: int = 0):
     """Write header + records.  ``record_bytes`` is a bytes-like of concatenated records; when
     ``rec_off`` is given (n+1 offsets, possibly with alignment padding between records) the padding
-    is removed so the file is a standard BAM stream."""
+    is removed so the file is a standard BAM stream.  The header goes into its own block(s), the record
+    stream is cut every 0xFF00 bytes; blocks are deflated on ``threads`` threads (0: all cores; zlib
+    releases the GIL) and written in order."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
     import numpy as np
 
     buf = memoryview(record_bytes)
-    with open(path, "wb") as fp:
-        pending = bytearray(bam_header_bytes(refs))
-
-        def flush(force=False):
-            nonlocal pending
-            while len(pending) >= _MAX_BLOCK or (force and pending):
-                chunk = bytes(pending[:_MAX_BLOCK])
-                del pending[:_MAX_BLOCK]
-                fp.write(bgzf_block(chunk, level))
-
-        flush(force=True)  # header in its own block(s)
-        if rec_off is None:
-            pending += buf
-            flush(force=True)
+    if rec_off is None:
+        stream = buf
+    else:
+        off = np.asarray(rec_off, dtype=np.uint64)
+        n = len(off) - 1
+        raw = np.frombuffer(buf, dtype=np.uint8)
+        starts = off[:-1].astype(np.int64)
+        if n and np.all(starts % 4 == 0) and len(raw) % 4 == 0:
+            lens = raw.view("<i4")[starts // 4].astype(np.int64) + 4
         else:
-            off = np.asarray(rec_off, dtype=np.uint64)
-            for i in range(len(off) - 1):
-                s = int(off[i])
-                bs = struct.unpack_from("<i", buf, s)[0]
-                pending += buf[s:s + 4 + bs]
-                if len(pending) >= _MAX_BLOCK:
-                    flush()
-            flush(force=True)
+            lens = np.array([struct.unpack_from("<i", buf, int(s))[0] + 4 for s in starts], np.int64)
+        dst = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+        out = np.empty(int(dst[-1]), np.uint8)
+        for s, d, ln in zip(starts.tolist(), dst[:-1].tolist(), lens.tolist()):
+            out[d:d + ln] = raw[s:s + ln]
+        stream = memoryview(out)
+    nthreads = threads or os.cpu_count() or 1
+
+    def blocks(mv):
+        for a in range(0, len(mv), _MAX_BLOCK):
+            yield bytes(mv[a:a + _MAX_BLOCK])
+    with open(path, "wb") as fp, ThreadPoolExecutor(nthreads) as pool:
+        for chunk in blocks(memoryview(bam_header_bytes(refs))):
+            fp.write(bgzf_block(chunk, level))
+        batch = []
+        for chunk in blocks(stream):
+            batch.append(chunk)
+            if len(batch) == 64 * nthreads:
+                for blk in pool.map(lambda c: bgzf_block(c, level), batch):
+                    fp.write(blk)
+                batch = []
+        for blk in pool.map(lambda c: bgzf_block(c, level), batch):
+            fp.write(blk)
         fp.write(_EOF)

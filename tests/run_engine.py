@@ -4,9 +4,12 @@ Executed by the tests in a subprocess with PYTHONHASHSEED=0: the reference itera
 names in find_interval_i (infer_breakpoint_graph.py:432), so the order of new_bp_list depends on the string
 hash seed; the golden fixtures were produced with PYTHONHASHSEED=0 as well.
 """
+import faulthandler
 import json
 import os
 import sys
+
+faulthandler.enable()
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
@@ -14,7 +17,7 @@ sys.path.insert(0, HERE)
 import util  # noqa: E402
 
 
-def sharded_states(world, bam, cn_seg, seed):
+def sharded_states(world, bam, cn_seg, seed, peer=False):
     """`world` shards of the file as `world` threads on cuda:0, exchanging through ThreadComm (the collective's test
     double; the kernels are the real ones).  Every rank must end in the same state; rank 0's is returned."""
     import threading
@@ -25,8 +28,12 @@ def sharded_states(world, bam, cn_seg, seed):
 
     def body(r):
         try:
-            eng = sharded.make_sharded_engine(fh, seed, comms[r], device=0)
+            # peer: the exchanges as kernels over "peer" memory (thread ranks share the device: plain addresses)
+            x = sharded.make_xchg(comms[r], 0, timeout_s=60) if peer else None
+            eng = sharded.make_sharded_engine(fh, seed, comms[r], device=0, xchg=x)
             out[r] = util.jsonify(util.run_pipeline(eng, cn_seg))
+            if x is not None:
+                sharded.close_xchg(comms[r], x)
         except Exception as ex:      # noqa
             import traceback
             traceback.print_exc()
@@ -46,8 +53,8 @@ def sharded_states(world, bam, cn_seg, seed):
 
 def main():
     kind, bam, cn_seg, seed, out = sys.argv[1:6]
-    if kind.startswith("cuda-sharded:"):
-        st = sharded_states(int(kind.split(":")[1]), bam, cn_seg, seed)
+    if kind.startswith("cuda-sharded"):
+        st = sharded_states(int(kind.split(":")[1]), bam, cn_seg, seed, peer=kind.startswith("cuda-sharded-peer:"))
     else:
         if kind == "oracle":
             eng = util.oracle_engine(bam, seed)

@@ -24,12 +24,12 @@ def load_golden(case):
 _DS = {}
 
 
-def golden_dataset(case, tmp_path_factory):
+def golden_dataset(case, tmp_path_factory, outdir=None):
     if case not in _DS:
         from sim.generate import simulate, write_dataset
         cfg = make_golden.make_cfg(case)
         data = simulate(cfg)
-        paths = write_dataset(data, str(tmp_path_factory.mktemp("g_" + case)))
+        paths = write_dataset(data, outdir if outdir is not None else str(tmp_path_factory.mktemp("g_" + case)))
         _DS[case] = (cfg, data, paths)
     return _DS[case]
 
@@ -40,7 +40,7 @@ def run_engine(kind, paths, tmp_path_factory):
     out = str(tmp_path_factory.mktemp("state") / "state.json")
     env = dict(os.environ, PYTHONHASHSEED="0")
     subprocess.check_call([sys.executable, os.path.join(HERE, "run_engine.py"), kind, paths["bam"], paths["cn_seg"],
-                           paths["seed"], out], env=env)
+                           paths["seed"], out], env=env, timeout=1800)
     return json.load(open(out))
 
 

@@ -19,6 +19,24 @@ def test_sharded_pipeline_matches_reference(built_lib, case, world, tmp_path_fac
         assert g_got["graph_txt"] == g_ref["graph_txt"]
 
 
+@pytest.mark.parametrize("case,world", [("c2_small", 2), ("c4_small", 3), ("c5_mini", 4), ("c3_small", 2)])
+def test_sharded_pipeline_over_peer_memory_matches_reference(built_lib, case, world, tmp_path):
+    """The same pipeline with the exchanges as kernels over peer memory (csrc/xchg.cu): `world` PROCESSES on cuda:0 that
+    map each other's windows through CUDA IPC, as one-process-per-GPU ranks do (tests/run_rank.py)."""
+    import json
+    import util
+    gold = G.load_golden(case)
+    out = str(tmp_path / "state.json")
+    util.spawn_ranks(["pipeline", case, out], world)
+    res = json.load(open(out))
+    assert len(set(res["digests"])) == 1, "ranks ended in different states"
+    assert res["timeouts"] == [0] * world
+    got = res["state"]
+    assert G.compare_states(got, gold["stages"]) == []
+    for g_got, g_ref in zip(got["assign_cov"]["graphs"], gold["stages"]["assign_cov"]["graphs"]):
+        assert g_got["graph_txt"] == g_ref["graph_txt"]
+
+
 # ---- the packed device-side exchange on its own (csrc/exchange.cu) against the whole file ----------------------------
 def _packed_rows(shards, refs):
     """Runs the fetch exchange for `shards` (list of (rec, rec_off)) the way N ranks do, sequentially on one device.

@@ -80,6 +80,31 @@ def run_pipeline(eng, cn_seg, stop_after=None, defer_cov=False):
     return st
 
 
+def spawn_ranks(args, world, timeout=1200):
+    """Run tests/run_rank.py as `world` processes (one rank each, all on cuda:0, gloo for the host side) and wait."""
+    import os
+    import socket
+    import subprocess
+    here = os.path.dirname(os.path.abspath(__file__))
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    procs = []
+    for r in range(world):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), LOCAL_RANK="0", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
+                   PYTHONHASHSEED="0", CUDA_DEVICE_MAX_CONNECTIONS="32", GLOO_SOCKET_IFNAME="lo")
+        procs.append(subprocess.Popen([sys.executable, os.path.join(here, "run_rank.py")] + [str(a) for a in args], env=env))
+    rcs = []
+    try:
+        for p in procs:
+            rcs.append(p.wait(timeout=timeout))
+    finally:
+        for p in procs:
+            if p.poll() is None:
+                p.kill()
+    assert rcs == [0] * world, "rank exit codes %s" % rcs
+
+
 def jsonify(x):
     import json
     return json.loads(json.dumps(x))
