@@ -135,6 +135,7 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     }
     c->loaded = false;
     c->rows_only = false;
+    for (auto& q : c->rows_fill_ptr) q = nullptr;     // the scan rewrites the columns coral_unpack_rows keeps constant
     c->sa_side_valid = false;
     c->pass.invalidate();                  // recorded sizes belong to the previous records
     if (c->pass.active) { c->err = "coral_load_records inside a pass"; return CORAL_E_STATE; }

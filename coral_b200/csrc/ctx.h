@@ -242,6 +242,8 @@ struct coral_ctx {
     bool has_ordinal = false;
     bool force_full_name_sort = false;   // test hook: take the 128-bit name sort of coral_fetch (its fallback path)
     bool rows_only = false;   // ctx was filled by coral_load_rows: only fetch / candidates / cluster are valid
+    const void* rows_fill_ptr[10] = {};   // coral_unpack_rows: constant columns already filled (buffer, bytes)
+    size_t rows_fill_bytes[10] = {};
     int32_t fetch_part_rank = 0, fetch_part_world = 1;   // options "fetch_part_rank" / "fetch_part_world" (see coral_set_option)
 
     RecordTable rt;

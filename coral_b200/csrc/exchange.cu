@@ -100,15 +100,21 @@ __global__ void k_collect_names(MsgSet s, uint64_t* __restrict__ lo, uint32_t* _
 }
 
 // position in the lo-sorted gathered names of the FIRST entry equal to (lo, hi), or -1
+// (the names are sorted on the low NAME_SORT_BITS bits of the low hash word only — 5 radix passes instead of 8; entries
+// that share those bits sit next to each other in arbitrary order and are told apart by the full 128 bits here)
+constexpr int NAME_SORT_BITS = 40;
+constexpr uint64_t NAME_SORT_MASK = ((uint64_t)1 << NAME_SORT_BITS) - 1;
 __device__ __forceinline__ int64_t name_slot(const MsgSet& s, const uint64_t* __restrict__ slo, const uint32_t* __restrict__ sidx,
                                              int64_t m, uint64_t lo, uint64_t hi) {
+    const uint64_t key = lo & NAME_SORT_MASK;
     int64_t a = 0, b = m;
     while (a < b) {
         const int64_t mid = (a + b) >> 1;
-        if (slo[mid] < lo) a = mid + 1; else b = mid;
+        if ((slo[mid] & NAME_SORT_MASK) < key) a = mid + 1; else b = mid;
     }
-    for (; a < m && slo[a] == lo; a++)
-        if (msg_row(s, sidx[a])->hi == hi) return a;
+    // the FIRST entry of the run that carries this very name: every prober of a name must pick the same slot
+    for (; a < m && (slo[a] & NAME_SORT_MASK) == key; a++)
+        if (slo[a] == lo && msg_row(s, sidx[a])->hi == hi) return a;
     return -1;
 }
 
@@ -182,6 +188,20 @@ __global__ void k_unpack_rows(UnpackPlan p, RowCols o) {
     o.flag_mapq[out] = m->flag_mapq; o.lseq[out] = m->l_seq; o.nm[out] = m->nm;
     o.sa_off[out] = m->sa_len ? m->name_len : 0u;     // slot = name (with NUL) + SA text; 0 keeps meaning "no SA tag"
     o.sa_len[out] = m->sa_len;
+}
+
+// the text of every message -> its place in the rows-only ctx's text buffer (both sides 16-byte aligned): one kernel
+// instead of 2 N copy-engine operations between kernels
+struct TextCopy {
+    const uint4* src[2 * CORAL_XCHG_MAX_RANKS];
+    uint4* dst[2 * CORAL_XCHG_MAX_RANKS];
+    uint64_t nvec[2 * CORAL_XCHG_MAX_RANKS];
+    int n;
+};
+__global__ void k_copy_text(TextCopy t) {
+    const int seg = blockIdx.y;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < t.nvec[seg]; i += stride) t.dst[seg][i] = t.src[seg][i];
 }
 
 __global__ void k_collect_hdrs(MsgSet a, MsgSet b, uint64_t* __restrict__ out) {
@@ -336,7 +356,7 @@ int coral_pack_extra_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf, c
         uint64_t* lo_in = c->s4.as<uint64_t>(); uint64_t* lo_out = lo_in + m;
         uint32_t* ix_in = c->s5.as<uint32_t>(); uint32_t* ix_out = ix_in + m; uint32_t* first = ix_out + m;
         LAUNCH_1D(k_collect_names, m, set, lo_in, ix_in);
-        CORAL_TRY(sort_pairs_u64(c, lo_in, lo_out, ix_in, ix_out, m));
+        CORAL_TRY(sort_pairs_u64(c, lo_in, lo_out, ix_in, ix_out, m, 0, NAME_SORT_BITS));
         CORAL_CUDA(c, cudaMemsetAsync(first, 0xFF, (size_t)m * 4, c->stream));
         LAUNCH_1D(k_extra_probe, n, n, t.flag_mapq.as<uint32_t>(), t.sa_off.as<uint32_t>(), t.name_lo.as<uint64_t>(),
                   t.name_hi.as<uint64_t>(), set, lo_out, ix_out, m, first, c->s6.as<int32_t>());
@@ -372,8 +392,8 @@ int coral_unpack_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf1, cons
     for (int r = 0; r < n_ranks; r++) {
         p.out_base[r] = rows;
         rows += h1[r].n_rows + h2[r].n_rows;
-        p.text_sa[r] = text; text += h1[r].text_bytes;
-        p.text_ex[r] = text; text += h2[r].text_bytes;
+        p.text_sa[r] = text; text += (h1[r].text_bytes + 15) & ~(uint64_t)15;      // every message's text starts 16-byte aligned
+        p.text_ex[r] = text; text += (h2[r].text_bytes + 15) & ~(uint64_t)15;
         if (nm_sum) nm_sum[r] = h2[r].nm_sum;
         if (nm_sumsq) nm_sumsq[r] = h2[r].nm_sq;
         if (nm_n) nm_n[r] = h2[r].nm_n;
@@ -384,13 +404,31 @@ int coral_unpack_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf1, cons
     c->rows_only = true;
     const int64_t n = (int64_t)rows;
     CORAL_CUDA(c, c->recs_owned.ensure(text + 64));
-    for (int r = 0; r < n_ranks; r++) {
-        const uint8_t* t1 = p.sa.base[r] + sizeof(MsgHdr) + h1[r].n_rows * sizeof(RowMsg);
-        const uint8_t* t2 = p.ex.base[r] + sizeof(MsgHdr) + h2[r].n_rows * sizeof(RowMsg);
-        if (h1[r].text_bytes)
-            CORAL_CUDA(c, cudaMemcpyAsync(c->recs_owned.as<uint8_t>() + p.text_sa[r], t1, h1[r].text_bytes, cudaMemcpyDeviceToDevice, c->stream));
-        if (h2[r].text_bytes)
-            CORAL_CUDA(c, cudaMemcpyAsync(c->recs_owned.as<uint8_t>() + p.text_ex[r], t2, h2[r].text_bytes, cudaMemcpyDeviceToDevice, c->stream));
+    {
+        TextCopy tc;
+        tc.n = 0;
+        uint64_t most = 0;
+        for (int r = 0; r < n_ranks; r++) {
+            const uint8_t* t1 = p.sa.base[r] + sizeof(MsgHdr) + h1[r].n_rows * sizeof(RowMsg);
+            const uint8_t* t2 = p.ex.base[r] + sizeof(MsgHdr) + h2[r].n_rows * sizeof(RowMsg);
+            const uint8_t* srcs[2] = {t1, t2};
+            const uint64_t bytes[2] = {h1[r].text_bytes, h2[r].text_bytes};
+            const uint64_t dsts[2] = {p.text_sa[r], p.text_ex[r]};
+            for (int k = 0; k < 2; k++) {
+                if (!bytes[k]) continue;
+                tc.src[tc.n] = reinterpret_cast<const uint4*>(srcs[k]);      // messages pad their text to 16 bytes
+                tc.dst[tc.n] = reinterpret_cast<uint4*>(c->recs_owned.as<uint8_t>() + dsts[k]);
+                tc.nvec[tc.n] = (bytes[k] + 15) >> 4;
+                most = std::max(most, tc.nvec[tc.n]);
+                tc.n++;
+            }
+        }
+        if (tc.n) {
+            const unsigned bx = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>((most + 1023) / 1024, (uint64_t)c->sm_count));
+            k_copy_text<<<dim3(bx, (unsigned)tc.n), 256, 0, c->stream>>>(tc);
+            c->n_launches++;
+            CORAL_CUDA(c, cudaGetLastError());
+        }
     }
     CORAL_CUDA(c, cudaMemsetAsync(c->recs_owned.as<uint8_t>() + text, 0, 64, c->stream));
     c->d_recs = c->recs_owned.as<uint8_t>();
@@ -407,12 +445,17 @@ int coral_unpack_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf1, cons
     RowCols o{c->d_off.as<uint64_t>(), t.name_lo.as<uint64_t>(), t.name_hi.as<uint64_t>(), t.flag_mapq.as<uint32_t>(),
               t.lseq.as<uint32_t>(), t.sa_off.as<uint32_t>(), t.sa_len.as<uint32_t>(), t.nm.as<int32_t>()};
     LAUNCH_1D(k_unpack_rows, n, p, o);
-    CORAL_CUDA(c, t.tid.ensure(n4));
-    CORAL_CUDA(c, cudaMemsetAsync(t.tid.p, 0xFF, n4, c->stream));          // tid -1: rows carry no placement
-    DevBuf* zero4[] = {&t.pos, &t.endpos, &t.ncig, &t.infer, &t.mbases, &t.nonacgt, &t.fbs, &t.lbe, &t.ngap};
-    for (DevBuf* b : zero4) {
+    // columns a row does not carry: tid -1 (no placement), the rest 0.  Nothing ever writes them on a rows-only ctx, so a
+    // later unpack only fills what a regrown buffer has lost (ten memsets per pass otherwise)
+    DevBuf* fill[] = {&t.tid, &t.pos, &t.endpos, &t.ncig, &t.infer, &t.mbases, &t.nonacgt, &t.fbs, &t.lbe, &t.ngap};
+    for (int k = 0; k < 10; k++) {
+        DevBuf* b = fill[k];
         CORAL_CUDA(c, b->ensure(n4));
-        CORAL_CUDA(c, cudaMemsetAsync(b->p, 0, n4, c->stream));
+        if (c->rows_fill_ptr[k] != b->p || c->rows_fill_bytes[k] < n4) {
+            CORAL_CUDA(c, cudaMemsetAsync(b->p, k == 0 ? 0xFF : 0, b->cap, c->stream));
+            c->rows_fill_ptr[k] = b->p;
+            c->rows_fill_bytes[k] = b->cap;
+        }
     }
     c->gaps.n = 0;
     CORAL_CUDA(c, c->status.ensure(64));
