@@ -713,6 +713,8 @@ def main():
         ctx = _abi.Context(local)
         ctx.set_references([c for c, _ in cfg.refs])
         ctx.load_records(data.rec, data.rec_off)
+        if os.environ.get("CORAL_SCAN_ORDER"):          # development aid: the record queue's order (0 file, 1 big first, 2 by size)
+            ctx.set_option("scan_order", int(os.environ["CORAL_SCAN_ORDER"]))
         for _ in range(warm):
             ctx.rescan()
         ms = []

@@ -554,6 +554,21 @@ class Context(object):
     def get_chimeric(self, nr, na, out=None):
         """coral_get_chimeric of the table on the device (after fetch / merge_chimeric) -> dict of numpy arrays."""
         out = {} if out is None else out
+        if self._pass_keep is not None and self._pinned_results:
+            # one page-locked block, one packing kernel, one copy (coral_get_chimeric_packed): the arrays are views of it
+            cols = (("read_first_rec", np.uint32, nr), ("read_len", np.int64, nr), ("read_status", np.int32, nr),
+                    ("aln_ptr", np.uint32, nr + 1), ("qs", np.int32, na), ("qe", np.int32, na), ("tid", np.int32, na),
+                    ("rstart", np.int32, na), ("rend", np.int32, na), ("strand", np.uint8, na), ("mapq", np.int32, na),
+                    ("nm", np.int64, na))
+            total = sum((np.dtype(dt).itemsize * n + 63) & ~63 for _, dt, n in cols)
+            blk = self._z(max(total, 64), np.uint8)
+            offs = np.zeros(12, np.uint64)
+            self._check(self._L.coral_get_chimeric_packed(self._h, _p(blk), ctypes.c_uint64(blk.nbytes), _p(offs)))
+            out.update({"n_reads": nr, "n_aln": na})
+            for (name, dt, n), o in zip(cols, offs.tolist()):
+                out[name] = blk[int(o):int(o) + np.dtype(dt).itemsize * n].view(dt)
+            self._hold(out, blk)
+            return out
         out.update({"n_reads": nr, "n_aln": na,
                "read_first_rec": self._z(nr, np.uint32), "read_len": self._z(nr, np.int64),
                "read_status": self._z(nr, np.int32), "aln_ptr": self._z(nr + 1, np.uint32)})

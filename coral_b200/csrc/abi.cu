@@ -48,7 +48,7 @@ void coral_destroy(coral_ctx* c) {
     // coral_adopt_stream destroys this ctx before, or synchronises, the owner — sharded.py keeps the owner alive)
     if (c->stream && c->owns_stream) cudaStreamSynchronize(c->stream);
     if (c->host_registered) cudaHostUnregister(c->host_registered);
-    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status, &c->scan_status, &c->sa_side, &c->sa_side_off, &c->xmsg[0], &c->xmsg[1], &c->xmsg[2], &c->xmsg[3],
+    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status, &c->scan_status, &c->sa_side, &c->sa_side_off, &c->xmsg[0], &c->xmsg[1], &c->xmsg[2], &c->xmsg[3], &c->scan_order, &c->pack_buf,
                      &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->s6, &c->s7, &c->cub_tmp,
                      &c->rt.tid, &c->rt.pos, &c->rt.endpos, &c->rt.flag_mapq, &c->rt.lseq, &c->rt.ncig, &c->rt.infer,
                      &c->rt.mbases, &c->rt.nonacgt, &c->rt.fbs, &c->rt.lbe, &c->rt.name_lo, &c->rt.name_hi,
@@ -100,6 +100,7 @@ int coral_set_option(coral_ctx* c, const char* name, int64_t value) {
     if (std::string(name) == "full_name_sort") { c->force_full_name_sort = value != 0; return CORAL_OK; }
     if (std::string(name) == "fetch_part_world") { if (value < 1 || value > 16) return CORAL_E_ARG; c->fetch_part_world = (int32_t)value; c->pass.invalidate(); return CORAL_OK; }
     if (std::string(name) == "fetch_part_rank") { if (value < 0 || value > 15) return CORAL_E_ARG; c->fetch_part_rank = (int32_t)value; c->pass.invalidate(); return CORAL_OK; }
+    if (std::string(name) == "scan_order") { if (value < 0 || value > 2) return CORAL_E_ARG; c->scan_order_mode = (int)value; c->scan_order_valid = false; return CORAL_OK; }
     if (std::string(name) == "pass_fork") { c->pass.fork = value != 0; return CORAL_OK; }
     if (std::string(name) == "pass_scan_reserve") { c->pass.scan_reserve = value; return CORAL_OK; }
     if (std::string(name) == "pass_overlap_scan") { c->pass.overlap_scan = value != 0; c->pass.invalidate(); return CORAL_OK; }
@@ -136,6 +137,7 @@ int coral_load_records(coral_ctx* c, const uint8_t* recs, uint64_t nbytes, const
     c->loaded = false;
     c->rows_only = false;
     for (auto& q : c->rows_fill_ptr) q = nullptr;     // the scan rewrites the columns coral_unpack_rows keeps constant
+    c->scan_order_valid = false;
     c->sa_side_valid = false;
     c->pass.invalidate();                  // recorded sizes belong to the previous records
     if (c->pass.active) { c->err = "coral_load_records inside a pass"; return CORAL_E_STATE; }

@@ -278,6 +278,11 @@ struct coral_ctx {
     DevBuf sa_side, sa_side_off;          // SA strings copied to HBM by the pre-scan, and where each record's sits
     bool sa_side_valid = false;
     bool scan_lazy = false;               // CORAL_RECORDS_HOST_MAPPED_LAZY: pre-scan done, full scan not started yet
+    DevBuf pack_buf;                      // coral_get_chimeric_packed: the table's columns side by side
+    DevBuf scan_order;                    // the record queue's permutation (largest records first), built once per load
+    size_t scan_order_at = 0;
+    bool scan_order_valid = false;
+    int scan_order_mode = 2;              // option "scan_order"
 
     // scratch
     DevBuf s0, s1, s2, s3, s4, s5, s6, s7;

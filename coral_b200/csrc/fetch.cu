@@ -23,11 +23,14 @@ namespace coral {
 // part_world > 1 (rows-only ctx of the multi-GPU engine): this rank only parses the reads whose name hash falls into
 // its residue class — every rank holds all gathered rows, the reads are split N ways, the parsed tables are merged
 // (chimeric_merge.cu)
-__global__ void k_flag_sa(int64_t n, const uint32_t* __restrict__ sa_off, const uint64_t* __restrict__ name_lo,
-                          uint32_t part_rank, uint32_t part_world, uint8_t* __restrict__ flag) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) flag[i] = sa_off[i] != 0 && (part_world <= 1 || (uint32_t)((name_lo[i] >> 20) % part_world) == part_rank);
-}
+struct SaFlag {               // evaluated inside the ordered compaction (no flag array, no kernel of its own)
+    const uint32_t* sa_off;
+    const uint64_t* name_lo;
+    uint32_t part_rank, part_world;
+    __host__ __device__ uint8_t operator()(uint32_t i) const {
+        return sa_off[i] != 0 && (part_world <= 1 || (uint32_t)((name_lo[i] >> 20) % part_world) == part_rank);
+    }
+};
 
 // warp per SA record: number of entries of s[:-1].split(';')
 __global__ void k_count_entries(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off,
@@ -42,7 +45,10 @@ __global__ void k_count_entries(const uint8_t* __restrict__ recs, const uint64_t
     uint32_t cnt = 0;
     for (uint32_t b = lane; b < len; b += 32) cnt += s[b] == ';';
     cnt = (uint32_t)warp_sum_i64(cnt);
-    if (lane == 0) n_ent[w] = cnt + 1;
+    if (lane == 0) {
+        n_ent[w] = cnt + 1;
+        if (w == 0) n_ent[n_sa] = 0;       // the scan below runs over n_sa + 1 elements (its last output = the total)
+    }
 }
 
 // ---- 2. ------------------------------------------------------------------------------------------
@@ -169,11 +175,13 @@ __global__ void k_parse_entries(const uint8_t* __restrict__ recs, const uint64_t
 // ---- 4. ------------------------------------------------------------------------------------------
 // iota (nullable): also writes the identity permutation (saves a launch before the first sort)
 __global__ void k_gather_name(int64_t n, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
-                              const uint64_t* __restrict__ name, uint64_t* __restrict__ key, uint32_t* __restrict__ iota) {
+                              const uint64_t* __restrict__ name, uint64_t* __restrict__ key, uint32_t* __restrict__ iota,
+                              uint32_t* __restrict__ zero_word) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     key[i] = name[ent[perm ? perm[i] : i].rec];
     if (iota) iota[i] = (uint32_t)i;
+    if (zero_word && i == 0) *zero_word = 0;       // k_heads' "mixed" flag of this round
 }
 __global__ void k_iota(int64_t n, uint32_t* p) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -240,9 +248,11 @@ __global__ void k_first_primary(int64_t n_rec, const uint32_t* __restrict__ flag
 __global__ void k_seg_names(int64_t n_seg, const SaEntry* __restrict__ ent, const uint32_t* __restrict__ perm,
                             const uint32_t* __restrict__ seg_start, const uint64_t* __restrict__ nlo,
                             const uint64_t* __restrict__ nhi, uint64_t* __restrict__ seg_lo, uint64_t* __restrict__ seg_hi,
-                            uint64_t* __restrict__ seg_first_emit, uint32_t* __restrict__ first_primary) {
+                            uint64_t* __restrict__ seg_first_emit, uint32_t* __restrict__ first_primary,
+                            uint32_t* __restrict__ seg_idx) {
     int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_seg) return;
+    seg_idx[s] = (uint32_t)s;
     const uint32_t e0 = perm[seg_start[s]];  // stable sort => smallest emission index of the segment
     const uint32_t rec = ent[e0].rec;
     seg_lo[s] = nlo[rec];
@@ -451,9 +461,21 @@ int coral_run_fetch(coral_ctx* c) {
     uint8_t* d_flag = c->s0.as<uint8_t>();
     uint32_t* d_sa_rec = c->s1.as<uint32_t>();
     uint32_t* d_cnt = d_sa_rec + std::max<int64_t>(n, 1);
-    LAUNCH_1D(k_flag_sa, n, n, rt.sa_off.as<uint32_t>(), rt.name_lo.as<uint64_t>(), (uint32_t)c->fetch_part_rank,
-              (uint32_t)c->fetch_part_world, d_flag);
-    CORAL_TRY(select_flagged_iota(c, d_flag, d_sa_rec, d_cnt, n));
+    (void)d_flag;
+    {
+        cub::CountingInputIterator<uint32_t> iota(0);
+        cub::TransformInputIterator<uint8_t, SaFlag, cub::CountingInputIterator<uint32_t>> flags(
+            iota, SaFlag{rt.sa_off.as<uint32_t>(), rt.name_lo.as<uint64_t>(), (uint32_t)c->fetch_part_rank, (uint32_t)c->fetch_part_world});
+        if (n > 0) {
+            size_t bytes = 0;
+            CORAL_CUDA(c, cub::DeviceSelect::Flagged(nullptr, bytes, iota, flags, d_sa_rec, d_cnt, (int)n, c->stream));
+            CORAL_CUDA(c, c->cub_tmp.ensure(bytes));
+            CORAL_CUDA(c, cub::DeviceSelect::Flagged(c->cub_tmp.p, bytes, iota, flags, d_sa_rec, d_cnt, (int)n, c->stream));
+            c->n_launches += 1;
+        } else {
+            CORAL_CUDA(c, cudaMemsetAsync(d_cnt, 0, 4, c->stream));
+        }
+    }
     uint32_t n_sa = 0;
     // the per-block partial sums are a RESULT (inside a pipelined pass they arrive at coral_pass_end) ...
     auto part = std::make_shared<std::vector<double>>((size_t)std::max<int64_t>(nblk, 1) * 4, 0.0);
@@ -476,7 +498,6 @@ int coral_run_fetch(coral_ctx* c) {
     uint32_t* d_nent = c->s2.as<uint32_t>();
     uint32_t* d_base = d_nent + n_sa + 1;
     LAUNCH_WARP(k_count_entries, n_sa, recs, off, d_sa_rec, (int64_t)n_sa, rt.sa_off.as<uint32_t>(), rt.sa_len.as<uint32_t>(), d_nent);
-    CORAL_CUDA(c, cudaMemsetAsync(d_nent + n_sa, 0, 4, c->stream));
     CORAL_TRY(exclusive_sum_u32(c, d_nent, d_base, (int64_t)n_sa + 1));
     uint32_t n_ent = 0;
     CORAL_TRY(pass_resolve_lazy(c, &n_ent, d_base + n_sa));
@@ -511,17 +532,16 @@ int coral_run_fetch(coral_ctx* c) {
     uint64_t name_key_mask = 0;
     for (int full = c->force_full_name_sort ? 1 : 0; full < 2; full++) {
         name_key_mask = full ? 0 : ((1ull << 40) - 1);
-        LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, (const uint32_t*)nullptr, rt.name_lo.as<uint64_t>(), key_a, perm_a);
+        LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, (const uint32_t*)nullptr, rt.name_lo.as<uint64_t>(), key_a, perm_a, d_mixed);
         if (!full) {
             CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_a, perm_b, n_ent, 0, 40));
             perm = perm_b;
         } else {
             CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_a, perm_b, n_ent));
-            LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, perm_b, rt.name_hi.as<uint64_t>(), key_a, (uint32_t*)nullptr);
+            LAUNCH_1D(k_gather_name, (int64_t)n_ent, (int64_t)n_ent, ent, perm_b, rt.name_hi.as<uint64_t>(), key_a, (uint32_t*)nullptr, (uint32_t*)nullptr);
             CORAL_TRY(sort_pairs_u64(c, key_a, key_b, perm_b, perm_a, n_ent));
             perm = perm_a;
         }
-        CORAL_CUDA(c, cudaMemsetAsync(d_mixed, 0, 4, c->stream));
         LAUNCH_1D(k_heads, (int64_t)n_ent, (int64_t)n_ent, ent, perm, rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(),
                   full ? ~0ull : name_key_mask, head, d_mixed);
         CORAL_TRY(inclusive_sum_u32(c, head, head, n_ent));
@@ -545,7 +565,7 @@ int coral_run_fetch(coral_ctx* c) {
     uint32_t* order = seg_idx + n_seg;
     int32_t* seg_status = reinterpret_cast<int32_t*>(order + n_seg);
     LAUNCH_1D(k_seg_names, (int64_t)n_seg, (int64_t)n_seg, ent, perm, seg_start, rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(),
-              seg_lo, seg_hi, seg_emit, first_primary);
+              seg_lo, seg_hi, seg_emit, first_primary, seg_idx);
     LAUNCH_1D(k_first_primary, n, n, rt.flag_mapq.as<uint32_t>(), rt.name_lo.as<uint64_t>(), rt.name_hi.as<uint64_t>(), (int64_t)n_seg,
               seg_lo, seg_hi, name_key_mask, first_primary);
 
@@ -558,7 +578,6 @@ int coral_run_fetch(coral_ctx* c) {
     uint32_t* seg_cnt = c->s0.as<uint32_t>();
     uint32_t* cnt_ranked = seg_cnt + n_seg;
     LAUNCH_1D(k_read_counts, (int64_t)n_seg, (int64_t)n_seg, (int64_t)n_ent, ent, perm, seg_start, keep, first_primary, seg_status, seg_cnt);
-    LAUNCH_1D(k_iota, (int64_t)n_seg, (int64_t)n_seg, seg_idx);
     int emit_bits = 1;                                            // keys are entry indices < n_ent
     while (emit_bits < 32 && ((uint64_t)1 << emit_bits) < (uint64_t)n_ent) emit_bits++;
     CORAL_TRY(sort_pairs_u64(c, seg_emit, seg_emit_sorted, seg_idx, order, n_seg, 0, emit_bits));
@@ -685,6 +704,61 @@ extern "C" int coral_get_chimeric(coral_ctx* c, uint32_t* read_first_rec, int64_
     if (strand) CORAL_TRY(d2h_result(c, strand, T.strand.p, na));
     if (mapq) CORAL_TRY(d2h_result(c, mapq, T.mapq.p, na));
     if (nm) CORAL_TRY(d2h_result(c, nm, T.nm.p, na));
+    return pass_sync(c);
+}
+
+// ---- the whole chimeric table in ONE result copy ------------------------------------------------------------------
+namespace coral {
+struct ColPack {
+    const uint8_t* src[12];
+    uint64_t dst_off[12], bytes[12];
+};
+__global__ void k_pack_cols(ColPack p, uint8_t* __restrict__ out) {
+    const int seg = blockIdx.y;
+    const uint8_t* src = p.src[seg];
+    uint8_t* dst = out + p.dst_off[seg];
+    const uint64_t nb = p.bytes[seg], nw = nb >> 2;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint64_t i = t; i < nw; i += stride) reinterpret_cast<uint32_t*>(dst)[i] = reinterpret_cast<const uint32_t*>(src)[i];
+    if (t < (nb & 3)) dst[4 * nw + t] = src[4 * nw + t];
+}
+}  // namespace coral
+
+// coral_get_chimeric with all twelve columns in one caller buffer: column k starts at offsets[k] (64-byte aligned, in the
+// order of coral_get_chimeric's arguments).  One packing kernel + ONE device-to-host copy instead of twelve (inside a
+// pipelined pass both run on the pass's side stream); out_bytes must hold offsets[11] + 8 * n_alignments.
+extern "C" int coral_get_chimeric_packed(coral_ctx* c, uint8_t* out, uint64_t out_bytes, uint64_t* offsets) {
+    coral::PassLane lane__(c);
+    using namespace coral;
+    if (!c || !out || !offsets) return CORAL_E_ARG;
+    if (!c->chim.valid) { c->err = "coral_get_chimeric_packed before coral_fetch"; return CORAL_E_STATE; }
+    cudaSetDevice(c->device);
+    ChimericTable& T = c->chim;
+    const uint64_t nr = (uint64_t)T.n_reads, na = (uint64_t)T.n_aln;
+    const uint64_t sizes[12] = {nr * 4, nr * 8, nr * 4, (nr + 1) * 4, na * 4, na * 4, na * 4, na * 4, na * 4, na, na * 4, na * 8};
+    const void* srcs[12] = {T.read_first_rec.p, T.read_len.p, T.read_status.p, T.aln_ptr.p, T.qs.p, T.qe.p, T.tid.p, T.rs.p, T.re.p,
+                            T.strand.p, T.mapq.p, T.nm.p};
+    uint64_t total = 0;
+    ColPack p;
+    uint64_t most = 0;
+    for (int k = 0; k < 12; k++) {
+        offsets[k] = total;
+        p.src[k] = static_cast<const uint8_t*>(srcs[k]); p.dst_off[k] = total; p.bytes[k] = nr == 0 ? 0 : sizes[k];
+        most = std::max(most, sizes[k]);
+        total += (sizes[k] + 63) & ~(uint64_t)63;
+    }
+    if (out_bytes < total) { c->err = "coral_get_chimeric_packed: buffer too small"; return CORAL_E_ARG; }
+    if (nr == 0) { memset(out + offsets[3], 0, 4); return CORAL_OK; }
+    CORAL_CUDA(c, c->pack_buf.ensure(total));
+    CORAL_TRY(pass_side_begin(c, SIDE_CHIM));  // the table stays as it is until the next coral_fetch / merge
+    PassState& P = c->pass;
+    cudaStream_t st = (P.active && P.side_on) ? P.side_stream : c->stream;
+    const unsigned bx = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>((most / 4 + 1023) / 1024, 64));
+    k_pack_cols<<<dim3(bx, 12), 256, 0, st>>>(p, c->pack_buf.as<uint8_t>());
+    c->n_launches++;
+    CORAL_CUDA(c, cudaGetLastError());
+    CORAL_TRY(d2h_result(c, out, c->pack_buf.p, (size_t)total));
     return pass_sync(c);
 }
 

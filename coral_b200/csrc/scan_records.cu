@@ -293,8 +293,12 @@ enum { G_NEW = 0, G_R1 = 1, G_AUX = 2, G_DONE = 3 };
 
 // Lane 0: produce the next segment of the warp's record stream into stage s.
 // `ahead` = record index fetched from the queue one grab early (the atomic's latency is off the critical path).
+// `order` (nullable): the queue hands out positions of this permutation instead of record indices — records sorted by
+// decreasing size, so that the longest records (a 120 kb ONT read takes a warp > 100 us) start first and the kernel's
+// tail is made of the shortest ones.
 __device__ __noinline__ uint32_t gen_next(uint32_t ctl, uint32_t s, const uint8_t* __restrict__ recs,
-                                          const uint64_t* __restrict__ off, uint32_t n, unsigned int* queue, uint32_t ahead) {
+                                          const uint64_t* __restrict__ off, uint32_t n, unsigned int* queue, uint32_t ahead,
+                                          const uint32_t* __restrict__ order) {
     const uint32_t bar = ctl + WC_BAR + 8 * s;
     const uint32_t dst = lds32(ctl + WC_DESC + 16 * s + 12);
     uint4 g0 = lds128(ctl + WC_GEN), g1 = lds128(ctl + WC_GEN + 16);     // base lo/hi, rec, cov | r1_end, a0, a1, state
@@ -314,11 +318,12 @@ __device__ __noinline__ uint32_t gen_next(uint32_t ctl, uint32_t s, const uint8_
         flags = SF_VALID | SF_LAST | SF_AUX;
         g1.w = G_NEW;
     } else if ((st & 255u) == G_NEW) {
-        const uint32_t idx = ahead;
-        if (idx >= n) {
+        const uint32_t qpos = ahead;
+        if (qpos >= n) {
             g1.w = G_DONE;
         } else {
             ahead = atomicAdd(queue, 1u);
+            const uint32_t idx = order ? __ldg(order + qpos) : qpos;
             const uint64_t o0 = __ldg(off + idx), o1 = __ldg(off + idx + 1);
             const uint32_t len16 = (uint32_t)(o1 - o0);
             const uint4 ca = __ldg(reinterpret_cast<const uint4*>(recs + o0));
@@ -367,7 +372,8 @@ __device__ __noinline__ uint32_t gen_next(uint32_t ctl, uint32_t s, const uint8_
 #endif
 __global__ void __launch_bounds__(SC_WARPS * 32, SC_MINB)
 k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ off, uint32_t n, int32_t min_del_len,
-               ScanCols o, ScanEvents ev, int32_t* __restrict__ status, unsigned int* __restrict__ queue, uint32_t write_aux) {
+               ScanCols o, ScanEvents ev, int32_t* __restrict__ status, unsigned int* __restrict__ queue, uint32_t write_aux,
+               const uint32_t* __restrict__ order) {
     extern __shared__ __align__(128) uint8_t smem[];
     const uint32_t lane = lane_id();
     const uint32_t warp = threadIdx.x >> 5;
@@ -387,7 +393,7 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
         ahead = atomicAdd(queue, 1u);
 #pragma unroll 1
         for (uint32_t s = 0; s < SC_NST; s++)
-            ahead = gen_next(ctl, s, recs, off, n, queue, ahead);
+            ahead = gen_next(ctl, s, recs, off, n, queue, ahead, order);
     }
     __syncwarp();
 
@@ -688,7 +694,7 @@ k_scan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__ of
             }
         }
         __syncwarp();          // every lane is done with the stage before the copy engine overwrites it
-        if (lane == 0) ahead = gen_next(ctl, s, recs, off, n, queue, ahead);
+        if (lane == 0) ahead = gen_next(ctl, s, recs, off, n, queue, ahead, order);
         __syncwarp();
     }
 }
@@ -804,6 +810,36 @@ k_prescan_records(const uint8_t* __restrict__ recs, const uint64_t* __restrict__
 namespace {
 using namespace coral;
 
+// size class of every record, larger first: key = 0xFFFF - min(size >> 9, 0xFFFF)
+__global__ void k_order_keys(int64_t n, const uint64_t* __restrict__ off, uint64_t big, uint64_t* __restrict__ key, uint32_t* __restrict__ idx) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t sz = off[i + 1] - off[i];
+    key[i] = big ? (sz >= big ? 0u : 1u) : 0xFFFFu - min(sz >> 9, (uint64_t)0xFFFFu);
+    idx[i] = (uint32_t)i;
+}
+
+// The permutation the record queue of k_scan_records follows (option "scan_order": 2 = records by decreasing size class,
+// stable, the default; 1 = records of more than twice the mean size first, the rest in file order; 0 = file order).
+// Built once per load on the ctx's stream (the offsets do not change between rescans).  nullptr = file order.
+const uint32_t* scan_order(coral_ctx* ctx) {
+    using namespace coral;
+    const int64_t n = ctx->nrec;
+    if (ctx->scan_order_mode == 0 || n < 2) return nullptr;
+    if (ctx->scan_order_valid) return ctx->scan_order.as<uint32_t>() + ctx->scan_order_at;
+    if (ctx->scan_order.ensure((size_t)n * 8) != cudaSuccess || ctx->s4.ensure((size_t)n * 16) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    uint64_t* key_a = ctx->s4.as<uint64_t>(); uint64_t* key_b = key_a + n;
+    uint32_t* idx = ctx->scan_order.as<uint32_t>(); uint32_t* out = idx + n;
+    const uint64_t big = ctx->scan_order_mode == 1 ? 2 * (ctx->nbytes / (uint64_t)n) : 0;
+    k_order_keys<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, ctx->d_off.as<uint64_t>(), big, key_a, idx);
+    ctx->n_launches++;
+    coral_ctx* c = ctx;
+    if (sort_pairs_u64(c, key_a, key_b, idx, out, n, 0, big ? 1 : 16) != CORAL_OK) return nullptr;
+    ctx->scan_order_at = (size_t)n;
+    ctx->scan_order_valid = true;
+    return out;
+}
+
 int scan_ensure_tables(coral_ctx* ctx) {
     const int64_t n = ctx->nrec;
     RecordTable& t = ctx->rt;
@@ -880,6 +916,7 @@ int coral_start_scan_async(coral_ctx* ctx, bool launch_full_scan) {
     const int64_t n = ctx->nrec;
     CORAL_TRY(scan_ensure_tables(ctx));
     if (!ctx->scan_stream) CORAL_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->scan_stream, cudaStreamNonBlocking));
+    const uint32_t* ord = scan_order(ctx);       // (built on the ctx's stream, ahead of everything below)
     GapEvents& g = ctx->gaps;
     CORAL_CUDA(ctx, cudaMemsetAsync(g.counter.p, 0, 16, ctx->stream));
     CORAL_CUDA(ctx, cudaMemsetAsync(ctx->scan_status.p, 0, 64, ctx->stream));
@@ -924,7 +961,7 @@ int coral_start_scan_async(coral_ctx* ctx, bool launch_full_scan) {
     cudaEventRecord(ctx->ev_beg[CORAL_STAGE_SCAN], ctx->scan_stream);
     k_scan_records<<<blocks, SC_WARPS * 32, SC_SMEM_TOTAL, ctx->scan_stream>>>(
         ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, ctx->prm.min_del_len, o, e, ctx->scan_status.as<int32_t>(),
-        reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1), 0u);
+        reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1), 0u, ord);
     cudaEventRecord(ctx->ev_end[CORAL_STAGE_SCAN], ctx->scan_stream);
     ctx->ev_valid[CORAL_STAGE_SCAN] = true;
     ctx->n_launches++;
@@ -953,6 +990,7 @@ int coral_start_scan_overlapped(coral_ctx* ctx) {
     CORAL_TRY(scan_ensure_tables(ctx));
     if (!ctx->scan_stream) CORAL_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->scan_stream, cudaStreamNonBlocking));
     if (!ctx->ev_fork) CORAL_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    const uint32_t* ord = scan_order(ctx);
     GapEvents& g = ctx->gaps;
     CORAL_CUDA(ctx, cudaMemsetAsync(g.counter.p, 0, 16, ctx->stream));
     CORAL_CUDA(ctx, cudaMemsetAsync(ctx->scan_status.p, 0, 64, ctx->stream));
@@ -984,7 +1022,7 @@ int coral_start_scan_overlapped(coral_ctx* ctx) {
     cudaEventRecord(ctx->ev_beg[CORAL_STAGE_SCAN], ctx->scan_stream);
     k_scan_records<<<blocks, SC_WARPS * 32, SC_SMEM_TOTAL, ctx->scan_stream>>>(
         ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, ctx->prm.min_del_len, o, e, ctx->scan_status.as<int32_t>(),
-        reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1), 0u);
+        reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1), 0u, ord);
     cudaEventRecord(ctx->ev_end[CORAL_STAGE_SCAN], ctx->scan_stream);
     ctx->ev_valid[CORAL_STAGE_SCAN] = true;
     ctx->n_launches++;
@@ -1044,7 +1082,7 @@ int coral_run_scan(coral_ctx* ctx) {
             ctx->stage_begin(CORAL_STAGE_SCAN);
             k_scan_records<<<blocks, SC_WARPS * 32, SC_SMEM_TOTAL, ctx->stream>>>(
                 ctx->d_recs, ctx->d_off.as<uint64_t>(), (uint32_t)n, ctx->prm.min_del_len, o, e, ctx->scan_status.as<int32_t>(),
-                reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1), 1u);
+                reinterpret_cast<unsigned int*>(g.counter.as<unsigned long long>() + 1), 1u, scan_order(ctx));
             ctx->stage_end(CORAL_STAGE_SCAN);
             ctx->n_launches++;
             CORAL_CUDA(ctx, cudaGetLastError());

@@ -233,6 +233,11 @@ int coral_get_chimeric(coral_ctx* ctx, uint32_t* read_first_rec, int64_t* read_l
                        uint32_t* aln_ptr, int32_t* qs, int32_t* qe, int32_t* tid, int32_t* rstart, int32_t* rend,
                        uint8_t* strand, int32_t* mapq, int64_t* nm);
 
+/* The same table with all twelve columns in ONE caller buffer: column k (in the order of coral_get_chimeric's arguments)
+ * starts at offsets[k] (64-byte aligned); one packing kernel + one device-to-host copy instead of twelve copies.
+ * out_bytes >= sum over the columns of their sizes rounded up to 64 (n_reads / n_alignments from coral_fetch). */
+int coral_get_chimeric_packed(coral_ctx* ctx, uint8_t* out, uint64_t out_bytes, uint64_t* offsets);
+
 /* ---- multi-GPU exchange of `fetch` (one process per GPU, each holding a contiguous range of the file) --------
  * The reference unions the SA strings of all records of a read name in file order and takes read_length from
  * the first record with flag < 256 anywhere in the file (ibg:142-151).  A rank exports one row per SA-bearing

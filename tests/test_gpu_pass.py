@@ -129,6 +129,12 @@ def test_pipelined_pass_equals_call_by_call(built_lib, dataset, cfg_name, scale)
     ctx.pass_end()
     _same(_canon(got3), want2)
     assert np.array_equal(tab["endpos"], t["endpos"])
+    # result arrays in the ctx's page-locked arena (direct DMA, the chimeric table as one packed copy): same values
+    for k in range(2):
+        ctx.pass_begin(pinned_results=True)
+        got5 = _calls(ctx, plan, 5.0)
+        ctx.pass_end()
+        _same(_canon(got5), want2)
     # new records invalidate the recorded sizes
     ctx.load_records(data.rec, data.rec_off)
     ctx.pass_begin()
