@@ -623,6 +623,7 @@ def main():
                     help="N > 1: the exchanges of the sharded pass as kernels over peer memory (NVLink, csrc/xchg.cu; the pass "
                          "is then one stream of kernels per rank) or as torch.distributed / NCCL collectives issued by the "
                          "host between kernels (the baseline this is measured against)")
+    ap.add_argument("--overlap-scan", action="store_true", help="N > 1: start the exchange chain next to the record scan (measured slower; development aid)")
     ap.add_argument("--e2e-placement", default="mapped_async", choices=["mapped", "mapped_async", "copy"],
                     help="e2e arm: kernels read the pinned host records in place over PCIe (mapped; mapped_async = fetch and "
                          "the host steps after it run next to the scan, the default at N=1: 172 vs 200 ms per C2 pass) or after a full "
@@ -773,6 +774,13 @@ def main():
     ctx = eng0._ctx
     if world > 1:
         eng0.materialise = rank == 0       # the replicated result tables are delivered to rank 0's host only
+        if xchg is not None and a.overlap_scan:
+            # the exchange chain of a sharded pass (three all-gathers, the rank's share of fetch, the merge: ~100 small
+            # kernels) next to the record scan: coral_rescan = pre-scan + full scan on its own stream with 74 block slots
+            # left free.  Measured at N = 2: 2.42 ms per step against 2.15 ms with the chain behind the scan (the pre-scan
+            # costs 0.2 ms and the small kernels run at half speed next to the scan) -> off by default
+            ctx.set_option("pass_overlap_scan", 1)
+            ctx.set_option("pass_scan_reserve", 74)
     tab = ctx.record_table()
     aligned = int(tab["aligned_bases"].sum())
     n_bp = len(eng0.new_bp_list)

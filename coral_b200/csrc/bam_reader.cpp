@@ -77,11 +77,14 @@ int coral_bam_read(const char* path, int n_threads, coral_bam** out, char* err, 
         int64_t bsize = -1;
         while (q + 4 <= xend && xend <= fsz) {
             const uint32_t slen = rd16(&raw[q + 2]);
+            if (q + 4 + slen > xend) break;                       // a subfield that overruns the extra field: not read
             if (raw[q] == 'B' && raw[q + 1] == 'C' && slen == 2) bsize = rd16(&raw[q + 4]);
             q += 4 + slen;
         }
         if (bsize < 0 || p + (uint64_t)bsize + 1 > fsz) { set_err(err, err_len, "bad BGZF BC field"); return CORAL_E_FORMAT; }
         const uint64_t mend = p + (uint64_t)bsize + 1;
+        // the member must hold its header, extra field, CRC32 and ISIZE: otherwise the CDATA length below underflows
+        if (xend > fsz || mend < xend + 8) { set_err(err, err_len, "BGZF member shorter than its own header at offset " + std::to_string(p)); return CORAL_E_FORMAT; }
         const uint32_t isize = rd32(&raw[mend - 4]);
         mem.push_back({xend, mend - 8 - xend, total, isize});
         total += isize;

@@ -316,7 +316,9 @@ extern "C" {
 int coral_pack_sa_rows(coral_ctx* c, uint64_t* d_msg, uint64_t* nbytes) {
     if (!c) return CORAL_E_ARG;
     if (!c->loaded || c->rows_only) { c->err = "coral_pack_sa_rows needs a ctx with records"; return CORAL_E_STATE; }
-    CORAL_TRY(coral_wait_scan(c));
+    // like coral_fetch, the packing kernels only read columns of the pre-scan (core fields, name hash, SA / NM location)
+    // and record text: inside a pass whose rescan runs overlapped they start next to the full scan instead of joining it
+    if (!(c->pass.active && c->scan_pending)) CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
     coral::PassLane lane__(c);          // part of the chimeric chain: second lane inside a pipelined pass
     if (c->pass.active) pass_call(c, pass_hash(PASS_H0, "pack_sa_rows", 12));
@@ -334,7 +336,7 @@ int coral_pack_extra_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf, c
                           uint64_t* nbytes) {
     if (!c || !d_buf || !starts) return CORAL_E_ARG;
     if (!c->loaded || c->rows_only) { c->err = "coral_pack_extra_rows needs a ctx with records"; return CORAL_E_STATE; }
-    CORAL_TRY(coral_wait_scan(c));
+    if (!(c->pass.active && c->scan_pending)) CORAL_TRY(coral_wait_scan(c));
     cudaSetDevice(c->device);
     coral::PassLane lane__(c);
     if (c->pass.active) {

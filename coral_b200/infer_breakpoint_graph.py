@@ -84,7 +84,7 @@ class bam_to_breakpoint_nanopore(HostSteps):
         self._parse_cns(cns)
         segs, total = self._median_cn_segments()
         order = sorted(range(len(segs)), key=lambda k: (self._tid[segs[k][0]], segs[k][1]))
-        self._normal_pending = ([segs[k] for k in order], total)
+        self._normal_pending = ([segs[k] for k in order], total, self.min_bp_cov_factor)   # the factor as of this call
         if not self._scan_async:
             self._resolve_normal_cov()
 
@@ -94,11 +94,11 @@ class bam_to_breakpoint_nanopore(HostSteps):
         pending, self._normal_pending = self._normal_pending, None
         if pending is None:
             return
-        segs, total = pending
+        segs, total, factor = pending
         nnc = self._coverage_sum(segs)
         self._normal_cov = nnc * 1.0 / total
         logging.info(_t() + "LR normal cov = %f." % (self._normal_cov))
-        self._min_cluster_cutoff = max(self._min_cluster_cutoff, self.min_bp_cov_factor * self._normal_cov)
+        self._min_cluster_cutoff = max(self._min_cluster_cutoff, factor * self._normal_cov)
 
     @property
     def normal_cov(self):
@@ -108,6 +108,8 @@ class bam_to_breakpoint_nanopore(HostSteps):
 
     @normal_cov.setter
     def normal_cov(self, v):
+        if self._normal_pending is not None:      # the reference's "last assignment wins": read_cns's own assignment first
+            self._resolve_normal_cov()
         self._normal_cov = v
 
     @property
@@ -118,6 +120,8 @@ class bam_to_breakpoint_nanopore(HostSteps):
 
     @min_cluster_cutoff.setter
     def min_cluster_cutoff(self, v):
+        if self._normal_pending is not None:
+            self._resolve_normal_cov()
         self._min_cluster_cutoff = v
 
     def _coverage_sum(self, segs):

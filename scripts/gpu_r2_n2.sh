@@ -12,14 +12,20 @@ run() {  # name, extra args...
   echo "$name rc=$?" >> gpurun_out/rc_n${N}.txt
 }
 : > gpurun_out/rc_n${N}.txt
-run peer
-run nccl --exchange nccl
-run c4 --workload C4
+RUNS=${2:-"peer nccl c4"}
+for r in $RUNS; do
+  case $r in
+    peer) run peer ;;
+    nccl) run nccl --exchange nccl ;;
+    c4) run c4 --workload C4 ;;
+    c5) run c5 --workload C5 ;;
+  esac
+done
 cat gpurun_out/rc_n${N}.txt
 python - $N <<'PY'
 import json, sys
 N = sys.argv[1]
-for k in ("peer", "nccl", "c4"):
+for k in ("peer", "nccl", "c4", "c5"):
     try:
         d = json.loads(open("gpurun_out/n%s_%s.json" % (N, k)).read().strip().splitlines()[-1])
         print(k, "ms/step", round(d["ms_per_step"], 3), "rec/s", round(d["value"] / 1e6, 1), "M launches", d["gpu_launches"], "e2e ms", round(d["e2e"]["ms_per_step"], 1),
@@ -28,6 +34,8 @@ for k in ("peer", "nccl", "c4"):
         print("   ", {a: round(b, 3) for a, b in d.get("fetch_exchange_ms_per_step", {}).items()})
         print("   ", {a: round(b, 3) for a, b in d["stage_ms_per_step"].items()})
         if d["parity_ok"] is not True: print("   parity:", json.dumps(d.get("parity"))[:1500])
+    except FileNotFoundError:
+        pass
     except Exception as e:
         print(k, "parse failed", e); print(open("gpurun_out/n%s_%s.err" % (N, k)).read()[-2500:])
 PY

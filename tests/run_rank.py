@@ -144,7 +144,10 @@ def pass_mode(comm, case, out_path):
     plan = bench.build_plan(eng, cns)
     eng.materialise = True
     info = {"replayed": [], "bad": []}
-    for it in range(4):
+    for it in range(7):
+        if it == 4:       # the exchange chain next to the record scan (pre-scan + full scan on its own stream)
+            eng._ctx.set_option("pass_overlap_scan", 1)
+            eng._ctx.set_option("pass_scan_reserve", 74)
         got = bench.sharded_device_pass(eng, plan, gpu_ops, pipelined=(it > 0))
         info["replayed"].append(bool(got.get("replayed")))
         bad = same(want["fetch"], got["fetch"], skip=("read_first_rec", "nm_sum", "nm_sumsq"))
