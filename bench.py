@@ -153,7 +153,7 @@ WORKLOADS = {
     "C2": ("C2", {}, "C2 multi-segment ecDNA: 3 seeds/6 Mb, CN 40, 50x ONT 30 kb"),
     "C3": ("C3", {}, "C3 small-deletion-heavy amplicon: 60x HiFi 15 kb, 300 in-CIGAR deletions, dense D ops"),
     "C1": ("C1", {}, "C1 single ecDNA: 2 Mb amplicon, 4 SVs, 30x ONT 20 kb"),
-    "C1n": ("C1", {"p_n": 0.001}, "C1 single ecDNA with 0.1 % N bases (non-ACGT slow path of coverage)"),
+    "C1n": ("full_c1n", {}, "C1 single ecDNA with 0.1 % N bases (non-ACGT slow path of coverage)"),
     # BASELINE.json configs[3] / [4] on the sub-samples the unmodified reference could be run on in the build container
     # (tests/golden/full_digest.py: sub_c4, sub_c5 — committed reference digests).  With --gpus N > 1 ONE file is cut into N
     # contiguous genomic-bin shards (strong scaling): chimeric reads cross the shard cuts at every junction
@@ -166,12 +166,16 @@ STRONG = ("C4", "C5")          # workloads that are one file cut into N shards w
 def workload_config(scale, seed_shift=0, workload="C2"):
     from sim import configs
     name, over, _ = WORKLOADS[workload]
-    if name.startswith("sub_"):
+    if name.startswith("sub_") or name.startswith("full_"):      # the very configs the committed reference digests were made on
         sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
         import full_digest as FD
-        if scale != 1.0:
+        if name.startswith("sub_") and scale != 1.0:
             raise SystemExit("--workload %s is a fixed sub-sample (its reference digest is committed): use --scale 1.0" % workload)
-        return FD.make_cfg(name)
+        cname, kw, over, _ = FD.FULL_CASES[name]
+        cfg = configs.CONFIGS[cname](**dict(kw, scale=kw.get("scale", 1.0) * scale))
+        for k, v in over.items():
+            setattr(cfg, k, v)
+        return cfg
     if name == "C2":
         cfg = configs.c2_multi_segment(scale=scale, seed=20240215 + 2 + 1000 * seed_shift)
     else:

@@ -48,7 +48,7 @@ void coral_destroy(coral_ctx* c) {
     // coral_adopt_stream destroys this ctx before, or synchronises, the owner — sharded.py keeps the owner alive)
     if (c->stream && c->owns_stream) cudaStreamSynchronize(c->stream);
     if (c->host_registered) cudaHostUnregister(c->host_registered);
-    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status, &c->scan_status, &c->sa_side, &c->sa_side_off, &c->xmsg[0], &c->xmsg[1], &c->xmsg[2], &c->xmsg[3], &c->scan_order, &c->pack_buf,
+    DevBuf* all[] = {&c->d_chr_rank, &c->d_ref_hash, &c->recs_owned, &c->d_off, &c->d_ordinal, &c->status, &c->scan_status, &c->sa_side, &c->sa_side_off, &c->xmsg[0], &c->xmsg[1], &c->xmsg[2], &c->xmsg[3], &c->scan_order, &c->pack_buf, &c->nm_part,
                      &c->s0, &c->s1, &c->s2, &c->s3, &c->s4, &c->s5, &c->s6, &c->s7, &c->cub_tmp,
                      &c->rt.tid, &c->rt.pos, &c->rt.endpos, &c->rt.flag_mapq, &c->rt.lseq, &c->rt.ncig, &c->rt.infer,
                      &c->rt.mbases, &c->rt.nonacgt, &c->rt.fbs, &c->rt.lbe, &c->rt.name_lo, &c->rt.name_hi,

@@ -69,8 +69,17 @@ struct ChimColsW {
 
 __global__ void k_put_chim_hdr(MsgHdr* h, MsgHdr v) { *h = v; }
 
-__global__ void k_pack_chim(int64_t n_reads, int64_t n_aln, ChimColsC t, ChimRead* __restrict__ reads, ChimAln* __restrict__ alns) {
+// (the first thread also writes the header and zeroes the padding behind the reads and behind the alignments)
+__global__ void k_pack_chim(int64_t n_reads, int64_t n_aln, ChimColsC t, ChimRead* __restrict__ reads, ChimAln* __restrict__ alns,
+                            MsgHdr* __restrict__ hdr_out, MsgHdr hdr, uint32_t pad_reads, uint32_t pad_alns) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        *hdr_out = hdr;
+        uint8_t* p1 = reinterpret_cast<uint8_t*>(reads + n_reads);
+        for (uint32_t k = 0; k < pad_reads; k++) p1[k] = 0;
+        uint8_t* p2 = reinterpret_cast<uint8_t*>(alns + n_aln);
+        for (uint32_t k = 0; k < pad_alns; k++) p2[k] = 0;
+    }
     if (i < n_reads) {
         ChimRead r;
         r.first_rec = t.read_first_rec[i]; r.status = t.read_status[i]; r.read_len = t.read_len[i];
@@ -167,19 +176,16 @@ int coral_pack_chimeric(coral_ctx* c, uint64_t* d_msg, uint64_t* nbytes) {
     const uint64_t total = (sizeof(MsgHdr) + reads_bytes + na * sizeof(ChimAln) + 15) & ~(uint64_t)15;
     DevBuf& msg = c->xmsg[0];
     CORAL_CUDA(c, msg.ensure(total + 16));
-    // padding bytes first (they travel), then the header and the rows over them
-    CORAL_CUDA(c, cudaMemsetAsync(msg.as<uint8_t>() + total - 16, 0, 16, c->stream));
-    if (reads_bytes >= 16) CORAL_CUDA(c, cudaMemsetAsync(msg.as<uint8_t>() + sizeof(MsgHdr) + reads_bytes - 16, 0, 16, c->stream));
     MsgHdr h{};
     h.n_rows = nr; h.text_bytes = na; h.kind = MSG_CHIM;
-    k_put_chim_hdr<<<1, 1, 0, c->stream>>>(msg.as<MsgHdr>(), h);
-    c->n_launches++;
     ChimColsC t{T.read_first_rec.as<uint32_t>(), T.aln_ptr.as<uint32_t>(), T.read_len.as<int64_t>(), T.nm.as<int64_t>(),
                 T.read_status.as<int32_t>(), T.qs.as<int32_t>(), T.qe.as<int32_t>(), T.tid.as<int32_t>(), T.rs.as<int32_t>(),
                 T.re.as<int32_t>(), T.mapq.as<int32_t>(), T.strand.as<uint8_t>()};
-    const int64_t nthreads = (int64_t)std::max(nr, na);
+    const int64_t nthreads = (int64_t)std::max<uint64_t>(std::max(nr, na), 1);      // at least one thread: it writes the header
+    const uint64_t alns_bytes = total - sizeof(MsgHdr) - reads_bytes;
     LAUNCH_1D(k_pack_chim, nthreads, (int64_t)nr, (int64_t)na, t, reinterpret_cast<ChimRead*>(msg.as<uint8_t>() + sizeof(MsgHdr)),
-              reinterpret_cast<ChimAln*>(msg.as<uint8_t>() + sizeof(MsgHdr) + reads_bytes));
+              reinterpret_cast<ChimAln*>(msg.as<uint8_t>() + sizeof(MsgHdr) + reads_bytes), msg.as<MsgHdr>(), h,
+              (uint32_t)(reads_bytes - nr * sizeof(ChimRead)), (uint32_t)(alns_bytes - na * sizeof(ChimAln)));
     if (!c->pass.active) CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
     *d_msg = (uint64_t)reinterpret_cast<uintptr_t>(msg.p);
     *nbytes = total;
@@ -207,13 +213,11 @@ int coral_merge_chimeric(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf, co
         if (starts[r] & 15) { c->err = "message starts must be 16-byte aligned"; return CORAL_E_ARG; }
         set.base[r] = d_buf + starts[r];
     }
-    const int words = n_ranks * 8;
-    CORAL_CUDA(c, c->s7.ensure((size_t)words * 8));
-    k_chim_hdrs<<<1, words, 0, c->stream>>>(set, c->s7.as<uint64_t>());
-    c->n_launches++;
-    CORAL_CUDA(c, cudaGetLastError());
+    HdrPtrs hp;
+    hp.n = n_ranks;
+    for (int r = 0; r < n_ranks; r++) hp.base[r] = set.base[r];
     std::vector<MsgHdr> hdrs((size_t)n_ranks);
-    CORAL_TRY(pass_resolve_n(c, reinterpret_cast<uint64_t*>(hdrs.data()), c->s7.p, words));
+    CORAL_TRY(pass_resolve_hdrs(c, hp, reinterpret_cast<uint64_t*>(hdrs.data())));
     uint64_t R = 0, A = 0;
     set.row0[0] = 0;
     for (int r = 0; r < n_ranks; r++) {
@@ -240,7 +244,9 @@ int coral_merge_chimeric(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf, co
         uint64_t* key_a = c->s4.as<uint64_t>(); uint64_t* key_b = key_a + R;
         uint32_t* idx = c->s5.as<uint32_t>(); uint32_t* order = idx + R; uint32_t* cnt = order + R;
         LAUNCH_1D(k_chim_keys, (int64_t)R, set, key_a, idx);
-        CORAL_TRY(sort_pairs_u64(c, key_a, key_b, idx, order, (int64_t)R, 0, 32));
+        int key_bits = 1;                      // keys are row indices of the gathered rows (< this ctx's row count)
+        while (key_bits < 32 && ((uint64_t)1 << key_bits) < (uint64_t)std::max<int64_t>(c->nrec, 2)) key_bits++;
+        CORAL_TRY(sort_pairs_u64(c, key_a, key_b, idx, order, (int64_t)R, 0, key_bits));
         LAUNCH_1D(k_chim_counts, (int64_t)R, set, order, cnt);
         CORAL_TRY(exclusive_sum_u32(c, cnt, T.aln_ptr.as<uint32_t>(), (int64_t)R));
         ChimColsW o{T.read_first_rec.as<uint32_t>(), T.aln_ptr.as<uint32_t>(), T.read_len.as<int64_t>(), T.nm.as<int64_t>(),

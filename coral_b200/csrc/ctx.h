@@ -278,6 +278,7 @@ struct coral_ctx {
     DevBuf sa_side, sa_side_off;          // SA strings copied to HBM by the pre-scan, and where each record's sits
     bool sa_side_valid = false;
     bool scan_lazy = false;               // CORAL_RECORDS_HOST_MAPPED_LAZY: pre-scan done, full scan not started yet
+    DevBuf nm_part;                       // coral_fetch: per-block partial sums of nm_stats
     DevBuf pack_buf;                      // coral_get_chimeric_packed: the table's columns side by side
     DevBuf scan_order;                    // the record queue's permutation (largest records first), built once per load
     size_t scan_order_at = 0;

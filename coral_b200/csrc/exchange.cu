@@ -29,16 +29,20 @@ __global__ void k_flag_has_sa(int64_t n, const uint32_t* __restrict__ sa_off, ui
     if (i < n) f[i] = sa_off[i] != 0 ? 1u : 0u;
 }
 
-// slot bytes of every flagged record: read name (with its NUL) + SA text
-__global__ void k_slot_bytes(int64_t n, const uint32_t* __restrict__ f, const uint8_t* __restrict__ recs,
-                             const uint64_t* __restrict__ off, const uint32_t* __restrict__ sa_off,
-                             const uint32_t* __restrict__ sa_len, uint32_t* __restrict__ slot) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    uint32_t s = 0;
-    if (f[i]) s = (uint32_t)recs[off[i] + 12] + (sa_off[i] ? sa_len[i] : 0u);
-    slot[i] = s;
-}
+// Per record: (flagged ? 1 : 0) << 36 | slot bytes (read name with its NUL + SA text) — ONE inclusive scan gives every
+// flagged record its row index and the end of its text slot (rows < 2^28, text < 2^36 bytes per message).
+constexpr int PACK_SHIFT = 36;
+constexpr uint64_t PACK_MASK = ((uint64_t)1 << PACK_SHIFT) - 1;
+struct SlotFn {
+    const uint32_t* f;
+    const uint8_t* recs;
+    const uint64_t* off;
+    const uint32_t *sa_off, *sa_len;
+    __host__ __device__ uint64_t operator()(uint32_t i) const {
+        if (!f[i]) return 0;
+        return ((uint64_t)1 << PACK_SHIFT) | ((uint64_t)recs[off[i] + 12] + (sa_off[i] ? sa_len[i] : 0u));
+    }
+};
 
 struct PackIn {
     const uint8_t* recs;
@@ -48,19 +52,26 @@ struct PackIn {
     const int32_t* nm;
 };
 
-// one warp per flagged record: lane 0 writes the row, all lanes copy the slot text
-__global__ void k_pack_rows(int64_t n, const uint32_t* __restrict__ f, const uint32_t* __restrict__ row_incl,
-                            const uint64_t* __restrict__ text_incl, const uint32_t* __restrict__ slot, PackIn in,
-                            RowMsg* __restrict__ rows, uint8_t* __restrict__ text) {
+// one warp per flagged record: lane 0 writes the row, all lanes copy the slot text.  The first thread also writes the
+// header (nm sums from d_nm when given: reduced on the device) and zeroes the padding behind the text.
+__global__ void k_pack_rows(int64_t n, const uint32_t* __restrict__ f, const uint64_t* __restrict__ incl, PackIn in,
+                            MsgHdr* __restrict__ hdr_out, MsgHdr hdr, const double* __restrict__ d_nm,
+                            RowMsg* __restrict__ rows, uint8_t* __restrict__ text, uint32_t pad_bytes) {
     const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
+    if (i == 0 && lane == 0) {
+        if (d_nm) { hdr.nm_sum = d_nm[0]; hdr.nm_sq = d_nm[1]; hdr.nm_n = (int64_t)d_nm[2]; hdr.nm_zd = (int64_t)d_nm[3]; }
+        *hdr_out = hdr;
+        for (uint32_t k = 0; k < pad_bytes; k++) text[hdr.text_bytes + k] = 0;
+    }
     if (i >= n || !f[i]) return;
-    const uint32_t r = row_incl[i] - 1;
-    const uint64_t t0 = text_incl[i] - slot[i];
+    const uint64_t v = incl[i];
+    const uint32_t r = (uint32_t)(v >> PACK_SHIFT) - 1;
     const uint8_t* rec = in.recs + in.off[i];
     const uint32_t name_len = rec[12];
     const uint32_t so = in.sa_off[i];
     const uint32_t sl = so ? in.sa_len[i] : 0u;
+    const uint64_t t0 = (v & PACK_MASK) - (name_len + sl);
     if (lane == 0) {
         RowMsg m;
         m.lo = in.lo[i]; m.hi = in.hi[i];
@@ -70,12 +81,6 @@ __global__ void k_pack_rows(int64_t n, const uint32_t* __restrict__ f, const uin
     }
     for (uint32_t k = lane; k < name_len; k += 32) text[t0 + k] = rec[36 + k];
     for (uint32_t k = lane; k < sl; k += 32) text[t0 + name_len + k] = rec[so + k];
-}
-
-// d_nm (nullable): the four nm_stats sums, reduced on the device (k_nm_reduce)
-__global__ void k_write_hdr(MsgHdr* h, MsgHdr v, const double* d_nm) {
-    if (d_nm) { v.nm_sum = d_nm[0]; v.nm_sq = d_nm[1]; v.nm_n = (int64_t)d_nm[2]; v.nm_zd = (int64_t)d_nm[3]; }
-    *h = v;
 }
 
 // ---- extra primaries: membership of local non-SA primaries in the gathered SA-name set ----------------------
@@ -167,9 +172,10 @@ __device__ __forceinline__ uint64_t rows_below(const uint8_t* base, uint64_t n, 
     return a;
 }
 
-__global__ void k_unpack_rows(UnpackPlan p, RowCols o) {
+__global__ void k_unpack_rows(UnpackPlan p, RowCols o, uint64_t text_total) {
     const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint64_t n_sa = p.sa.row0[p.sa.n], n_ex = p.ex.row0[p.ex.n];
+    if (g == 0) o.off[n_sa + n_ex] = text_total;          // offsets[n]: the end of the text
     if (g >= n_sa + n_ex) return;
     int r;
     const RowMsg* m;
@@ -246,35 +252,32 @@ int inclusive_sum_u32_to_u64(coral_ctx* c, const uint32_t* in, uint64_t* out, in
 int pack_flagged(coral_ctx* c, int kind, MsgHdr hdr, DevBuf& msg, uint64_t* d_msg, uint64_t* nbytes, const double* d_nm = nullptr) {
     const int64_t n = c->nrec;
     RecordTable& t = c->rt;
-    uint32_t n_rows = 0;
-    uint64_t text_bytes = 0;
+    uint64_t last = 0;
     uint32_t* f = c->s0.as<uint32_t>();
+    if (n >= ((int64_t)1 << 28)) { c->err = "more than 2^28 records in one shard's exchange message"; return CORAL_E_ARG; }
     if (n > 0) {
-        CORAL_CUDA(c, c->s1.ensure((size_t)n * 4));
-        CORAL_CUDA(c, c->s2.ensure((size_t)n * 4));
         CORAL_CUDA(c, c->s3.ensure((size_t)n * 8));
-        LAUNCH_1D(k_slot_bytes, n, n, f, c->d_recs, c->d_off.as<uint64_t>(), t.sa_off.as<uint32_t>(), t.sa_len.as<uint32_t>(),
-                  c->s1.as<uint32_t>());
-        CORAL_TRY(inclusive_sum_u32(c, f, c->s2.as<uint32_t>(), n));
-        CORAL_TRY(inclusive_sum_u32_to_u64(c, c->s1.as<uint32_t>(), c->s3.as<uint64_t>(), n));
-        // the two sizes shape the message: read back (outside a pass / while recording) or replayed and checked
-        CORAL_TRY(pass_resolve(c, &n_rows, c->s2.as<uint32_t>() + (n - 1)));
-        CORAL_TRY(pass_resolve(c, &text_bytes, c->s3.as<uint64_t>() + (n - 1)));
+        cub::CountingInputIterator<uint32_t> iota(0);
+        cub::TransformInputIterator<uint64_t, SlotFn, cub::CountingInputIterator<uint32_t>> it(
+            iota, SlotFn{f, c->d_recs, c->d_off.as<uint64_t>(), t.sa_off.as<uint32_t>(), t.sa_len.as<uint32_t>()});
+        size_t bytes = 0;
+        CORAL_CUDA(c, cub::DeviceScan::InclusiveSum(nullptr, bytes, it, c->s3.as<uint64_t>(), (int)n, c->stream));
+        CORAL_CUDA(c, c->cub_tmp.ensure(bytes));
+        CORAL_CUDA(c, cub::DeviceScan::InclusiveSum(c->cub_tmp.p, bytes, it, c->s3.as<uint64_t>(), (int)n, c->stream));
+        c->n_launches += 1;
+        // rows and text bytes shape the message: read back (outside a pass / while recording) or replayed and checked
+        CORAL_TRY(pass_resolve(c, &last, c->s3.as<uint64_t>() + (n - 1)));
     }
-    const uint64_t body = sizeof(MsgHdr) + (uint64_t)n_rows * sizeof(RowMsg);
+    const uint64_t n_rows = last >> PACK_SHIFT, text_bytes = last & PACK_MASK;
+    const uint64_t body = sizeof(MsgHdr) + n_rows * sizeof(RowMsg);
     const uint64_t total = body + ((text_bytes + 15) & ~(uint64_t)15);
     CORAL_CUDA(c, msg.ensure(total));
     hdr.n_rows = n_rows; hdr.text_bytes = text_bytes; hdr.kind = (uint64_t)kind; hdr.pad = 0;
-    k_write_hdr<<<1, 1, 0, c->stream>>>(msg.as<MsgHdr>(), hdr, d_nm);
-    c->n_launches++;
-    if (total > body) CORAL_CUDA(c, cudaMemsetAsync(msg.as<uint8_t>() + total - 16, 0, 16, c->stream));
-    if (n_rows) {
-        PackIn in{c->d_recs, c->d_off.as<uint64_t>(), t.name_lo.as<uint64_t>(), t.name_hi.as<uint64_t>(), t.flag_mapq.as<uint32_t>(),
-                  t.lseq.as<uint32_t>(), t.sa_off.as<uint32_t>(), t.sa_len.as<uint32_t>(), t.nm.as<int32_t>()};
-        const int64_t threads = n * 32;
-        LAUNCH_1D(k_pack_rows, threads, n, f, c->s2.as<uint32_t>(), c->s3.as<uint64_t>(), c->s1.as<uint32_t>(), in,
-                  reinterpret_cast<RowMsg*>(msg.as<uint8_t>() + sizeof(MsgHdr)), msg.as<uint8_t>() + body);
-    }
+    PackIn in{c->d_recs, c->d_off.as<uint64_t>(), t.name_lo.as<uint64_t>(), t.name_hi.as<uint64_t>(), t.flag_mapq.as<uint32_t>(),
+              t.lseq.as<uint32_t>(), t.sa_off.as<uint32_t>(), t.sa_len.as<uint32_t>(), t.nm.as<int32_t>()};
+    const int64_t threads = std::max<int64_t>(n, 1) * 32;      // at least one warp: the header is written by the first thread
+    LAUNCH_1D(k_pack_rows, threads, n, f, c->s3.as<uint64_t>(), in, msg.as<MsgHdr>(), hdr, d_nm,
+              reinterpret_cast<RowMsg*>(msg.as<uint8_t>() + sizeof(MsgHdr)), msg.as<uint8_t>() + body, (uint32_t)(total - body - text_bytes));
     if (!c->pass.active) CORAL_CUDA(c, cudaStreamSynchronize(c->stream));
     if (d_msg) *d_msg = (uint64_t)reinterpret_cast<uintptr_t>(msg.p);
     if (nbytes) *nbytes = total;
@@ -290,16 +293,12 @@ int read_msgs(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf, const uint64_
         if (starts[r] & 15) { c->err = "message starts must be 16-byte aligned"; return CORAL_E_ARG; }
         set->base[r] = d_buf + starts[r];
     }
-    MsgSet none;
-    none.n = 0;
-    const int words = n_ranks * (int)(sizeof(MsgHdr) / 8);
-    CORAL_CUDA(c, c->s7.ensure((size_t)words * 8));
-    k_collect_hdrs<<<1, words, 0, c->stream>>>(*set, none, c->s7.as<uint64_t>());
-    c->n_launches++;
-    CORAL_CUDA(c, cudaGetLastError());
+    HdrPtrs hp;
+    hp.n = n_ranks;
+    for (int r = 0; r < n_ranks; r++) hp.base[r] = set->base[r];
     hdrs->resize((size_t)n_ranks);
     static_assert(sizeof(MsgHdr) == 64, "8 words per header");
-    CORAL_TRY(pass_resolve_n(c, reinterpret_cast<uint64_t*>(hdrs->data()), c->s7.p, words));
+    CORAL_TRY(pass_resolve_hdrs(c, hp, reinterpret_cast<uint64_t*>(hdrs->data())));
     set->row0[0] = 0;
     for (int r = 0; r < n_ranks; r++) {
         if ((*hdrs)[r].kind != (uint64_t)kind) { c->err = "unexpected message kind in the gathered buffer"; return CORAL_E_FORMAT; }
@@ -443,10 +442,9 @@ int coral_unpack_rows(coral_ctx* c, int32_t n_ranks, const uint8_t* d_buf1, cons
     for (DevBuf* b : b8) CORAL_CUDA(c, b->ensure(n8));
     DevBuf* b4[] = {&t.flag_mapq, &t.lseq, &t.nm, &t.sa_off, &t.sa_len};
     for (DevBuf* b : b4) CORAL_CUDA(c, b->ensure(n4));
-    CORAL_TRY(h2d(c, c->d_off.as<uint64_t>() + n, &text, 1));
     RowCols o{c->d_off.as<uint64_t>(), t.name_lo.as<uint64_t>(), t.name_hi.as<uint64_t>(), t.flag_mapq.as<uint32_t>(),
               t.lseq.as<uint32_t>(), t.sa_off.as<uint32_t>(), t.sa_len.as<uint32_t>(), t.nm.as<int32_t>()};
-    LAUNCH_1D(k_unpack_rows, n, p, o);
+    LAUNCH_1D(k_unpack_rows, std::max<int64_t>(n, 1), p, o, text);
     // columns a row does not carry: tid -1 (no placement), the rest 0.  Nothing ever writes them on a rows-only ctx, so a
     // later unpack only fills what a regrown buffer has lost (ten memsets per pass otherwise)
     DevBuf* fill[] = {&t.tid, &t.pos, &t.endpos, &t.ncig, &t.infer, &t.mbases, &t.nonacgt, &t.fbs, &t.lbe, &t.ngap};

@@ -446,14 +446,26 @@ int coral_run_fetch(coral_ctx* c) {
     c->stage_begin(CORAL_STAGE_FETCH);
 
     // nm_stats partials
-    const int64_t nblk = (n + NM_BLOCK - 1) / NM_BLOCK;
-    CORAL_CUDA(c, c->s7.ensure((size_t)std::max<int64_t>(nblk, 1) * 32));
-    if (n > 0) {
+    // (rows of a rows-only ctx carry no placement, tid -1: they contribute nothing — the shards' sums travel in the
+    // headers of the exchange — so the kernel and its copy are skipped there)
+    const int64_t nblk = c->rows_only ? 0 : (n + NM_BLOCK - 1) / NM_BLOCK;
+    auto part = std::make_shared<std::vector<double>>((size_t)std::max<int64_t>(nblk, 1) * 4, 0.0);
+    if (nblk > 0) {
+        // partials in a buffer of their own: their copy (a RESULT: inside a pipelined pass it arrives at coral_pass_end)
+        // runs on the pass's side stream, off the chain of dependent kernels below
+        CORAL_CUDA(c, c->nm_part.ensure((size_t)nblk * 32));
         k_nm_stats<<<(unsigned)nblk, NM_BLOCK, 0, c->stream>>>(n, rt.sa_off.as<uint32_t>(), rt.flag_mapq.as<uint32_t>(),
                                                               rt.tid.as<int32_t>(), rt.nm.as<int32_t>(), rt.lseq.as<uint32_t>(),
-                                                              c->s7.as<double>());
+                                                              c->nm_part.as<double>());
         c->n_launches++;
         CORAL_CUDA(c, cudaGetLastError());
+        if (c->pass.active) {
+            CORAL_TRY(pass_side_begin(c, SIDE_CHIM));
+            CORAL_TRY(d2h_result(c, part->data(), c->nm_part.p, (size_t)nblk * 4));
+            CORAL_TRY(pass_sync(c));
+        } else {
+            CORAL_TRY(d2h_result(c, part->data(), c->nm_part.p, (size_t)nblk * 4));
+        }
     }
     // 1. SA-bearing records in record order
     CORAL_CUDA(c, c->s0.ensure((size_t)std::max<int64_t>(n, 1)));          // flags u8
@@ -477,9 +489,6 @@ int coral_run_fetch(coral_ctx* c) {
         }
     }
     uint32_t n_sa = 0;
-    // the per-block partial sums are a RESULT (inside a pipelined pass they arrive at coral_pass_end) ...
-    auto part = std::make_shared<std::vector<double>>((size_t)std::max<int64_t>(nblk, 1) * 4, 0.0);
-    CORAL_TRY(d2h_result(c, part->data(), c->s7.p, (size_t)nblk * 4));
     // ... the number of SA-bearing records sizes the launches below
     CORAL_TRY(pass_resolve_lazy(c, &n_sa, d_cnt));
     CORAL_TRY(pass_after(c, [c, part, nblk]() {

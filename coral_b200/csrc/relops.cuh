@@ -192,6 +192,36 @@ inline int pass_resolve_n(coral_ctx* c, uint64_t* out, const void* d_src, int n)
     return CORAL_OK;
 }
 
+// The 64-byte headers of up to 16 gathered messages (8 words each) as host values: read back (outside a pass / while
+// recording: one gathering kernel + one copy) or replayed and compared IN PLACE by one kernel.
+struct HdrPtrs { const uint8_t* base[16]; int n; };
+static __global__ void k_hdrs_collect(HdrPtrs h, uint64_t* __restrict__ out) {
+    const int t = threadIdx.x, k = t >> 3;
+    if (k < h.n) out[t] = reinterpret_cast<const uint64_t*>(h.base[k])[t & 7];
+}
+static __global__ void k_hdrs_check(HdrPtrs h, PassWords expect, uint32_t* flag) {
+    const int t = threadIdx.x, k = t >> 3;
+    if (k < h.n && reinterpret_cast<const uint64_t*>(h.base[k])[t & 7] != expect.w[t]) atomicAdd(flag, 1u);
+}
+inline int pass_resolve_hdrs(coral_ctx* c, const HdrPtrs& h, uint64_t* out) {
+    const int n = h.n * 8;
+    if (h.n < 1 || h.n > 16) { c->err = "1..16 messages per exchange"; return CORAL_E_ARG; }
+    PassState& P = c->pass;
+    if (P.active && P.replay && P.cur + (size_t)n <= P.vals.size()) {
+        PassWords ex;
+        for (int i = 0; i < n; i++) { out[i] = P.vals[P.cur + i]; ex.w[i] = out[i]; }
+        P.cur += (size_t)n;
+        k_hdrs_check<<<1, 128, 0, c->stream>>>(h, ex, P.d_flag);
+        c->n_launches++;
+        return CORAL_OK;
+    }
+    CORAL_CUDA(c, c->s7.ensure((size_t)n * 8));
+    k_hdrs_collect<<<1, 128, 0, c->stream>>>(h, c->s7.as<uint64_t>());
+    c->n_launches++;
+    CORAL_CUDA(c, cudaGetLastError());
+    return pass_resolve_n(c, out, c->s7.p, n);
+}
+
 inline uint8_t* pass_stage(coral_ctx* c, size_t bytes) {          // page-locked staging for one deferred copy
     PassState& P = c->pass;
     bytes = (bytes + 63) & ~(size_t)63;

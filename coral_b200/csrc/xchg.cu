@@ -1,15 +1,15 @@
 // coral_b200/csrc/xchg.cu — the multi-GPU exchanges of SURVEY.md §8e as kernels over peer memory (NVLink / NVSwitch).
 //
 // One process per GPU; every rank owns one "window" in its own HBM (cudaMalloc + CUDA IPC handle, opened by the
-// peers once).  An all-gather of one variable-length message per rank is TWO kernels on the caller's stream and no
-// host round trip:
+// peers once).  An all-gather of one variable-length message per rank is ONE kernel on the caller's stream and no host
+// round trip (k_xchg_push):
 //
-//   k_xchg_push   copies this rank's message into ITS slot of EVERY peer's window with 16-byte stores over NVLink
-//                 (the rank's own window included), then — last block, after a system-scope fence — writes the slot
-//                 header (size, sequence number) and releases the sequence number into the peer's flag word;
-//   k_xchg_wait   one warp: lane r polls the flag word of rank r in the LOCAL window (acquire, system scope) until it
-//                 carries this exchange's sequence number, then publishes the size of message r.  Bounded: after
-//                 `timeout` seconds it gives up and reports (a lost peer must not hang the GPU).
+//   push   every block copies its share of this rank's message into ITS slot of EVERY peer's window with 16-byte stores
+//          over NVLink (the rank's own window included); the block that finishes last writes the slot header (size,
+//          sequence number) and — after a system-scope fence — releases the sequence number into each peer's flag word;
+//   wait   that same block then polls, thread r for rank r, the flag words of the LOCAL window (acquire, system scope)
+//          until they carry this exchange's sequence number, and publishes the size of message r.  Bounded: after
+//          `timeout` seconds it gives up and reports (a lost peer must not hang the GPU).
 //
 // After the wait the gathered messages sit in local HBM, message r at a fixed offset, and go straight into the next
 // kernel (coral_pack_extra_rows, coral_unpack_rows, coral_merge_chimeric, coral_count_name_msgs ...).  Inside a
@@ -71,7 +71,20 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
     return t;
 }
 
-__global__ void k_xchg_push(const uint4* __restrict__ src, uint64_t nbytes, PushArgs a, uint64_t seq, uint32_t* done) {
+// One kernel per exchange: every block copies its share of the message into this rank's slot of every peer's window;
+// the block that finishes last publishes (slot header, then the sequence number into each peer's flag word, release at
+// system scope) and then WAITS: thread r polls rank r's flag in the local window (acquire, system scope) until it carries
+// this exchange's sequence number and records the size of message r (~0 after the timeout).  The other blocks have left
+// by then: one resident block per waiting rank, no second launch.
+struct WaitArgs {
+    const uint64_t* flags;       // local window: flag words of this channel
+    const uint8_t* slots;        // local window: slot set of this exchange
+    uint64_t cap, timeout_ns;
+    uint64_t* sizes;
+    int32_t* status;
+};
+__global__ void k_xchg_push(const uint4* __restrict__ src, uint64_t nbytes, PushArgs a, uint64_t seq, uint32_t* done, WaitArgs w) {
+    __shared__ int s_last;
     const uint64_t nvec = nbytes >> 4;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
@@ -82,7 +95,8 @@ __global__ void k_xchg_push(const uint4* __restrict__ src, uint64_t nbytes, Push
     __syncthreads();
     if (threadIdx.x == 0) {
         const uint32_t prev = atomicAdd(done, 1u);
-        if (prev == gridDim.x - 1) {              // every block's stores are behind its own fence: publish
+        s_last = prev == gridDim.x - 1;
+        if (s_last) {                             // every block's stores are behind its own fence: publish
             *done = 0;
             __threadfence();
             for (int p = 0; p < a.world; p++) {
@@ -93,24 +107,21 @@ __global__ void k_xchg_push(const uint4* __restrict__ src, uint64_t nbytes, Push
             for (int p = 0; p < a.world; p++) st_release_sys(a.flag[p], seq);
         }
     }
-}
-
-// lane r: wait for rank r's message of exchange `seq` in the local window; sizes[r] = its size (~0 on timeout)
-__global__ void k_xchg_wait(const uint64_t* flags, const uint8_t* slots, uint64_t cap, int world, uint64_t seq,
-                            uint64_t timeout_ns, uint64_t* __restrict__ sizes, int32_t* status) {
+    __syncthreads();
+    if (!s_last) return;
     const int r = threadIdx.x;
-    if (r >= world) return;
+    if (r >= a.world) return;
     const uint64_t t0 = global_timer_ns();
     bool ok = true;
-    while (ld_acquire_sys(flags + r) < seq) {
-        if (global_timer_ns() - t0 > timeout_ns) { ok = false; break; }
+    while (ld_acquire_sys(w.flags + r) < seq) {
+        if (global_timer_ns() - t0 > w.timeout_ns) { ok = false; break; }
         __nanosleep(200);
     }
     if (ok) {
-        sizes[r] = *reinterpret_cast<const volatile uint64_t*>(slots + (uint64_t)r * cap);
+        w.sizes[r] = *reinterpret_cast<const volatile uint64_t*>(w.slots + (uint64_t)r * w.cap);
     } else {
-        sizes[r] = ~0ull;
-        atomicAdd(status, 1);
+        w.sizes[r] = ~0ull;
+        atomicAdd(w.status, 1);
     }
 }
 
@@ -153,13 +164,10 @@ static int xchg_round(coral_ctx* c, coral_xchg* x, int ch, const void* d_msg, ui
     }
     const uint64_t nvec = nbytes >> 4;
     const unsigned blocks = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>((nvec + 1023) / 1024, (uint64_t)c->sm_count));
-    k_xchg_push<<<blocks, 256, 0, c->stream>>>(static_cast<const uint4*>(d_msg), nbytes, a, seq, x->d_done + ch);
-    c->n_launches++;
-    CORAL_CUDA(c, cudaGetLastError());
     const uint8_t* set = x->local + set_off;
-    k_xchg_wait<<<1, 32, 0, c->stream>>>(reinterpret_cast<const uint64_t*>(x->local) + (size_t)ch * CORAL_XCHG_MAX_RANKS, set,
-                                         x->cap[ch], x->world, seq, (uint64_t)(x->timeout_s * 1e9),
-                                         x->d_sizes + (size_t)ch * CORAL_XCHG_MAX_RANKS, x->d_status);
+    WaitArgs w{reinterpret_cast<const uint64_t*>(x->local) + (size_t)ch * CORAL_XCHG_MAX_RANKS, set, x->cap[ch],
+               (uint64_t)(x->timeout_s * 1e9), x->d_sizes + (size_t)ch * CORAL_XCHG_MAX_RANKS, x->d_status};
+    k_xchg_push<<<blocks, 256, 0, c->stream>>>(static_cast<const uint4*>(d_msg), nbytes, a, seq, x->d_done + ch, w);
     c->n_launches++;
     CORAL_CUDA(c, cudaGetLastError());
     *slots = set;

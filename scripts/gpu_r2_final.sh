@@ -23,6 +23,10 @@ echo "ingest rc=$?" >> gpurun_out/rc_final.txt
 ( timeout 900 ncu --set full --clock-control none -k regex:k_inflate_members -c 1 -f -o gpurun_out/r2_inflate \
     python scripts/ingest_timing.py --scale 0.05 --reps 1 ) > gpurun_out/final_ncu_inflate.log 2>&1
 echo "inflate capture rc=$?" >> gpurun_out/rc_final.txt
+for w in C3 C1n; do
+  ( timeout 600 python bench.py --steps 20 --warmup 5 --workload $w --no-cpu --no-file ) > gpurun_out/final_bench_$w.json 2> gpurun_out/final_bench_$w.err
+  echo "bench $w rc=$?" >> gpurun_out/rc_final.txt
+done
 tail -4 gpurun_out/final_tests.log; cat gpurun_out/rc_final.txt; cat gpurun_out/final_ingest.json; tail -c 600 gpurun_out/final_reference.json
 python - <<'PY'
 import json
