@@ -282,8 +282,8 @@ int coral_unpack_rows(coral_ctx* ctx, int32_t n_ranks, const uint8_t* d_buf1, co
  * The transport of the multi-GPU form of the path (the one real exchange is the SA union / first-primary
  * rule of fetch, ibg:141-151; coverage sums and concordant name sets are combined the same way).  One process per GPU;
  * every rank owns a WINDOW in its own HBM that the peers map once (CUDA IPC).  An all-gather of one variable-length
- * message per rank is two kernels on the ctx's stream — a push that stores the message into this rank's slot of every
- * peer's window and releases a sequence number, a one-warp wait on the local flags — and no host round trip: inside a
+ * message per rank is one kernel on the ctx's stream — it stores the message into this rank's slot of every peer's
+ * window, releases a sequence number and then waits on the local flags — and no host round trip: inside a
  * pipelined pass the message sizes are replayed and checked on the device like every other launch size.
  *   coral_xchg_create  : slot_bytes[CORAL_XCHG_CHANNELS] = largest message per channel (0: channel unused); the window
  *                        holds 2 x world slots per channel.  A message beyond the slot size fails with CORAL_E_NOMEM.
