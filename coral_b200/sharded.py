@@ -340,6 +340,22 @@ _SDEL_ROW = np.dtype([("rec", "<u4"), ("ai", "<i4"), ("next_start", "<i4"), ("pr
                       ("last_end", "<i4"), ("mapq", "<i4"), ("pad", "<u4"), ("lo", "<i8"), ("hi", "<i8")])
 
 
+def merge_smalldel_msgs(raws):
+    """Gathered coral_smalldel_pack messages (one uint8 array per rank: 64-byte header whose first word is the row count,
+    then 48-byte rows, csrc/chimeric_merge.cu SdelRow) -> rows (rank, rec, ai, next_start, prev_end, first_start, last_end,
+    mapq, name hash lo, hi) in the reference's emission order (ibg:750-762): interval list order, then rank (= file) order,
+    then the rank's own row order (file order, block order)."""
+    out = []
+    for r, raw in enumerate(raws):
+        raw = np.ascontiguousarray(raw).view(np.uint8)
+        n = int(np.frombuffer(raw[:8].tobytes(), np.uint64)[0])
+        body = np.frombuffer(raw[64:64 + 48 * n].tobytes(), _SDEL_ROW)
+        out.extend((r, int(x["rec"]), int(x["ai"]), int(x["next_start"]), int(x["prev_end"]), int(x["first_start"]),
+                    int(x["last_end"]), int(x["mapq"]), int(x["lo"]), int(x["hi"])) for x in body)
+    out.sort(key=lambda x: x[2])          # stable
+    return out
+
+
 def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", presharded=False, xchg=None):
     """Factory (keeps the CUDA-bound import out of the CPU tests of the exchange logic).
     `records`: the whole file (every rank then takes its range of shard_ranges) or, with presharded=True, this rank's
@@ -460,16 +476,7 @@ def make_sharded_engine(records, seedfile, comm, device=0, placement="auto", pre
 
         @staticmethod
         def _smalldel_merge(raws):
-            """Gathered messages -> rows (rank, rec, ai, next_start, prev_end, first_start, last_end, mapq, lo, hi) in the
-            reference's emission order: interval, then rank (= file) order, then block order."""
-            out = []
-            for r, raw in enumerate(raws):
-                n = int(np.frombuffer(raw[:8].tobytes(), np.uint64)[0])
-                body = np.frombuffer(raw[64:64 + 48 * n].tobytes(), _SDEL_ROW)
-                out.extend((r, int(x["rec"]), int(x["ai"]), int(x["next_start"]), int(x["prev_end"]), int(x["first_start"]),
-                            int(x["last_end"]), int(x["mapq"]), int(x["lo"]), int(x["hi"])) for x in body)
-            out.sort(key=lambda x: x[2])          # stable
-            return out
+            return merge_smalldel_msgs(raws)
 
         def _smalldel_rows(self, t, s, e):
             rows, raws = self._smalldel_gather(t, s, e)

@@ -282,3 +282,25 @@ def test_gather_msgs_over_gloo_world2():
     res = sorted(q.get(timeout=300) for _ in range(2))
     [p.join(60) for p in ps]
     assert all(p.exitcode == 0 for p in ps) and all(ok for _, ok in res)
+
+
+def test_merge_of_packed_smalldel_messages_restores_the_emission_order():
+    """The device-packed small-deletion messages (csrc/chimeric_merge.cu: 64-byte header + 48-byte rows) of three ranks,
+    one of them empty, merged on the host: interval order first, then rank (= file) order, then the rank's row order —
+    the order find_smalldel_breakpoints' loops emit in (ibg:750-762)."""
+    import numpy as np
+    from coral_b200 import sharded
+
+    def msg(rows):
+        hdr = np.zeros(8, np.uint64)
+        hdr[0] = len(rows); hdr[6] = 5
+        body = np.zeros(len(rows), sharded._SDEL_ROW)
+        for k, r in enumerate(rows):
+            body[k] = r
+        return np.concatenate([hdr.view(np.uint8), body.view(np.uint8)])
+    r0 = [(5, 0, 100, 90, 10, 900, 60, 0, 11, 12), (9, 2, 300, 290, 20, 800, 50, 0, 13, 14)]
+    r2 = [(1, 0, 120, 95, 15, 950, 40, 0, 21, 22), (2, 1, 220, 200, 25, 850, 30, 0, -23, 24), (2, 1, 260, 240, 25, 850, 30, 0, -23, 24)]
+    got = sharded.merge_smalldel_msgs([msg(r0), msg([]), msg(r2)])
+    assert [(g[0], g[1], g[2]) for g in got] == [(0, 5, 0), (2, 1, 0), (2, 2, 1), (2, 2, 1), (0, 9, 2)]
+    assert got[3][3:8] == (260, 240, 25, 850, 30) and got[1][8:] == (21, 22) and got[2][8:] == (-23, 24)
+    assert sharded.merge_smalldel_msgs([msg([])]) == []
