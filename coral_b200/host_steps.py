@@ -100,6 +100,7 @@ class HostSteps(PathConstraintSteps):
         self.read_length = {}
         self.chimeric_alignments = {}
         self.chimeric_alignments_seg = {}
+        self._read_seg_pairs = {}    # read -> [(chromosome, CN-segment index)] of its alignments (find_interval_i's cache)
         self.large_indel_alignments = {}
         self.nm_stats = [0.0, 0.0, 0]
         self.amplicon_intervals = []
@@ -233,6 +234,7 @@ class HostSteps(PathConstraintSteps):
         """CN-segment indices of both ends of every alignment.  Lookups are batched per chromosome (binary search
         over the non-overlapping segments); the sets and chimeric_alignments_seg are then filled in read order,
         exactly as the per-alignment loop of the reference does."""
+        self._read_seg_pairs = {}
         tabs = self._cni_tables()
         if tabs is None:
             return self._hash_alignment_to_seg_scalar()
@@ -504,21 +506,29 @@ class HostSteps(PathConstraintSteps):
                 continue
 
             # reads hashed to the CN segments of this interval that also map outside it (ibg:369-384)
+            # (same insertion order of chromosomes into d1 as the reference's nested loops — the loop over d1.keys()
+            # below depends on it; the (chromosome, segment) pairs of a read, without the -1 entries that never insert
+            # anything, are spelled out once per read and reused by every interval that meets the read)
             d1 = {}
+            seg_here = self.chimeric_alignments_seg[chrom]
+            pairs_of = self._read_seg_pairs
+            ca_all = self.chimeric_alignments
             for i in range(si, ei + 1):
-                if i in self.chimeric_alignments_seg[chrom]:
-                    for r in self.chimeric_alignments_seg[chrom][i]:
-                        for int_ in self.chimeric_alignments[r][1]:
-                            for i_ in int_[-1]:
-                                if (int_[0] != chrom) or (i_ <= si or i_ >= ei):
-                                    try:
-                                        if i_ != -1:
-                                            d1[int_[0]][i_].add(r)
-                                    except:  # noqa: E722
-                                        if int_[0] not in d1:
-                                            d1[int_[0]] = {}
-                                        if i_ != -1:
-                                            d1[int_[0]][i_] = set([r])
+                if i in seg_here:
+                    for r in seg_here[i]:
+                        pr = pairs_of.get(r)
+                        if pr is None:
+                            pr = pairs_of[r] = [(int_[0], i_) for int_ in ca_all[r][1] for i_ in int_[-1] if i_ != -1]
+                        for c_r, i_ in pr:
+                            if c_r != chrom or i_ <= si or i_ >= ei:
+                                dc = d1.get(c_r)
+                                if dc is None:
+                                    dc = d1[c_r] = {}
+                                st = dc.get(i_)
+                                if st is None:
+                                    dc[i_] = {r}
+                                else:
+                                    st.add(r)
             for c_ in list(d1.keys()):   # ibg:386-398
                 for segi in [k for k in d1[c_].keys() if len(d1[c_][k]) < self.min_cluster_cutoff]:
                     del d1[c_][segi]
