@@ -81,15 +81,23 @@ CORAL_HD uint64_t frame_len(const uint8_t* s, uint64_t p) { return ((uint64_t)ld
 // ---- kernels ---------------------------------------------------------------------------------------------------
 constexpr int INF_WARPS = 8;
 
-// One warp per BGZF member.  Lane 0 owns the bit reader and the Huffman decode (a serial dependency chain); the
-// operation it pulls is broadcast and all lanes emit it, so that match copies and stored runs are coalesced stores.
+// One warp per BGZF member.  Lane 0 owns the bit reader and the Huffman decode (a serial dependency chain).  It decodes
+// a RUN: up to INF_LITS literals into the warp's shared-memory buffer, ended by the first operation that is not a
+// literal (or by the full buffer).  The run is broadcast once; all lanes store the literals (coalesced) and then emit the
+// closing operation, so that match copies and stored runs are coalesced too.  (The first version broadcast and
+// synchronised per literal: BAM's QUAL bytes barely compress, so most of a member is literals — 9 GB/s of output,
+// DRAM writes 2.4 x the output, profiles/r2_ingest.txt.)
 // status[0] counts members that failed (bad stream, or a length different from the member's ISIZE).
+constexpr uint32_t INF_LITS = 128;
+constexpr uint32_t OP_NONE = 99;               // the literal buffer filled up: nothing closes this run
 __global__ void __launch_bounds__(INF_WARPS * 32)
 k_inflate_members(const uint8_t* __restrict__ comp, const Member* __restrict__ mem, uint32_t n_mem, uint8_t* out,
                   int32_t* __restrict__ status) {
     __shared__ dfl::Tables tabs[INF_WARPS];
+    __shared__ uint8_t lits[INF_WARPS][INF_LITS];
     const uint32_t lane = lane_id();
     dfl::Tables& t = tabs[threadIdx.x >> 5];
+    uint8_t* lb = lits[threadIdx.x >> 5];
     const uint32_t nw = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t m = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; m < n_mem; m += nw) {
         const Member mm = mem[m];
@@ -99,17 +107,29 @@ k_inflate_members(const uint8_t* __restrict__ comp, const Member* __restrict__ m
         dfl::init(st, src, mm.in_len);
         uint32_t o = 0;
         bool fail = false;
-        // every operation emits at least one byte or ends the stream, so the loop is bounded by out_len + blocks
+        // every run emits at least one byte or ends the stream, so the loop is bounded by out_len + blocks
         for (uint32_t guard = 0; guard < 2u * 65536u + 64u; guard++) {
-            dfl::OpOut op{dfl::OP_END, 0, 0};
-            if (lane == 0) op = dfl::next_op(st, t);
+            dfl::OpOut op{OP_NONE, 0, 0};
+            uint32_t nl = 0;
+            if (lane == 0) {
+                for (;;) {
+                    op = dfl::next_op(st, t);
+                    if (op.op != dfl::OP_LIT) break;
+                    lb[nl++] = (uint8_t)op.a;
+                    if (nl == INF_LITS) { op.op = OP_NONE; break; }
+                }
+            }
+            __syncwarp();              // lane 0's literals in shared memory are visible to the warp
+            nl = __shfl_sync(FULL_MASK, nl, 0);
             const uint32_t kind = __shfl_sync(FULL_MASK, op.op, 0);
             const uint32_t a = __shfl_sync(FULL_MASK, op.a, 0), b = __shfl_sync(FULL_MASK, op.b, 0);
-            if (kind == dfl::OP_LIT) {
-                if (o >= mm.out_len) { fail = true; break; }
-                if (lane == 0) dst[o] = (uint8_t)a;
-                o++;
-            } else if (kind == dfl::OP_MATCH) {
+            if (nl) {
+                if (o + nl > mm.out_len) { fail = true; break; }
+                for (uint32_t i = lane; i < nl; i += 32) dst[o + i] = lb[i];
+                o += nl;
+                __syncwarp();          // the bytes just written are input of the closing match; lb is reused next round
+            }
+            if (kind == dfl::OP_MATCH) {
                 if (b > o || o + a > mm.out_len) { fail = true; break; }
                 const uint8_t* from = dst + o - b;
                 if (b >= a) { for (uint32_t i = lane; i < a; i += 32) dst[o + i] = from[i]; }
@@ -119,7 +139,7 @@ k_inflate_members(const uint8_t* __restrict__ comp, const Member* __restrict__ m
                 if (o + b > mm.out_len) { fail = true; break; }
                 for (uint32_t i = lane; i < b; i += 32) dst[o + i] = src[a + i];
                 o += b;
-            } else {
+            } else if (kind != OP_NONE) {
                 fail = kind != dfl::OP_END;
                 break;
             }
