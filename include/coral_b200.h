@@ -389,7 +389,8 @@ int coral_set_chimeric(coral_ctx* ctx, int64_t n_reads, const uint32_t* aln_ptr,
  *   n_sub[c]: number of bpc2bp calls made for cluster c; sub_of[i]: the call (0-based) whose bpr received
  *   candidate i, or -1;
  *   row arrays indexed cluster_ptr[c] + k for call k: called pos1/pos2, len(bpr), the candidate that was
- *   bp_cluster[0] of that call (supplies bp[0], bp[2], bp[3], bp[5..8]), and bp_stats_[6]. */
+ *   bp_cluster[0] of that call (supplies bp[0], bp[2], bp[3], bp[5..8]), and bp_stats_[6].  Only the first n_sub[c]
+ *   slots of a cluster are written; the others are undefined. */
 int coral_cluster_call(coral_ctx* ctx, int64_t n, const int32_t* chr1, const int32_t* pos1, const uint8_t* o1,
                        const int32_t* chr2, const int32_t* pos2, const uint8_t* o2, const int32_t* rgap,
                        const uint8_t* flag, const int32_t* mq1, const int32_t* mq2, double min_cluster_size,
