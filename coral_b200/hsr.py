@@ -17,9 +17,19 @@ from .breakpoint_utilities import interval2bp, interval_include, interval_overla
 
 
 def fetch(lr_bamfh, device=0):
-    """reference :21-49.  `lr_bamfh`: coral_b200._abi.BamFile (or any record set the engine accepts).
+    """reference :21-49.  `lr_bamfh`: coral_b200._abi.BamFile (or any record set the engine accepts), or the PATH of a
+    .bam file: the file is then inflated and framed on the GPU (placement "device_ingest": the host reader's zlib pass
+    is most of what this call costs on a large file).
     -> (read_length of the chimeric reads, chimeric_alignments); reads without a primary record are dropped."""
     from .infer_breakpoint_graph import bam_to_breakpoint_nanopore
+    if isinstance(lr_bamfh, str):
+        eng = bam_to_breakpoint_nanopore(lr_bamfh, None, device=device, placement="device_ingest")
+        eng._nm_stats_required = False
+        eng._warn_no_primary = False
+        eng.fetch()
+        out = eng.read_length, eng.chimeric_alignments
+        eng.closebam()
+        return out
     slack = int(getattr(lr_bamfh, "rec_slack", 0))
     # only core / name / aux bytes are needed: the lazy placement never runs the CIGAR + SEQ scan for this caller
     eng = bam_to_breakpoint_nanopore(None, None, device=device, records=lr_bamfh,
@@ -168,24 +178,25 @@ def integration_points(bp_refined, ecdna_intervals_ext, cns_dict, normal_cov):
     return out
 
 
-def locate_hsrs(args, device=0, lr_bamfh=None):
-    """reference :52-225 without the figure.  -> dict(bp_refined, bp_stats, points)."""
+def locate_hsrs(args, device=0, lr_bamfh=None, device_ingest=False):
+    """reference :52-225 without the figure.  -> dict(bp_refined, bp_stats, points).
+    device_ingest: hand the .bam file to the GPU as it is on disk instead of inflating it with zlib on the host."""
     from . import _abi
     ecdna, ecdna_ext = read_ecdna_intervals(args.cycles, args.bp_match_cutoff)
     print("ecDNA intervals:")
     for ival in ecdna:
         print(ival)
     cns = read_cn_segments(args.cn_seg)
-    fh = lr_bamfh if lr_bamfh is not None else _abi.BamFile(args.lr_bam)
+    fh = lr_bamfh if lr_bamfh is not None else (None if device_ingest else _abi.BamFile(args.lr_bam))
     gpu_ops.set_default_device(device)
-    _, chimeric = fetch(fh, device=device)
+    _, chimeric = fetch(args.lr_bam if fh is None else fh, device=device)
     print("Fetched %d chimeric alignments." % len(chimeric))
     bp_list = candidate_breakpoints(chimeric, ecdna)
     t = float(args.normal_cov) * 0.5
     bp_refined, bp_stats = refine(called_breakpoints_device(bp_list, t, args.bp_match_cutoff, args.bp_match_cutoff_clustering),
                                   t, args.bp_match_cutoff)
     print("Found %d breakpoints connecting ecDNA and chromosomes." % len(bp_refined))
-    if lr_bamfh is None:
+    if lr_bamfh is None and fh is not None:
         fh.close()
     pts = integration_points(bp_refined, ecdna_ext, cns, args.normal_cov)
     for line, _, _ in pts:

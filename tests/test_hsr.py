@@ -79,10 +79,11 @@ def test_hsr_locate_on_gpu(built_lib, case, tmp_path_factory):
         assert json.loads(json.dumps(canon_chimeric(chim))) == gold["fetch"]
         assert all(name in read_length for name in chim)
         fh.close()
-    out = io.StringIO()
-    with contextlib.redirect_stdout(out):
-        res = hsr.locate_hsrs(args)
-    lines = [ln for ln in out.getvalue().splitlines() if ln.startswith(("Fetched", "Found", "Breakpoint"))]
-    assert lines == gold["lines"]
-    assert res["points"] == gold["points"]
-    assert len(res["bp_refined"]) == len(res["bp_stats"]) > 0
+    for device_ingest in (False, True):        # host reader (zlib) / the .bam bytes inflated and framed on the GPU
+        out = io.StringIO()
+        with contextlib.redirect_stdout(out):
+            res = hsr.locate_hsrs(args, device_ingest=device_ingest)
+        lines = [ln for ln in out.getvalue().splitlines() if ln.startswith(("Fetched", "Found", "Breakpoint"))]
+        assert lines == gold["lines"]
+        assert res["points"] == gold["points"]
+        assert len(res["bp_refined"]) == len(res["bp_stats"]) > 0
