@@ -2,10 +2,10 @@
 // GPU, so that what crosses PCIe is the compressed file and the host does no zlib work.  Replaces, for callers that
 // opt in, the host reader of bam_reader.cpp (reference: pysam.AlignmentFile(path, 'rb'), infer_breakpoint_graph.py:65).
 //
-// STATUS: written and verified on the CPU only (the decoder core and every per-element step below are
-// __host__ __device__ and run against zlib / the host reader in tests/test_ingest_cpu.py); the kernels have not run
-// on a B200 yet (the round's GPU budget was spent) — the GPU tests are opt-in (CORAL_TEST_UNVERIFIED=1) and nothing
-// on the default path calls this file.
+// STATUS: the decoder core and every per-element step below are __host__ __device__ and run against zlib / the host
+// reader on the CPU (tests/test_ingest_cpu.py); the kernels are verified on the B200 against the host reader and the
+// golden fixtures (tests/test_gpu_device_ingest.py) and timed in bench.py (e2e_from_file) — DESIGN.md 4.3.  Opt-in
+// (placement="device_ingest"); the default path uses the host reader.
 //
 //   host    member table (18-byte BGZF headers, sequential but trivial) + BAM header (first members, host run of the
 //           same decoder) -> references, offset of the first record

@@ -468,7 +468,8 @@ int coral_get_alignment_paths(coral_ctx* ctx, uint32_t* rec, int32_t* iv, int32_
  *   coral_get_read_names : read names of the given records (any placement), 256 bytes per record, NUL padded — what
  *                       a caller without a host copy of the records uses for pysam's query_name.
  *   coral_ingest_host_check : the same decoder and framing steps run on the CPU (test hook; mode 1 forces the serial
- *                       chase).  STATUS: CPU-verified; not yet run on a B200. */
+ *                       chase).  Verified on the CPU against the zlib reader and on the B200 (tests/test_gpu_device_ingest.py); timing in
+ *                       DESIGN.md 4.3. */
 int coral_ingest_open(coral_ctx* ctx, const uint8_t* file, uint64_t n_bytes);
 int32_t coral_ingest_n_ref(const coral_ctx* ctx);
 const char* coral_ingest_ref_name(const coral_ctx* ctx, int32_t tid);
