@@ -12,9 +12,11 @@ every result table copied back to the host.
   e2e   : records/s through the public drop-in class (bam_to_breakpoint_nanopore) starting from a pinned HOST
           record buffer: H2D of the records, all kernels, D2H of all tables, Python materialisation, graph build
   roofline : the record-scan kernel (the only kernel that touches record bytes): algorithmic bytes / CUDA-event time
-  cpu_baseline : the oracle (CPU port of the reference path) on a bounded sample, 1 core
-`--impl reference` times that CPU port alone (the reference itself is Python and cannot travel to the GPU box;
-pysam is unavailable — the port is oracle/coral_oracle.py over oracle/pysam_shim.py, "reference-on-shim").
+  cpu_baseline : the UNMODIFIED reference (oracle/_ref under the oracle's pysam / intervaltree stand-ins; the CPU port when
+          that copy is absent) on a bounded sample, 1 core
+`--impl reference` times the same reference on the GPU arm's own full-size input ("reference-on-shim": pysam is not
+installable on this box).  --gpus N > 1: one process per GPU (torchrun), the file's shards exchange over peer memory
+(csrc/xchg.cu; --exchange nccl = the collective baseline); --workload C4 / C5: one file cut into N shards.
 """
 import argparse
 import os as _os
