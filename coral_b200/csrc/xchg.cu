@@ -57,8 +57,10 @@ struct PushArgs {
     int world;
 };
 
-__device__ __forceinline__ void st_release_sys(uint64_t* p, uint64_t v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+// relaxed store at system scope: ordered behind the ONE system-scope fence the publishing thread executes before its
+// flag stores (fence + relaxed store = the release pattern; st.release per flag costs a MEMBAR.ALL.SYS per peer)
+__device__ __forceinline__ void st_relaxed_sys(uint64_t* p, uint64_t v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ uint64_t ld_acquire_sys(const uint64_t* p) {
     uint64_t v;
@@ -103,8 +105,8 @@ __global__ void k_xchg_push(const uint4* __restrict__ src, uint64_t nbytes, Push
                 reinterpret_cast<uint64_t*>(a.slot[p])[0] = nbytes;
                 reinterpret_cast<uint64_t*>(a.slot[p])[1] = seq;
             }
-            __threadfence_system();
-            for (int p = 0; p < a.world; p++) st_release_sys(a.flag[p], seq);
+            __threadfence_system();               // data and headers are visible at system scope before any flag below
+            for (int p = 0; p < a.world; p++) st_relaxed_sys(a.flag[p], seq);
         }
     }
     __syncthreads();
